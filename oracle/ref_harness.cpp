@@ -1,0 +1,701 @@
+// TEST INFRASTRUCTURE ONLY -- never linked, imported or executed by the product path.
+//
+// oracle/_ref/libsgref.so: the UNMODIFIED reference (lanl/singularity-eos headers where they
+// lie under /root/reference) compiled for the host with PORTABILITY_STRATEGY_NONE, wrapped in
+// a small C API so tests/ and bench.py's cpu_baseline / --impl reference legs can run the
+// reference's own code on the same inputs as the CUDA path.
+//
+// What runs here is reference code:
+//   vector lookups  -> Variant vector overloads, eos/eos_variant.hpp:56-143 -> eos_base.hpp:169-230
+//   FillEos         -> eos/eos_variant.hpp:652-708 -> eos_base.hpp:503-531
+//   Spiner EOS      -> the real SpinerEOSDependsRhoT / SpinerEOSDependsRhoSie constructors
+//                      (eos_spiner_rho_temp.hpp:373-424, eos_spiner_rho_sie.hpp:980-1040) reading
+//                      an in-memory .sp5 tree through oracle/hdf5_shim (libhdf5 is absent)
+//   PTE             -> the cell loop of test/test_pte.cpp:177-265 around PTESolverRhoT/PT +
+//                      PTESolver (closure/mixed_cell_models.hpp:883-1446,2188-2291), Eigen 3x3
+// The only additions are the C wrapper, the .sp5 tree builder, and an OpenMP `parallel for`
+// over cells / chunks (the reference's portableFor is a serial loop without Kokkos,
+// utils/ports-of-call/ports-of-call/portability.hpp:224-236).
+//
+// `private`/`protected` are opened up so the harness can read the post-fix-up DataBoxes for
+// table-level parity checks; no reference behaviour changes.
+#include <algorithm>
+#include <array>
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <fstream>
+#include <map>
+#include <memory>
+#include <sstream>
+#include <string>
+#include <vector>
+#include <unistd.h>
+
+#define private public
+#define protected public
+#include <singularity-eos/closure/mixed_cell_models.hpp>
+#include <singularity-eos/eos/eos.hpp>
+#undef private
+#undef protected
+
+#include <singularity-eos/base/spiner_table_utils.hpp>
+
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+#include "../include/sgx_b200.h" // POD layouts only (sgx_sp5_tables, sgx_mix_params, enums)
+
+using namespace singularity;
+using DataBox = spiner_common::DataBox;
+
+namespace {
+
+struct StridedLambda {
+  Real *base;
+  int stride;
+  PORTABLE_FORCEINLINE_FUNCTION Real *operator[](const int i) const {
+    return base ? base + static_cast<std::ptrdiff_t>(stride) * i : nullptr;
+  }
+};
+
+// Type-indexed lambda with NO LogTemperature slot (finding 6):
+// {MeanAtomicMass, MeanAtomicNumber} at lambda[stride*i + {0,1}].
+using AZIndexer = IndexerUtils::VariadicPointerIndexer<IndexableTypes::MeanAtomicMass,
+                                                       IndexableTypes::MeanAtomicNumber>;
+struct StridedAZLambda {
+  Real *base;
+  int stride;
+  PORTABLE_FORCEINLINE_FUNCTION AZIndexer operator[](const int i) const {
+    return AZIndexer(base + static_cast<std::ptrdiff_t>(stride) * i);
+  }
+};
+
+int nthreads_for(int requested) {
+#ifdef _OPENMP
+  return requested > 0 ? requested : omp_get_max_threads();
+#else
+  (void)requested;
+  return 1;
+#endif
+}
+
+// ---- .sp5 tree builder ------------------------------------------------------------
+void put_grid(h5shim::Node *grids, int axis_k /*1-based*/, const sgx_grid1d &g) {
+  const std::string name = "grid_[" + std::to_string(axis_k) + "]";
+  auto put_regular = [](h5shim::Node *parent, const std::string &nm, double mn, double mx,
+                        double dx, int np) {
+    const double range[3] = {mn, mx, dx};
+    h5shim::set_dataset(parent, nm, range, 3);
+    h5shim::set_attr_int(parent->child(nm, false), "npoints", {np});
+  };
+  if (g.ngrids == 1) {
+    put_regular(grids, name, g.min[0], g.max[0], g.dx[0], g.npoints[0]);
+  } else {
+    h5shim::Node *grp = grids->child(name, true);
+    h5shim::set_attr_int(grp, "ngrids", {g.ngrids});
+    for (int p = 0; p < g.ngrids; ++p) {
+      put_regular(grp, "patch_[" + std::to_string(p + 1) + "]", g.min[p], g.max[p], g.dx[p],
+                  g.npoints[p]);
+    }
+  }
+}
+int grid_total(const sgx_grid1d &g) {
+  int n = 0;
+  for (int p = 0; p < g.ngrids; ++p)
+    n += g.npoints[p];
+  return n;
+}
+// rank-2 databox: dims (fastest first) = {n_fast, n_slow}
+void put_db2(h5shim::Node *parent, const char *name, const double *data,
+             const sgx_grid1d &fast, const sgx_grid1d &slow) {
+  if (data == nullptr) return;
+  h5shim::Node *db = parent->child(name, true);
+  const int nf = grid_total(fast), ns = grid_total(slow);
+  h5shim::set_attr_int(db, "rank", {2});
+  h5shim::set_attr_int(db, "dims", {nf, ns});
+  h5shim::set_attr_int(db, "index_types", {0, 0});
+  h5shim::set_dataset(db, "data", data, static_cast<std::size_t>(nf) * ns);
+  h5shim::Node *grids = db->child("grids", true);
+  put_grid(grids, 1, fast);
+  put_grid(grids, 2, slow);
+}
+void put_db1(h5shim::Node *parent, const char *name, const double *data,
+             const sgx_grid1d &g) {
+  if (data == nullptr) return;
+  h5shim::Node *db = parent->child(name, true);
+  const int n = grid_total(g);
+  h5shim::set_attr_int(db, "rank", {1});
+  h5shim::set_attr_int(db, "dims", {n});
+  h5shim::set_attr_int(db, "index_types", {0});
+  h5shim::set_dataset(db, "data", data, n);
+  h5shim::Node *grids = db->child("grids", true);
+  put_grid(grids, 1, g);
+}
+
+int g_file_counter = 0;
+
+std::string build_sp5(const sgx_sp5_tables *raw, int matid) {
+  // the constructors insist the path exists on disk (eos_spiner_common.hpp:128-134)
+  std::string fname = "/tmp/sgx_oracle_" + std::to_string(::getpid()) + "_" +
+                      std::to_string(g_file_counter++) + ".sp5";
+  { std::ofstream touch(fname); }
+  h5shim::drop_file(fname);
+  h5shim::Node *root = h5shim::file_root(fname, true);
+  h5shim::set_attr_int(root, SP5::logType, {static_cast<int>(FastMath::Settings::log_type)});
+  h5shim::Node *mat = root->child(std::to_string(matid), true);
+  h5shim::set_attr_double(mat, SP5::Offsets::rho, raw->rho_offset);
+  h5shim::set_attr_double(mat, SP5::Offsets::T, raw->T_offset);
+  h5shim::set_attr_double(mat, SP5::Offsets::sie, raw->sie_offset);
+  h5shim::set_attr_double(mat, SP5::Material::normalDensity, raw->normal_density);
+  h5shim::set_attr_double(mat, SP5::Material::meanAtomicMass, raw->mean_atomic_mass);
+  h5shim::set_attr_double(mat, SP5::Material::meanAtomicNumber, raw->mean_atomic_number);
+  h5shim::set_attr_int(mat, SP5::Material::matid, {matid});
+
+  h5shim::Node *lT = mat->child(SP5::Depends::logRhoLogT, true);
+  put_db2(lT, SP5::Fields::P, raw->P, raw->lT, raw->lrho);
+  put_db2(lT, SP5::Fields::sie, raw->sie, raw->lT, raw->lrho);
+  put_db2(lT, SP5::Fields::bMod, raw->bMod, raw->lT, raw->lrho);
+  put_db2(lT, SP5::Fields::dPdRho, raw->dPdRho, raw->lT, raw->lrho);
+  put_db2(lT, SP5::Fields::dPdE, raw->dPdE, raw->lT, raw->lrho);
+  put_db2(lT, SP5::Fields::dTdRho, raw->dTdRho, raw->lT, raw->lrho);
+  put_db2(lT, SP5::Fields::dTdE, raw->dTdE, raw->lT, raw->lrho);
+  put_db2(lT, SP5::Fields::dEdRho, raw->dEdRho, raw->lT, raw->lrho);
+  put_db2(lT, SP5::Fields::dEdT, raw->dEdT, raw->lT, raw->lrho);
+
+  h5shim::Node *lE = mat->child(SP5::Depends::logRhoLogSie, true);
+  put_db2(lE, SP5::Fields::T, raw->T_re, raw->lE, raw->lrho);
+  put_db2(lE, SP5::Fields::P, raw->P_re, raw->lE, raw->lrho);
+  put_db2(lE, SP5::Fields::bMod, raw->bMod_re, raw->lE, raw->lrho);
+  put_db2(lE, SP5::Fields::dPdRho, raw->dPdRho_re, raw->lE, raw->lrho);
+  put_db2(lE, SP5::Fields::dPdE, raw->dPdE_re, raw->lE, raw->lrho);
+  put_db2(lE, SP5::Fields::dTdRho, raw->dTdRho_re, raw->lE, raw->lrho);
+  put_db2(lE, SP5::Fields::dTdE, raw->dTdE_re, raw->lE, raw->lrho);
+  put_db2(lE, SP5::Fields::dEdRho, raw->dEdRho_re, raw->lE, raw->lrho);
+
+  h5shim::Node *cold = mat->child(SP5::Depends::coldCurve, true);
+  put_db1(cold, SP5::Fields::P, raw->PCold, raw->lrho);
+  put_db1(cold, SP5::Fields::sie, raw->sieCold, raw->lrho);
+  put_db1(cold, SP5::Fields::bMod, raw->bModCold, raw->lrho);
+  put_db1(cold, SP5::Fields::dPdRho, raw->dPdRhoCold, raw->lrho);
+  return fname;
+}
+
+template <typename F>
+int guarded(F &&f) {
+  try {
+    f();
+    return 0;
+  } catch (const std::exception &e) {
+    std::fprintf(stderr, "[sgref] reference threw: %s\n", e.what());
+    return -1;
+  }
+}
+
+int64_t copy_db(const DataBox &db, double *out, int64_t cap) {
+  const int64_t n = db.size();
+  if (out == nullptr) return n;
+  const int64_t m = std::min(n, cap);
+  for (int64_t i = 0; i < m; ++i)
+    out[i] = db.data()[i];
+  return m;
+}
+
+} // namespace
+
+extern "C" {
+
+int ref_abi_version() { return SGX_ABI_VERSION; }
+int ref_num_threads() { return nthreads_for(0); }
+
+// ---- FastMath (base/fast-math/logs.hpp) -----------------------------------------
+void ref_fastmath_eval(int which, const double *x, double *y, int64_t n) {
+  for (int64_t i = 0; i < n; ++i) {
+    switch (which) {
+    case 0:
+      y[i] = FastMath::log10(x[i]);
+      break;
+    case 1:
+      y[i] = FastMath::pow10(x[i]);
+      break;
+    case 2:
+      y[i] = FastMath::lg(x[i]);
+      break;
+    default:
+      y[i] = FastMath::pow2(x[i]);
+      break;
+    }
+  }
+}
+
+// ---- regula falsi on a 1-D piecewise-linear table (root_finding.hpp:154-240) ------
+// f(x) = DataBox(y over RegularGrid1D(xmin,xmax,ny)).interpToReal(x)
+int ref_regula_falsi_table(const double *y, int ny, double xmin, double xmax, double ytarget,
+                           double guess, double a, double b, double xtol, double ytol,
+                           double *xroot) {
+  DataBox db(Spiner::AllocationTarget::Host, ny);
+  db.setRange(0, spiner_common::Grid_t(
+                     std::vector<Spiner::RegularGrid1D<Real>>{{xmin, xmax, (size_t)ny}}));
+  for (int i = 0; i < ny; ++i)
+    db(i) = y[i];
+  const callable_interp::interp f(db);
+  auto st = RootFinding1D::regula_falsi(f, ytarget, guess, a, b, xtol, ytol, *xroot);
+  free(db);
+  return st == RootFinding1D::Status::SUCCESS ? 0 : 1;
+}
+
+// ---- solver utils (closure/mixed_cell_models.hpp:176-305) -------------------------
+int ref_solve_Ax_b(int n, double *a, double *b) {
+  double scr[16];
+  return mix_impl::solve_Ax_b_wscr(n, a, b, scr) ? 1 : 0;
+}
+double ref_sum_neumaier(const double *x, int n) { return mix_impl::sum_neumaier(x, n); }
+
+// ---- EOS handles ----------------------------------------------------------------
+void *ref_eos_ideal(double gm1, double Cv) { return new EOS(IdealGas(gm1, Cv)); }
+void *ref_eos_gruneisen(double C0, double s1, double s2, double s3, double G0, double b,
+                        double rho0, double T0, double P0, double Cv, double rho_max) {
+  if (rho_max > 0) return new EOS(Gruneisen(C0, s1, s2, s3, G0, b, rho0, T0, P0, Cv, rho_max));
+  return new EOS(Gruneisen(C0, s1, s2, s3, G0, b, rho0, T0, P0, Cv));
+}
+void *ref_eos_davis_reactants(double rho0, double e0, double P0, double T0, double A,
+                              double B, double C, double G0, double Z, double alpha,
+                              double Cv0) {
+  return new EOS(DavisReactants(rho0, e0, P0, T0, A, B, C, G0, Z, alpha, Cv0));
+}
+void *ref_eos_davis_products(double a, double b, double k, double n, double vc, double pc,
+                             double Cv) {
+  return new EOS(DavisProducts(a, b, k, n, vc, pc, Cv));
+}
+void *ref_eos_vinet(double rho0, double T0, double B0, double BP0, double A0, double Cv0,
+                    double E0, double S0, const double *d2to40) {
+  return new EOS(Vinet(rho0, T0, B0, BP0, A0, Cv0, E0, S0, d2to40));
+}
+void *ref_eos_spiner_rhot(const sgx_sp5_tables *raw, int reproducible, int pmin_vapor_dome) {
+  EOS *out = nullptr;
+  int rc = guarded([&]() {
+    const int matid = 1;
+    std::string f = build_sp5(raw, matid);
+    out = new EOS(SpinerEOSDependsRhoT(f, matid, reproducible != 0, pmin_vapor_dome != 0));
+    h5shim::drop_file(f);
+    std::remove(f.c_str());
+  });
+  return rc == 0 ? out : nullptr;
+}
+void *ref_eos_spiner_rhosie(const sgx_sp5_tables *raw, int reproducible,
+                            int pmin_vapor_dome) {
+  EOS *out = nullptr;
+  int rc = guarded([&]() {
+    const int matid = 1;
+    std::string f = build_sp5(raw, matid);
+    out = new EOS(SpinerEOSDependsRhoSie(f, matid, reproducible != 0, pmin_vapor_dome != 0));
+    h5shim::drop_file(f);
+    std::remove(f.c_str());
+  });
+  return rc == 0 ? out : nullptr;
+}
+void *ref_eos_helmholtz(const char *path, const sgx_helm_options *o) {
+  EOS *out = nullptr;
+  int rc = guarded([&]() {
+    out = new EOS(Helmholtz(std::string(path), o->enable_rad != 0, o->enable_gas != 0,
+                            o->enable_coulomb != 0, o->gas_ionized != 0,
+                            o->gas_degenerate != 0, false, o->use_newton_raphson != 0));
+  });
+  return rc == 0 ? out : nullptr;
+}
+void ref_eos_free(void *h) {
+  EOS *e = static_cast<EOS *>(h);
+  if (!e) return;
+  e->Finalize();
+  delete e;
+}
+int ref_eos_nlambda(void *h) { return static_cast<EOS *>(h)->nlambda(); }
+unsigned long ref_eos_preferred_input(void *h) {
+  return static_cast<EOS *>(h)->PreferredInput();
+}
+double ref_eos_maximum_density(void *h) { return static_cast<EOS *>(h)->MaximumDensity(); }
+
+// Post-fix-up tables of the real Spiner classes, by the reference's member names.
+int64_t ref_eos_get_table(void *h, const char *name, double *out, int64_t cap) {
+  EOS *e = static_cast<EOS *>(h);
+  const std::string nm(name);
+  if (e->IsType<SpinerEOSDependsRhoT>()) {
+    const auto s = e->get<SpinerEOSDependsRhoT>();
+    const std::map<std::string, const DataBox *> m = {
+        {"P", &s.P_},
+        {"sie", &s.sie_},
+        {"bMod", &s.bMod_},
+        {"dPdRho", &s.dPdRho_},
+        {"dPdE", &s.dPdE_},
+        {"dTdRho", &s.dTdRho_},
+        {"dTdE", &s.dTdE_},
+        {"dEdRho", &s.dEdRho_},
+        {"dEdT", &s.dEdT_},
+        {"PMax", &s.PMax_},
+        {"sielTMax", &s.sielTMax_},
+        {"dEdTMax", &s.dEdTMax_},
+        {"gm1Max", &s.gm1Max_},
+        {"lTColdCrit", &s.lTColdCrit_},
+        {"PCold", &s.PCold_},
+        {"sieCold", &s.sieCold_},
+        {"bModCold", &s.bModCold_},
+        {"dPdRhoCold", &s.dPdRhoCold_},
+        {"dPdECold", &s.dPdECold_},
+        {"dTdRhoCold", &s.dTdRhoCold_},
+        {"dTdECold", &s.dTdECold_},
+        {"dEdTCold", &s.dEdTCold_},
+        {"rho_at_pmin", &s.rho_at_pmin_}};
+    auto it = m.find(nm);
+    return it == m.end() ? -1 : copy_db(*it->second, out, cap);
+  }
+  if (e->IsType<SpinerEOSDependsRhoSie>()) {
+    const auto s = e->get<SpinerEOSDependsRhoSie>();
+    const std::map<std::string, const DataBox *> m = {
+        {"sie", &s.sie_},
+        {"T_re", &s.T_},
+        {"rho_at_pmin", &s.rho_at_pmin_},
+        {"P", &s.dependsRhoT_.P},
+        {"bMod", &s.dependsRhoT_.bMod},
+        {"dPdRho", &s.dependsRhoT_.dPdRho},
+        {"dPdE", &s.dependsRhoT_.dPdE},
+        {"dTdRho", &s.dependsRhoT_.dTdRho},
+        {"dTdE", &s.dependsRhoT_.dTdE},
+        {"dEdRho", &s.dependsRhoT_.dEdRho},
+        {"P_re", &s.dependsRhoSie_.P},
+        {"bMod_re", &s.dependsRhoSie_.bMod},
+        {"dPdRho_re", &s.dependsRhoSie_.dPdRho},
+        {"dPdE_re", &s.dependsRhoSie_.dPdE},
+        {"dTdRho_re", &s.dependsRhoSie_.dTdRho},
+        {"dTdE_re", &s.dependsRhoSie_.dTdE},
+        {"dEdRho_re", &s.dependsRhoSie_.dEdRho},
+        {"PlRhoMax", &s.PlRhoMax_},
+        {"dPdRhoMax", &s.dPdRhoMax_},
+        {"PCold", &s.PCold_},
+        {"sieCold", &s.sieCold_},
+        {"bModCold", &s.bModCold_},
+        {"dPdRhoCold", &s.dPdRhoCold_}};
+    auto it = m.find(nm);
+    return it == m.end() ? -1 : copy_db(*it->second, out, cap);
+  }
+  return -1;
+}
+int ref_eos_get_scalar(void *h, const char *name, double *out) {
+  EOS *e = static_cast<EOS *>(h);
+  const std::string nm(name);
+  if (e->IsType<SpinerEOSDependsRhoT>()) {
+    const auto s = e->get<SpinerEOSDependsRhoT>();
+    const std::map<std::string, double> m = {
+        {"lRhoMin", s.lRhoMin_},       {"lRhoMax", s.lRhoMax_},   {"rhoMax", s.rhoMax_},
+        {"lTMin", s.lTMin_},           {"lTMax", s.lTMax_},       {"TMax", s.TMax_},
+        {"PMin", s.PMin_},             {"rhoNormal", s.rhoNormal_}, {"TNormal", s.TNormal_},
+        {"sieNormal", s.sieNormal_},   {"PNormal", s.PNormal_},   {"CvNormal", s.CvNormal_},
+        {"bModNormal", s.bModNormal_}, {"dPdENormal", s.dPdENormal_},
+        {"dVdTNormal", s.dVdTNormal_}, {"lRhoOffset", s.lRhoOffset_},
+        {"lTOffset", s.lTOffset_}};
+    auto it = m.find(nm);
+    if (it == m.end()) return -1;
+    *out = it->second;
+    return 0;
+  }
+  if (e->IsType<SpinerEOSDependsRhoSie>()) {
+    const auto s = e->get<SpinerEOSDependsRhoSie>();
+    const std::map<std::string, double> m = {
+        {"lRhoMin", s.lRhoMin_},       {"lRhoMax", s.lRhoMax_},   {"rhoMax", s.rhoMax_},
+        {"PMin", s.PMin_},             {"rhoNormal", s.rhoNormal_}, {"TNormal", s.TNormal_},
+        {"sieNormal", s.sieNormal_},   {"PNormal", s.PNormal_},   {"CvNormal", s.CvNormal_},
+        {"bModNormal", s.bModNormal_}, {"dPdENormal", s.dPdENormal_},
+        {"dVdTNormal", s.dVdTNormal_}, {"lRhoOffset", s.lRhoOffset_},
+        {"lTOffset", s.lTOffset_},     {"lEOffset", s.lEOffset_}};
+    auto it = m.find(nm);
+    if (it == m.end()) return -1;
+    *out = it->second;
+    return 0;
+  }
+  return -1;
+}
+
+// ---- vector lookups through the reference's Variant vector API -------------------
+// method: enum sgx_method.  The array is cut into one chunk per OpenMP thread; each chunk is
+// ONE call of the reference vector overload with Exec::Host() on a thread-private copy of the
+// (shallow, trivially copyable) EOS object.
+int ref_eos_eval(void *h, int method, const double *in1, const double *in2, double *out,
+                 int64_t n, double *lambda, int lambda_stride, int nthreads) {
+  const EOS *eos = static_cast<const EOS *>(h);
+  const int nt = nthreads_for(nthreads);
+  int rc = 0;
+#pragma omp parallel for num_threads(nt) schedule(static)
+  for (int t = 0; t < nt; ++t) {
+    const int64_t lo = n * t / nt, hi = n * (t + 1) / nt;
+    const int cnt = static_cast<int>(hi - lo);
+    if (cnt <= 0) continue;
+    EOS local = *eos;
+    const double *a = in1 + lo, *b = in2 + lo;
+    double *o = out + lo;
+    StridedLambda lam{lambda ? lambda + lo * lambda_stride : nullptr, lambda_stride};
+    auto host = PortsOfCall::Exec::Host();
+    int lrc = guarded([&]() {
+      switch (method) {
+      case SGX_P_FROM_RHO_T:
+        local.PressureFromDensityTemperature(host, a, b, o, cnt, lam);
+        break;
+      case SGX_E_FROM_RHO_T:
+        local.InternalEnergyFromDensityTemperature(host, a, b, o, cnt, lam);
+        break;
+      case SGX_T_FROM_RHO_E:
+        local.TemperatureFromDensityInternalEnergy(host, a, b, o, cnt, lam);
+        break;
+      case SGX_P_FROM_RHO_E:
+        local.PressureFromDensityInternalEnergy(host, a, b, o, cnt, lam);
+        break;
+      case SGX_CV_FROM_RHO_T:
+        local.SpecificHeatFromDensityTemperature(host, a, b, o, cnt, lam);
+        break;
+      case SGX_CV_FROM_RHO_E:
+        local.SpecificHeatFromDensityInternalEnergy(host, a, b, o, cnt, lam);
+        break;
+      case SGX_BMOD_FROM_RHO_T:
+        local.BulkModulusFromDensityTemperature(host, a, b, o, cnt, lam);
+        break;
+      case SGX_BMOD_FROM_RHO_E:
+        local.BulkModulusFromDensityInternalEnergy(host, a, b, o, cnt, lam);
+        break;
+      case SGX_GAMMA_FROM_RHO_T:
+        local.GruneisenParamFromDensityTemperature(host, a, b, o, cnt, lam);
+        break;
+      case SGX_GAMMA_FROM_RHO_E:
+        local.GruneisenParamFromDensityInternalEnergy(host, a, b, o, cnt, lam);
+        break;
+      default:
+        throw std::runtime_error("bad method");
+      }
+    });
+    if (lrc != 0) {
+#pragma omp atomic write
+      rc = -1;
+    }
+  }
+  return rc;
+}
+
+// FillEos vector overload.  az_only != 0 => type-indexed {Abar,Zbar} lambda (no lT slot).
+int ref_eos_fill(void *h, double *rho, double *T, double *e, double *P, double *cv,
+                 double *bmod, int64_t n, unsigned long output, double *lambda,
+                 int lambda_stride, int az_only, int nthreads) {
+  const EOS *eos = static_cast<const EOS *>(h);
+  const int nt = nthreads_for(nthreads);
+  int rc = 0;
+#pragma omp parallel for num_threads(nt) schedule(static)
+  for (int t = 0; t < nt; ++t) {
+    const int64_t lo = n * t / nt, hi = n * (t + 1) / nt;
+    const int cnt = static_cast<int>(hi - lo);
+    if (cnt <= 0) continue;
+    EOS local = *eos;
+    auto host = PortsOfCall::Exec::Host();
+    int lrc = guarded([&]() {
+      if (az_only) {
+        StridedAZLambda lam{lambda + lo * lambda_stride, lambda_stride};
+        local.FillEos(host, rho + lo, T + lo, e + lo, P + lo, cv + lo, bmod + lo, cnt, output,
+                      lam);
+      } else {
+        StridedLambda lam{lambda ? lambda + lo * lambda_stride : nullptr, lambda_stride};
+        local.FillEos(host, rho + lo, T + lo, e + lo, P + lo, cv + lo, bmod + lo, cnt, output,
+                      lam);
+      }
+    });
+    if (lrc != 0) {
+#pragma omp atomic write
+      rc = -1;
+    }
+  }
+  return rc;
+}
+
+// ---- PTE: the cell loop of test/test_pte.cpp:177-265 ------------------------------
+namespace {
+struct RowIndexer { // == Indexer2D over a [ncell][nmat] row-major array
+  double *row;
+  PORTABLE_FORCEINLINE_FUNCTION double &operator[](const int i) const { return row[i]; }
+};
+struct EosIndexer {
+  EOS *e;
+  PORTABLE_FORCEINLINE_FUNCTION EOS &operator[](const int i) const { return e[i]; }
+};
+MixParams to_params(const sgx_mix_params *p) {
+  MixParams m;
+  if (!p) return m;
+  m.verbose = p->verbose != 0;
+  m.iterate_t_guess = p->iterate_t_guess != 0;
+  m.derivative_eps = p->derivative_eps;
+  m.pte_rel_tolerance_p = p->pte_rel_tolerance_p;
+  m.pte_rel_tolerance_t = p->pte_rel_tolerance_t;
+  m.pte_rel_tolerance_e = p->pte_rel_tolerance_e;
+  m.pte_rel_tolerance_v = p->pte_rel_tolerance_v;
+  m.pte_abs_tolerance_p = p->pte_abs_tolerance_p;
+  m.pte_abs_tolerance_t = p->pte_abs_tolerance_t;
+  m.pte_slow_convergence_thresh = p->pte_slow_convergence_thresh;
+  m.pte_rel_tolerance_p_sufficient = p->pte_rel_tolerance_p_sufficient;
+  m.pte_rel_tolerance_t_sufficient = p->pte_rel_tolerance_t_sufficient;
+  m.pte_rel_tolerance_e_sufficient = p->pte_rel_tolerance_e_sufficient;
+  m.pte_rel_tolerance_v_sufficient = p->pte_rel_tolerance_v_sufficient;
+  m.pte_abs_tolerance_p_sufficient = p->pte_abs_tolerance_p_sufficient;
+  m.pte_abs_tolerance_t_sufficient = p->pte_abs_tolerance_t_sufficient;
+  m.pte_max_iter_per_mat = p->pte_max_iter_per_mat;
+  m.line_search_alpha = p->line_search_alpha;
+  m.line_search_max_iter = p->line_search_max_iter;
+  m.line_search_fac = p->line_search_fac;
+  m.vfrac_safety_fac = p->vfrac_safety_fac;
+  m.temperature_limit = p->temperature_limit;
+  m.default_tguess = p->default_tguess;
+  m.min_dtde = p->min_dtde;
+  m.pte_small_step_tries = p->pte_small_step_tries;
+  m.pte_small_step_thresh = p->pte_small_step_thresh;
+  m.pte_max_dpdv = p->pte_max_dpdv;
+  m.pte_reduced_system_exclude_idx = p->pte_reduced_system_exclude_idx;
+  return m;
+}
+uint64_t pack_status(const SolverStatus &s, std::size_t niter) {
+  auto clamp = [](std::size_t v, std::size_t mx) { return v > mx ? mx : v; };
+  uint64_t w = 0;
+  w |= s.converged ? 1ull : 0ull;
+  w |= s.slow_convergence_detected ? 2ull : 0ull;
+  w |= static_cast<uint64_t>(clamp(niter, 0xffff)) << 8;
+  w |= static_cast<uint64_t>(clamp(s.max_line_niter, 0xff)) << 24;
+  w |= static_cast<uint64_t>(clamp(s.small_step_iters, 0xffff)) << 32;
+  w |= static_cast<uint64_t>(clamp(s.max_niter, 0xffff)) << 48;
+  return w;
+}
+} // namespace
+
+void ref_mix_params_default(sgx_mix_params *p) {
+  MixParams m;
+  p->verbose = m.verbose;
+  p->iterate_t_guess = m.iterate_t_guess;
+  p->derivative_eps = m.derivative_eps;
+  p->pte_rel_tolerance_p = m.pte_rel_tolerance_p;
+  p->pte_rel_tolerance_t = m.pte_rel_tolerance_t;
+  p->pte_rel_tolerance_e = m.pte_rel_tolerance_e;
+  p->pte_rel_tolerance_v = m.pte_rel_tolerance_v;
+  p->pte_abs_tolerance_p = m.pte_abs_tolerance_p;
+  p->pte_abs_tolerance_t = m.pte_abs_tolerance_t;
+  p->pte_slow_convergence_thresh = m.pte_slow_convergence_thresh;
+  p->pte_rel_tolerance_p_sufficient = m.pte_rel_tolerance_p_sufficient;
+  p->pte_rel_tolerance_t_sufficient = m.pte_rel_tolerance_t_sufficient;
+  p->pte_rel_tolerance_e_sufficient = m.pte_rel_tolerance_e_sufficient;
+  p->pte_rel_tolerance_v_sufficient = m.pte_rel_tolerance_v_sufficient;
+  p->pte_abs_tolerance_p_sufficient = m.pte_abs_tolerance_p_sufficient;
+  p->pte_abs_tolerance_t_sufficient = m.pte_abs_tolerance_t_sufficient;
+  p->pte_max_iter_per_mat = m.pte_max_iter_per_mat;
+  p->line_search_alpha = m.line_search_alpha;
+  p->line_search_max_iter = m.line_search_max_iter;
+  p->line_search_fac = m.line_search_fac;
+  p->vfrac_safety_fac = m.vfrac_safety_fac;
+  p->temperature_limit = m.temperature_limit;
+  p->default_tguess = m.default_tguess;
+  p->min_dtde = m.min_dtde;
+  p->pte_small_step_tries = m.pte_small_step_tries;
+  p->pte_small_step_thresh = m.pte_small_step_thresh;
+  p->pte_max_dpdv = m.pte_max_dpdv;
+  p->pte_reduced_system_exclude_idx = m.pte_reduced_system_exclude_idx;
+}
+
+int ref_pte_solve(int solver, void **eos_handles, int nmat, int64_t ncell, double *rho,
+                  double *vfrac, double *sie, double *temp, double *press,
+                  const double *sie_tot_in, const double *vfrac_tot_in,
+                  const double *Tguess_in, const sgx_mix_params *params, uint64_t *status,
+                  double *residual, double *Tguess_out, int nthreads) {
+  const MixParams mp = to_params(params);
+  const int nt = nthreads_for(nthreads);
+  std::vector<EOS> eos_vec(nmat);
+  for (int m = 0; m < nmat; ++m)
+    eos_vec[m] = *static_cast<EOS *>(eos_handles[m]);
+  int rc = 0;
+#pragma omp parallel num_threads(nt)
+  {
+    std::vector<EOS> eos_local(eos_vec);
+    EosIndexer eos{eos_local.data()};
+    const int nscr = std::max(PTESolverRhoTRequiredScratch(nmat), PTESolverPTRequiredScratch(nmat));
+    std::vector<double> scratch(nscr);
+#pragma omp for schedule(dynamic, 256)
+    for (int64_t t = 0; t < ncell; ++t) {
+      NullIndexer lambda;
+      RowIndexer r{rho + t * nmat}, vf{vfrac + t * nmat}, e{sie + t * nmat},
+          tp{temp + t * nmat}, pr{press + t * nmat};
+      Real sie_tot = 0.0, rho_tot = 0.0;
+      for (int i = 0; i < nmat; i++) { // test/test_pte.cpp:188-195
+        const Real rhobar = r[i] * vf[i];
+        rho_tot += rhobar;
+        sie_tot += rhobar * e[i];
+      }
+      sie_tot /= rho_tot;
+      if (sie_tot_in) sie_tot = sie_tot_in[t];
+      const Real vfrac_tot = vfrac_tot_in ? vfrac_tot_in[t] : 1.0;
+      Real Tguess;
+      if (Tguess_in) {
+        Tguess = Tguess_in[t];
+      } else {
+        Tguess = ApproxTemperatureFromRhoMatU(nmat, eos, rho_tot * sie_tot, r, vf);
+      }
+      if (Tguess_out) Tguess_out[t] = Tguess;
+      SolverStatus st;
+      std::size_t niter = 0;
+      int lrc = guarded([&]() {
+        if (solver == SGX_PTE_RHOT) {
+          PTESolverRhoT<EosIndexer, RowIndexer, NullIndexer> method(
+              nmat, eos, vfrac_tot, sie_tot, r, vf, e, tp, pr, lambda, scratch.data(), Tguess,
+              mp);
+          st = PTESolver(method);
+          niter = method.Niter();
+        } else {
+          PTESolverPT<EosIndexer, RowIndexer, NullIndexer> method(
+              nmat, eos, vfrac_tot, sie_tot, r, vf, e, tp, pr, lambda, scratch.data(), Tguess,
+              mp);
+          st = PTESolver(method);
+          niter = method.Niter();
+        }
+      });
+      if (lrc != 0) {
+#pragma omp atomic write
+        rc = -1;
+      }
+      if (status) status[t] = pack_status(st, niter);
+      if (residual) residual[t] = st.residual;
+    }
+  }
+  return rc;
+}
+
+// ApproxTemperatureFromRhoMatU alone (closure/mixed_cell_models.hpp:790-847)
+void ref_pte_approx_T(void **eos_handles, int nmat, int64_t ncell, const double *rho,
+                      const double *vfrac, const double *u_tot, double *Tout) {
+  std::vector<EOS> eos_vec(nmat);
+  for (int m = 0; m < nmat; ++m)
+    eos_vec[m] = *static_cast<EOS *>(eos_handles[m]);
+  EosIndexer eos{eos_vec.data()};
+  for (int64_t t = 0; t < ncell; ++t) {
+    RowIndexer r{const_cast<double *>(rho) + t * nmat},
+        vf{const_cast<double *>(vfrac) + t * nmat};
+    Tout[t] = ApproxTemperatureFromRhoMatU(nmat, eos, u_tot[t], r, vf);
+  }
+}
+
+// ---- synthetic-table helpers: reference Bounds grids (base/spiner_table_utils.hpp:56-70) --
+// Single-patch log grid exactly as sesame2spiner builds it; also returns the linear-space
+// node positions i2lin(i) (:137-146).
+int ref_bounds_log_grid(double xmin, double xmax, int n, sgx_grid1d *grid, double *offset,
+                        double *nodes_lin) {
+  table_utils::Bounds<3> b(xmin, xmax, n, true);
+  grid->ngrids = 1;
+  grid->npoints[0] = n;
+  grid->min[0] = b.grid.min();
+  grid->max[0] = b.grid.max();
+  grid->dx[0] = b.grid.dx(0);
+  *offset = b.offset;
+  for (int i = 0; i < n; ++i)
+    nodes_lin[i] = b.i2lin(i);
+  return 0;
+}
+
+} // extern "C"

@@ -1,0 +1,71 @@
+"""Build libsgx_b200.so (sm_100a) in-tree with nvcc.  `python singularity-eos_b200/build.py`.
+
+The library is plain CUDA C++ behind a C ABI (include/sgx_b200.h); no torch headers.  It is
+written to  singularity-eos_b200/lib/libsgx_b200.so  (git-ignored, travels with gpurun).
+"""
+import hashlib
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, "csrc")
+LIBDIR = os.path.join(HERE, "lib")
+LIB = os.path.join(LIBDIR, "libsgx_b200.so")
+SOURCES = ["sgx_api.cu", "sgx_spiner_host.cu", "sgx_pte.cu", "sgx_helm.cu"]
+NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+# -fmad=false: no FMA contraction, so device arithmetic rounds like the reference's x86-64
+# build (parity contract: 1e-12 lookups, 1e-10 PTE states, identical flags).
+FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a", "-std=c++17", "-O3", "-lineinfo",
+    "-fmad=false", "-Xcompiler", "-fPIC,-O2,-ffp-contract=off", "-Xptxas", "-v",
+    "--expt-relaxed-constexpr", "-cudart", "static",
+]
+
+
+def _digest():
+    h = hashlib.sha256()
+    for root, _, files in os.walk(CSRC):
+        for f in sorted(files):
+            with open(os.path.join(root, f), "rb") as fh:
+                h.update(f.encode())
+                h.update(fh.read())
+    with open(os.path.join(HERE, "..", "include", "sgx_b200.h"), "rb") as fh:
+        h.update(fh.read())
+    h.update(" ".join(FLAGS).encode())
+    return h.hexdigest()
+
+
+def build(force=False, verbose=False):
+    os.makedirs(LIBDIR, exist_ok=True)
+    stamp = os.path.join(LIBDIR, ".stamp")
+    dig = _digest()
+    if (not force and os.path.exists(LIB) and os.path.exists(stamp)
+            and open(stamp).read().strip() == dig):
+        return LIB
+    objs = []
+    procs = []
+    for src in SOURCES:
+        obj = os.path.join(LIBDIR, src.replace(".cu", ".o"))
+        objs.append(obj)
+        cmd = [NVCC] + FLAGS + ["-c", os.path.join(CSRC, src), "-o", obj]
+        log = open(obj + ".log", "w")
+        procs.append((subprocess.Popen(cmd, stdout=log, stderr=subprocess.STDOUT), cmd, log, obj))
+    for p, cmd, log, obj in procs:
+        rc = p.wait()
+        log.close()
+        if rc != 0:
+            sys.stderr.write(open(obj + ".log").read())
+            raise RuntimeError("nvcc failed: " + " ".join(cmd))
+        if verbose:
+            sys.stdout.write(open(obj + ".log").read())
+    cmd = [NVCC, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-cudart", "static",
+           "-o", LIB] + objs
+    subprocess.check_call(cmd)
+    with open(stamp, "w") as fh:
+        fh.write(dig)
+    return LIB
+
+
+if __name__ == "__main__":
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

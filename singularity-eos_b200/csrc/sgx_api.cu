@@ -1,0 +1,802 @@
+// libsgx_b200 C ABI: EOS handles, vector lookup / FillEos kernels and their launchers.
+// See include/sgx_b200.h for the contract and the reference interfaces each entry replaces.
+//
+// Kernel design (all FP64, HBM-streaming):
+//  * one generic grid-stride kernel per (EOS model, method), the EOS struct passed by value
+//    in constant parameter space (the reference captures the EOS by value in its
+//    portableFor lambda, eos/eos_base.hpp:178-182);
+//  * each thread handles two adjacent cells per trip: 16-byte ld.global.nc / st.global
+//    on the cell arrays, (ρ,T)→(lRho,lT) lambda write-back as one 16-byte store when
+//    lambda_stride == 2;
+//  * grid = (#SMs × resident blocks) so every SM streams from the first wave;
+//  * table gathers go through the read-only path and stay L2-resident (≤ 5 MiB per EOS,
+//    persisting access-policy window set at create time).
+#include <cstring>
+#include <new>
+
+#include "sgx_internal.hpp"
+
+namespace sgx {
+
+std::atomic<unsigned long long> g_launches{0};
+
+int sm_count() {
+  static int cached[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+  if (dev < 0 || dev >= 64) return 148;
+  if (cached[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+      n = 148;
+    cached[dev] = n;
+  }
+  return cached[dev];
+}
+
+LaunchCfg stream_cfg(int64_t work_items, int threads, int blocks_per_sm) {
+  const int64_t need = (work_items + threads - 1) / threads;
+  int64_t blocks = (int64_t)sm_count() * blocks_per_sm;
+  if (need < blocks) blocks = need;
+  if (blocks < 1) blocks = 1;
+  return LaunchCfg{(int)blocks, threads};
+}
+
+int upload_tables(sgx_eos_s *e) {
+  TableStore &ts = e->tables;
+  const size_t bytes = ts.host.size() * sizeof(double);
+  if (bytes == 0) return SGX_OK;
+  SGX_CUDA_OK(cudaGetDevice(&e->device));
+  SGX_CUDA_OK(cudaMalloc((void **)&ts.dev, bytes));
+  SGX_CUDA_OK(cudaMemcpy(ts.dev, ts.host.data(), bytes, cudaMemcpyHostToDevice));
+  return SGX_OK;
+}
+
+int ensure_staging(sgx_eos_s *e, size_t pinned_bytes, size_t device_bytes) {
+  if (e->own_stream == nullptr) SGX_CUDA_OK(cudaStreamCreate(&e->own_stream));
+  if (pinned_bytes > e->pinned_bytes) {
+    if (e->pinned) cudaFreeHost(e->pinned);
+    e->pinned = nullptr;
+    e->pinned_bytes = 0;
+    SGX_CUDA_OK(cudaMallocHost(&e->pinned, pinned_bytes));
+    e->pinned_bytes = pinned_bytes;
+  }
+  if (device_bytes > e->dscratch_bytes) {
+    if (e->dscratch) cudaFree(e->dscratch);
+    e->dscratch = nullptr;
+    e->dscratch_bytes = 0;
+    SGX_CUDA_OK(cudaMalloc(&e->dscratch, device_bytes));
+    e->dscratch_bytes = device_bytes;
+  }
+  return SGX_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// kernels
+// ---------------------------------------------------------------------------------------
+template <int METHOD, class EOS>
+SGX_D double call_method(const EOS &eos, const double a, const double b, double *lam) {
+  if constexpr (METHOD == SGX_P_FROM_RHO_T) return eos.P_from_rho_T(a, b, lam);
+  if constexpr (METHOD == SGX_E_FROM_RHO_T) return eos.e_from_rho_T(a, b, lam);
+  if constexpr (METHOD == SGX_T_FROM_RHO_E) return eos.T_from_rho_e(a, b, lam);
+  if constexpr (METHOD == SGX_P_FROM_RHO_E) return eos.P_from_rho_e(a, b, lam);
+  if constexpr (METHOD == SGX_CV_FROM_RHO_T) return eos.cv_from_rho_T(a, b, lam);
+  if constexpr (METHOD == SGX_CV_FROM_RHO_E) return eos.cv_from_rho_e(a, b, lam);
+  if constexpr (METHOD == SGX_BMOD_FROM_RHO_T) return eos.bmod_from_rho_T(a, b, lam);
+  if constexpr (METHOD == SGX_BMOD_FROM_RHO_E) return eos.bmod_from_rho_e(a, b, lam);
+  if constexpr (METHOD == SGX_GAMMA_FROM_RHO_T) return eos.gamma_from_rho_T(a, b, lam);
+  if constexpr (METHOD == SGX_GAMMA_FROM_RHO_E) return eos.gamma_from_rho_e(a, b, lam);
+  return 0.0;
+}
+
+SGX_D double2 ld_stream2(const double *p) {
+  double2 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v2.f64 {%0,%1}, [%2];"
+               : "=d"(v.x), "=d"(v.y)
+               : "l"(p));
+  return v;
+}
+SGX_D double ld_stream1(const double *p) {
+  double v;
+  asm volatile("ld.global.nc.L1::no_allocate.f64 %0, [%1];" : "=d"(v) : "l"(p));
+  return v;
+}
+SGX_D void st_stream2(double *p, const double x, const double y) {
+  asm volatile("st.global.cs.v2.f64 [%0], {%1,%2};" ::"l"(p), "d"(x), "d"(y) : "memory");
+}
+SGX_D void st_stream1(double *p, const double x) {
+  asm volatile("st.global.cs.f64 [%0], %1;" ::"l"(p), "d"(x) : "memory");
+}
+
+// OUT[i] = eos.METHOD(IN1[i], IN2[i], lambda[i])   (eos_base.hpp:174-183)
+// VEC: arrays are 16-byte aligned -> two cells per thread per trip.
+template <int METHOD, class EOS, bool VEC>
+__global__ void __launch_bounds__(256)
+    eval_kernel(const __grid_constant__ EOS eos, const double *__restrict__ in1,
+                const double *__restrict__ in2, double *__restrict__ out, const int64_t n,
+                double *__restrict__ lambda, const int lstride) {
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t nthr = (int64_t)gridDim.x * blockDim.x;
+  if constexpr (VEC) {
+    const int64_t npair = n >> 1;
+    for (int64_t p = tid; p < npair; p += nthr) {
+      const int64_t i = p << 1;
+      const double2 a = ld_stream2(in1 + i);
+      const double2 b = ld_stream2(in2 + i);
+      double *l0 = lambda ? lambda + i * lstride : nullptr;
+      double *l1 = lambda ? l0 + lstride : nullptr;
+      const double r0 = call_method<METHOD>(eos, a.x, b.x, l0);
+      const double r1 = call_method<METHOD>(eos, a.y, b.y, l1);
+      st_stream2(out + i, r0, r1);
+    }
+    if ((n & 1) && tid == 0) {
+      const int64_t i = n - 1;
+      out[i] = call_method<METHOD>(eos, in1[i], in2[i], lambda ? lambda + i * lstride : nullptr);
+    }
+  } else {
+    for (int64_t i = tid; i < n; i += nthr) {
+      out[i] = call_method<METHOD>(eos, ld_stream1(in1 + i), ld_stream1(in2 + i),
+                                   lambda ? lambda + i * lstride : nullptr);
+    }
+  }
+}
+
+// Fused P(rho,T) + e(rho,T) (one read of rho,T; 32 B/cell)
+template <class EOS>
+__global__ void __launch_bounds__(256)
+    eval_pe_kernel(const __grid_constant__ EOS eos, const double *__restrict__ rho,
+                   const double *__restrict__ T, double *__restrict__ P,
+                   double *__restrict__ E, const int64_t n, double *__restrict__ lambda,
+                   const int lstride) {
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t nthr = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = tid; i < n; i += nthr) {
+    const double r = ld_stream1(rho + i), t = ld_stream1(T + i);
+    double *l = lambda ? lambda + i * lstride : nullptr;
+    st_stream1(P + i, eos.P_from_rho_T(r, t, l));
+    st_stream1(E + i, eos.e_from_rho_T(r, t, l));
+  }
+}
+
+// FillEos vector overload (eos_base.hpp:503-518)
+template <class EOS>
+__global__ void __launch_bounds__(256)
+    fill_kernel(const __grid_constant__ EOS eos, double *__restrict__ rho,
+                double *__restrict__ T, double *__restrict__ en, double *__restrict__ P,
+                double *__restrict__ cv, double *__restrict__ bmod, const int64_t n,
+                const unsigned long output, double *__restrict__ lambda, const int lstride,
+                int *__restrict__ err) {
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t nthr = (int64_t)gridDim.x * blockDim.x;
+  const unsigned long input = ~output;
+  for (int64_t i = tid; i < n; i += nthr) {
+    double r = 0, t = 0, e = 0, p = 0, c = 0, b = 0;
+    if ((input & TQ_DENSITY) && rho) r = rho[i];
+    if ((input & TQ_TEMPERATURE) && T) t = T[i];
+    if ((input & TQ_SIE) && en) e = en[i];
+    if ((input & TQ_PRESSURE) && P) p = P[i];
+    const bool ok = eos.fill(r, t, e, p, c, b, output, lambda ? lambda + i * lstride : nullptr);
+    if (!ok) {
+      if (err) *err = 1;
+      continue;
+    }
+    if ((output & TQ_DENSITY) && rho) rho[i] = r;
+    if ((output & TQ_TEMPERATURE) && T) T[i] = t;
+    if ((output & TQ_SIE) && en) en[i] = e;
+    if ((output & TQ_PRESSURE) && P) P[i] = p;
+    if ((output & TQ_CV) && cv) cv[i] = c;
+    if ((output & TQ_BMOD) && bmod) bmod[i] = b;
+  }
+}
+
+__global__ void fastmath_kernel(const int which, const double *__restrict__ x,
+                                double *__restrict__ y, const int64_t n) {
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t nthr = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = tid; i < n; i += nthr) {
+    const double v = x[i];
+    double r;
+    switch (which) {
+    case 0:
+      r = fastmath::log10(v);
+      break;
+    case 1:
+      r = fastmath::pow10(v);
+      break;
+    case 2:
+      r = fastmath::lg(v);
+      break;
+    default:
+      r = fastmath::pow2(v);
+      break;
+    }
+    y[i] = r;
+  }
+}
+
+__global__ void solve_kernel(const int n, double *__restrict__ a, double *__restrict__ b,
+                             int *__restrict__ ok, const int64_t batch) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= batch) return;
+  double la[9], lb[3];
+  for (int k = 0; k < n * n; ++k)
+    la[k] = a[i * n * n + k];
+  for (int k = 0; k < n; ++k)
+    lb[k] = b[i * n + k];
+  const bool good = mix::solve_Ax_b<3>(n, la, lb);
+  for (int k = 0; k < n * n; ++k)
+    a[i * n * n + k] = la[k];
+  for (int k = 0; k < n; ++k)
+    b[i * n + k] = lb[k];
+  if (ok) ok[i] = good ? 1 : 0;
+}
+
+// ---------------------------------------------------------------------------------------
+// launchers
+// ---------------------------------------------------------------------------------------
+template <int METHOD, class EOS>
+int launch_eval_m(const EOS &eos, const double *in1, const double *in2, double *out, int64_t n,
+                  double *lambda, int lstride, cudaStream_t s, int blocks_per_sm) {
+  const bool aligned = ((((uintptr_t)in1) | ((uintptr_t)in2) | ((uintptr_t)out)) & 15) == 0;
+  if (aligned && n >= 2) {
+    const LaunchCfg c = stream_cfg(n / 2, 256, blocks_per_sm);
+    eval_kernel<METHOD, EOS, true><<<c.blocks, c.threads, 0, s>>>(eos, in1, in2, out, n, lambda,
+                                                                   lstride);
+  } else {
+    const LaunchCfg c = stream_cfg(n, 256, blocks_per_sm);
+    eval_kernel<METHOD, EOS, false><<<c.blocks, c.threads, 0, s>>>(eos, in1, in2, out, n,
+                                                                    lambda, lstride);
+  }
+  count_launch();
+  SGX_CUDA_OK(cudaGetLastError());
+  return SGX_OK;
+}
+
+template <class EOS>
+int launch_eval(const EOS &eos, int method, const double *in1, const double *in2, double *out,
+                int64_t n, double *lambda, int lstride, cudaStream_t s, int bps) {
+  switch (method) {
+#define SGX_CASE(M)                                                                      \
+  case M:                                                                                \
+    return launch_eval_m<M>(eos, in1, in2, out, n, lambda, lstride, s, bps);
+    SGX_CASE(SGX_P_FROM_RHO_T)
+    SGX_CASE(SGX_E_FROM_RHO_T)
+    SGX_CASE(SGX_T_FROM_RHO_E)
+    SGX_CASE(SGX_P_FROM_RHO_E)
+    SGX_CASE(SGX_CV_FROM_RHO_T)
+    SGX_CASE(SGX_CV_FROM_RHO_E)
+    SGX_CASE(SGX_BMOD_FROM_RHO_T)
+    SGX_CASE(SGX_BMOD_FROM_RHO_E)
+    SGX_CASE(SGX_GAMMA_FROM_RHO_T)
+    SGX_CASE(SGX_GAMMA_FROM_RHO_E)
+#undef SGX_CASE
+  default:
+    return fail(SGX_ERR_INVALID, "unknown method %d", method);
+  }
+}
+
+template <class EOS>
+int launch_fill(sgx_eos_s *h, const EOS &eos, double *rho, double *T, double *en, double *P,
+                double *cv, double *bmod, int64_t n, unsigned long output, double *lambda,
+                int lstride, cudaStream_t s) {
+  const LaunchCfg c = stream_cfg(n, 256, 8);
+  fill_kernel<EOS><<<c.blocks, c.threads, 0, s>>>(eos, rho, T, en, P, cv, bmod, n, output,
+                                                  lambda, lstride, nullptr);
+  count_launch();
+  SGX_CUDA_OK(cudaGetLastError());
+  return SGX_OK;
+}
+
+template <class EOS>
+int launch_pe(const EOS &eos, const double *rho, const double *T, double *P, double *E,
+              int64_t n, double *lambda, int lstride, cudaStream_t s) {
+  const LaunchCfg c = stream_cfg(n, 256, 8);
+  eval_pe_kernel<EOS><<<c.blocks, c.threads, 0, s>>>(eos, rho, T, P, E, n, lambda, lstride);
+  count_launch();
+  SGX_CUDA_OK(cudaGetLastError());
+  return SGX_OK;
+}
+
+static int check_handle(sgx_eos_t e) {
+  if (!e) return fail(SGX_ERR_INVALID, "null EOS handle");
+  cudaError_t err = cudaSetDevice(e->device);
+  if (err != cudaSuccess)
+    return fail(SGX_ERR_CUDA, "cudaSetDevice(%d): %s", e->device, cudaGetErrorString(err));
+  return SGX_OK;
+}
+
+static int new_handle(int kind, sgx_eos_s **out) {
+  if (!out) return fail(SGX_ERR_INVALID, "null output handle pointer");
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t err = cudaGetDeviceCount(&ndev);
+  if (err != cudaSuccess || ndev <= 0)
+    return fail(SGX_ERR_CUDA, "no CUDA device available (%s); libsgx_b200 has no CPU path",
+                cudaGetErrorString(err));
+  sgx_eos_s *e = new (std::nothrow) sgx_eos_s();
+  if (!e) return fail(SGX_ERR_NOMEM, "out of host memory");
+  e->kind = kind;
+  std::memset(&e->analytic, 0, sizeof(e->analytic));
+  e->analytic.kind = kind;
+  err = cudaGetDevice(&e->device);
+  if (err != cudaSuccess) {
+    delete e;
+    return fail(SGX_ERR_CUDA, "cudaGetDevice: %s", cudaGetErrorString(err));
+  }
+  *out = e;
+  return SGX_OK;
+}
+
+// Gruneisen::ComputeRhoMax (eos_gruneisen.hpp:231-329), host only
+static double gruneisen_rho_max(const double s1, const double s2, const double s3,
+                                const double rho0) {
+  auto poly = [=](double eta) { return 1 - s1 * eta - s2 * pow2i(eta) - s3 * pow3i(eta); };
+  auto near_zero = [](double v, double tol) { return std::abs(v) < tol; };
+  auto find_min_bounded_val = [](double v1, double v2, double mn, double mx) {
+    const double minval = std::min(v1, v2), maxval = std::max(v1, v2);
+    if (minval > mn && minval < mx) return minval;
+    if (maxval > mn && maxval < mx) return maxval;
+    return -std::numeric_limits<double>::infinity();
+  };
+  constexpr double EPS = kEps;
+  double root_ = -1.;
+  double discriminant, root1, root2;
+  if (near_zero(s2, EPS) && near_zero(s3, EPS) && s1 > 1.) {
+    root_ = 1. / s1;
+  } else if (near_zero(s3, EPS) && !near_zero(s2, EPS)) {
+    discriminant = pow2i(s1) + 4. * s2;
+    if (discriminant < 0.) {
+      root_ = -1.;
+    } else {
+      root1 = (s1 + std::sqrt(discriminant)) / (-2. * s2);
+      root2 = (s1 - std::sqrt(discriminant)) / (-2. * s2);
+      root_ = find_min_bounded_val(root1, root2, 0., 1.);
+    }
+  } else if (!near_zero(s3, EPS)) {
+    discriminant = -18. * s3 * s2 * s1 - 4. * pow3i(-s2) + pow2i(s2) * pow2i(s1) -
+                   4. * s3 * pow3i(s1) - 27. * pow2i(s3);
+    double minbound = 0.;
+    double maxbound = 1.;
+    if (discriminant >= 0) {
+      const double extremum1 = (s2 + std::sqrt(pow2i(s2) - 3. * s3 * s1)) / (-3. * s3);
+      const double extremum2 = (s2 - std::sqrt(pow2i(s2) - 3. * s3 * s1)) / (-3. * s3);
+      const double min_extremum = std::min(extremum1, extremum2);
+      const double max_extremum = std::max(extremum1, extremum2);
+      if (s3 < 0.) {
+        minbound = std::max(min_extremum, minbound);
+        maxbound = std::min(std::max(max_extremum, minbound), maxbound);
+      } else {
+        if (min_extremum > 0) maxbound = std::min(min_extremum, maxbound);
+      }
+    }
+    if (poly(minbound) * poly(maxbound) < 0.) {
+      constexpr double factor = 100;
+      constexpr double xtol = factor * EPS;
+      constexpr double ytol = factor / 10 * EPS;
+      constexpr double eta_guess = 0.001;
+      root::regula_falsi(poly, 0., eta_guess, minbound, maxbound, xtol, ytol, root_);
+    } else if (near_zero(poly(minbound), EPS)) {
+      root_ = minbound;
+    } else if (near_zero(poly(maxbound), EPS)) {
+      root_ = maxbound;
+    } else {
+      root_ = -1.;
+    }
+  }
+  if (root_ > 0. && root_ < 1.) return rho0 / ((1 - root_) + EPS);
+  return std::numeric_limits<double>::infinity();
+}
+
+} // namespace sgx
+
+using namespace sgx;
+
+// =======================================================================================
+// extern "C"
+// =======================================================================================
+extern "C" {
+
+int sgx_abi_version(void) { return SGX_ABI_VERSION; }
+const char *sgx_last_error(void) { return last_error().c_str(); }
+int sgx_device_count(void) {
+  int n = 0;
+  cudaError_t err = cudaGetDeviceCount(&n);
+  if (err != cudaSuccess) return fail(SGX_ERR_CUDA, "cudaGetDeviceCount: %s", cudaGetErrorString(err));
+  return n;
+}
+int sgx_set_device(int device) {
+  SGX_CUDA_OK(cudaSetDevice(device));
+  return SGX_OK;
+}
+uint64_t sgx_launch_count(void) { return g_launches.load(); }
+
+int sgx_eos_create_ideal(double gm1, double Cv, sgx_eos_t *out) {
+  if (!(Cv >= 0) || !(gm1 >= 0))
+    return fail(SGX_ERR_INVALID, "IdealGas::CheckParams: Cv and gm1 must be non-negative");
+  sgx_eos_s *e;
+  int rc = new_handle(SGX_EOS_IDEAL, &e);
+  if (rc) return rc;
+  e->analytic.ideal.Cv = Cv;
+  e->analytic.ideal.gm1 = gm1;
+  *out = e;
+  return SGX_OK;
+}
+
+int sgx_eos_create_gruneisen(double C0, double s1, double s2, double s3, double G0, double b,
+                             double rho0, double T0, double P0, double Cv, double rho_max,
+                             sgx_eos_t *out) {
+  sgx_eos_s *e;
+  int rc = new_handle(SGX_EOS_GRUNEISEN, &e);
+  if (rc) return rc;
+  Gruneisen &g = e->analytic.gr;
+  g.C0 = C0;
+  g.s1 = s1;
+  g.s2 = s2;
+  g.s3 = s3;
+  g.G0 = G0;
+  g.b = b;
+  g.rho0 = rho0;
+  g.T0 = T0;
+  g.P0 = P0;
+  g.Cv = Cv;
+  g.rho_max = rho_max > 0 ? rho_max : 0.99 * gruneisen_rho_max(s1, s2, s3, rho0);
+  *out = e;
+  return SGX_OK;
+}
+
+int sgx_eos_create_davis_reactants(double rho0, double e0, double P0, double T0, double A,
+                                   double B, double C, double G0, double Z, double alpha,
+                                   double Cv0, sgx_eos_t *out) {
+  sgx_eos_s *e;
+  int rc = new_handle(SGX_EOS_DAVIS_REACTANTS, &e);
+  if (rc) return rc;
+  DavisReactants &d = e->analytic.dr;
+  d.rho0 = rho0;
+  d.spvol0 = 1.0 / rho0;
+  d.e0 = e0;
+  d.P0 = P0;
+  d.T0 = T0;
+  d.A = A;
+  d.B = B;
+  d.C = C;
+  d.G0 = G0;
+  d.Z = Z;
+  d.alpha = alpha;
+  d.i1pa = 1.0 / (1.0 + alpha);
+  d.Cv0 = Cv0;
+  d.A2oB = A * A / B;
+  *out = e;
+  return SGX_OK;
+}
+
+int sgx_eos_create_davis_products(double a, double b, double k, double n, double vc,
+                                  double pc, double Cv, sgx_eos_t *out) {
+  sgx_eos_s *e;
+  int rc = new_handle(SGX_EOS_DAVIS_PRODUCTS, &e);
+  if (rc) return rc;
+  DavisProducts &d = e->analytic.dp;
+  d.a = a;
+  d.b = b;
+  d.k = k;
+  d.n = n;
+  d.aon = a / n;
+  d.vc = vc;
+  d.pc = pc;
+  d.Cv = Cv;
+  *out = e;
+  return SGX_OK;
+}
+
+int sgx_eos_create_spiner_rhot(const sgx_sp5_tables *raw, int reproducibility_mode,
+                               int pmin_vapor_dome, sgx_eos_t *out) {
+  sgx_eos_s *e;
+  int rc = new_handle(SGX_EOS_SPINER_RHOT, &e);
+  if (rc) return rc;
+  rc = build_spiner_rhot(raw, reproducibility_mode, pmin_vapor_dome, e);
+  if (rc) {
+    sgx_eos_destroy(e);
+    *out = nullptr;
+    return rc;
+  }
+  *out = e;
+  return SGX_OK;
+}
+
+int sgx_eos_create_spiner_rhosie(const sgx_sp5_tables *raw, int reproducibility_mode,
+                                 int pmin_vapor_dome, sgx_eos_t *out) {
+  sgx_eos_s *e;
+  int rc = new_handle(SGX_EOS_SPINER_RHOSIE, &e);
+  if (rc) return rc;
+  rc = build_spiner_rhosie(raw, reproducibility_mode, pmin_vapor_dome, e);
+  if (rc) {
+    sgx_eos_destroy(e);
+    *out = nullptr;
+    return rc;
+  }
+  *out = e;
+  return SGX_OK;
+}
+
+void sgx_helm_default_options(sgx_helm_options *opt) {
+  if (!opt) return;
+  opt->enable_rad = opt->enable_gas = opt->enable_coulomb = 1;
+  opt->gas_ionized = opt->gas_degenerate = 1;
+  opt->use_newton_raphson = 1;
+  opt->lambda_has_lT_slot = 1;
+}
+
+int sgx_eos_create_helmholtz(const char *table_path, const sgx_helm_options *opt,
+                             sgx_eos_t *out) {
+  sgx_eos_s *e;
+  int rc = new_handle(SGX_EOS_HELMHOLTZ, &e);
+  if (rc) return rc;
+  rc = build_helmholtz(table_path, opt, e);
+  if (rc) {
+    sgx_eos_destroy(e);
+    *out = nullptr;
+    return rc;
+  }
+  *out = e;
+  return SGX_OK;
+}
+
+int sgx_eos_destroy(sgx_eos_t e) {
+  if (!e) return SGX_OK;
+  cudaSetDevice(e->device);
+  if (e->tables.dev) cudaFree(e->tables.dev);
+  if (e->pinned) cudaFreeHost(e->pinned);
+  if (e->dscratch) cudaFree(e->dscratch);
+  if (e->own_stream) cudaStreamDestroy(e->own_stream);
+  delete e;
+  return SGX_OK;
+}
+
+int sgx_eos_type(sgx_eos_t e) { return e ? e->kind : SGX_ERR_INVALID; }
+int sgx_eos_nlambda(sgx_eos_t e) {
+  if (!e) return SGX_ERR_INVALID;
+  switch (e->kind) {
+  case SGX_EOS_SPINER_RHOT:
+    return 2;
+  case SGX_EOS_SPINER_RHOSIE:
+    return 1;
+  case SGX_EOS_HELMHOLTZ:
+    return 3;
+  default:
+    return 0;
+  }
+}
+unsigned long sgx_eos_preferred_input(sgx_eos_t e) {
+  if (!e) return 0;
+  switch (e->kind) {
+  case SGX_EOS_IDEAL:
+    return IdealGas::preferred_input;
+  case SGX_EOS_GRUNEISEN:
+  case SGX_EOS_DAVIS_REACTANTS:
+  case SGX_EOS_DAVIS_PRODUCTS:
+    return TQ_DENSITY | TQ_SIE;
+  default:
+    return TQ_DENSITY | TQ_TEMPERATURE;
+  }
+}
+uint64_t sgx_eos_scratch_bytes(sgx_eos_t, int, int64_t) { return 0; }
+double sgx_eos_maximum_density(sgx_eos_t e) {
+  if (!e) return 0;
+  if (e->kind == SGX_EOS_GRUNEISEN) return e->analytic.gr.rho_max;
+  if (e->kind == SGX_EOS_HELMHOLTZ) return 1e15;
+  return 1e100;
+}
+int64_t sgx_eos_get_table(sgx_eos_t e, const char *name, double *out, int64_t cap) {
+  if (!e || !name) return fail(SGX_ERR_INVALID, "null argument");
+  auto it = e->tables.index.find(name);
+  if (it == e->tables.index.end()) return fail(SGX_ERR_INVALID, "no table named '%s'", name);
+  const int64_t n = (int64_t)it->second.second;
+  if (!out) return n;
+  const int64_t m = n < cap ? n : cap;
+  // read back from the DEVICE copy: this is what the kernels see
+  if (check_handle(e)) return SGX_ERR_CUDA;
+  cudaError_t err = cudaMemcpy(out, e->tables.dev + it->second.first, m * sizeof(double),
+                               cudaMemcpyDeviceToHost);
+  if (err != cudaSuccess) return fail(SGX_ERR_CUDA, "cudaMemcpy: %s", cudaGetErrorString(err));
+  return m;
+}
+int sgx_eos_get_scalar(sgx_eos_t e, const char *name, double *out) {
+  if (!e || !name || !out) return fail(SGX_ERR_INVALID, "null argument");
+  auto it = e->tables.scalars.find(name);
+  if (it == e->tables.scalars.end())
+    return fail(SGX_ERR_INVALID, "no scalar named '%s'", name);
+  *out = it->second;
+  return SGX_OK;
+}
+
+int sgx_eos_eval(sgx_eos_t e, int method, const double *in1, const double *in2, double *out,
+                 int64_t n, double *lambda, int lambda_stride, sgx_stream_t stream) {
+  int rc = check_handle(e);
+  if (rc) return rc;
+  if (n < 0) return fail(SGX_ERR_INVALID, "negative n");
+  if (n == 0) return SGX_OK;
+  if (!in1 || !in2 || !out) return fail(SGX_ERR_INVALID, "null array");
+  if (lambda && lambda_stride < sgx_eos_nlambda(e))
+    return fail(SGX_ERR_INVALID, "lambda_stride %d < nlambda %d", lambda_stride,
+                sgx_eos_nlambda(e));
+  cudaStream_t s = (cudaStream_t)stream;
+  switch (e->kind) {
+  case SGX_EOS_IDEAL:
+    return launch_eval(e->analytic.ideal, method, in1, in2, out, n, nullptr, 0, s, 8);
+  case SGX_EOS_GRUNEISEN:
+    return launch_eval(e->analytic.gr, method, in1, in2, out, n, nullptr, 0, s, 8);
+  case SGX_EOS_DAVIS_REACTANTS:
+    return launch_eval(e->analytic.dr, method, in1, in2, out, n, nullptr, 0, s, 8);
+  case SGX_EOS_DAVIS_PRODUCTS:
+    return launch_eval(e->analytic.dp, method, in1, in2, out, n, nullptr, 0, s, 8);
+  case SGX_EOS_SPINER_RHOT:
+    return launch_eval(e->rhot, method, in1, in2, out, n, lambda, lambda_stride, s, 8);
+  case SGX_EOS_SPINER_RHOSIE:
+    return launch_eval(e->rhosie, method, in1, in2, out, n, lambda, lambda_stride, s, 8);
+  case SGX_EOS_HELMHOLTZ:
+    return launch_helm_eval(e, method, in1, in2, out, n, lambda, lambda_stride, s);
+  default:
+    return fail(SGX_ERR_INVALID, "bad EOS kind %d", e->kind);
+  }
+}
+
+int sgx_PressureFromDensityTemperature(sgx_eos_t e, const double *rhos, const double *temps,
+                                       double *out, int64_t n, double *lambda, int ls,
+                                       sgx_stream_t s) {
+  return sgx_eos_eval(e, SGX_P_FROM_RHO_T, rhos, temps, out, n, lambda, ls, s);
+}
+int sgx_InternalEnergyFromDensityTemperature(sgx_eos_t e, const double *rhos,
+                                             const double *temps, double *out, int64_t n,
+                                             double *lambda, int ls, sgx_stream_t s) {
+  return sgx_eos_eval(e, SGX_E_FROM_RHO_T, rhos, temps, out, n, lambda, ls, s);
+}
+int sgx_TemperatureFromDensityInternalEnergy(sgx_eos_t e, const double *rhos,
+                                             const double *sies, double *out, int64_t n,
+                                             double *lambda, int ls, sgx_stream_t s) {
+  return sgx_eos_eval(e, SGX_T_FROM_RHO_E, rhos, sies, out, n, lambda, ls, s);
+}
+int sgx_PressureFromDensityInternalEnergy(sgx_eos_t e, const double *rhos, const double *sies,
+                                          double *out, int64_t n, double *lambda, int ls,
+                                          sgx_stream_t s) {
+  return sgx_eos_eval(e, SGX_P_FROM_RHO_E, rhos, sies, out, n, lambda, ls, s);
+}
+
+int sgx_PressureEnergyFromDensityTemperature(sgx_eos_t e, const double *rhos,
+                                             const double *temps, double *P, double *E,
+                                             int64_t n, double *lambda, int ls,
+                                             sgx_stream_t stream) {
+  int rc = check_handle(e);
+  if (rc) return rc;
+  if (n <= 0) return n == 0 ? SGX_OK : fail(SGX_ERR_INVALID, "negative n");
+  if (!rhos || !temps || !P || !E) return fail(SGX_ERR_INVALID, "null array");
+  cudaStream_t s = (cudaStream_t)stream;
+  switch (e->kind) {
+  case SGX_EOS_IDEAL:
+    return launch_pe(e->analytic.ideal, rhos, temps, P, E, n, nullptr, 0, s);
+  case SGX_EOS_GRUNEISEN:
+    return launch_pe(e->analytic.gr, rhos, temps, P, E, n, nullptr, 0, s);
+  case SGX_EOS_DAVIS_REACTANTS:
+    return launch_pe(e->analytic.dr, rhos, temps, P, E, n, nullptr, 0, s);
+  case SGX_EOS_DAVIS_PRODUCTS:
+    return launch_pe(e->analytic.dp, rhos, temps, P, E, n, nullptr, 0, s);
+  case SGX_EOS_SPINER_RHOT:
+    return launch_pe(e->rhot, rhos, temps, P, E, n, lambda, ls, s);
+  case SGX_EOS_SPINER_RHOSIE:
+    return launch_pe(e->rhosie, rhos, temps, P, E, n, lambda, ls, s);
+  default:
+    return fail(SGX_ERR_UNSUPPORTED, "fused P+e not available for EOS kind %d", e->kind);
+  }
+}
+
+int sgx_FillEos(sgx_eos_t e, double *rhos, double *temps, double *energies, double *presses,
+                double *cvs, double *bmods, int64_t n, unsigned long output, double *lambda,
+                int ls, sgx_stream_t stream) {
+  int rc = check_handle(e);
+  if (rc) return rc;
+  if (n <= 0) return n == 0 ? SGX_OK : fail(SGX_ERR_INVALID, "negative n");
+  if (output == 0) return fail(SGX_ERR_UNSUPPORTED, "FillEos: output == thermalqs::none");
+  cudaStream_t s = (cudaStream_t)stream;
+  switch (e->kind) {
+  case SGX_EOS_IDEAL:
+    return launch_fill(e, e->analytic.ideal, rhos, temps, energies, presses, cvs, bmods, n,
+                       output, nullptr, 0, s);
+  case SGX_EOS_GRUNEISEN:
+    return launch_fill(e, e->analytic.gr, rhos, temps, energies, presses, cvs, bmods, n,
+                       output, nullptr, 0, s);
+  case SGX_EOS_DAVIS_REACTANTS:
+    return launch_fill(e, e->analytic.dr, rhos, temps, energies, presses, cvs, bmods, n,
+                       output, nullptr, 0, s);
+  case SGX_EOS_DAVIS_PRODUCTS:
+    return launch_fill(e, e->analytic.dp, rhos, temps, energies, presses, cvs, bmods, n,
+                       output, nullptr, 0, s);
+  case SGX_EOS_SPINER_RHOT:
+    return launch_fill(e, e->rhot, rhos, temps, energies, presses, cvs, bmods, n, output,
+                       lambda, ls, s);
+  case SGX_EOS_SPINER_RHOSIE:
+    return launch_fill(e, e->rhosie, rhos, temps, energies, presses, cvs, bmods, n, output,
+                       lambda, ls, s);
+  case SGX_EOS_HELMHOLTZ:
+    return launch_helm_fill(e, rhos, temps, energies, presses, cvs, bmods, n, output, lambda,
+                            ls, s);
+  default:
+    return fail(SGX_ERR_INVALID, "bad EOS kind %d", e->kind);
+  }
+}
+
+// ---- host-pointer forms ---------------------------------------------------------------
+int sgx_eos_eval_host(sgx_eos_t e, int method, const double *in1, const double *in2,
+                      double *out, int64_t n, double *lambda, int ls) {
+  int rc = check_handle(e);
+  if (rc) return rc;
+  if (n <= 0) return n == 0 ? SGX_OK : fail(SGX_ERR_INVALID, "negative n");
+  if (!in1 || !in2 || !out) return fail(SGX_ERR_INVALID, "null array");
+  const size_t nb = (size_t)n * sizeof(double);
+  const size_t lb = lambda ? nb * ls : 0;
+  rc = ensure_staging(e, 0, 3 * nb + lb);
+  if (rc) return rc;
+  cudaStream_t s = e->own_stream;
+  double *d1 = (double *)e->dscratch, *d2 = d1 + n, *dout = d2 + n;
+  double *dl = lambda ? dout + n : nullptr;
+  SGX_CUDA_OK(cudaMemcpyAsync(d1, in1, nb, cudaMemcpyHostToDevice, s));
+  SGX_CUDA_OK(cudaMemcpyAsync(d2, in2, nb, cudaMemcpyHostToDevice, s));
+  if (lambda) SGX_CUDA_OK(cudaMemcpyAsync(dl, lambda, lb, cudaMemcpyHostToDevice, s));
+  rc = sgx_eos_eval(e, method, d1, d2, dout, n, dl, ls, s);
+  if (rc) return rc;
+  SGX_CUDA_OK(cudaMemcpyAsync(out, dout, nb, cudaMemcpyDeviceToHost, s));
+  if (lambda) SGX_CUDA_OK(cudaMemcpyAsync(lambda, dl, lb, cudaMemcpyDeviceToHost, s));
+  SGX_CUDA_OK(cudaStreamSynchronize(s));
+  return SGX_OK;
+}
+
+int sgx_FillEos_host(sgx_eos_t e, double *rhos, double *temps, double *energies,
+                     double *presses, double *cvs, double *bmods, int64_t n,
+                     unsigned long output, double *lambda, int ls) {
+  int rc = check_handle(e);
+  if (rc) return rc;
+  if (n <= 0) return n == 0 ? SGX_OK : fail(SGX_ERR_INVALID, "negative n");
+  const size_t nb = (size_t)n * sizeof(double);
+  const size_t lb = lambda ? nb * ls : 0;
+  rc = ensure_staging(e, 0, 6 * nb + lb);
+  if (rc) return rc;
+  cudaStream_t s = e->own_stream;
+  double *h[6] = {rhos, temps, energies, presses, cvs, bmods};
+  const unsigned long bits[6] = {TQ_DENSITY, TQ_TEMPERATURE, TQ_SIE, TQ_PRESSURE, TQ_CV, TQ_BMOD};
+  double *d[6];
+  for (int k = 0; k < 6; ++k)
+    d[k] = h[k] ? (double *)e->dscratch + (size_t)k * n : nullptr;
+  double *dl = lambda ? (double *)e->dscratch + 6 * (size_t)n : nullptr;
+  for (int k = 0; k < 4; ++k) // cv / bmod are never inputs
+    if (h[k] && !(output & bits[k]))
+      SGX_CUDA_OK(cudaMemcpyAsync(d[k], h[k], nb, cudaMemcpyHostToDevice, s));
+  if (lambda) SGX_CUDA_OK(cudaMemcpyAsync(dl, lambda, lb, cudaMemcpyHostToDevice, s));
+  rc = sgx_FillEos(e, d[0], d[1], d[2], d[3], d[4], d[5], n, output, dl, ls, s);
+  if (rc) return rc;
+  for (int k = 0; k < 6; ++k)
+    if (h[k] && (output & bits[k]))
+      SGX_CUDA_OK(cudaMemcpyAsync(h[k], d[k], nb, cudaMemcpyDeviceToHost, s));
+  if (lambda) SGX_CUDA_OK(cudaMemcpyAsync(lambda, dl, lb, cudaMemcpyDeviceToHost, s));
+  SGX_CUDA_OK(cudaStreamSynchronize(s));
+  return SGX_OK;
+}
+
+// ---- building blocks ------------------------------------------------------------------
+int sgx_fastmath_eval(int which, const double *x, double *y, int64_t n, sgx_stream_t stream) {
+  if (n <= 0) return n == 0 ? SGX_OK : fail(SGX_ERR_INVALID, "negative n");
+  if (!x || !y) return fail(SGX_ERR_INVALID, "null array");
+  const LaunchCfg c = stream_cfg(n, 256, 8);
+  fastmath_kernel<<<c.blocks, c.threads, 0, (cudaStream_t)stream>>>(which, x, y, n);
+  count_launch();
+  SGX_CUDA_OK(cudaGetLastError());
+  return SGX_OK;
+}
+int sgx_solve_Ax_b(int n, double *a, double *b, int *ok, int64_t batch, sgx_stream_t stream) {
+  if (n < 1 || n > 3) return fail(SGX_ERR_INVALID, "n must be 1..3");
+  if (batch <= 0) return batch == 0 ? SGX_OK : fail(SGX_ERR_INVALID, "negative batch");
+  const int threads = 128;
+  const int blocks = (int)((batch + threads - 1) / threads);
+  solve_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(n, a, b, ok, batch);
+  count_launch();
+  SGX_CUDA_OK(cudaGetLastError());
+  return SGX_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,106 @@
+// Host-side internals of libsgx_b200 shared by the translation units: the opaque EOS handle,
+// error plumbing, launch accounting and pinned staging buffers.  Not part of the public ABI.
+#ifndef SGX_INTERNAL_HPP_
+#define SGX_INTERNAL_HPP_
+
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <map>
+#include <string>
+#include <utility>
+#include <vector>
+
+#include "../../include/sgx_b200.h"
+#include "sgx_helmholtz.cuh"
+#include "sgx_pte.cuh"
+#include "sgx_spiner.cuh"
+
+namespace sgx {
+
+// thread-local last-error text
+inline std::string &last_error() {
+  static thread_local std::string e;
+  return e;
+}
+inline int fail(int code, const char *fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  last_error() = buf;
+  return code;
+}
+#define SGX_CUDA_OK(expr)                                                                \
+  do {                                                                                   \
+    cudaError_t _e = (expr);                                                             \
+    if (_e != cudaSuccess)                                                               \
+      return sgx::fail(SGX_ERR_CUDA, "%s failed: %s (%s:%d)", #expr,                     \
+                       cudaGetErrorString(_e), __FILE__, __LINE__);                      \
+  } while (0)
+
+extern std::atomic<unsigned long long> g_launches;
+inline void count_launch(int n = 1) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+// Named host copies of every table + where it sits in the single device allocation.
+struct TableStore {
+  std::vector<double> host;                                          // concatenated, padded
+  std::map<std::string, std::pair<size_t, size_t>> index;            // name -> (offset, count)
+  std::map<std::string, double> scalars;
+  double *dev = nullptr;
+  // 256-byte aligned slots so vector loads / TMA-friendly strides stay possible
+  size_t add(const std::string &name, const double *src, size_t n) {
+    const size_t off = (host.size() + 31) & ~size_t(31);
+    host.resize(off + n, 0.0);
+    if (src) std::copy(src, src + n, host.begin() + off);
+    index[name] = {off, n};
+    return off;
+  }
+  double *h(const std::string &name) { return host.data() + index.at(name).first; }
+  const double *d(const std::string &name) const { return dev + index.at(name).first; }
+  bool has(const std::string &name) const { return index.count(name) != 0; }
+};
+
+} // namespace sgx
+
+struct sgx_eos_s {
+  int kind = -1;
+  int device = 0;
+  sgx::AnyEos analytic;    // kinds 0-3
+  sgx::SpinerRhoT rhot;    // kind 4
+  sgx::SpinerRhoSie rhosie; // kind 5
+  sgx::HelmDev helm;       // kind 6
+  sgx::TableStore tables;
+  // pinned staging for the *_host entry points (grown on demand)
+  void *pinned = nullptr;
+  size_t pinned_bytes = 0;
+  void *dscratch = nullptr;
+  size_t dscratch_bytes = 0;
+  cudaStream_t own_stream = nullptr;
+};
+
+namespace sgx {
+int upload_tables(sgx_eos_s *e);   // cudaMalloc + H2D of e->tables.host, L2 persistence hint
+int ensure_staging(sgx_eos_s *e, size_t pinned_bytes, size_t device_bytes);
+int build_spiner_rhot(const sgx_sp5_tables *raw, int reproducible, int pmin_vapor_dome,
+                      sgx_eos_s *e);
+int build_spiner_rhosie(const sgx_sp5_tables *raw, int reproducible, int pmin_vapor_dome,
+                        sgx_eos_s *e);
+int build_helmholtz(const char *path, const sgx_helm_options *opt, sgx_eos_s *e);
+int launch_helm_fill(sgx_eos_s *e, double *rho, double *T, double *en, double *P, double *cv,
+                     double *bmod, int64_t n, unsigned long output, double *lambda,
+                     int stride, cudaStream_t s);
+int launch_helm_eval(sgx_eos_s *e, int method, const double *in1, const double *in2,
+                     double *out, int64_t n, double *lambda, int stride, cudaStream_t s);
+// launch geometry: persistent-ish grid-stride, multiple of the SM count
+struct LaunchCfg {
+  int blocks, threads;
+};
+LaunchCfg stream_cfg(int64_t work_items, int threads, int blocks_per_sm);
+int sm_count();
+} // namespace sgx
+
+#endif // SGX_INTERNAL_HPP_

@@ -1,0 +1,384 @@
+// Device-side numerics shared by every kernel of libsgx_b200: the reference's
+// "not-quite-transcendental" logs, robust division, Spiner grid weights and multilinear
+// interpolation, and the 1-D root finders.  FP64 throughout, compiled with -fmad=false so
+// every expression rounds exactly like the reference's x86-64 build (no FMA contraction).
+//
+// Reference (paths relative to the lanl/singularity-eos checkout):
+//   base/fast-math/logs.hpp:188-292              lg / pow2 / log10 / pow10 (NQT order 2, aliased)
+//   base/robust_utils.hpp:27-70                  SMALL, EPS, sgn, ratio
+//   base/math_utils.hpp:32-60                    pow<N>, pow10
+//   eos/eos_spiner_common.hpp:52-57              to_log / from_log
+//   utils/spiner/spiner/regular_grid_1d.hpp:66-87     bound / index / weights
+//   utils/spiner/spiner/piecewise_grid_1d.hpp:73-126  findGrid / weights
+//   utils/spiner/spiner/databox.hpp:451-475      interpToReal 1-D / 2-D
+//   base/root-finding-1d/root_finding.hpp:114-310     check_bracket, set_bracket,
+//                                                regula_falsi, newton_raphson
+#ifndef SGX_MATH_CUH_
+#define SGX_MATH_CUH_
+
+#include <cfloat>
+#include <climits>
+#include <cstdint>
+
+#ifdef __CUDACC__
+#define SGX_HD __host__ __device__ __forceinline__
+#define SGX_HDI __host__ __device__ inline
+#define SGX_D __device__ __forceinline__
+#else
+#define SGX_HD inline
+#define SGX_HDI inline
+#define SGX_D inline
+#endif
+#include <cmath>
+#include <cstring>
+
+namespace sgx {
+
+// ---------------------------------------------------------------------------------------
+// robust utils
+// ---------------------------------------------------------------------------------------
+constexpr double kSmall = 10.0 * DBL_MIN;    // robust::SMALL()
+constexpr double kEps = 10.0 * DBL_EPSILON;  // robust::EPS()
+
+SGX_HD int sgn(const double v) { return (0.0 <= v) - (v < 0.0); }
+// a / (b + sgn(b) * SMALL)
+SGX_HD double ratio(const double a, const double b) { return a / (b + sgn(b) * kSmall); }
+// std::max / std::min argument-order semantics (matter only for NaN / signed zero)
+SGX_HD double stdmax(const double a, const double b) { return (a < b) ? b : a; }
+SGX_HD double stdmin(const double a, const double b) { return (b < a) ? b : a; }
+
+// math_utils::pow<N>: same association as the recursive template
+SGX_HD double pow2i(const double x) { return x * x; }
+SGX_HD double pow3i(const double x) { return x * (x * x); }
+SGX_HD double pow4i(const double x) { return (x * x) * (x * x); }
+SGX_HD double pow5i(const double x) { return x * ((x * x) * (x * x)); }
+
+// static_cast<int>(double) as the x86-64 host does it (cvttsd2si: "integer indefinite" =
+// INT_MIN when out of range or NaN); CUDA's cvt.rzi saturates instead.
+SGX_HD int cvt_int_x86(const double v) {
+#ifdef __CUDA_ARCH__
+  return (v >= 2147483648.0 || v <= -2147483649.0 || v != v) ? INT_MIN : __double2int_rz(v);
+#else
+  return static_cast<int>(v);
+#endif
+}
+SGX_HD long long cvt_ll_x86(const double v) {
+#ifdef __CUDA_ARCH__
+  return (v >= 9223372036854775808.0 || v < -9223372036854775808.0 || v != v)
+             ? LLONG_MIN
+             : __double2ll_rz(v);
+#else
+  return static_cast<long long>(v);
+#endif
+}
+SGX_HD long long as_int(const double x) {
+#ifdef __CUDA_ARCH__
+  return __double_as_longlong(x);
+#else
+  long long i;
+  std::memcpy(&i, &x, sizeof(i));
+  return i;
+#endif
+}
+SGX_HD double as_double(const long long i) {
+#ifdef __CUDA_ARCH__
+  return __longlong_as_double(i);
+#else
+  double x;
+  std::memcpy(&x, &i, sizeof(x));
+  return x;
+#endif
+}
+SGX_HD double sqrt_rn(const double x) {
+#ifdef __CUDA_ARCH__
+  return __dsqrt_rn(x);
+#else
+  return std::sqrt(x);
+#endif
+}
+
+// ---------------------------------------------------------------------------------------
+// FastMath NQT order-2, integer aliased (the reference default build)
+// ---------------------------------------------------------------------------------------
+namespace fastmath {
+constexpr long long one = 1;
+constexpr long long one_as_int = (one << 62) - (one << 52);
+constexpr double scale_down = 2.22044604925031e-16; // literal as in logs.hpp:112
+constexpr double scale_up = (double)(one << 52);
+constexpr long long mantissa_mask = (one << 52) - one;
+constexpr long long low_mask = (one << 26) - 1;
+
+SGX_HD double lg(const double x) {
+  const long long x_as_int = as_int(x) - one_as_int;
+  const long long frac_as_int = x_as_int & mantissa_mask;
+  const long long frac_high = frac_as_int >> 26;
+  const long long frac_low = frac_as_int & low_mask;
+  const long long frac_squared = frac_high * frac_high + ((frac_high * frac_low) >> 25);
+  return static_cast<double>(x_as_int + ((frac_as_int - frac_squared) / 3)) * scale_down;
+}
+SGX_HD double pow2(const double x) {
+  constexpr long long a = 9007199254740992ll;  // 2 * 2^52
+  constexpr double b = 67108864.0;             // 2^26
+  constexpr long long c = 18014398509481984ll; // 4 * 2^52
+  const long long x_as_int = cvt_ll_x86(x * scale_up);
+  const long long frac_as_int = x_as_int & mantissa_mask;
+  const long long frac_sqrt =
+      cvt_ll_x86(b * sqrt_rn(static_cast<double>(c - 3 * frac_as_int)));
+  return as_double(x_as_int + a - frac_sqrt - frac_as_int + one_as_int);
+}
+SGX_HD double log10(const double x) {
+  constexpr double LOG2OLOG10 = 0.301029995663981195;
+  return LOG2OLOG10 * lg(x);
+}
+SGX_HD double pow10(const double x) {
+  constexpr double LOG10OLOG2 = 3.321928094887362626;
+  return pow2(LOG10OLOG2 * x);
+}
+} // namespace fastmath
+
+// spiner_common::to_log / from_log
+SGX_HD double to_log(const double x, const double offset) {
+  return fastmath::log10(fabs(stdmax(x, -offset) + offset) + kEps);
+}
+SGX_HD double from_log(const double lx, const double offset) {
+  return fastmath::pow10(lx) - offset;
+}
+
+// ---------------------------------------------------------------------------------------
+// Spiner grids + interpolation
+// ---------------------------------------------------------------------------------------
+struct Grid1D {
+  int ngrids;
+  int npoints[3];
+  int ptot[3]; // pointTotals_
+  double min[3], max[3], dx[3], idx[3];
+
+  SGX_HD int n_total() const { return ptot[ngrids - 1] + npoints[ngrids - 1]; }
+  SGX_HD double gmin() const { return min[0]; }
+  SGX_HD double gmax() const { return max[ngrids - 1]; }
+  // PiecewiseGrid1D::findGrid + findGridFromPosition
+  SGX_HD int find_grid(const double x) const {
+    if (ngrids == 1) return 0;
+    int l = 0, r = ngrids - 1;
+    for (int iter = 0; iter < ngrids; iter++) {
+      const int m = (l + r) / 2;
+      const int d = (x < min[m]) ? -1 : ((x > max[m]) ? 1 : 0);
+      if (d < 0) {
+        if (m == 0) return 0;
+        r = m - 1;
+      } else if (d > 0) {
+        if (m >= ngrids - 1) return ngrids - 1;
+        l = m + 1;
+      } else {
+        return m;
+      }
+    }
+    return 0; // unreachable for well-formed grids (reference aborts)
+  }
+  // PiecewiseGrid1D::x(i)
+  SGX_HD double x(const int i) const {
+    int ig = 0;
+    for (int g = ngrids - 1; g > 0; --g) {
+      if (i >= ptot[g]) {
+        ig = g;
+        break;
+      }
+    }
+    return (i - ptot[ig]) * dx[ig] + min[ig];
+  }
+  SGX_HD void weights(const double x, int &ix, double &w0, double &w1) const {
+    const int ig = find_grid(x);
+    int i = cvt_int_x86(idx[ig] * (x - min[ig]));
+    if (i < 0) i = 0;
+    if (i >= npoints[ig] - 1) i = npoints[ig] - 2;
+    const double floor_x = (double)i * dx[ig] + min[ig];
+    w1 = idx[ig] * (x - floor_x);
+    w0 = (1. - w1);
+    ix = i + ptot[ig];
+  }
+};
+
+SGX_HD double ldg(const double *p) {
+#ifdef __CUDA_ARCH__
+  return __ldg(p);
+#else
+  return *p;
+#endif
+}
+
+// DataBox::interpToReal(x), rank 1
+SGX_HD double interp1d(const double *__restrict__ a, const Grid1D &g, const double x) {
+  int ix;
+  double w0, w1;
+  g.weights(x, ix, w0, w1);
+  return w0 * ldg(a + ix) + w1 * ldg(a + ix + 1);
+}
+// The four-corner blend of DataBox::interpToReal(x2, x1), databox.hpp:471-474
+SGX_HD double blend2d(const double *__restrict__ a, const int n1, const int ix2,
+                     const double w20, const double w21, const int ix1, const double w10,
+                     const double w11) {
+  const double *r0 = a + (size_t)ix2 * n1 + ix1;
+  const double *r1 = r0 + n1;
+  return (w20 * (w10 * ldg(r0) + w11 * ldg(r0 + 1)) + w21 * (w10 * ldg(r1) + w11 * ldg(r1 + 1)));
+}
+// DataBox::interpToReal(x2, x1), rank 2: g1 = fastest axis (range(0)), g2 = range(1)
+SGX_HD double interp2d(const double *__restrict__ a, const Grid1D &g2, const Grid1D &g1,
+                      const int n1, const double x2, const double x1) {
+  int ix1, ix2;
+  double w10, w11, w20, w21;
+  g1.weights(x1, ix1, w10, w11);
+  g2.weights(x2, ix2, w20, w21);
+  return blend2d(a, n1, ix2, w20, w21, ix1, w10, w11);
+}
+// Position along one axis, computed once and shared by several tables
+struct AxisPos {
+  int ix;
+  double w0, w1;
+  SGX_HD AxisPos() {}
+  SGX_HD AxisPos(const Grid1D &g, const double x) { g.weights(x, ix, w0, w1); }
+};
+SGX_HD double interp1d(const double *__restrict__ a, const AxisPos &p) {
+  return p.w0 * ldg(a + p.ix) + p.w1 * ldg(a + p.ix + 1);
+}
+SGX_HD double interp2d(const double *__restrict__ a, const int n1, const AxisPos &p2,
+                      const AxisPos &p1) {
+  return blend2d(a, n1, p2.ix, p2.w0, p2.w1, p1.ix, p1.w0, p1.w1);
+}
+
+// ---------------------------------------------------------------------------------------
+// Root finding
+// ---------------------------------------------------------------------------------------
+namespace root {
+enum Status { SUCCESS = 0, FAIL = 1 };
+
+SGX_HD bool check_bracket(const double ya, const double yb) { return (ya * yb <= 0.0); }
+
+// set_bracket, root_finding.hpp:118-151.  f already has ytarget subtracted.
+template <typename F>
+SGX_HDI bool set_bracket(const F &f, double &a, const double guess, double &b,
+                                   double &ya, const double yg, double &yb) {
+  constexpr int max_search_depth = 6;
+  const double dx = b - a;
+  for (int level = 0; level < max_search_depth; level++) {
+    const int nlev = (1 << level);
+    for (int i = 0; i < nlev; i++) {
+      const double x = a + (i + 0.5) * dx;
+      const double yx = f(x);
+      if (check_bracket(yx, yg)) {
+        if (x < guess) {
+          a = x;
+          ya = yx;
+          b = guess;
+          yb = yg;
+        } else {
+          a = guess;
+          ya = yg;
+          b = x;
+          yb = yx;
+        }
+        return true;
+      }
+    }
+  }
+  return false;
+}
+
+// regula_falsi (Illinois variant), root_finding.hpp:154-240.  `niter` receives the loop count.
+template <typename F>
+SGX_HDI Status regula_falsi(const F &f, const double ytarget, const double guess,
+                                      double a, double b, const double xtol,
+                                      const double ytol, double &xroot, int *niter = nullptr) {
+  constexpr int max_iter = 1000; // SECANT_NITER_MAX
+  auto func = [&](const double x) { return f(x) - ytarget; };
+  double ya = func(a);
+  double yg = func(guess);
+  double yb;
+
+  if (check_bracket(ya, yg)) {
+    b = guess;
+    yb = yg;
+  } else {
+    yb = func(b);
+    if (check_bracket(yg, yb)) {
+      a = guess;
+      ya = yg;
+    } else {
+      if (!set_bracket(func, a, guess, b, ya, yg, yb)) {
+        if (niter) *niter = 0;
+        return FAIL;
+      }
+    }
+  }
+
+  const double sign = (ya < 0 ? 1.0 : -1.0);
+  ya *= sign;
+  yb *= sign;
+
+  int b1 = 0;
+  int b2 = 0;
+  int iteration_count = 0;
+  while (b - a > 2.0 * xtol && (fabs(ya) > ytol || fabs(yb) > ytol) &&
+         iteration_count < max_iter) {
+    const double c = (a * yb - b * ya) / (yb - ya);
+    if (c == a) {
+      b = a;
+      continue;
+    } else if (c == b) {
+      a = b;
+      continue;
+    }
+    const double yc = sign * func(c);
+    if (yc > 0.0) {
+      b = c;
+      yb = yc;
+      b1++;
+      ya *= (b1 > 1 ? 0.5 : 1.0);
+      b2 = 0;
+    } else if (yc < 0.0) {
+      a = c;
+      ya = yc;
+      b2++;
+      yb *= (b2 > 1 ? 0.5 : 1.0);
+      b1 = 0;
+    } else {
+      a = c;
+      b = c;
+    }
+    iteration_count++;
+  }
+  if (niter) *niter = iteration_count;
+  xroot = 0.5 * (a + b);
+  return (iteration_count == max_iter) ? FAIL : SUCCESS;
+}
+
+// newton_raphson, root_finding.hpp:246-310.  f(x, y, dy) returns value and derivative.
+template <typename F>
+SGX_HDI Status newton_raphson(const F &f, const double ytarget, const double guess,
+                                        const double a, const double b, const double ytol,
+                                        double &xroot, const bool fail_on_bound_root = true) {
+  constexpr int max_iter = 100; // NEWTON_RAPHSON_NITER_MAX
+  double _x = guess;
+  double _xold = 0.0;
+  Status status = SUCCESS;
+  double yg, dfunc;
+  int iter;
+  for (iter = 0; iter < max_iter; iter++) {
+    f(_x, yg, dfunc);
+    if (fabs(yg - ytarget) < fabs(ytol * ytarget)) break;
+    _xold = _x;
+    _x = _x - (yg - ytarget) / dfunc;
+    if ((_x <= a && _xold <= a) || (_x >= b && _xold >= b)) {
+      if (fail_on_bound_root) status = FAIL;
+      break;
+    }
+    _x = stdmax(stdmin(_x, b), a);
+  }
+  if (iter >= max_iter) status = FAIL;
+  xroot = _x;
+  return status;
+}
+} // namespace root
+
+} // namespace sgx
+
+#endif // SGX_MATH_CUH_

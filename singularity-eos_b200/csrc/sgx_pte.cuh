@@ -1,0 +1,1016 @@
+// PTE mixed-cell closure on device: PTESolverRhoT, PTESolverPT, the PTESolver Newton /
+// line-search driver, ApproxTemperatureFromRhoMatU and the small dense solve.  One thread
+// owns one cell; all solver scratch (the reference's 39 / 18 doubles per cell) lives in
+// registers / local memory, never in HBM.
+//
+// Reference: singularity-eos/closure/mixed_cell_models.hpp
+//   :43-78    MixParams                   :80-87     SolverStatus
+//   :161-278  check_nans, solve_Ax_b_wscr :287-305   sum_neumaier
+//   :329-786  PTESolverBase               :790-847   ApproxTemperatureFromRhoMatU
+//   :883-1193 PTESolverRhoT               :1207-1446 PTESolverPT
+//   :2188-2291 PTESolver
+// Sequential order of every floating-point reduction is preserved (Neumaier sums, Jacobian
+// assembly, line-search acceptance) so converged states and flags match the reference.
+#ifndef SGX_PTE_CUH_
+#define SGX_PTE_CUH_
+
+#include "sgx_analytic.cuh"
+#include "sgx_math.cuh"
+
+namespace sgx {
+
+constexpr int kMaxMat = 8;
+
+struct MixParamsDev {
+  int iterate_t_guess;
+  double derivative_eps;
+  double pte_rel_tolerance_p, pte_rel_tolerance_t, pte_rel_tolerance_e, pte_rel_tolerance_v;
+  double pte_abs_tolerance_p, pte_abs_tolerance_t;
+  double pte_slow_convergence_thresh;
+  double pte_rel_tolerance_p_sufficient, pte_rel_tolerance_t_sufficient,
+      pte_rel_tolerance_e_sufficient, pte_rel_tolerance_v_sufficient;
+  double pte_abs_tolerance_p_sufficient, pte_abs_tolerance_t_sufficient;
+  unsigned long long pte_max_iter_per_mat;
+  double line_search_alpha;
+  unsigned long long line_search_max_iter;
+  double line_search_fac;
+  double vfrac_safety_fac;
+  double temperature_limit;
+  double default_tguess;
+  double min_dtde;
+  unsigned long long pte_small_step_tries;
+  double pte_small_step_thresh;
+  double pte_max_dpdv;
+  long long pte_reduced_system_exclude_idx;
+};
+
+struct SolverStatusDev {
+  bool converged = false;
+  bool slow_convergence_detected = false;
+  unsigned long long max_niter = 0;
+  unsigned long long max_line_niter = 0;
+  unsigned long long small_step_iters = 0;
+  double residual;
+};
+
+// One material = tagged union of the analytic models (the Variant of the reference).
+struct AnyEos {
+  int kind; // enum sgx_eos_kind
+  union {
+    IdealGas ideal;
+    Gruneisen gr;
+    DavisReactants dr;
+    DavisProducts dp;
+  };
+};
+struct EosSet {
+  int nmat;
+  AnyEos e[kMaxMat];
+};
+
+#ifdef __CUDACC__
+
+#define SGX_EOS_DISPATCH(m, CALL)                                                        \
+  switch (set.e[m].kind) {                                                               \
+  case 0:                                                                                \
+    return set.e[m].ideal.CALL;                                                          \
+  case 1:                                                                                \
+    return set.e[m].gr.CALL;                                                             \
+  case 2:                                                                                \
+    return set.e[m].dr.CALL;                                                             \
+  default:                                                                               \
+    return set.e[m].dp.CALL;                                                             \
+  }
+
+// Runtime-dispatched accessor (eos[m].X(...) through the Variant's visit,
+// eos/eos_variant.hpp:236-267).
+struct DynEos {
+  const EosSet &set;
+  __device__ DynEos(const EosSet &s) : set(s) {}
+  SGX_D unsigned long preferred(int m) const {
+    switch (set.e[m].kind) {
+    case 0:
+      return IdealGas::preferred_input;
+    default:
+      return TQ_DENSITY | TQ_SIE;
+    }
+  }
+  SGX_D double e_from_rho_T(int m, double rho, double T) const {
+    SGX_EOS_DISPATCH(m, e_from_rho_T(rho, T))
+  }
+  SGX_D double P_from_rho_e(int m, double rho, double e) const {
+    SGX_EOS_DISPATCH(m, P_from_rho_e(rho, e))
+  }
+  SGX_D double P_from_rho_T(int m, double rho, double T) const {
+    SGX_EOS_DISPATCH(m, P_from_rho_T(rho, T))
+  }
+  SGX_D double cv_from_rho_T(int m, double rho, double T) const {
+    SGX_EOS_DISPATCH(m, cv_from_rho_T(rho, T))
+  }
+  SGX_D double cv_from_rho_e(int m, double rho, double e) const {
+    SGX_EOS_DISPATCH(m, cv_from_rho_e(rho, e))
+  }
+  SGX_D double RhoPmin(int m, double T) const { SGX_EOS_DISPATCH(m, RhoPmin(T)) }
+  SGX_D double MaximumDensity(int m) const { SGX_EOS_DISPATCH(m, MaximumDensity()) }
+  SGX_D double MinimumTemperature(int m) const { SGX_EOS_DISPATCH(m, MinimumTemperature()) }
+  SGX_D double MinimumPressure(int m) const { SGX_EOS_DISPATCH(m, MinimumPressure()) }
+  SGX_D double MaximumPressureAtTemperature(int m, double T) const {
+    SGX_EOS_DISPATCH(m, MaximumPressureAtTemperature(T))
+  }
+  __device__ inline void rho_e_from_P_T(int m, double P, double T, double &rho,
+                                        double &sie) const {
+    switch (set.e[m].kind) {
+    case 0:
+      set.e[m].ideal.rho_e_from_P_T(P, T, nullptr, rho, sie);
+      return;
+    case 1:
+      set.e[m].gr.rho_e_from_P_T(P, T, nullptr, rho, sie);
+      return;
+    case 2:
+      set.e[m].dr.rho_e_from_P_T(P, T, nullptr, rho, sie);
+      return;
+    default:
+      set.e[m].dp.rho_e_from_P_T(P, T, nullptr, rho, sie);
+      return;
+    }
+  }
+};
+
+// The benchmark mixture of test/pte_test_3mat_analytic.hpp:38-50 with the material types
+// resolved at compile time: with `m` a literal after unrolling, each call inlines the one
+// model it needs and the Variant switch disappears.
+struct Mix3GrDrDp {
+  const EosSet &set;
+  __device__ Mix3GrDrDp(const EosSet &s) : set(s) {}
+  SGX_D unsigned long preferred(int) const { return TQ_DENSITY | TQ_SIE; }
+#define SGX_MIX3(CALL)                                                                   \
+  if (m == 0) return set.e[0].gr.CALL;                                                   \
+  if (m == 1) return set.e[1].dr.CALL;                                                   \
+  return set.e[2].dp.CALL;
+  SGX_D double e_from_rho_T(int m, double rho, double T) const {
+    SGX_MIX3(e_from_rho_T(rho, T))
+  }
+  SGX_D double P_from_rho_e(int m, double rho, double e) const {
+    SGX_MIX3(P_from_rho_e(rho, e))
+  }
+  SGX_D double P_from_rho_T(int m, double rho, double T) const {
+    SGX_MIX3(P_from_rho_T(rho, T))
+  }
+  SGX_D double cv_from_rho_T(int m, double rho, double T) const {
+    SGX_MIX3(cv_from_rho_T(rho, T))
+  }
+  SGX_D double cv_from_rho_e(int m, double rho, double e) const {
+    SGX_MIX3(cv_from_rho_e(rho, e))
+  }
+  SGX_D double RhoPmin(int, double) const { return 0.0; }
+  SGX_D double MaximumDensity(int m) const { return m == 0 ? set.e[0].gr.rho_max : 1e100; }
+  SGX_D double MinimumTemperature(int) const { return 0; }
+  SGX_D double MinimumPressure(int m) const {
+    return m == 0 ? set.e[0].gr.MinimumPressure() : 0.0;
+  }
+  SGX_D double MaximumPressureAtTemperature(int m, double T) const {
+    return m == 0 ? set.e[0].gr.MaximumPressureAtTemperature(T) : 1e100;
+  }
+  __device__ inline void rho_e_from_P_T(int m, double P, double T, double &rho,
+                                        double &sie) const {
+    if (m == 0) {
+      set.e[0].gr.rho_e_from_P_T(P, T, nullptr, rho, sie);
+    } else if (m == 1) {
+      set.e[1].dr.rho_e_from_P_T(P, T, nullptr, rho, sie);
+    } else {
+      set.e[2].dp.rho_e_from_P_T(P, T, nullptr, rho, sie);
+    }
+  }
+#undef SGX_MIX3
+};
+
+namespace mix {
+
+// error_utils::bad_value == !is_normal_or_zero (base/error_utils.hpp:31-76)
+SGX_D bool is_normal(const double v) {
+  const double a = fabs(v);
+  return (a >= DBL_MIN) && (a <= DBL_MAX); // excludes 0, subnormal, inf, NaN
+}
+SGX_D bool bad_value(const double v) {
+  const bool good = (v == 0.0) || (is_normal(1.0e10 * v) && is_normal(v));
+  return !good;
+}
+SGX_D bool isfinite_ref(const double a) { return (a == a) && ((a == 0) || (a != 2 * a)); }
+
+// sum_neumaier (:287-305)
+template <typename Op>
+SGX_D double sum_neumaier(const double *data, const int n, const int offset, const int iskip,
+                          const Op &op) {
+  double sum = 0;
+  double c = 0;
+  for (int i = 0; i < n; ++i) {
+    if (iskip >= 0 && i == iskip) continue;
+    const double x = op(data[i + offset]);
+    const double t = sum + x;
+    if (fabs(sum) >= fabs(x)) {
+      c += (sum - t) + x;
+    } else {
+      c += (x - t) + sum;
+    }
+    sum = t;
+  }
+  return sum + c;
+}
+SGX_D double sum_neumaier(const double *data, const int n, const int offset = 0,
+                          const int iskip = -1) {
+  return sum_neumaier(data, n, offset, iskip, [](const double x) { return x; });
+}
+
+// Column-pivoted Householder QR solve for n >= 3 (the reference delegates to Eigen's
+// colPivHouseholderQr, :266-273).  a is row-major n x n (destroyed), b -> x.
+template <int NMAX>
+__device__ inline void qr_solve(const int n, double *a, double *b) {
+  int perm[NMAX];
+  double cn[NMAX];
+  for (int j = 0; j < n; ++j) {
+    perm[j] = j;
+    double s = 0;
+    for (int i = 0; i < n; ++i)
+      s += a[i * n + j] * a[i * n + j];
+    cn[j] = s;
+  }
+  for (int k = 0; k < n; ++k) {
+    // pivot: largest remaining column norm (recomputed: n is tiny)
+    int piv = k;
+    double best = -1;
+    for (int j = k; j < n; ++j) {
+      double s = 0;
+      for (int i = k; i < n; ++i)
+        s += a[i * n + j] * a[i * n + j];
+      cn[j] = s;
+      if (s > best) {
+        best = s;
+        piv = j;
+      }
+    }
+    if (piv != k) {
+      for (int i = 0; i < n; ++i) {
+        const double t = a[i * n + k];
+        a[i * n + k] = a[i * n + piv];
+        a[i * n + piv] = t;
+      }
+      const int tp = perm[k];
+      perm[k] = perm[piv];
+      perm[piv] = tp;
+    }
+    // Householder vector for column k, rows k..n-1
+    const double c0 = a[k * n + k];
+    double tail = 0;
+    for (int i = k + 1; i < n; ++i)
+      tail += a[i * n + k] * a[i * n + k];
+    if (tail == 0.0) continue; // already triangular in this column
+    double beta = sqrt(c0 * c0 + tail);
+    if (c0 >= 0) beta = -beta;
+    const double tau = (beta - c0) / beta;
+    const double inv = 1.0 / (c0 - beta);
+    // v = [1, a[k+1..]/ (c0-beta)]
+    for (int i = k + 1; i < n; ++i)
+      a[i * n + k] *= inv;
+    a[k * n + k] = beta;
+    // apply H = I - tau v v^T to the trailing columns and to b
+    for (int j = k + 1; j < n; ++j) {
+      double s = a[k * n + j];
+      for (int i = k + 1; i < n; ++i)
+        s += a[i * n + k] * a[i * n + j];
+      s *= tau;
+      a[k * n + j] -= s;
+      for (int i = k + 1; i < n; ++i)
+        a[i * n + j] -= s * a[i * n + k];
+    }
+    double s = b[k];
+    for (int i = k + 1; i < n; ++i)
+      s += a[i * n + k] * b[i];
+    s *= tau;
+    b[k] -= s;
+    for (int i = k + 1; i < n; ++i)
+      b[i] -= s * a[i * n + k];
+  }
+  // back substitution R y = Q^T b
+  double y[NMAX];
+  for (int i = n - 1; i >= 0; --i) {
+    double s = b[i];
+    for (int j = i + 1; j < n; ++j)
+      s -= a[i * n + j] * y[j];
+    y[i] = s / a[i * n + i];
+  }
+  for (int j = 0; j < n; ++j)
+    b[perm[j]] = y[j];
+}
+
+// solve_Ax_b_wscr (:176-278)
+template <int NMAX>
+__device__ inline bool solve_Ax_b(const int n, double *a, double *b) {
+  for (int row = 0; row < n; ++row) {
+    double maxabs = 0;
+    for (int column = 0; column < n; ++column) {
+      maxabs = stdmax(fabs(a[row * n + column]), maxabs);
+    }
+    if (maxabs == 0) return false;
+    for (int column = 0; column < n; ++column) {
+      a[row * n + column] /= maxabs;
+    }
+    b[row] /= maxabs;
+  }
+  if (n == 1) {
+    b[0] = ratio(b[0], a[0]);
+  } else if (n == 2) {
+    const double det = a[0] * a[3] - a[1] * a[2];
+    const double x0 = ratio(a[3] * b[0] - a[1] * b[1], det);
+    const double x1 = ratio(a[0] * b[1] - a[2] * b[0], det);
+    b[0] = x0;
+    b[1] = x1;
+  } else {
+    qr_solve<NMAX>(n, a, b);
+  }
+  bool retval = true;
+  for (int i = 0; i < n; ++i)
+    if (!isfinite_ref(b[i])) retval = false;
+  return retval;
+}
+
+// ApproxTemperatureFromRhoMatU (:790-847); lambdas are NullIndexer here.
+template <int NM, class Eos>
+__device__ inline double ApproxTemperatureFromRhoMatU(const Eos &eos, const double u_tot,
+                                                      const double *rho, const double *vfrac,
+                                                      const double Tguess = 0.0) {
+  constexpr double minimum_temperature = 1.e-9;
+  constexpr double maximum_temperature = 1.e9;
+  auto ufunc = [&](const double T) {
+    double usum = 0.0;
+#pragma unroll
+    for (int m = 0; m < NM; m++) {
+      usum += rho[m] * vfrac[m] * eos.e_from_rho_T(m, rho[m], T);
+    }
+    return usum;
+  };
+  double ulo = ufunc(minimum_temperature);
+  if (u_tot < ulo) return minimum_temperature;
+  double uhi = ufunc(maximum_temperature);
+  if (u_tot > uhi) return maximum_temperature;
+  double lTlo = fastmath::lg(minimum_temperature);
+  double lThi = fastmath::lg(maximum_temperature);
+  if (Tguess > minimum_temperature && Tguess < maximum_temperature) {
+    const double ug = ufunc(Tguess);
+    if (ug < u_tot) {
+      lTlo = fastmath::lg(Tguess);
+      ulo = ug;
+    } else {
+      lThi = fastmath::lg(Tguess);
+      uhi = ug;
+    }
+  }
+  int iter = 0;
+  constexpr int max_iter = 10;
+  while (lThi - lTlo > 0.01 && iter < max_iter) {
+    const double lT = 0.5 * (lTlo + lThi);
+    const double uT = ufunc(fastmath::pow2(lT));
+    if (uT < u_tot) {
+      lTlo = lT;
+      ulo = uT;
+    } else {
+      lThi = lT;
+      uhi = uT;
+    }
+    iter++;
+  }
+  const double alpha = ratio((u_tot - ulo), (uhi - ulo));
+  return fastmath::pow2((1.0 - alpha) * lTlo + alpha * lThi);
+}
+
+// ---------------------------------------------------------------------------------------
+// PTESolverBase (:329-786) -- state shared by the RhoT and PT systems
+// ---------------------------------------------------------------------------------------
+template <int NM, int NEQ, class Eos>
+struct Base {
+  static constexpr int nmat = NM;
+  static constexpr int neq = NEQ;
+  const Eos &eos;
+  const MixParamsDev &params_;
+  int niter;
+  double vfrac_total, sie_total;
+  double rho[NM], vfrac[NM], sie[NM], temp[NM], press[NM];
+  double jacobian[NEQ * NEQ], dx[NEQ], residual[NEQ], u[NM], rhobar[NM];
+  double rho_total, uscale, utotal_scale, Tnorm;
+
+  __device__ Base(const Eos &e, const MixParamsDev &p) : eos(e), params_(p), niter(0) {}
+
+  SGX_D void InitRhoBarandRho() {
+#pragma unroll
+    for (int m = 0; m < NM; ++m)
+      rhobar[m] = rho[m] * vfrac[m];
+    rho_total = sum_neumaier(rhobar, NM);
+  }
+  SGX_D void NormalizeVfrac() {
+    const double vfrac_sum = sum_neumaier(vfrac, NM);
+#pragma unroll
+    for (int m = 0; m < NM; ++m)
+      vfrac[m] *= ratio(vfrac_total, vfrac_sum);
+  }
+  SGX_D double get_vfrac_max(const double T, const int m) const {
+    constexpr double safety = 0.9;
+    const double rho_min = eos.RhoPmin(m, T);
+    return stdmin(safety * ratio(rhobar[m], rho_min), 1.0);
+  }
+  // SetVfracFromT (:423-498); returns true on FAIL like the reference
+  __device__ inline bool SetVfracFromT(const double T) {
+    constexpr double min_dv = 1e-12;
+    double vfrac_max_sum = 0;
+#pragma unroll
+    for (int m = 0; m < NM; ++m) {
+      const double vfrac_max = get_vfrac_max(T, m);
+      if (vfrac[m] <= 0) vfrac[m] = vfrac_max;
+      vfrac_max_sum += vfrac_max;
+    }
+    if (vfrac_max_sum < vfrac_total) return true;
+    NormalizeVfrac();
+    for (int it = 0; it < NM; ++it) {
+      double remaining_vfrac = 0;
+      int n_uncapped_materials = NM;
+#pragma unroll
+      for (int m = 0; m < NM; ++m) {
+        const double vfrac_max = get_vfrac_max(T, m);
+        const double vnew = stdmin(vfrac_max, vfrac[m]);
+        const double dv = vfrac[m] - vnew;
+        vfrac[m] -= dv;
+        remaining_vfrac += dv;
+        n_uncapped_materials -= (dv > min_dv);
+      }
+      if (fabs(remaining_vfrac) < min_dv) break;
+#pragma unroll
+      for (int m = 0; m < NM; ++m) {
+        const bool uncapped = ((get_vfrac_max(T, m) - vfrac[m]) > min_dv);
+        if (uncapped) {
+          // robust::ratio(Real, std::size_t): sgn(unsigned) == 1 and SMALL<size_t>() == 0,
+          // so this is a plain division (robust_utils.hpp:27-62)
+          vfrac[m] += remaining_vfrac / (double)(unsigned long long)n_uncapped_materials;
+        }
+      }
+    }
+    NormalizeVfrac();
+    return false;
+  }
+  // GetPressureFromPreferred (:583-597)
+  SGX_D double GetPressureFromPreferred(const int m, const double rho_, const double T,
+                                        double sie_, const bool do_e_lookup) const {
+    if (eos.preferred(m) & TQ_SIE) {
+      if (do_e_lookup) sie_ = eos.e_from_rho_T(m, rho_, T);
+      return eos.P_from_rho_e(m, rho_, sie_);
+    }
+    return eos.P_from_rho_T(m, rho_, T);
+  }
+  // GetSieCvFromTAndPreferred (:601-620)
+  SGX_D void GetSieCvFromTAndPreferred(const int m, double rho_, const double P,
+                                       const double T, double &sie_, double &cv) const {
+    if (eos.preferred(m) & TQ_PRESSURE) {
+      const double Pmin = eos.MinimumPressure(m);
+      const double Pmax = eos.MaximumPressureAtTemperature(m, T);
+      double Pguess;
+      if (bad_value(P)) {
+        Pguess = 0.5 * (Pmin + Pmax);
+      } else {
+        Pguess = stdmax(Pmin, stdmin(Pmax, P));
+      }
+      eos.rho_e_from_P_T(m, Pguess, T, rho_, sie_);
+      cv = eos.cv_from_rho_e(m, rho_, sie_);
+    } else {
+      sie_ = eos.e_from_rho_T(m, rho_, T);
+      cv = eos.cv_from_rho_T(m, rho_, T);
+    }
+  }
+  // GetTguess (:500-581)
+  __device__ inline double GetTguess() {
+    double Tguess;
+    if (Tnorm > 0.0) {
+      Tguess = Tnorm;
+    } else {
+      Tguess = params_.default_tguess;
+#pragma unroll
+      for (int m = 0; m < NM; ++m)
+        Tguess = stdmax(Tguess, temp[m]);
+    }
+    auto newton_step = [this](const double T) {
+      double dudt = 0;
+      double usum = 0;
+#pragma unroll
+      for (int m = 0; m < NM; ++m) {
+        const double rho_max = eos.MaximumDensity(m);
+        double sie_, cv;
+        GetSieCvFromTAndPreferred(m, stdmin(rho[m], rho_max), press[m], T, sie_, cv);
+        usum += rhobar[m] * sie_;
+        dudt += rhobar[m] * cv;
+      }
+      return T - ratio((usum - utotal_scale * uscale), dudt);
+    };
+    const double Tfactor = 10.0;
+    bool bad_vfrac_guess = false;
+    for (int i = 0; i < 3; i++) {
+      if (params_.iterate_t_guess) {
+        Tguess = stdmin(params_.temperature_limit, stdmax(Tguess, newton_step(Tguess)));
+      }
+#pragma unroll
+      for (int m = 0; m < NM; ++m)
+        Tguess = stdmax(eos.MinimumTemperature(m), Tguess);
+      bad_vfrac_guess = SetVfracFromT(Tguess);
+      if (bad_vfrac_guess) {
+        Tguess *= Tfactor;
+        continue;
+      }
+#pragma unroll
+      for (int m = 0; m < NM; ++m)
+        rho[m] = ratio(rhobar[m], vfrac[m]);
+      bad_vfrac_guess = false;
+      for (int m = 0; m < NM; ++m) {
+        const double rho_min = eos.RhoPmin(m, Tguess);
+        if (rho[m] < rho_min) {
+          bad_vfrac_guess = true;
+          Tguess *= Tfactor;
+          break;
+        }
+      }
+      if (!bad_vfrac_guess) break;
+    }
+    return Tguess;
+  }
+  // InitBase (:627-662)
+  __device__ inline void InitBase() {
+    InitRhoBarandRho();
+    const double utotal = rho_total * sie_total;
+    uscale = stdmax(fabs(utotal), 1.0e-14);
+    utotal_scale = ratio(utotal, uscale);
+    const double Tguess = GetTguess();
+    Tnorm = Tguess;
+#pragma unroll
+    for (int m = 0; m < NM; m++) {
+      temp[m] = 1.0;
+      sie[m] = eos.e_from_rho_T(m, rho[m], Tguess);
+      const unsigned long prefinput = eos.preferred(m);
+      if ((prefinput & TQ_PRESSURE) && !(bad_value(press[m]))) {
+        press[m] = ratio(press[m], uscale);
+      } else {
+        press[m] = ratio(GetPressureFromPreferred(m, rho[m], Tguess, sie[m], false), uscale);
+      }
+    }
+#pragma unroll
+    for (int m = 0; m < NM; ++m)
+      u[m] = sie[m] * ratio(rhobar[m], uscale);
+  }
+  SGX_D double ResidualNorm() const {
+    return 0.5 * sum_neumaier(residual, NEQ, 0, -1, [](const double x) { return x * x; });
+  }
+  SGX_D bool Solve() {
+#pragma unroll
+    for (int m = 0; m < NEQ; m++)
+      dx[m] = residual[m];
+    return solve_Ax_b<NEQ>(NEQ, jacobian, dx);
+  }
+};
+
+// ---------------------------------------------------------------------------------------
+// PTESolverRhoT (:883-1193): unknowns T and the NM-1 non-excluded volume fractions
+// ---------------------------------------------------------------------------------------
+template <int NM, class Eos>
+struct RhoT : public Base<NM, NM, Eos> {
+  using B = Base<NM, NM, Eos>;
+  using B::dx;
+  using B::eos;
+  using B::jacobian;
+  using B::params_;
+  using B::press;
+  using B::residual;
+  using B::rho;
+  using B::rhobar;
+  using B::sie;
+  using B::temp;
+  using B::Tnorm;
+  using B::u;
+  using B::uscale;
+  using B::utotal_scale;
+  using B::vfrac;
+  double dpdv[NM], dedv[NM], dpdT[NM], vtemp[NM];
+  double Tequil, Ttemp;
+  int ms;
+
+  __device__ RhoT(const Eos &e, const MixParamsDev &p) : B(e, p) {}
+
+  __device__ inline double Init() {
+    B::InitBase();
+    if (params_.pte_reduced_system_exclude_idx >= 0) {
+      ms = (int)params_.pte_reduced_system_exclude_idx;
+    } else {
+      ms = 0;
+      double xmax = 0;
+#pragma unroll
+      for (int m = 0; m < NM; ++m) {
+        const double x = ratio(rhobar[m], B::rho_total);
+        if (x > xmax) {
+          xmax = x;
+          ms = m;
+        }
+      }
+    }
+    Residual();
+    Tequil = temp[0];
+    return B::ResidualNorm();
+  }
+  SGX_D void Fixup() {
+    if (params_.pte_reduced_system_exclude_idx < 0) {
+      double alphamax = 0;
+      ms = 0;
+#pragma unroll
+      for (int m = 0; m < NM; ++m) {
+        if (vfrac[m] > alphamax) {
+          alphamax = vfrac[m];
+          ms = m;
+        }
+      }
+      Residual();
+    }
+  }
+  SGX_D void Finalize() {
+#pragma unroll
+    for (int m = 0; m < NM; m++) {
+      temp[m] *= Tnorm;
+      u[m] *= uscale;
+      press[m] *= uscale;
+    }
+  }
+  SGX_D void Residual() {
+    const double esum = sum_neumaier(u, NM);
+    residual[0] = utotal_scale - esum;
+    int ires = 1;
+#pragma unroll
+    for (int m = 0; m < NM; ++m) {
+      if (m == ms) continue;
+      residual[ires++] = press_at(ms) - press[m];
+    }
+  }
+  SGX_D double press_at(const int i) const {
+    double v = press[0];
+#pragma unroll
+    for (int m = 1; m < NM; ++m)
+      if (m == i) v = press[m];
+    return v;
+  }
+  SGX_D void CheckPTE(bool &converged, bool &acceptable) const {
+    double mean_p = 0;
+#pragma unroll
+    for (int m = 0; m < NM; ++m)
+      mean_p += vfrac[m] * press[m];
+    const double error_p =
+        sqrt(sum_neumaier(residual, NM - 1, 1, -1, [](const double x) { return x * x; }));
+    const double error_u = fabs(residual[0]);
+    const bool converged_p = (error_p < params_.pte_rel_tolerance_p * fabs(mean_p) ||
+                              error_p < params_.pte_abs_tolerance_p);
+    const bool converged_u = (error_u < params_.pte_rel_tolerance_e);
+    const bool acceptable_p =
+        (error_p < params_.pte_rel_tolerance_p_sufficient * fabs(mean_p) ||
+         error_p < params_.pte_abs_tolerance_p_sufficient);
+    const bool acceptable_u = (error_u < params_.pte_rel_tolerance_e_sufficient);
+    converged = converged_p && converged_u;
+    acceptable = acceptable_p && acceptable_u;
+  }
+  __device__ inline void Jacobian() {
+    double dedT_sum = 0.0;
+#pragma unroll
+    for (int m = 0; m < NM; m++) {
+      const double dv = (vfrac[m] < 0.5 ? 1.0 : -1.0) * vfrac[m] * params_.derivative_eps;
+      const double vf_pert = vfrac[m] + dv;
+      const double rho_pert = ratio(rhobar[m], vf_pert);
+      double e_pert = eos.e_from_rho_T(m, rho_pert, Tnorm * Tequil);
+      double p_pert = ratio(
+          B::GetPressureFromPreferred(m, rho_pert, Tnorm * Tequil, e_pert, false), uscale);
+      dpdv[m] = stdmin(ratio((p_pert - press[m]), dv), -fabs(params_.pte_max_dpdv));
+      dedv[m] = ratio(rhobar[m] * ratio(e_pert, uscale) - u[m], dv);
+      const double dT = Tequil * params_.derivative_eps;
+      e_pert = eos.e_from_rho_T(m, rho[m], Tnorm * (Tequil + dT));
+      p_pert = ratio(
+          B::GetPressureFromPreferred(m, rho[m], Tnorm * (Tequil + dT), e_pert, false),
+          uscale);
+      dpdT[m] = ratio((p_pert - press[m]), dT);
+      dedT_sum += ratio(rhobar[m] * ratio(e_pert, uscale) - u[m], dT);
+    }
+#pragma unroll
+    for (int i = 0; i < NM * NM; ++i)
+      jacobian[i] = 0.0;
+    const double dedv_s = pick(dedv, ms), dpdT_s = pick(dpdT, ms), dpdv_s = pick(dpdv, ms);
+    jacobian[0] = dedT_sum;
+    int col = 1;
+#pragma unroll
+    for (int m = 0; m < NM; ++m) {
+      if (m == ms) continue;
+      jacobian[col++] = dedv[m] - dedv_s;
+    }
+    int row = 1;
+#pragma unroll
+    for (int m = 0; m < NM; m++) {
+      if (m == ms) continue;
+      jacobian[row * NM + 0] = dpdT[m] - dpdT_s;
+      int c = 1;
+#pragma unroll
+      for (int mm = 0; mm < NM; ++mm) {
+        if (mm == ms) continue;
+        jacobian[row * NM + c] = (mm == m) ? dpdv[m] + dpdv_s : dpdv_s;
+        c++;
+      }
+      row++;
+    }
+  }
+  SGX_D static double pick(const double *a, const int i) {
+    double v = a[0];
+#pragma unroll
+    for (int m = 1; m < NM; ++m)
+      if (m == i) v = a[m];
+    return v;
+  }
+  __device__ inline double ScaleDx() {
+    double scale = 1.0;
+    const double dalphaskip = -sum_neumaier(dx, NM - 1, 1);
+    int idx = 1;
+#pragma unroll
+    for (int m = 0; m < NM; ++m) {
+      const double mydx = (m == ms) ? dalphaskip : dx[idx++];
+      if (scale * mydx < -params_.vfrac_safety_fac * vfrac[m]) {
+        scale = stdmin(scale, fabs(params_.vfrac_safety_fac * ratio(vfrac[m], mydx)));
+      }
+    }
+    const double Tnew = Tequil + scale * dx[0];
+    idx = 1;
+#pragma unroll
+    for (int m = 0; m < NM; m++) {
+      const double rho_min =
+          stdmax(eos.RhoPmin(m, Tnorm * Tequil), eos.RhoPmin(m, Tnorm * Tnew));
+      const double alpha_max = stdmin(1.0, ratio(rhobar[m], rho_min));
+      if (alpha_max < vfrac[m]) continue; // NB: skips idx++ exactly like the reference
+      const double mydx = (m == ms) ? dalphaskip : dx[idx++];
+      if (scale * mydx > 0.5 * (alpha_max - vfrac[m])) {
+        scale = stdmin(ratio(0.5 * (alpha_max - vfrac[m]), mydx), scale);
+      }
+    }
+    if (scale * dx[0] < -0.95 * Tequil) {
+      scale = stdmin(scale, ratio(-0.95 * Tequil, dx[0]));
+    }
+#pragma unroll
+    for (int i = 0; i < NM; ++i)
+      dx[i] *= scale;
+    return scale;
+  }
+  __device__ inline double TestUpdate(const double scale, const bool cache_state = false) {
+    if (cache_state) {
+      Ttemp = Tequil;
+#pragma unroll
+      for (int m = 0; m < NM; ++m)
+        vtemp[m] = vfrac[m];
+    }
+    Tequil = Ttemp + scale * dx[0];
+    int idx = 1;
+#pragma unroll
+    for (int m = 0; m < NM; ++m) {
+      if (ms == m) continue;
+      vfrac[m] = vtemp[m] + scale * dx[idx++];
+    }
+    const double vsum_others = sum_neumaier(vfrac, NM, 0, ms);
+#pragma unroll
+    for (int m = 0; m < NM; ++m)
+      if (m == ms) vfrac[m] = 1 - vsum_others;
+#pragma unroll
+    for (int m = 0; m < NM; ++m) {
+      rho[m] = ratio(rhobar[m], vfrac[m]);
+      u[m] = rhobar[m] * eos.e_from_rho_T(m, rho[m], Tnorm * Tequil);
+      sie[m] = ratio(u[m], rhobar[m]);
+      u[m] = ratio(u[m], uscale);
+      temp[m] = Tequil;
+      press[m] =
+          ratio(B::GetPressureFromPreferred(m, rho[m], Tnorm * Tequil, sie[m], false), uscale);
+    }
+    Residual();
+    return B::ResidualNorm();
+  }
+};
+
+// ---------------------------------------------------------------------------------------
+// PTESolverPT (:1207-1446): unknowns (T, P); every state update inverts each material's
+// P(rho,T) with the EOS's own DensityEnergyFromPressureTemperature.
+// ---------------------------------------------------------------------------------------
+template <int NM, class Eos>
+struct PT : public Base<NM, 2, Eos> {
+  using B = Base<NM, 2, Eos>;
+  using B::dx;
+  using B::eos;
+  using B::jacobian;
+  using B::params_;
+  using B::press;
+  using B::residual;
+  using B::rho;
+  using B::rhobar;
+  using B::sie;
+  using B::temp;
+  using B::Tnorm;
+  using B::u;
+  using B::uscale;
+  using B::utotal_scale;
+  using B::vfrac;
+  double Pequil, Tequil, Ptemp, Ttemp;
+
+  __device__ PT(const Eos &e, const MixParamsDev &p) : B(e, p) {}
+
+  __device__ inline double Init() {
+    B::InitBase();
+    Residual();
+    Pequil = 0;
+#pragma unroll
+    for (int m = 0; m < NM; ++m)
+      Pequil += fabs(press[m]) * vfrac[m];
+    const double vsum = sum_neumaier(vfrac, NM);
+    Pequil /= vsum;
+    Tequil = 1;
+#pragma unroll
+    for (int m = 0; m < NM; ++m) {
+      eos.rho_e_from_P_T(m, Pequil * uscale, Tequil * Tnorm, rho[m], sie[m]);
+      vfrac[m] = ratio(rhobar[m], rho[m]);
+      u[m] = ratio(sie[m] * rhobar[m], uscale);
+      temp[m] = Tequil;
+    }
+    Residual();
+    return B::ResidualNorm();
+  }
+  SGX_D void Fixup() {}
+  SGX_D void Finalize() {
+#pragma unroll
+    for (int m = 0; m < NM; m++) {
+      press[m] = Pequil * uscale;
+      temp[m] = Tequil * Tnorm;
+      u[m] *= uscale;
+    }
+  }
+  SGX_D void Residual() {
+    const double vsum = sum_neumaier(vfrac, NM);
+    const double esum = sum_neumaier(u, NM);
+    residual[0] = B::vfrac_total - vsum;
+    residual[1] = utotal_scale - esum;
+  }
+  SGX_D void CheckPTE(bool &converged, bool &acceptable) const {
+    const double error_v = fabs(residual[0]);
+    const double error_u = fabs(residual[1]);
+    const bool converged_u = error_u < params_.pte_rel_tolerance_e;
+    const bool converged_v = error_v < params_.pte_rel_tolerance_v;
+    const bool acceptable_u = error_u < params_.pte_rel_tolerance_e_sufficient;
+    const bool acceptable_v = error_v < params_.pte_rel_tolerance_v_sufficient;
+    converged = converged_v && converged_u;
+    acceptable = acceptable_u && acceptable_v;
+  }
+  __device__ inline void Jacobian() {
+    double dudT_P_sum = 0.0, dudP_T_sum = 0.0, rbor2_dr_dT_P_sum = 0.0,
+           rbor2_dr_dP_T_sum = 0.0;
+#pragma unroll
+    for (int m = 0; m < NM; ++m) {
+      double r_pert = rho[m];
+      double e_pert = sie[m];
+      const double dp = -Pequil * params_.derivative_eps;
+      eos.rho_e_from_P_T(m, uscale * (Pequil + dp), Tnorm * Tequil, r_pert, e_pert);
+      const double drdp = ratio(r_pert - rho[m], dp);
+      const double dudp = ratio(ratio(rhobar[m] * e_pert, uscale) - u[m], dp);
+      rbor2_dr_dP_T_sum += ratio(rhobar[m], rho[m] * rho[m]) * drdp;
+      dudP_T_sum += dudp;
+      const double dT = Tequil * params_.derivative_eps;
+      eos.rho_e_from_P_T(m, uscale * Pequil, Tnorm * (Tequil + dT), r_pert, e_pert);
+      const double drdT = ratio(r_pert - rho[m], dT);
+      const double dudT = ratio(ratio(rhobar[m] * e_pert, uscale) - u[m], dT);
+      rbor2_dr_dT_P_sum += ratio(rhobar[m], rho[m] * rho[m]) * drdT;
+      dudT_P_sum += dudT;
+    }
+    jacobian[0] = -rbor2_dr_dT_P_sum;
+    jacobian[1] = -rbor2_dr_dP_T_sum;
+    jacobian[2] = dudT_P_sum;
+    jacobian[3] = dudP_T_sum;
+  }
+  __device__ inline double ScaleDx() {
+    double scale = 1.0;
+    if (scale * dx[0] < -0.95 * Tequil) {
+      scale = ratio(-0.95 * Tequil, dx[0]);
+    }
+    auto bounded = [this](const double Pbound, const double delta) {
+      return ratio(ratio(Pbound, uscale) - Pequil, delta);
+    };
+#pragma unroll
+    for (int m = 0; m < NM; ++m) {
+      const double Pmin = eos.MinimumPressure(m);
+      scale = stdmin(fabs(scale), fabs(0.95 * bounded(Pmin, dx[1])));
+    }
+#pragma unroll
+    for (int m = 0; m < NM; ++m) {
+      const double Ttest = (Tequil + scale * dx[0]) * Tnorm;
+      const double Pmax = eos.MaximumPressureAtTemperature(m, Ttest);
+      scale = stdmin(fabs(scale), fabs(0.95 * bounded(Pmax, dx[0])));
+    }
+    dx[0] *= scale;
+    dx[1] *= scale;
+    return scale;
+  }
+  __device__ inline double TestUpdate(const double scale, const bool cache_state = false) {
+    if (cache_state) {
+      Ttemp = Tequil;
+      Ptemp = Pequil;
+    }
+    Tequil = Ttemp + scale * dx[0];
+    Pequil = Ptemp + scale * dx[1];
+#pragma unroll
+    for (int m = 0; m < NM; ++m) {
+      eos.rho_e_from_P_T(m, Pequil * uscale, Tequil * Tnorm, rho[m], sie[m]);
+      vfrac[m] = ratio(rhobar[m], rho[m]);
+      u[m] = ratio(sie[m] * rhobar[m], uscale);
+      temp[m] = Tequil;
+      press[m] = Pequil;
+    }
+    Residual();
+    return B::ResidualNorm();
+  }
+};
+
+// ---------------------------------------------------------------------------------------
+// PTESolver (:2188-2291)
+// ---------------------------------------------------------------------------------------
+template <class System>
+__device__ inline SolverStatusDev PTESolver(System &s) {
+  SolverStatusDev status;
+  double &err = status.residual;
+  bool &converged = status.converged;
+  bool close_enough = false;
+
+  err = s.Init();
+  const MixParamsDev &params = s.params_;
+  converged = false;
+  const unsigned long long pte_max_iter =
+      (unsigned long long)System::nmat * params.pte_max_iter_per_mat;
+  int &niter = s.niter;
+  unsigned long long &small_step_iters = status.small_step_iters;
+  for (niter = 0; (unsigned long long)niter < pte_max_iter; ++niter) {
+    status.max_niter =
+        status.max_niter > (unsigned long long)niter ? status.max_niter : niter;
+    s.CheckPTE(converged, close_enough);
+    if (converged) break;
+    s.Jacobian();
+    const bool success = s.Solve();
+    if (!success) {
+      converged = false;
+      break;
+    }
+    double scale = stdmin(1.0, s.ScaleDx());
+    if (fabs(scale) < params.pte_small_step_thresh) small_step_iters++;
+    if (small_step_iters >= params.pte_small_step_tries) {
+      converged = false;
+      break;
+    }
+    const double gradfdx = -2.0 * scale * err;
+    scale = 1.0;
+    const double err_old = err;
+    err = s.TestUpdate(scale, true);
+    if (err > err_old + params.line_search_alpha * gradfdx) {
+      scale = 0.5;
+      const double err_mid = s.TestUpdate(scale);
+      if (err_mid < err && err_mid < err_old) {
+        scale = 0.75 + 0.5 * ratio(err_mid - err, err - 2.0 * err_mid + err_old);
+      }
+      for (unsigned long long line_iter = 0; line_iter < params.line_search_max_iter;
+           line_iter++) {
+        err = s.TestUpdate(scale);
+        if (err < err_old + params.line_search_alpha * scale * gradfdx) break;
+        scale *= params.line_search_fac;
+        status.max_line_niter =
+            line_iter > status.max_line_niter ? line_iter : status.max_line_niter;
+      }
+    }
+    s.Fixup();
+    if (((err > params.pte_slow_convergence_thresh * err_old) ||
+         (unsigned long long)niter == pte_max_iter - 1) &&
+        close_enough) {
+      converged = true;
+      status.slow_convergence_detected = true;
+      break;
+    }
+  }
+  s.Fixup();
+  s.Finalize();
+  return status;
+}
+
+SGX_D unsigned long long pack_status(const SolverStatusDev &s, const int niter) {
+  auto clamp = [](unsigned long long v, unsigned long long mx) { return v > mx ? mx : v; };
+  unsigned long long w = 0;
+  w |= s.converged ? 1ull : 0ull;
+  w |= s.slow_convergence_detected ? 2ull : 0ull;
+  w |= clamp((unsigned long long)niter, 0xffff) << 8;
+  w |= clamp(s.max_line_niter, 0xff) << 24;
+  w |= clamp(s.small_step_iters, 0xffff) << 32;
+  w |= clamp(s.max_niter, 0xffff) << 48;
+  return w;
+}
+
+} // namespace mix
+#endif // __CUDACC__
+} // namespace sgx
+#endif // SGX_PTE_CUH_

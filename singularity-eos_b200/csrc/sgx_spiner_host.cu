@@ -1,0 +1,472 @@
+// Host-side construction of the tabulated Spiner EOS: everything the reference does once at
+// load time after reading the .sp5 databoxes, then one upload to the device.
+//
+// Reference:
+//   SpinerEOSDependsRhoT::loadDataboxes_   eos/eos_spiner_rho_temp.hpp:545-687
+//   fixBulkModulus_                        eos/eos_spiner_rho_temp.hpp:689-714
+//   setlTColdCrit_                         eos/eos_spiner_rho_temp.hpp:716-775
+//   SetRhoPMin                             eos/eos_spiner_common.hpp:59-109
+//   SpinerEOSDependsRhoSie::loadDataboxes_ eos/eos_spiner_rho_sie.hpp:434-577
+//   calcBMod_                              eos/eos_spiner_rho_sie.hpp:579-601
+// The arithmetic reuses the same host/device inline functions the kernels use
+// (sgx_math.cuh), so derived tables equal the reference's to the last bit when both run on
+// x86-64 without FMA contraction.
+#include <algorithm>
+#include <cmath>
+#include <limits>
+
+#include "sgx_internal.hpp"
+
+namespace sgx {
+
+namespace {
+
+constexpr double ROOM_TEMPERATURE = 293; // base/constants.hpp:42
+
+Grid1D make_grid(const sgx_grid1d &g) {
+  Grid1D o{};
+  o.ngrids = g.ngrids;
+  int tot = 0;
+  for (int p = 0; p < 3; ++p) {
+    if (p < g.ngrids) {
+      o.npoints[p] = g.npoints[p];
+      o.ptot[p] = tot;
+      tot += g.npoints[p];
+      o.min[p] = g.min[p];
+      o.max[p] = g.max[p];
+      o.dx[p] = g.dx[p];
+      o.idx[p] = 1. / g.dx[p]; // RegularGrid1D::loadHDF: idx_ = 1./dx_
+    } else {
+      o.npoints[p] = 0;
+      o.ptot[p] = tot;
+      o.min[p] = o.max[p] = o.dx[p] = o.idx[p] = std::numeric_limits<double>::quiet_NaN();
+    }
+  }
+  return o;
+}
+
+bool grid_ok(const sgx_grid1d &g) {
+  if (g.ngrids < 1 || g.ngrids > 3) return false;
+  for (int p = 0; p < g.ngrids; ++p)
+    if (g.npoints[p] < 2 || !(g.dx[p] > 0) || !(g.max[p] > g.min[p])) return false;
+  return true;
+}
+
+// SetRhoPMin, eos_spiner_common.hpp:59-109.  P is [NR][NT]; rho_at_pmin is [NT].
+double SetRhoPMin(const double *P, const Grid1D &gT, const Grid1D &gRho, double *rho_at_pmin,
+                  const bool pmin_vapor_dome, const double VAPOR_DPDR_THRESH,
+                  const double lRhoOffset) {
+  double PMin = std::numeric_limits<double>::max();
+  const int NT = gT.n_total();
+  const int NR = gRho.n_total();
+  for (int i = 0; i < NT; ++i) {
+    double PMin_at_T = std::numeric_limits<double>::max();
+    int jmax = 0;
+    for (int j = 0; j < NR; ++j) {
+      const double Pji = P[(size_t)j * NT + i];
+      if (Pji < PMin_at_T) {
+        PMin_at_T = Pji;
+        jmax = j;
+      }
+      if ((j > 1) && pmin_vapor_dome) {
+        const double dP = Pji - P[(size_t)(j - 2) * NT + i];
+        const double dr = from_log(gRho.x(j), lRhoOffset) - from_log(gRho.x(j - 2), lRhoOffset);
+        const double dpdr = ratio(dP, dr);
+        if (dpdr < VAPOR_DPDR_THRESH) jmax = j;
+      }
+    }
+    if ((PMin_at_T > 0) && !pmin_vapor_dome) {
+      rho_at_pmin[i] = 0;
+      PMin_at_T = 0;
+    } else {
+      rho_at_pmin[i] = from_log(gRho.x(jmax), lRhoOffset);
+    }
+    PMin = std::min(PMin_at_T, PMin);
+  }
+  if (pmin_vapor_dome) {
+    for (int i = NT - 2; i >= 0; i--) {
+      if (rho_at_pmin[i] < rho_at_pmin[i + 1]) rho_at_pmin[i] = rho_at_pmin[i + 1];
+    }
+  }
+  return PMin;
+}
+
+} // namespace
+
+int build_spiner_rhot(const sgx_sp5_tables *raw, int reproducible, int pmin_vapor_dome,
+                      sgx_eos_s *e) {
+  if (!raw) return fail(SGX_ERR_INVALID, "null sgx_sp5_tables");
+  if (!grid_ok(raw->lrho) || !grid_ok(raw->lT))
+    return fail(SGX_ERR_INVALID, "malformed lrho/lT grid");
+  const double *req[] = {raw->P,      raw->sie,   raw->bMod,    raw->dPdRho,  raw->dPdE,
+                         raw->dTdRho, raw->dTdE,  raw->dEdRho,  raw->dEdT,    raw->PCold,
+                         raw->sieCold, raw->bModCold, raw->dPdRhoCold};
+  for (const double *p : req)
+    if (!p) return fail(SGX_ERR_INVALID, "SpinerEOSDependsRhoT needs all (rho,T) and cold tables");
+
+  SpinerRhoT &s = e->rhot;
+  TableStore &ts = e->tables;
+  s.gRho = make_grid(raw->lrho);
+  s.gT = make_grid(raw->lT);
+  const int numRho = s.gRho.n_total(), numT = s.gT.n_total();
+  s.numRho = numRho;
+  s.numT = numT;
+  const size_t n2 = (size_t)numRho * numT;
+  s.lRhoOffset = std::abs(raw->rho_offset);
+  s.lTOffset = std::abs(raw->T_offset);
+  double rhoNormal = std::abs(raw->normal_density);
+  s.reproducible = reproducible ? 1 : 0;
+
+  ts.add("P", raw->P, n2);
+  ts.add("sie", raw->sie, n2);
+  ts.add("bMod", raw->bMod, n2);
+  ts.add("dPdRho", raw->dPdRho, n2);
+  ts.add("dPdE", raw->dPdE, n2);
+  ts.add("dTdRho", raw->dTdRho, n2);
+  ts.add("dTdE", raw->dTdE, n2);
+  ts.add("dEdRho", raw->dEdRho, n2);
+  ts.add("dEdT", raw->dEdT, n2);
+  ts.add("PCold", raw->PCold, numRho);
+  ts.add("sieCold", raw->sieCold, numRho);
+  ts.add("bModCold", raw->bModCold, numRho);
+  ts.add("dPdRhoCold", raw->dPdRhoCold, numRho);
+  for (const char *nm : {"dPdECold", "dTdRhoCold", "dTdECold", "dEdTCold", "lTColdCrit", "PMax",
+                         "dEdTMax", "gm1Max", "sielTMax"})
+    ts.add(nm, nullptr, numRho);
+  ts.add("rho_at_pmin", nullptr, numT);
+
+  // NB: take the pointers only after every add() (the vector may have been reallocated)
+  double *P = ts.h("P"), *sie = ts.h("sie"), *bMod = ts.h("bMod"), *dPdRho = ts.h("dPdRho"),
+         *dPdE = ts.h("dPdE"), *dTdRho = ts.h("dTdRho"), *dTdE = ts.h("dTdE"),
+         *dEdRho = ts.h("dEdRho"), *dEdT = ts.h("dEdT");
+  double *sieCold = ts.h("sieCold"), *bModCold = ts.h("bModCold");
+  double *dPdECold = ts.h("dPdECold"), *dTdRhoCold = ts.h("dTdRhoCold"),
+         *dTdECold = ts.h("dTdECold"), *dEdTCold = ts.h("dEdTCold"),
+         *lTColdCrit = ts.h("lTColdCrit");
+  double *PMax = ts.h("PMax"), *dEdTMax = ts.h("dEdTMax"), *gm1Max = ts.h("gm1Max"),
+         *sielTMax = ts.h("sielTMax");
+
+  // bounds (:607-613)
+  s.lRhoMin = s.gRho.gmin();
+  s.lRhoMax = s.gRho.gmax();
+  s.rhoMax = from_log(s.lRhoMax, s.lRhoOffset);
+  s.lTMin = s.gT.gmin();
+  s.lTMax = s.gT.gmax();
+  s.TMax = from_log(s.lTMax, s.lTOffset);
+  auto rho_ = [&](const double lRho) {
+    const double r = from_log(lRho, s.lRhoOffset);
+    return r < 0 ? 0 : r;
+  };
+  auto I2 = [&](const double *tab, double lRho, double lT) {
+    return interp2d(tab, s.gRho, s.gT, numT, lRho, lT);
+  };
+
+  // fixBulkModulus_ (:689-714)
+  for (int j = 0; j < numRho; j++) {
+    const double lRho = s.gRho.x(j);
+    const double rho = rho_(lRho);
+    for (int i = 0; i < numT; i++) {
+      const double lT = s.gT.x(i);
+      const double press = I2(P, lRho, lT);
+      const double DPDR_E = I2(dPdRho, lRho, lT);
+      const double DPDE_R = I2(dPdE, lRho, lT);
+      const double DEDR_T = I2(dEdRho, lRho, lT);
+      const double DPDR_T = DPDR_E + DPDE_R * DEDR_T;
+      double bm;
+      if (DPDE_R > 0.0 && rho > 0.0) {
+        bm = rho * DPDR_E + DPDE_R * (press / rho);
+      } else if (rho > 0.0) {
+        bm = std::max(rho * DPDR_T, 0.0);
+      } else {
+        bm = 0.0;
+      }
+      bMod[(size_t)j * numT + i] = std::max(bm, std::abs(kEps));
+    }
+  }
+
+  // setlTColdCrit_ (:716-775)
+  for (int j = 0; j < numRho; j++) {
+    const double lRho = s.gRho.x(j);
+    const double sieColdj = interp1d(sieCold, s.gRho, lRho);
+    std::vector<int> crossings;
+    int last_pos_crossing = -1;
+    for (int i = 0; i < numT - 1; i++) {
+      const double sign_curr = sie[(size_t)j * numT + i] - sieColdj;
+      const double sign_next = sie[(size_t)j * numT + i + 1] - sieColdj;
+      if (sign_curr < 0 && sign_next > 0) {
+        crossings.push_back(i);
+        last_pos_crossing = (int)crossings.size() - 1;
+      } else if (sign_curr > 0 && sign_next < 0) {
+        crossings.push_back(i);
+      }
+    }
+    if (last_pos_crossing <= 0) {
+      lTColdCrit[j] = s.lTMin;
+    } else {
+      auto sieFunc = [&](const double x) { return I2(sie, lRho, x); };
+      double lT;
+      const int ilast = crossings[last_pos_crossing];
+      const double lTlower = s.gT.x(ilast) - 1.0e-14;
+      const double lTupper = s.gT.x(ilast + 1) + 1.0e-14;
+      const double lTGuess = 0.5 * (lTlower + lTupper);
+      const auto status =
+          root::regula_falsi(sieFunc, sieColdj, lTGuess, lTlower, lTupper,
+                             SpinerRhoT::ROOT_THRESH, SpinerRhoT::ROOT_THRESH, lT);
+      if (status != root::SUCCESS) lT = lTGuess;
+      lTColdCrit[j] = lT;
+    }
+    lTColdCrit[j] = std::max(s.lTMin, lTColdCrit[j]);
+  }
+
+  // minimum pressure as a function of temperature (:625)
+  s.PMin = SetRhoPMin(P, s.gT, s.gRho, ts.h("rho_at_pmin"), pmin_vapor_dome != 0, 1e-8,
+                      s.lRhoOffset);
+
+  // cold-curve extrapolation tables (:638-649)
+  for (int j = 0; j < numRho; j++) {
+    const double lRho = s.gRho.x(j);
+    const double lT = lTColdCrit[j];
+    bModCold[j] = I2(bMod, lRho, lT);
+    dPdECold[j] = I2(dPdE, lRho, lT);
+    dTdRhoCold[j] = I2(dTdRho, lRho, lT);
+    dTdECold[j] = I2(dTdE, lRho, lT);
+    dEdTCold[j] = I2(dEdT, lRho, lT);
+  }
+  // top-of-table curves (:652-663)
+  for (int j = 0; j < numRho; j++) {
+    const double lRho = s.gRho.x(j);
+    const double rho = rho_(lRho);
+    PMax[j] = P[(size_t)j * numT + numT - 1];
+    dEdTMax[j] = dEdT[(size_t)j * numT + numT - 1];
+    gm1Max[j] = ratio(dPdE[(size_t)j * numT + numT - 1], rho);
+    sielTMax[j] = sie[(size_t)j * numT + numT - 1];
+  }
+  // reference state (:665-684)
+  double lRhoNormal = to_log(rhoNormal, s.lRhoOffset);
+  if (!(s.lRhoMin < lRhoNormal && lRhoNormal < s.lRhoMax)) {
+    lRhoNormal = 0.5 * (s.lRhoMin + s.lRhoMax);
+    rhoNormal = rho_(lRhoNormal);
+  }
+  double TNormal = ROOM_TEMPERATURE;
+  double lTNormal = to_log(TNormal, s.lTOffset);
+  if (!(s.lTMin < lTNormal && lTNormal < s.lTMax)) {
+    lTNormal = 0.5 * (s.lTMin + s.lTMax);
+    TNormal = from_log(lTNormal, s.lTOffset);
+  }
+  auto &sc = ts.scalars;
+  sc["rhoNormal"] = rhoNormal;
+  sc["TNormal"] = TNormal;
+  sc["sieNormal"] = I2(sie, lRhoNormal, lTNormal);
+  sc["PNormal"] = I2(P, lRhoNormal, lTNormal);
+  sc["CvNormal"] = I2(dEdT, lRhoNormal, lTNormal);
+  sc["bModNormal"] = I2(bMod, lRhoNormal, lTNormal);
+  sc["dPdENormal"] = I2(dPdE, lRhoNormal, lTNormal);
+  const double dPdR = I2(dPdRho, lRhoNormal, lTNormal);
+  sc["dVdTNormal"] = sc["dPdENormal"] * sc["CvNormal"] / (rhoNormal * rhoNormal * dPdR);
+  sc["lRhoMin"] = s.lRhoMin;
+  sc["lRhoMax"] = s.lRhoMax;
+  sc["rhoMax"] = s.rhoMax;
+  sc["lTMin"] = s.lTMin;
+  sc["lTMax"] = s.lTMax;
+  sc["TMax"] = s.TMax;
+  sc["PMin"] = s.PMin;
+  sc["lRhoOffset"] = s.lRhoOffset;
+  sc["lTOffset"] = s.lTOffset;
+  sc["meanAtomicMass"] = raw->mean_atomic_mass;
+  sc["meanAtomicNumber"] = raw->mean_atomic_number;
+
+  // CheckParams (:94-106)
+  if (!(numRho > 0 && numT > 0 && s.lRhoMax > s.lRhoMin && s.rhoMax > 0 &&
+        s.lTMax > s.lTMin && s.TMax > 0))
+    return fail(SGX_ERR_INVALID, "SpinerEOSDependsRhoT::CheckParams failed");
+
+  int rc = upload_tables(e);
+  if (rc) return rc;
+  s.P = ts.d("P");
+  s.sie = ts.d("sie");
+  s.bMod = ts.d("bMod");
+  s.dPdRho = ts.d("dPdRho");
+  s.dPdE = ts.d("dPdE");
+  s.dTdRho = ts.d("dTdRho");
+  s.dTdE = ts.d("dTdE");
+  s.dEdRho = ts.d("dEdRho");
+  s.dEdT = ts.d("dEdT");
+  s.PMax = ts.d("PMax");
+  s.sielTMax = ts.d("sielTMax");
+  s.dEdTMax = ts.d("dEdTMax");
+  s.gm1Max = ts.d("gm1Max");
+  s.lTColdCrit = ts.d("lTColdCrit");
+  s.PCold = ts.d("PCold");
+  s.sieCold = ts.d("sieCold");
+  s.bModCold = ts.d("bModCold");
+  s.dPdRhoCold = ts.d("dPdRhoCold");
+  s.dPdECold = ts.d("dPdECold");
+  s.dTdRhoCold = ts.d("dTdRhoCold");
+  s.dTdECold = ts.d("dTdECold");
+  s.dEdTCold = ts.d("dEdTCold");
+  s.rho_at_pmin = ts.d("rho_at_pmin");
+  return SGX_OK;
+}
+
+int build_spiner_rhosie(const sgx_sp5_tables *raw, int reproducible, int pmin_vapor_dome,
+                        sgx_eos_s *e) {
+  if (!raw) return fail(SGX_ERR_INVALID, "null sgx_sp5_tables");
+  if (!grid_ok(raw->lrho) || !grid_ok(raw->lT) || !grid_ok(raw->lE))
+    return fail(SGX_ERR_INVALID, "malformed lrho/lT/lE grid");
+  const double *req[] = {raw->sie,      raw->P,       raw->bMod,    raw->dPdRho,  raw->dPdE,
+                         raw->dTdRho,   raw->dTdE,    raw->dEdRho,  raw->T_re,    raw->P_re,
+                         raw->bMod_re,  raw->dPdRho_re, raw->dPdE_re, raw->dTdRho_re,
+                         raw->dTdE_re,  raw->dEdRho_re, raw->PCold,  raw->sieCold,
+                         raw->bModCold, raw->dPdRhoCold};
+  for (const double *p : req)
+    if (!p) return fail(SGX_ERR_INVALID, "SpinerEOSDependsRhoSie needs both table sets");
+
+  SpinerRhoSie &s = e->rhosie;
+  TableStore &ts = e->tables;
+  s.gRho = make_grid(raw->lrho);
+  s.gT = make_grid(raw->lT);
+  s.gE = make_grid(raw->lE);
+  const int numRho = s.gRho.n_total(), numT = s.gT.n_total(), numE = s.gE.n_total();
+  s.numRho = numRho;
+  s.numT = numT;
+  s.numE = numE;
+  const size_t nT2 = (size_t)numRho * numT, nE2 = (size_t)numRho * numE;
+  s.lRhoOffset = std::abs(raw->rho_offset);
+  s.lTOffset = std::abs(raw->T_offset);
+  s.lEOffset = std::abs(raw->sie_offset);
+  double rhoNormal = std::abs(raw->normal_density);
+  s.reproducible = reproducible ? 1 : 0;
+
+  ts.add("sie", raw->sie, nT2);
+  ts.add("P", raw->P, nT2);
+  ts.add("bMod", raw->bMod, nT2);
+  ts.add("dPdRho", raw->dPdRho, nT2);
+  ts.add("dPdE", raw->dPdE, nT2);
+  ts.add("dTdRho", raw->dTdRho, nT2);
+  ts.add("dTdE", raw->dTdE, nT2);
+  ts.add("dEdRho", raw->dEdRho, nT2);
+  ts.add("T_re", raw->T_re, nE2);
+  ts.add("P_re", raw->P_re, nE2);
+  ts.add("bMod_re", raw->bMod_re, nE2);
+  ts.add("dPdRho_re", raw->dPdRho_re, nE2);
+  ts.add("dPdE_re", raw->dPdE_re, nE2);
+  ts.add("dTdRho_re", raw->dTdRho_re, nE2);
+  ts.add("dTdE_re", raw->dTdE_re, nE2);
+  ts.add("dEdRho_re", raw->dEdRho_re, nE2);
+  ts.add("PCold", raw->PCold, numRho);
+  ts.add("sieCold", raw->sieCold, numRho);
+  ts.add("bModCold", raw->bModCold, numRho);
+  ts.add("dPdRhoCold", raw->dPdRhoCold, numRho);
+  ts.add("rho_at_pmin", nullptr, numT);
+  ts.add("PlRhoMax", nullptr, numT);
+  ts.add("dPdRhoMax", nullptr, numT);
+
+  // calcBMod_ (:579-601) on both table sets
+  auto calcBMod = [&](const char *sfx, int n1) {
+    const std::string x(sfx);
+    double *P = ts.h("P" + x), *bMod = ts.h("bMod" + x), *dPdRho = ts.h("dPdRho" + x),
+           *dPdE = ts.h("dPdE" + x), *dEdRho = ts.h("dEdRho" + x);
+    for (int j = 0; j < numRho; j++) {
+      const double lRho = s.gRho.x(j);
+      const double rho = from_log(lRho, s.lRhoOffset);
+      for (int i = 0; i < n1; i++) {
+        const size_t k = (size_t)j * n1 + i;
+        const double press = P[k];
+        const double DPDR_E = dPdRho[k];
+        const double DPDE_R = dPdE[k];
+        const double DEDR_T = dEdRho[k];
+        const double DPDR_T = DPDR_E + DPDE_R * DEDR_T;
+        double bm;
+        if (DPDE_R > 0.0 && rho > 0.0) {
+          bm = rho * DPDR_E + DPDE_R * (press / rho);
+        } else if (rho > 0.0) {
+          bm = std::max(rho * DPDR_T, 0.0);
+        } else {
+          bm = 0.0;
+        }
+        bMod[k] = std::max(bm, kEps);
+      }
+    }
+  };
+  calcBMod("", numT);
+  calcBMod("_re", numE);
+
+  s.lRhoMin = s.gRho.gmin();
+  s.lRhoMax = s.gRho.gmax();
+  s.rhoMax = from_log(s.lRhoMax, s.lRhoOffset);
+  // slices at the maximum density (:529-530)
+  {
+    const double *P = ts.h("P"), *dPdRho = ts.h("dPdRho");
+    double *a = ts.h("PlRhoMax"), *b = ts.h("dPdRhoMax");
+    for (int i = 0; i < numT; ++i) {
+      a[i] = P[(size_t)(numRho - 1) * numT + i];
+      b[i] = dPdRho[(size_t)(numRho - 1) * numT + i];
+    }
+  }
+  s.PMin = SetRhoPMin(ts.h("P"), s.gT, s.gRho, ts.h("rho_at_pmin"), pmin_vapor_dome != 0, 1e-8,
+                      s.lRhoOffset);
+  // reference state (:536-560)
+  double lRhoNormal = to_log(rhoNormal, s.lRhoOffset);
+  if (!(s.lRhoMin < lRhoNormal && lRhoNormal < s.lRhoMax)) {
+    lRhoNormal = 0.5 * (s.lRhoMin + s.lRhoMax);
+    rhoNormal = from_log(lRhoNormal, s.lRhoOffset);
+  }
+  double TNormal = ROOM_TEMPERATURE;
+  double lTNormal = to_log(TNormal, s.lTOffset);
+  const double lTMin = s.gT.gmin(), lTMax = s.gT.gmax();
+  if (!(lTMin < lTNormal && lTNormal < lTMax)) {
+    lTNormal = 0.5 * (lTMin + lTMax);
+    TNormal = from_log(lTNormal, s.lTOffset);
+  }
+  auto I2 = [&](const char *nm) {
+    return interp2d(ts.h(nm), s.gRho, s.gT, numT, lRhoNormal, lTNormal);
+  };
+  auto &sc = ts.scalars;
+  sc["rhoNormal"] = rhoNormal;
+  sc["TNormal"] = TNormal;
+  sc["sieNormal"] = I2("sie");
+  sc["PNormal"] = I2("P");
+  sc["CvNormal"] = 1. / I2("dTdE");
+  sc["bModNormal"] = I2("bMod");
+  sc["dPdENormal"] = I2("dPdE");
+  const double dPdR = I2("dPdRho");
+  sc["dVdTNormal"] = sc["dPdENormal"] * sc["CvNormal"] / (rhoNormal * rhoNormal * dPdR);
+  sc["lRhoMin"] = s.lRhoMin;
+  sc["lRhoMax"] = s.lRhoMax;
+  sc["rhoMax"] = s.rhoMax;
+  sc["PMin"] = s.PMin;
+  sc["lRhoOffset"] = s.lRhoOffset;
+  sc["lTOffset"] = s.lTOffset;
+  sc["lEOffset"] = s.lEOffset;
+  sc["meanAtomicMass"] = raw->mean_atomic_mass;
+  sc["meanAtomicNumber"] = raw->mean_atomic_number;
+
+  int rc = upload_tables(e);
+  if (rc) return rc;
+  s.sie = ts.d("sie");
+  s.P = ts.d("P");
+  s.bMod = ts.d("bMod");
+  s.dPdRho = ts.d("dPdRho");
+  s.dPdE = ts.d("dPdE");
+  s.dTdRho = ts.d("dTdRho");
+  s.dTdE = ts.d("dTdE");
+  s.dEdRho = ts.d("dEdRho");
+  s.T_re = ts.d("T_re");
+  s.P_re = ts.d("P_re");
+  s.bMod_re = ts.d("bMod_re");
+  s.dPdRho_re = ts.d("dPdRho_re");
+  s.dPdE_re = ts.d("dPdE_re");
+  s.dTdRho_re = ts.d("dTdRho_re");
+  s.dTdE_re = ts.d("dTdE_re");
+  s.dEdRho_re = ts.d("dEdRho_re");
+  s.PCold = ts.d("PCold");
+  s.sieCold = ts.d("sieCold");
+  s.bModCold = ts.d("bModCold");
+  s.dPdRhoCold = ts.d("dPdRhoCold");
+  s.rho_at_pmin = ts.d("rho_at_pmin");
+  s.PlRhoMax = ts.d("PlRhoMax");
+  s.dPdRhoMax = ts.d("dPdRhoMax");
+  return SGX_OK;
+}
+
+} // namespace sgx

@@ -1,0 +1,207 @@
+"""Synthetic table generators for the benchmark configurations.
+
+The reference has no path that tabulates an analytic EOS into a Spiner EOS (its .sp5 files
+come from sesame2spiner + proprietary EOSPAC), and the shipped Helmholtz table is absent from
+the checkout.  These generators produce inputs of the same *shape and format*:
+
+* `vinet_sp5_tables`  -- the raw contents of one .sp5 material (every dataset
+  SpinerEOSDependsRhoT / RhoSie::loadDataboxes_ reads, eos_spiner_rho_temp.hpp:545-583,
+  eos_spiner_rho_sie.hpp:434-488) tabulated from the analytic Vinet EOS
+  (eos/eos_vinet.hpp:228-292) on NQT-log grids built like table_utils::Bounds
+  (base/spiner_table_utils.hpp:56-70,190-206).
+* `write_synthetic_helm_table` -- a 4-block ASCII file in the layout
+  Helmholtz reads (eos_helmholtz.hpp:962-975).
+
+This is data generation, not the hot path: the same raw tables are handed to the CUDA library
+and to the oracle, each of which then performs its own load-time fix-ups.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+
+# ---------------------------------------------------------------------------------------
+# NQT order-2 logs on numpy int64 (base/fast-math/logs.hpp:188-214) -- used for grid bounds
+# ---------------------------------------------------------------------------------------
+_ONE_AS_INT = (1 << 62) - (1 << 52)
+_MANT = (1 << 52) - 1
+_LOW = (1 << 26) - 1
+_SCALE_DOWN = 2.22044604925031e-16
+_SCALE_UP = float(1 << 52)
+
+
+def fast_lg(x):
+    x = np.asarray(x, dtype=np.float64)
+    xi = x.view(np.int64) - np.int64(_ONE_AS_INT)
+    frac = xi & np.int64(_MANT)
+    fh = frac >> np.int64(26)
+    fl = frac & np.int64(_LOW)
+    fsq = fh * fh + ((fh * fl) >> np.int64(25))
+    num = frac - fsq
+    q = np.where(num >= 0, num // 3, -((-num) // 3))  # C++ truncating division
+    return (xi + q).astype(np.float64) * _SCALE_DOWN
+
+
+def fast_pow2(x):
+    x = np.asarray(x, dtype=np.float64)
+    a, b, c = np.int64(9007199254740992), 67108864.0, np.int64(18014398509481984)
+    xi = np.trunc(x * _SCALE_UP).astype(np.int64)
+    frac = xi & np.int64(_MANT)
+    fsqrt = np.trunc(b * np.sqrt((c - np.int64(3) * frac).astype(np.float64))).astype(np.int64)
+    return (xi + a - fsqrt - frac + np.int64(_ONE_AS_INT)).view(np.float64)
+
+
+def fast_log10(x):
+    return 0.301029995663981195 * fast_lg(x)
+
+
+def fast_pow10(x):
+    return fast_pow2(3.321928094887362626 * np.asarray(x, dtype=np.float64))
+
+
+def log_bounds(xmin, xmax, n):
+    """Single-patch Bounds(min, max, N, convertToLog=True): returns (Grid1D, offset, nodes)."""
+    eps = np.finfo(np.float64).eps
+    offset = 0.0
+    if xmin <= 0:
+        offset = 1.1 * abs(xmin) + 10 * eps
+    lmin = float(fast_log10(np.abs(np.float64(xmin + offset))))
+    lmax = float(fast_log10(np.abs(np.float64(xmax + offset))))
+    dx = (lmax - lmin) / float(n - 1)
+    g = _lib.Grid1D()
+    g.ngrids = 1
+    g.npoints[0] = n
+    g.min[0], g.max[0], g.dx[0] = lmin, lmax, dx
+    i = np.arange(n, dtype=np.float64)
+    lnodes = i * dx + lmin  # RegularGrid1D::x
+    nodes = np.minimum(xmax, np.maximum(xmin, fast_pow10(lnodes) - offset))  # Bounds::log2lin
+    return g, offset, nodes
+
+
+# ---------------------------------------------------------------------------------------
+# Vinet (eos/eos_vinet.hpp:204-292)
+# ---------------------------------------------------------------------------------------
+class Vinet:
+    def __init__(self, rho0=8.93, T0=298.0, B0=1.3448466e12, BP0=4.956, A0=5.19245e-05,
+                 Cv0=0.383e7, E0=0.0, S0=5.05e8, d2to40=None):
+        self.rho0, self.T0, self.B0, self.BP0 = rho0, T0, B0, BP0
+        self.A0, self.Cv0, self.E0, self.S0 = A0, Cv0, E0, S0
+        d = np.zeros(39) if d2to40 is None else np.asarray(d2to40, dtype=np.float64)
+        self.d = d
+        vip = np.zeros(43)
+        vip[0] = B0 / rho0 + A0 * A0 * B0 * B0 * T0 / (rho0 * rho0 * Cv0)
+        vip[1] = 1.5 * (BP0 - 1.0)
+        vip[2], vip[3] = 1.0, 0.0
+        vip[4:] = d
+        for ind in range(41, 1, -1):
+            vip[ind] = vip[ind] - ind / vip[1] * vip[ind + 1]
+        self.vip = vip
+
+    def eval(self, rho, T):
+        """Returns e, P, dPdrho_T, dPdT_rho, dedT_rho, dedrho_T (Vinet_F_DT_func)."""
+        rho = np.asarray(rho, dtype=np.float64)
+        T = np.asarray(T, dtype=np.float64)
+        vip, d = self.vip, self.d
+        x = np.cbrt(self.rho0 / rho)
+        x2inv = 1.0 / (x * x)
+        onemx = 1.0 - x
+        eta1mx = vip[1] * onemx
+        ex = np.exp(eta1mx)
+        sumP = np.zeros_like(x)
+        sumB = np.zeros_like(x)
+        sumE = np.zeros_like(x)
+        for ind in range(40, 1, -1):
+            sumP = d[ind - 2] + onemx * sumP
+            sumB = d[ind - 2] * ind + onemx * sumB
+            sumE = vip[2 + ind] + onemx * sumE
+        for ind in (1, 0):
+            sumE = vip[2 + ind] + onemx * sumE
+        sumP = 1.0 + sumP * (onemx * onemx)
+        sumB = sumB * onemx
+        sumE = vip[1] * onemx * sumE
+        AB = self.A0 * self.B0
+        energy = (9.0 * self.B0 / (vip[1] * vip[1] * self.rho0) * (vip[2] - ex * (vip[2] - sumE))
+                  - AB * (self.T0 / self.rho0 - self.T0 / rho))
+        pressure = 3.0 * self.B0 * x2inv * onemx * ex * sumP
+        tmp = (1.0 + onemx * (vip[1] * x + 1.0)) * sumP + x * onemx * sumB
+        tmp = self.B0 / self.rho0 * x * ex * tmp
+        energy = energy + self.Cv0 * (T - self.T0) + self.E0
+        pressure = pressure + AB * (T - self.T0)
+        dpdrho = tmp + 0.0 * T
+        dpdt = AB + 0.0 * pressure
+        dedt = self.Cv0 + 0.0 * pressure
+        dedrho = (pressure - T * AB) / (rho * rho)
+        return energy, pressure, dpdrho, dpdt, dedt, dedrho
+
+    def T_from_rho_e(self, rho, e):
+        e0, *_ = self.eval(rho, np.full_like(np.asarray(rho, dtype=np.float64), self.T0))
+        return self.T0 + (e - e0 - 0.0) / self.Cv0
+
+
+class Sp5Raw:
+    """Owns the numpy arrays a sgx_sp5_tables struct points into."""
+
+    def __init__(self):
+        self.struct = _lib.Sp5Tables()
+        self.arrays = {}
+
+    def set(self, name, arr):
+        a = np.ascontiguousarray(arr, dtype=np.float64)
+        self.arrays[name] = a
+        setattr(self.struct, name, a.ctypes.data_as(C.POINTER(C.c_double)))
+
+    def byref(self):
+        return C.byref(self.struct)
+
+
+def _derived(rho, e, P, dpdrho_T, dpdt, cv, dedrho_T):
+    out = {}
+    out["dPdRho"] = dpdrho_T - dpdt * dedrho_T / cv  # (dP/drho)_e
+    out["dPdE"] = dpdt / cv  # (dP/de)_rho
+    out["dTdRho"] = -dedrho_T / cv  # (dT/drho)_e
+    out["dTdE"] = 1.0 / cv
+    out["dEdRho"] = dedrho_T
+    out["dEdT"] = cv
+    out["bMod"] = rho * out["dPdRho"] + (P / rho) * out["dPdE"]
+    return out
+
+
+def vinet_sp5_tables(nrho=256, nT=256, nE=256, rho_min=1.0, rho_max=30.0, T_min=1.0,
+                     T_max=1.0e5, vinet=None):
+    """Vinet copper on 256x256 single-patch NQT-log grids."""
+    v = vinet or Vinet()
+    raw = Sp5Raw()
+    gR, offR, rho_n = log_bounds(rho_min, rho_max, nrho)
+    gT, offT, T_n = log_bounds(T_min, T_max, nT)
+    R, TT = np.meshgrid(rho_n, T_n, indexing="ij")  # [nrho][nT], T fastest
+    e, P, dpdr, dpdt, cv, dedr = v.eval(R, TT)
+    der = _derived(R, e, P, dpdr, dpdt, cv, dedr)
+    raw.set("P", P)
+    raw.set("sie", e)
+    for k in ("bMod", "dPdRho", "dPdE", "dTdRho", "dTdE", "dEdRho", "dEdT"):
+        raw.set(k, der[k])
+    # cold curve = T=0 isotherm (sesame2spiner/io_eospac.cpp:250)
+    e0, P0, dpdr0, dpdt0, cv0, dedr0 = v.eval(rho_n, np.zeros_like(rho_n))
+    der0 = _derived(rho_n, e0, P0, dpdr0, dpdt0, cv0, dedr0)
+    raw.set("PCold", P0)
+    raw.set("sieCold", e0)
+    raw.set("bModCold", der0["bMod"])
+    raw.set("dPdRhoCold", der0["dPdRho"])
+    # (rho, sie) set
+    gE, offE, e_n = log_bounds(float(e.min()), float(e.max()), nE)
+    R2, EE = np.meshgrid(rho_n, e_n, indexing="ij")
+    T2 = v.T_from_rho_e(R2, EE)
+    e2, P2, dpdr2, dpdt2, cv2, dedr2 = v.eval(R2, T2)
+    der2 = _derived(R2, e2, P2, dpdr2, dpdt2, cv2, dedr2)
+    raw.set("T_re", T2)
+    raw.set("P_re", P2)
+    for k in ("bMod", "dPdRho", "dPdE", "dTdRho", "dTdE", "dEdRho"):
+        raw.set(k + "_re", der2[k])
+    s = raw.struct
+    s.lrho, s.lT, s.lE = gR, gT, gE
+    s.rho_offset, s.T_offset, s.sie_offset = offR, offT, offE
+    s.normal_density = v.rho0
+    s.mean_atomic_mass, s.mean_atomic_number = 63.546, 29.0
+    raw.nodes = {"rho": rho_n, "T": T_n, "e": e_n}
+    return raw
