@@ -1,0 +1,408 @@
+#!/usr/bin/env python
+"""bench.py -- BASELINE.json's metric on B200: Gcells/s for the EOS lookup configurations and
+PTE cell-solves/s, next to the reference's own CPU implementation timed on the host cores.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    torchrun --nproc-per-node N ... bench.py --gpus N ...     (one rank per GPU, NCCL)
+
+One JSON line on stdout (rank 0).  A "step" is one pass of the headline hot path over one
+batch: SpinerEOSDependsRhoT::PressureFromDensityTemperature over 2^26 cells per GPU
+(BASELINE.json configs[1]); cells are sharded contiguously over ranks, tables replicated,
+no data-path collective (weak scaling).  The other configurations are measured in the same
+run and reported under "configs".
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "Gcells/s EOS lookups (SpinerEOSDependsRhoT P(rho,T), 2^26 cells/GPU); PTE cell solves/s in configs"
+UNIT = "Gcells/s"
+N_LOOKUP = 1 << 26
+N_IDEAL = 1 << 20
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--cells", type=int, default=N_LOOKUP, help="cells per GPU for lookup configs")
+    ap.add_argument("--pte-cells", type=int, default=1 << 24, help="PTE cells per GPU")
+    ap.add_argument("--pte-full", action="store_true", help="PTE at 2^27 cells per GPU")
+    ap.add_argument("--quick", action="store_true", help="headline config only")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons DURING the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx = gpu_index
+        self.rows = []
+        self._stop = threading.Event()
+        self._t = None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True,
+                                     text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([c.strip() for c in out.split(",")])
+            except Exception:
+                pass
+            self._stop.wait(0.2)
+
+    def start(self):
+        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._t:
+            self._t.join(timeout=6)
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                mx.append(float(r[2]))
+            except Exception:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown",
+                                "sw_power_cap"), r[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None,
+                "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def measured_peak_gbs():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(p) as fh:
+            return float(json.load(fh)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+# ------------------------------------------------------------------------------------------
+def time_steps(torch, fn, steps, warmup, dist=None):
+    """W warm-ups, then K steps between CUDA events on the launching (current) stream,
+    bracketed by barrier + synchronize; returns max-over-ranks seconds for the K steps."""
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0 = torch.cuda.Event(enable_timing=True)
+    e1 = torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    secs = e0.elapsed_time(e1) * 1e-3
+    if dist is not None:
+        t = torch.tensor([secs], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        secs = float(t.item())
+    return secs
+
+
+def run_ours(args):
+    import torch
+
+    import __graft_entry__ as g
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py (impl=ours) needs a CUDA device: there is no CPU path")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+
+        dist_mod.init_process_group("nccl", device_id=torch.device("cuda", local))
+        dist = dist_mod
+    pkg = g.load_package()
+    L = pkg._lib
+    lib = L.load()
+    W = pkg.workloads
+    dev = torch.device("cuda", local)
+    K, Wu = args.steps, max(args.warmup, 3)
+    n = args.cells
+    start = rank * n  # contiguous shard of the global index space
+    peak, peak_src = measured_peak_gbs()
+    results = {}
+
+    raw = pkg.tablegen.vinet_sp5_tables()
+    eos_rt = pkg.SpinerEOSDependsRhoT(raw)
+    rho, T = W.spiner_inputs(n, start, xp=torch, device=dev)
+    out = torch.empty_like(rho)
+    lam = torch.full((n, 2), float("nan"), dtype=torch.float64, device=dev)
+
+    # ---- headline: config 2, P(rho,T) with (lRho,lT) lambda write-back: 40 B/cell ------
+    sampler = ClockSampler(local)
+    launches0 = lib.sgx_launch_count()
+    if rank == 0:
+        sampler.start()
+    secs = time_steps(torch, lambda: eos_rt.PressureFromDensityTemperature(rho, T, out, n, lam),
+                      K, Wu, dist)
+    clocks = sampler.stop() if rank == 0 else None
+    launches = lib.sgx_launch_count() - launches0 - Wu
+    cells_total = n * world * K
+    value = cells_total / secs / 1e9
+    bytes_per_cell = 40
+    achieved = n * bytes_per_cell / (secs / K) / 1e9
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "kernel": "eval_kernel<P_FROM_RHO_T, SpinerRhoT, VEC>",
+                "algorithmic_bytes_per_cell": bytes_per_cell}
+    results["spiner_rhot_P_rhoT_lambda"] = {"Gcells_per_s": value, "GBps_per_gpu": achieved,
+                                            "frac_hbm": achieved / peak, "cells_per_gpu": n}
+
+    def lookup(name, fn, bpc, cells=n, steps=K):
+        s = time_steps(torch, fn, steps, Wu, dist)
+        gbs = cells * bpc / (s / steps) / 1e9
+        results[name] = {"Gcells_per_s": cells * world * steps / s / 1e9, "GBps_per_gpu": gbs,
+                         "frac_hbm": gbs / peak, "cells_per_gpu": cells,
+                         "algorithmic_bytes_per_cell": bpc}
+
+    if not args.quick:
+        lookup("spiner_rhot_P_rhoT_nolambda",
+               lambda: eos_rt.PressureFromDensityTemperature(rho, T, out, n), 24)
+        # config 3a: regula-falsi T(rho,e), cold start (NaN lambda) and warm start
+        sie = torch.empty_like(rho)
+        eos_rt.InternalEnergyFromDensityTemperature(rho, T, sie, n, lam)
+        lam_warm = lam.clone()
+
+        def cold():
+            lam.fill_(float("nan"))
+            eos_rt.TemperatureFromDensityInternalEnergy(rho, sie, out, n, lam)
+
+        def warm():
+            lam.copy_(lam_warm)
+            eos_rt.TemperatureFromDensityInternalEnergy(rho, sie, out, n, lam)
+        ks = max(3, K // 4)
+        lookup("spiner_rhot_T_rhoe_rootfind_cold(+lambda refill)", cold, 40, steps=ks)
+        lookup("spiner_rhot_T_rhoe_rootfind_warm(+lambda refill)", warm, 40, steps=ks)
+        # config 3b: RhoSie direct lookup
+        eos_rs = pkg.SpinerEOSDependsRhoSie(raw)
+        lam1 = torch.full((n, 1), float("nan"), dtype=torch.float64, device=dev)
+        lookup("spiner_rhosie_T_rhoe", lambda: eos_rs.TemperatureFromDensityInternalEnergy(
+            rho, sie, out, n, lam1), 32)
+        del lam1, lam_warm
+        # config 1: IdealGas at 2^20 (launch-latency bound; CUDA graph of 100 pairs) and 2^26
+        ideal = pkg.IdealGas(0.4, 7.16e6)
+        r1, t1 = W.ideal_inputs(N_IDEAL, rank * N_IDEAL, xp=torch, device=dev)
+        p1, e1 = torch.empty_like(r1), torch.empty_like(r1)
+
+        def pair_small():
+            ideal.PressureFromDensityTemperature(r1, t1, p1, N_IDEAL)
+            ideal.InternalEnergyFromDensityTemperature(r1, t1, e1, N_IDEAL)
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            pair_small()
+        torch.cuda.current_stream().wait_stream(side)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            for _ in range(100):
+                pair_small()
+        s = time_steps(torch, graph.replay, 10, Wu, dist)
+        results["ideal_P+e_1M_cudagraph"] = {
+            "Gcells_per_s": N_IDEAL * world * 1000 / s / 1e9, "us_per_pair": s / 1000 * 1e6,
+            "note": "2^20 cells fit L2; launch-latency bound (SURVEY 8d)",
+            "cells_per_gpu": N_IDEAL}
+
+        def pair_big():
+            ideal.PressureFromDensityTemperature(rho, T, out, n)
+            ideal.InternalEnergyFromDensityTemperature(rho, T, sie, n)
+        lookup("ideal_P_then_e_64M", pair_big, 48)
+        lookup("ideal_fused_P+e_64M",
+               lambda: ideal.PressureEnergyFromDensityTemperature(rho, T, out, sie, n), 32)
+        del sie
+    del lam
+
+    # ---- config 5: PTE RhoT -------------------------------------------------------------
+    if not args.quick:
+        npte = (1 << 27) if args.pte_full else args.pte_cells
+        g3 = pkg.closure.set_eos_3mat_analytic()
+        sie0 = []
+        for m in range(3):
+            o = torch.empty(1, dtype=torch.float64, device=dev)
+            g3[m].InternalEnergyFromDensityTemperature(
+                torch.tensor([W.PTE_RHO[m]], dtype=torch.float64, device=dev),
+                torch.tensor([W.PTE_T], dtype=torch.float64, device=dev), o, 1)
+            sie0.append(float(o.item()))
+        state0 = W.pte_state_torch(npte, sie0, dev, start=rank * npte)
+        state = [a.clone() for a in state0]
+        status = torch.zeros(npte, dtype=torch.int64, device=dev)
+        stats = torch.zeros(L.PTE_NSTATS, dtype=torch.int64, device=dev)
+        prm = pkg.closure.test_pte_params()
+
+        def pte():
+            for a, b in zip(state, state0):
+                a.copy_(b)
+            pkg.closure.PTESolverRhoT(g3, *state, params=prm, status=status, stats=stats)
+        ks = 3
+        stats.zero_()
+        s = time_steps(torch, pte, ks, 1, dist)
+        if dist is not None:
+            dist.all_reduce(stats)  # the optional convergence-statistics all-reduce (NCCL)
+        st = stats.cpu().numpy()
+        results["pte_rhot_3mat"] = {
+            "cell_solves_per_s": npte * world * ks / s, "cells_per_gpu": npte,
+            "converged_frac": float(st[1]) / max(1, float(st[0])),
+            "niter_hist": [int(x) for x in st[8:24]],
+            "note": "includes the 5-array state reset copy each step (in-place solver)"}
+        del state, state0, status
+
+    # ---- e2e: host buffers through the C ABI (_host entry), H2D + D2H inside the timing --
+    ne = min(n, 1 << 24)
+    rho_h, T_h = W.spiner_inputs(ne, start)
+    rho_p = torch.from_numpy(rho_h).pin_memory().numpy()
+    T_p = torch.from_numpy(T_h).pin_memory().numpy()
+    out_p = torch.empty(ne, dtype=torch.float64).pin_memory().numpy()
+    lam_p = torch.full((ne, 2), float("nan"), dtype=torch.float64).pin_memory().numpy()
+    for _ in range(2):
+        eos_rt.eval_host(L.P_FROM_RHO_T, rho_p, T_p, out_p, lam_p)
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    t0 = time.perf_counter()
+    ke = 5
+    for _ in range(ke):
+        eos_rt.eval_host(L.P_FROM_RHO_T, rho_p, T_p, out_p, lam_p)
+    t_e2e = time.perf_counter() - t0
+    if dist is not None:
+        tt = torch.tensor([t_e2e], dtype=torch.float64, device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        t_e2e = float(tt.item())
+    e2e = {"value": ne * world * ke / t_e2e / 1e9, "unit": UNIT,
+           "h2d_bytes_per_step": ne * (8 + 8 + 16), "d2h_bytes_per_step": ne * (8 + 16),
+           "cells_per_step_per_gpu": ne,
+           "api": "sgx_eos_eval_host(P_FROM_RHO_T) with pinned host arrays"}
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K,
+        "warmup": Wu, "ms_per_step": secs / K * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "SpinerEOSDependsRhoT PressureFromDensityTemperature, 256x256 "
+                               "NQT-log table from analytic Vinet, lambda (lRho,lT) write-back",
+                   "cells_per_gpu": n, "global_cells": n * world,
+                   "l2_policy": "inputs (1 GiB/GPU) larger than L2; no flush needed",
+                   "parallelism": f"cells sharded contiguously over {world} GPU(s), tables replicated"},
+        "roofline": roofline, "e2e": e2e, "gpu_launches": int(launches),
+        "clocks": clocks, "configs": results,
+    }
+    if rank == 0 and not args.no_cpu:
+        line["cpu_baseline"] = cpu_baseline(pkg, raw, sample=1 << 22, reps=3)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------
+def cpu_baseline(pkg, raw, sample, reps):
+    """The reference's own code (oracle/_ref) on the host cores, bounded sample of the headline
+    workload.  This is the checker being *timed*, never part of the product path."""
+    import oracle_ref
+
+    ref = oracle_ref.load()
+    if ref is None:
+        return {"value": None, "unit": UNIT, "cores": 0, "kind": "reference",
+                "sample": "oracle/_ref/libsgref.so not present"}
+    L = pkg._lib
+    eos = ref.SpinerRhoT(raw)
+    rho, T = pkg.workloads.spiner_inputs(sample)
+    lam = np.full((sample, 2), np.nan)
+    cores = ref.num_threads()
+    eos.eval(L.P_FROM_RHO_T, rho, T, lam, nthreads=0)
+    best = 1e30
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        eos.eval(L.P_FROM_RHO_T, rho, T, lam, nthreads=0)
+        best = min(best, time.perf_counter() - t0)
+    return {"value": sample / best / 1e9, "unit": UNIT, "cores": cores, "kind": "reference",
+            "sample": f"{sample} cells of the headline workload, best of {reps}, OpenMP over the "
+                      "reference vector API (PORTABILITY_STRATEGY_NONE), g++ -O2"}
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the headline path on all host
+    threads; each step is a bounded sample of the workload.  Rank 0 only."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import __graft_entry__ as g
+    import oracle_ref
+
+    pkg = g.load_package()
+    ref = oracle_ref.load()
+    if ref is None:
+        print(json.dumps({"impl": "reference",
+                          "unavailable": "oracle/_ref/libsgref.so not built"}), flush=True)
+        return
+    L = pkg._lib
+    raw = pkg.tablegen.vinet_sp5_tables()
+    eos = ref.SpinerRhoT(raw)
+    sample = 1 << 23
+    rho, T = pkg.workloads.spiner_inputs(sample)
+    lam = np.full((sample, 2), np.nan)
+    K, Wu = args.steps, max(args.warmup, 1)
+    for _ in range(Wu):
+        eos.eval(L.P_FROM_RHO_T, rho, T, lam, nthreads=0)
+    t0 = time.perf_counter()
+    for _ in range(K):
+        eos.eval(L.P_FROM_RHO_T, rho, T, lam, nthreads=0)
+    secs = time.perf_counter() - t0
+    value = sample * K / secs / 1e9
+    cores = ref.num_threads()
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT,
+        "n_gpus": args.gpus, "steps": K, "warmup": Wu, "ms_per_step": secs / K * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic",
+        "config": {"workload": "SpinerEOSDependsRhoT PressureFromDensityTemperature, 256x256 "
+                               "NQT-log table from analytic Vinet, lambda (lRho,lT) write-back",
+                   "cells_per_step": sample, "note": "bounded sample of the 2^26-cell workload"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference",
+                         "sample": f"{sample} cells per step"},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

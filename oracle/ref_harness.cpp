@@ -200,7 +200,7 @@ int64_t copy_db(const DataBox &db, double *out, int64_t cap) {
   if (out == nullptr) return n;
   const int64_t m = std::min(n, cap);
   for (int64_t i = 0; i < m; ++i)
-    out[i] = db.data()[i];
+    out[i] = db.dataView_.data()[i]; // data() returns the base allocation even for slices
   return m;
 }
 

@@ -4,7 +4,7 @@ Drop-in for the hot path of lanl/singularity-eos behind a C ABI (include/sgx_b20
 The directory name contains a hyphen (it follows the repository naming), so import it
 through `__graft_entry__.load_package()` or as `singularity_eos_b200` after that call.
 """
-from . import _lib, closure, eos, rng, tablegen  # noqa: F401
+from . import _lib, closure, dist, eos, rng, tablegen, workloads  # noqa: F401
 from ._lib import SgxError, SgxLibraryMissing, thermalqs  # noqa: F401
 from .eos import (DavisProducts, DavisReactants, Gruneisen, Helmholtz, IdealGas,  # noqa: F401
                   SpinerEOSDependsRhoSie, SpinerEOSDependsRhoT)

@@ -1,0 +1,46 @@
+"""Shared test helpers (TEST INFRASTRUCTURE)."""
+import numpy as np
+
+
+def is_close(a, b, eps):
+    """isClose of test/eos_unit_test_helpers.hpp:60-64: |b-a| / (|a+b| + 1e-20) <= eps."""
+    a = np.asarray(a, dtype=np.float64)
+    b = np.asarray(b, dtype=np.float64)
+    return np.abs(b - a) / (np.abs(a + b) + 1e-20) <= eps
+
+
+def rel_err(a, b):
+    a = np.asarray(a, dtype=np.float64)
+    b = np.asarray(b, dtype=np.float64)
+    den = np.maximum(np.abs(b), 1e-300)
+    return np.abs(a - b) / den
+
+
+def assert_rel(a, b, tol, what=""):
+    a = np.asarray(a, dtype=np.float64)
+    b = np.asarray(b, dtype=np.float64)
+    assert a.shape == b.shape, (what, a.shape, b.shape)
+    both_nan = np.isnan(a) & np.isnan(b)
+    err = np.where(both_nan | (a == b), 0.0, rel_err(a, b))
+    worst = int(np.argmax(err))
+    assert err.flat[worst] <= tol, (
+        f"{what}: max rel err {err.flat[worst]:.3e} > {tol:g} at {worst}: "
+        f"got {a.flat[worst]!r} want {b.flat[worst]!r}")
+
+
+def assert_bits(a, b, what=""):
+    a = np.ascontiguousarray(a, dtype=np.float64)
+    b = np.ascontiguousarray(b, dtype=np.float64)
+    same = a.view(np.uint64) == b.view(np.uint64)
+    nz = np.isnan(a) & np.isnan(b)
+    ok = same | nz
+    if not ok.all():
+        i = int(np.argmin(ok))
+        raise AssertionError(f"{what}: {int((~ok).sum())}/{ok.size} values differ bitwise; first at "
+                             f"{i}: got {a.flat[i]!r} want {b.flat[i]!r}")
+
+
+def dev(t_np):
+    import torch
+
+    return torch.from_numpy(np.ascontiguousarray(t_np)).cuda()
