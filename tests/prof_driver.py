@@ -1,0 +1,56 @@
+"""Profiling driver (not a test): runs each hot kernel a few times at a size ncu can replay.
+usage: python tests/prof_driver.py [lookup|root|pte|rhosie|ideal|all] [log2 cells]"""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np, torch
+import __graft_entry__ as g
+pkg = g.load_package(); L = pkg._lib; W = pkg.workloads
+what = sys.argv[1] if len(sys.argv) > 1 else "all"
+lg = int(sys.argv[2]) if len(sys.argv) > 2 else 24
+n = 1 << lg
+dev = torch.device("cuda", 0)
+raw = pkg.tablegen.vinet_sp5_tables()
+rt = pkg.SpinerEOSDependsRhoT(raw)
+rho, T = W.spiner_inputs(n, 0, xp=torch, device=dev)
+out = torch.empty_like(rho); sie = torch.empty_like(rho)
+lam = torch.full((n, 2), float("nan"), dtype=torch.float64, device=dev)
+reps = 3
+def timed(name, fn):
+    fn(); torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps): fn()
+    e1.record(); torch.cuda.synchronize()
+    print(f"{name}: {e0.elapsed_time(e1)/reps:.4f} ms for {n} cells", flush=True)
+rt.InternalEnergyFromDensityTemperature(rho, T, sie, n, lam)
+if what in ("lookup", "all"):
+    timed("rhot_P_rhoT_lambda", lambda: rt.PressureFromDensityTemperature(rho, T, out, n, lam))
+    timed("rhot_P_rhoT_nolambda", lambda: rt.PressureFromDensityTemperature(rho, T, out, n))
+if what in ("root", "all"):
+    def cold():
+        lam.fill_(float("nan")); rt.TemperatureFromDensityInternalEnergy(rho, sie, out, n, lam)
+    timed("rhot_T_rhoe_cold", cold)
+if what in ("rhosie", "all"):
+    rs = pkg.SpinerEOSDependsRhoSie(raw)
+    lam1 = torch.full((n, 1), float("nan"), dtype=torch.float64, device=dev)
+    timed("rhosie_T_rhoe", lambda: rs.TemperatureFromDensityInternalEnergy(rho, sie, out, n, lam1))
+if what in ("ideal", "all"):
+    ig = pkg.IdealGas(0.4, 7.16e6)
+    timed("ideal_P", lambda: ig.PressureFromDensityTemperature(rho, T, out, n))
+if what in ("pte", "all"):
+    npte = 1 << (lg - 4)
+    g3 = pkg.closure.set_eos_3mat_analytic()
+    sie0 = []
+    for m in range(3):
+        o = torch.empty(1, dtype=torch.float64, device=dev)
+        g3[m].InternalEnergyFromDensityTemperature(torch.tensor([W.PTE_RHO[m]], dtype=torch.float64, device=dev), torch.tensor([W.PTE_T], dtype=torch.float64, device=dev), o, 1)
+        sie0.append(float(o.item()))
+    s0 = W.pte_state_torch(npte, sie0, dev)
+    st = [a.clone() for a in s0]
+    prm = pkg.closure.test_pte_params() if os.environ.get("PTE_PARAMS", "test") == "test" else pkg.closure.MixParams()
+    def pte():
+        for a, b in zip(st, s0): a.copy_(b)
+        pkg.closure.PTESolverRhoT(g3, *st, params=prm)
+    n_save = n; n = npte
+    timed("pte_rhot", pte)
+    n = n_save

@@ -55,7 +55,7 @@ def run():
     m = 4096
     s_h = W.pte_state_np(m, sie0)
     s_d = [dev(a) for a in s_h]
-    prm = pkg.closure.test_pte_params()
+    prm = pkg.closure.MixParams()  # library defaults: every flag is reproducible
     st_r, _, _ = ref.pte_solve(L.PTE_RHOT, r3, *s_h, prm, nthreads=0)
     status = torch.zeros(m, dtype=torch.int64, device="cuda")
     pkg.closure.PTESolverRhoT(g3, *s_d, params=prm, status=status)
