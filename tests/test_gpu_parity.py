@@ -344,7 +344,7 @@ def test_solve_Ax_b_known_answers(pkg, ref, torch_cuda):
 
 
 def _pte_compare(pkg, ref, torch, solver, vfrac_h, params, tol=PTE_TOL, what="",
-                 strict_flags=True):
+                 strict_flags=True, bulk=None):
     L = pkg._lib
     W = pkg.workloads
     g3, r3 = pkg.closure.set_eos_3mat_analytic(), ref.set_eos_3mat()
@@ -378,6 +378,10 @@ def _pte_compare(pkg, ref, torch, solver, vfrac_h, params, tol=PTE_TOL, what="",
     for got, want, nm in zip(state_d, (rho_h, vf_ref, sie_h, temp_h, press_h),
                              ("rho", "vfrac", "sie", "temp", "press")):
         assert_rel(got.cpu().numpy()[conv], want[conv], tol, f"{what} PTE state {nm}")
+        if bulk is not None:
+            from helpers import rel_err
+            frac = (rel_err(got.cpu().numpy()[conv], want[conv]) <= bulk[0]).mean()
+            assert frac >= bulk[1], f"{what} {nm}: only {frac:.4f} of values within {bulk[0]:g}"
     s = stats.cpu().numpy()
     assert s[0] == n and s[1] == conv.sum() and s[3] == n - conv.sum()
     hist_g = np.bincount(np.minimum(dg["niter"].astype(int), 31), minlength=32)
@@ -419,13 +423,20 @@ def test_pte_rhot_parity(pkg, ref, torch_cuda, which):
 @pytest.mark.parametrize("which", ["test_params", "default_params"])
 def test_pte_pt_parity(pkg, ref, torch_cuda, which):
     """PTESolverPT inverts every material with regula_falsi at xtol = ytol = 1e-8
-    (eos_gruneisen.hpp:521, eos_davis.hpp:488,574), so its states are only defined to ~1e-8:
-    tolerance 1e-6 here, identical `converged` flags."""
+    (eos_gruneisen.hpp:521, eos_davis.hpp:488,574), so every state update carries ~1e-8 of
+    root-finder noise and the FD Jacobian (derivative_eps 3e-6) amplifies it: the converged
+    state is only defined to the solver's own stopping tolerance.  With the tight tolerances
+    of test/test_pte.cpp the bar is 1e-6; with the library defaults (pte_rel_tolerance_p/e
+    1e-6, _t 1e-4, mixed_cell_models.hpp:51-58) it is 1e-4 on every cell AND 1e-7 on >= 99%
+    of the values.  `converged` flags must be identical in both."""
     n = 1 << 12
     vf = pkg.workloads.pte_vfracs(n)
-    params = pkg.closure.test_pte_params() if which == "test_params" else pkg.closure.MixParams()
-    _pte_compare(pkg, ref, torch_cuda, pkg._lib.PTE_PT, vf, params, tol=1e-6, what="PT/" + which,
-                 strict_flags=False)
+    if which == "test_params":
+        _pte_compare(pkg, ref, torch_cuda, pkg._lib.PTE_PT, vf, pkg.closure.test_pte_params(),
+                     tol=1e-6, what="PT/" + which, strict_flags=False)
+    else:
+        _pte_compare(pkg, ref, torch_cuda, pkg._lib.PTE_PT, vf, pkg.closure.MixParams(),
+                     tol=1e-4, what="PT/" + which, strict_flags=False, bulk=(1e-7, 0.99))
 
 
 def test_pte_properties_full_path(pkg, torch_cuda):
