@@ -205,3 +205,64 @@ def vinet_sp5_tables(nrho=256, nT=256, nE=256, rho_min=1.0, rho_max=30.0, T_min=
     s.mean_atomic_mass, s.mean_atomic_number = 63.546, 29.0
     raw.nodes = {"rho": rho_n, "T": T_n, "e": e_n}
     return raw
+
+
+# ---------------------------------------------------------------------------------------
+# Synthetic Helmholtz free-energy table (SURVEY 0 finding 4: data/helmholtz/helm_table.dat is
+# not in the checkout).  Same 4-block ASCII layout the reference reads
+# (eos_helmholtz.hpp:962-975): 101 (T) x 271 (rho) rows per block, T outer / rho inner;
+# block 1 = f fd ft fdd ftt fdt fddt fdtt fddtt, block 2 = dpdf dpdfd dpdft dpdfdt,
+# block 3 = ef efd eft efdt, block 4 = xf xfd xft xfdt.
+#
+# Physics: a non-degenerate ideal electron gas plus a cold (T-independent) Fermi-like term,
+# with every mixed derivative exact, so (de/dT)_rho > 0 everywhere and the reference's Newton
+# iteration on e(T) converges:
+#   f(d,T) = A T (L - 1) + B d^(2/3),  L = ln d - 1.5 ln T + C,  A = N_A k_B,  d = rho*Ye
+#   => p = d^2 f_d = A T d + (2/3) B d^(5/3),   e = f - T f_T = 1.5 A T + B d^(2/3)
+# ---------------------------------------------------------------------------------------
+HELM_NT, HELM_NRHO = 101, 271
+HELM_LT = (3.0, 13.0)
+HELM_LRHO = (-12.0, 15.0)
+_HELM_KB, _HELM_NA = 1.3806504e-16, 6.02214199e23
+_HELM_LN10 = 2.30258509299405e+00
+
+
+def synthetic_helm_arrays(B=1.0e13, C=-10.0):
+    """Returns the 21 node tables [NT][NRHO] in file-column order, grouped per block."""
+    A = _HELM_KB * _HELM_NA
+    dlr = (HELM_LRHO[1] - HELM_LRHO[0]) / float(HELM_NRHO - 1)
+    dlt = (HELM_LT[1] - HELM_LT[0]) / float(HELM_NT - 1)
+    # the node coordinates the reference itself uses: pow10(range.x(i)) = exp(ln10 * x)
+    d = np.exp(_HELM_LN10 * (np.arange(HELM_NRHO) * dlr + HELM_LRHO[0]))[None, :]
+    T = np.exp(_HELM_LN10 * (np.arange(HELM_NT) * dlt + HELM_LT[0]))[:, None]
+    one = np.ones((HELM_NT, HELM_NRHO))
+    L = np.log(d) - 1.5 * np.log(T) + C
+    d23 = d ** (2.0 / 3.0)
+    f = A * T * (L - 1.0) + B * d23
+    fd = A * T / d + (2.0 / 3.0) * B * d23 / d
+    ft = A * (L - 2.5) * one
+    fdd = -A * T / d**2 - (2.0 / 9.0) * B * d23 / d**2
+    ftt = -1.5 * A / T * one
+    fdt = A / d * one
+    fddt = -A / d**2 * one
+    fdtt = 0.0 * one
+    fddtt = 0.0 * one
+    blk1 = [f, fd, ft, fdd, ftt, fdt, fddt, fdtt, fddtt]
+    dpdf = A * T + (10.0 / 9.0) * B * d23
+    dpdfd = (20.0 / 27.0) * B * d23 / d * one
+    dpdft = A * one
+    dpdfdt = 0.0 * one
+    blk2 = [dpdf, dpdfd, dpdft, dpdfdt]
+    blk3 = [L * one, 1.0 / d * one, -1.5 / T * one, 0.0 * one]
+    blk4 = [_HELM_NA * d * one, _HELM_NA * one, 0.0 * one, 0.0 * one]
+    return [blk1, blk2, blk3, blk4]
+
+
+def write_synthetic_helm_table(path, B=1.0e13, C=-10.0):
+    """Write the synthetic table as text with 17 significant digits (round-trips exactly)."""
+    with open(path, "w") as fh:
+        for blk in synthetic_helm_arrays(B, C):
+            cols = np.stack([np.broadcast_to(a, (HELM_NT, HELM_NRHO)).reshape(-1) for a in blk],
+                            axis=1)
+            np.savetxt(fh, cols, fmt="%.17e")
+    return path

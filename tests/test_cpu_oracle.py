@@ -239,3 +239,28 @@ def test_ref_spiner_classes_load_and_invert(pkg, ref):
     assert np.median(np.abs(e / e_exact - 1)) < 1e-3
     T3 = rs.eval(L.T_FROM_RHO_E, rho, e, np.full((n, 1), np.nan))
     assert np.median(np.abs(T3 / T - 1)) < 5e-2
+
+
+def test_ref_helmholtz_on_synthetic_table(pkg, ref, tmp_path):
+    """The reference's own Helmholtz class loads the synthetic table (the shipped
+    helm_table.dat is absent from the checkout) and reproduces the closed forms the table was
+    generated from: with radiation and Coulomb off, e = 1.5 A T (Ye + Ytot) + Ye B d^(2/3) and
+    P = A T rho (Ye + Ytot) + (2/3) B d^(5/3) up to the biquintic interpolation error."""
+    L, tq = pkg._lib, pkg.thermalqs
+    path = pkg.tablegen.write_synthetic_helm_table(str(tmp_path / "helm.dat"))
+    eos = ref.Helmholtz(path, L.HelmOptions(0, 1, 0, 1, 1, 1, 1))
+    assert eos.nlambda() == 3
+    n = 4096
+    rho, T = pkg.workloads.helm_inputs(n)
+    abar, zbar = 4.0, 2.0
+    lam = np.tile([abar, zbar, -1.0], (n, 1))
+    e, P, cv, b = (np.zeros(n) for _ in range(4))
+    eos.fill(rho.copy(), T.copy(), e, P, cv, b, tq.specific_internal_energy | tq.pressure
+             | tq.specific_heat | tq.bulk_modulus, lam)
+    A, B = 1.3806504e-16 * 6.02214199e23, 1.0e13
+    ye, ytot = zbar / abar, 1.0 / abar
+    d = rho * ye
+    assert_rel(e, 1.5 * A * T * (ye + ytot) + ye * B * d ** (2.0 / 3.0), 1e-4, "e closed form")
+    assert_rel(P, A * T * rho * (ye + ytot) + (2.0 / 3.0) * B * d ** (5.0 / 3.0), 1e-4, "P")
+    assert (cv > 0).all() and (b > 0).all()
+    assert np.array_equal(lam[:, 2], np.log10(T))  # lT cache written by the (rho,T) mode
