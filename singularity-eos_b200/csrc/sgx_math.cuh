@@ -246,6 +246,66 @@ SGX_HD double interp2d(const double *__restrict__ a, const int n1, const AxisPos
 }
 
 // ---------------------------------------------------------------------------------------
+// Cell-major ("packed") 2-D tables for the device hot path.  At create time every 2-D table
+// A[n2][n1] is repacked into one 32-byte record per table cell (j, i), j < n2-1, i < n1-1:
+//   {A(j,i), A(j,i+1), A(j+1,i), A(j+1,i+1)}
+// so the four corners of DataBox::interpToReal(x2, x1) are ONE aligned sector fetched by ONE
+// 256-bit load (LDG.E.256) instead of four gathers over two cache lines.  ncu on the
+// node-major layout showed the L1TEX wavefront path, not HBM, bounding the lookup kernels
+// (profiles/r1a_lookup_details.txt).  Values and evaluation order are unchanged
+// (databox.hpp:471-474), so results are bit-identical to the node-major form.
+// The grid's weights() clamps ix to [0, n-2] within a patch, so (ix2, ix1) is always a cell.
+// ---------------------------------------------------------------------------------------
+struct Cell4 {
+  double c00, c01, c10, c11;
+};
+SGX_HD Cell4 ld_cell(const double *__restrict__ cells, const int n1, const int ix2,
+                     const int ix1) {
+  const double *p = cells + ((size_t)ix2 * (size_t)(n1 - 1) + (size_t)ix1) * 4;
+  Cell4 c;
+#ifdef __CUDA_ARCH__
+  asm("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];"
+      : "=d"(c.c00), "=d"(c.c01), "=d"(c.c10), "=d"(c.c11)
+      : "l"(p));
+#else
+  c.c00 = p[0];
+  c.c01 = p[1];
+  c.c10 = p[2];
+  c.c11 = p[3];
+#endif
+  return c;
+}
+SGX_HD double blend_cell(const Cell4 &c, const double w20, const double w21, const double w10,
+                         const double w11) {
+  return (w20 * (w10 * c.c00 + w11 * c.c01) + w21 * (w10 * c.c10 + w11 * c.c11));
+}
+SGX_HD double blend2c(const double *__restrict__ cells, const int n1, const int ix2,
+                      const double w20, const double w21, const int ix1, const double w10,
+                      const double w11) {
+  return blend_cell(ld_cell(cells, n1, ix2, ix1), w20, w21, w10, w11);
+}
+SGX_HD double interp2c(const double *__restrict__ cells, const int n1, const AxisPos &p2,
+                       const AxisPos &p1) {
+  return blend2c(cells, n1, p2.ix, p2.w0, p2.w1, p1.ix, p1.w0, p1.w1);
+}
+SGX_HD double interp2c(const double *__restrict__ cells, const Grid1D &g2, const Grid1D &g1,
+                       const int n1, const double x2, const double x1) {
+  return interp2c(cells, n1, AxisPos(g2, x2), AxisPos(g1, x1));
+}
+// host-side repack: node-major A[n2][n1] -> cells[(n2-1)*(n1-1)][4]
+inline void pack_cells(const double *a, const int n2, const int n1, double *cells) {
+  for (int j = 0; j < n2 - 1; ++j)
+    for (int i = 0; i < n1 - 1; ++i) {
+      double *c = cells + ((size_t)j * (n1 - 1) + i) * 4;
+      const double *r0 = a + (size_t)j * n1 + i;
+      c[0] = r0[0];
+      c[1] = r0[1];
+      c[2] = r0[n1];
+      c[3] = r0[n1 + 1];
+    }
+}
+
+// ---------------------------------------------------------------------------------------
 // Root finding
 // ---------------------------------------------------------------------------------------
 namespace root {

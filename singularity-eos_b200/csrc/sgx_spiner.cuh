@@ -21,7 +21,7 @@ enum TableStatus { OnTable = 0, OffBottom = 1, OffTop = 2 };
 struct SpinerRhoT {
   Grid1D gRho, gT; // gT = range(0) (fastest), gRho = range(1)
   int numRho, numT;
-  // (lRho, lT) tables
+  // (lRho, lT) tables, CELL-MAJOR packed (sgx_math.cuh: Cell4 / interp2c)
   const double *P, *sie, *bMod, *dPdRho, *dPdE, *dTdRho, *dTdE, *dEdRho, *dEdT;
   // 1-D over lRho
   const double *PMax, *sielTMax, *dEdTMax, *gm1Max, *lTColdCrit;
@@ -77,7 +77,7 @@ struct SpinerRhoT {
       const double e0 = interp1d(sielTMax, pr);
       return e0 + Cv * (T - TMax);
     }
-    return interp2d(sie, numT, pr, AxisPos(gT, lT));
+    return interp2c(sie, numT, pr, AxisPos(gT, lT));
   }
   SGX_D double PFromRholRhoTlT(const double rho, const AxisPos &pr, const double T,
                                const double lT, const TableStatus w) const {
@@ -89,7 +89,7 @@ struct SpinerRhoT {
       const double e = e0 + Cv * (T - TMax);
       return gm1 * rho * e;
     }
-    return interp2d(P, numT, pr, AxisPos(gT, lT));
+    return interp2c(P, numT, pr, AxisPos(gT, lT));
   }
   SGX_D double CvFromlRholT(const AxisPos &pr, const double lT, const TableStatus w) const {
     double Cv;
@@ -98,7 +98,7 @@ struct SpinerRhoT {
     } else if (w == OffTop) {
       Cv = interp1d(dEdTMax, pr);
     } else {
-      Cv = interp2d(dEdT, numT, pr, AxisPos(gT, lT));
+      Cv = interp2c(dEdT, numT, pr, AxisPos(gT, lT));
     }
     return Cv > kEps ? Cv : kEps;
   }
@@ -114,7 +114,7 @@ struct SpinerRhoT {
       const double e = e0 + Cv * (T - TMax);
       bm = (gm1 + 1) * gm1 * rho * e;
     } else {
-      bm = interp2d(bMod, numT, pr, AxisPos(gT, lT));
+      bm = interp2c(bMod, numT, pr, AxisPos(gT, lT));
     }
     return bm > kEps ? bm : kEps;
   }
@@ -150,7 +150,7 @@ struct SpinerRhoT {
         int ix1;
         double w10, w11;
         g1.weights(x, ix1, w10, w11);
-        return blend2d(tab, n1, pr.ix, pr.w0, pr.w1, ix1, w10, w11);
+        return blend2c(tab, n1, pr.ix, pr.w0, pr.w1, ix1, w10, w11);
       };
       status = root::regula_falsi(sieFunc, sie_in, lTGuess, lTMin, lTMax, ROOT_THRESH,
                                   ROOT_THRESH, lT, niter);
@@ -189,7 +189,7 @@ struct SpinerRhoT {
         int ix1;
         double w10, w11;
         g1.weights(x, ix1, w10, w11);
-        return blend2d(tab, n1, pr.ix, pr.w0, pr.w1, ix1, w10, w11);
+        return blend2c(tab, n1, pr.ix, pr.w0, pr.w1, ix1, w10, w11);
       };
       const int status = root::regula_falsi(PFunc, press, lTGuess, lTMin, lTMax, ROOT_THRESH,
                                             ROOT_THRESH, lT);
@@ -235,7 +235,7 @@ struct SpinerRhoT {
       const double *tab = P;
       const int n1 = numT;
       auto PFunc = [&](const double x) {
-        return interp2d(tab, n1, AxisPos(g2, x), pt);
+        return interp2c(tab, n1, AxisPos(g2, x), pt);
       };
       status = root::regula_falsi(PFunc, Pin, lRhoGuess, rhopmin, lRhoMax, ROOT_THRESH,
                                   ROOT_THRESH, lRho);
@@ -278,7 +278,7 @@ struct SpinerRhoT {
       const double gm1 = interp1d(gm1Max, pr);
       return gm1 * rho * sie_in;
     }
-    return interp2d(P, numT, pr, AxisPos(gT, lT));
+    return interp2c(P, numT, pr, AxisPos(gT, lT));
   }
   SGX_D double cv_from_rho_T(const double rho, const double T, double *lambda) const {
     double lRho, lT;
@@ -297,7 +297,7 @@ struct SpinerRhoT {
     } else if (w == OffTop) {
       Cv = interp1d(dEdTMax, pr);
     } else {
-      Cv = interp2d(dEdT, numT, pr, AxisPos(gT, lT));
+      Cv = interp2c(dEdT, numT, pr, AxisPos(gT, lT));
     }
     return Cv > kEps ? Cv : kEps;
   }
@@ -317,7 +317,7 @@ struct SpinerRhoT {
       const double gm1 = interp1d(gm1Max, pr);
       return (gm1 + 1) * gm1 * rho * sie_in;
     }
-    return interp2d(bMod, numT, pr, AxisPos(gT, lT));
+    return interp2c(bMod, numT, pr, AxisPos(gT, lT));
   }
   SGX_D double gamma_from_rho_T(const double rho, const double T, double *lambda) const {
     double lRho, lT;
@@ -329,7 +329,7 @@ struct SpinerRhoT {
       return ratio(fabs(dpde), fabs(rho));
     }
     if (w == OffTop) return interp1d(gm1Max, pr);
-    const double dpde = interp2d(dPdE, numT, pr, AxisPos(gT, lT));
+    const double dpde = interp2c(dPdE, numT, pr, AxisPos(gT, lT));
     return ratio(fabs(dpde), fabs(rho));
   }
   SGX_D double gamma_from_rho_e(const double rho, const double sie_in, double *lambda) const {
@@ -342,7 +342,7 @@ struct SpinerRhoT {
       return ratio(fabs(dpde), fabs(rho));
     }
     if (w == OffTop) return interp1d(gm1Max, pr);
-    const double dpde = interp2d(dPdE, numT, pr, AxisPos(gT, lT));
+    const double dpde = interp2c(dPdE, numT, pr, AxisPos(gT, lT));
     return ratio(fabs(dpde), fabs(rho));
   }
   // FillEos (eos_spiner_rho_temp.hpp:1043-1093)
@@ -408,9 +408,9 @@ struct SpinerRhoT {
 struct SpinerRhoSie {
   Grid1D gRho, gT, gE;
   int numRho, numT, numE;
-  // (lRho, lT)
+  // (lRho, lT), CELL-MAJOR packed (sgx_math.cuh: Cell4 / interp2c)
   const double *sie, *P, *bMod, *dPdRho, *dPdE, *dTdRho, *dTdE, *dEdRho;
-  // (lRho, lE)
+  // (lRho, lE), cell-major packed
   const double *T_re, *P_re, *bMod_re, *dPdRho_re, *dPdE_re, *dTdRho_re, *dTdE_re, *dEdRho_re;
   // 1-D over lRho
   const double *PCold, *sieCold, *bModCold, *dPdRhoCold;
@@ -430,14 +430,14 @@ struct SpinerRhoSie {
     const double lRho = to_log(rho, lRhoOffset);
     const double lT = to_log(T, lTOffset);
     if (lambda) lambda[0] = lRho;
-    return interp2d(db, gRho, gT, numT, lRho, lT);
+    return interp2c(db, gRho, gT, numT, lRho, lT);
   }
   SGX_D double interpRhoSie(const double rho, const double sie_in, const double *db,
                             double *lambda) const {
     const double lRho = to_log(rho, lRhoOffset);
     const double lE = to_log(sie_in, lEOffset);
     if (lambda) lambda[0] = lRho;
-    return interp2d(db, gRho, gE, numE, lRho, lE);
+    return interp2c(db, gRho, gE, numE, lRho, lE);
   }
   SGX_D double T_from_rho_e(double rho, double e, double *lambda) const {
     return interpRhoSie(rho, e, T_re, lambda);
@@ -471,7 +471,7 @@ struct SpinerRhoSie {
   SGX_D double gamma_from_rho_e(double rho, double e, double *) const {
     const double lRho = to_log(rho, lRhoOffset);
     const double lE = to_log(e, lEOffset);
-    const double dpde = interp2d(dPdE_re, gRho, gE, numE, lRho, lE);
+    const double dpde = interp2c(dPdE_re, gRho, gE, numE, lRho, lE);
     return dpde / rho;
   }
   // lRhoFromPlT_ (eos_spiner_rho_sie.hpp:941-986)
@@ -494,7 +494,7 @@ struct SpinerRhoSie {
       const double *tab = P;
       const int n1 = numT;
       const Grid1D &g2 = gRho;
-      auto PFunc = [&](const double x) { return interp2d(tab, n1, AxisPos(g2, x), pt); };
+      auto PFunc = [&](const double x) { return interp2c(tab, n1, AxisPos(g2, x), pt); };
       const int status =
           root::regula_falsi(PFunc, Pin, lRhoGuess, rhopmin, lRhoMax, kEps, kEps, lRho);
       if (status != root::SUCCESS) lRho = reproducible ? lRhoMax : lRhoGuess;
@@ -525,18 +525,18 @@ struct SpinerRhoSie {
     if (output & TQ_TEMPERATURE) {
       lE = to_log(energy, lEOffset);
       const AxisPos pe(gE, lE);
-      temp = interp2d(T_re, numE, pr, pe);
-      if (output & TQ_PRESSURE) press = interp2d(P_re, numE, pr, pe);
-      if (output & TQ_CV) cv = 1. / interp2d(dTdE_re, numE, pr, pe);
-      if (output & TQ_BMOD) bmod = interp2d(bMod_re, numE, pr, pe);
+      temp = interp2c(T_re, numE, pr, pe);
+      if (output & TQ_PRESSURE) press = interp2c(P_re, numE, pr, pe);
+      if (output & TQ_CV) cv = 1. / interp2c(dTdE_re, numE, pr, pe);
+      if (output & TQ_BMOD) bmod = interp2c(bMod_re, numE, pr, pe);
     }
     if (output & TQ_SIE) {
       lT = to_log(temp, lTOffset);
       const AxisPos pt(gT, lT);
-      energy = interp2d(sie, numT, pr, pt);
-      if (output & TQ_PRESSURE) press = interp2d(P, numT, pr, pt);
-      if (output & TQ_CV) cv = 1. / interp2d(dTdE, numT, pr, pt);
-      if (output & TQ_BMOD) bmod = interp2d(bMod, numT, pr, pt);
+      energy = interp2c(sie, numT, pr, pt);
+      if (output & TQ_PRESSURE) press = interp2c(P, numT, pr, pt);
+      if (output & TQ_CV) cv = 1. / interp2c(dTdE, numT, pr, pt);
+      if (output & TQ_BMOD) bmod = interp2c(bMod, numT, pr, pt);
     }
     return true;
   }

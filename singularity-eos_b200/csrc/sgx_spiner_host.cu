@@ -20,6 +20,13 @@
 namespace sgx {
 
 namespace {
+// Append the cell-major copy "<name>#cells" of the (already fixed-up) node-major table
+// `name` [n2][n1]; kernels read the packed copy, sgx_eos_get_table the node-major one.
+void add_packed(TableStore &ts, const std::string &name, const int n2, const int n1) {
+  const size_t ncell = (size_t)(n2 - 1) * (size_t)(n1 - 1);
+  const size_t off = ts.add(name + "#cells", nullptr, ncell * 4);
+  pack_cells(ts.h(name), n2, n1, ts.host.data() + off);
+}
 
 constexpr double ROOM_TEMPERATURE = 293; // base/constants.hpp:42
 
@@ -280,17 +287,20 @@ int build_spiner_rhot(const sgx_sp5_tables *raw, int reproducible, int pmin_vapo
         s.lTMax > s.lTMin && s.TMax > 0))
     return fail(SGX_ERR_INVALID, "SpinerEOSDependsRhoT::CheckParams failed");
 
+  static const char *k2d[] = {"P", "sie", "bMod", "dPdRho", "dPdE", "dTdRho", "dTdE", "dEdRho",
+                              "dEdT"};
+  for (const char *nm : k2d) add_packed(ts, nm, numRho, numT);
   int rc = upload_tables(e);
   if (rc) return rc;
-  s.P = ts.d("P");
-  s.sie = ts.d("sie");
-  s.bMod = ts.d("bMod");
-  s.dPdRho = ts.d("dPdRho");
-  s.dPdE = ts.d("dPdE");
-  s.dTdRho = ts.d("dTdRho");
-  s.dTdE = ts.d("dTdE");
-  s.dEdRho = ts.d("dEdRho");
-  s.dEdT = ts.d("dEdT");
+  s.P = ts.d("P#cells");
+  s.sie = ts.d("sie#cells");
+  s.bMod = ts.d("bMod#cells");
+  s.dPdRho = ts.d("dPdRho#cells");
+  s.dPdE = ts.d("dPdE#cells");
+  s.dTdRho = ts.d("dTdRho#cells");
+  s.dTdE = ts.d("dTdE#cells");
+  s.dEdRho = ts.d("dEdRho#cells");
+  s.dEdT = ts.d("dEdT#cells");
   s.PMax = ts.d("PMax");
   s.sielTMax = ts.d("sielTMax");
   s.dEdTMax = ts.d("dEdTMax");
@@ -441,24 +451,29 @@ int build_spiner_rhosie(const sgx_sp5_tables *raw, int reproducible, int pmin_va
   sc["meanAtomicMass"] = raw->mean_atomic_mass;
   sc["meanAtomicNumber"] = raw->mean_atomic_number;
 
+  static const char *k2dT[] = {"sie", "P", "bMod", "dPdRho", "dPdE", "dTdRho", "dTdE", "dEdRho"};
+  static const char *k2dE[] = {"T_re", "P_re", "bMod_re", "dPdRho_re", "dPdE_re", "dTdRho_re",
+                               "dTdE_re", "dEdRho_re"};
+  for (const char *nm : k2dT) add_packed(ts, nm, numRho, numT);
+  for (const char *nm : k2dE) add_packed(ts, nm, numRho, numE);
   int rc = upload_tables(e);
   if (rc) return rc;
-  s.sie = ts.d("sie");
-  s.P = ts.d("P");
-  s.bMod = ts.d("bMod");
-  s.dPdRho = ts.d("dPdRho");
-  s.dPdE = ts.d("dPdE");
-  s.dTdRho = ts.d("dTdRho");
-  s.dTdE = ts.d("dTdE");
-  s.dEdRho = ts.d("dEdRho");
-  s.T_re = ts.d("T_re");
-  s.P_re = ts.d("P_re");
-  s.bMod_re = ts.d("bMod_re");
-  s.dPdRho_re = ts.d("dPdRho_re");
-  s.dPdE_re = ts.d("dPdE_re");
-  s.dTdRho_re = ts.d("dTdRho_re");
-  s.dTdE_re = ts.d("dTdE_re");
-  s.dEdRho_re = ts.d("dEdRho_re");
+  s.sie = ts.d("sie#cells");
+  s.P = ts.d("P#cells");
+  s.bMod = ts.d("bMod#cells");
+  s.dPdRho = ts.d("dPdRho#cells");
+  s.dPdE = ts.d("dPdE#cells");
+  s.dTdRho = ts.d("dTdRho#cells");
+  s.dTdE = ts.d("dTdE#cells");
+  s.dEdRho = ts.d("dEdRho#cells");
+  s.T_re = ts.d("T_re#cells");
+  s.P_re = ts.d("P_re#cells");
+  s.bMod_re = ts.d("bMod_re#cells");
+  s.dPdRho_re = ts.d("dPdRho_re#cells");
+  s.dPdE_re = ts.d("dPdE_re#cells");
+  s.dTdRho_re = ts.d("dTdRho_re#cells");
+  s.dTdE_re = ts.d("dTdE_re#cells");
+  s.dEdRho_re = ts.d("dEdRho_re#cells");
   s.PCold = ts.d("PCold");
   s.sieCold = ts.d("sieCold");
   s.bModCold = ts.d("bModCold");
