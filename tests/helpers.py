@@ -44,3 +44,28 @@ def dev(t_np):
     import torch
 
     return torch.from_numpy(np.ascontiguousarray(t_np)).cuda()
+
+
+def build_cpp_shim_test():
+    """Compile tests/cpp/test_shim.cpp (the C++ host shim over the C ABI) with g++; returns the
+    binary path and the environment it needs."""
+    import os
+    import subprocess
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    src = os.path.join(root, "tests", "cpp", "test_shim.cpp")
+    out_dir = os.path.join(root, "tests", "cpp", "_build")
+    os.makedirs(out_dir, exist_ok=True)
+    exe = os.path.join(out_dir, "test_shim")
+    libdir = os.path.join(root, "singularity-eos_b200", "lib")
+    cuda = os.environ.get("CUDA_HOME", "/usr/local/cuda")
+    deps = [src, os.path.join(root, "include", "sgx_b200.h"),
+            os.path.join(root, "include", "sgx", "eos.hpp"),
+            os.path.join(root, "include", "sgx", "closure.hpp")]
+    if not os.path.exists(exe) or any(os.path.getmtime(d) > os.path.getmtime(exe) for d in deps):
+        subprocess.check_call(
+            ["/usr/bin/g++", "-std=c++17", "-O1", "-Wall", "-I" + os.path.join(root, "include"),
+             "-I" + os.path.join(cuda, "include"), src, "-o", exe, "-L" + libdir, "-lsgx_b200",
+             "-L" + os.path.join(cuda, "lib64"), "-lcudart", "-Wl,-rpath," + libdir,
+             "-Wl,-rpath," + os.path.join(cuda, "lib64")])
+    return exe

@@ -264,3 +264,17 @@ def test_ref_helmholtz_on_synthetic_table(pkg, ref, tmp_path):
     assert_rel(P, A * T * rho * (ye + ytot) + (2.0 / 3.0) * B * d ** (5.0 / 3.0), 1e-4, "P")
     assert (cv > 0).all() and (b > 0).all()
     assert np.array_equal(lam[:, 2], np.log10(T))  # lT cache written by the (rho,T) mode
+
+
+def test_cpp_shim_compiles_and_links(pkg):
+    """include/sgx/*.hpp (the C++ host side mirroring the reference's class and method names)
+    compiles with g++ -Wall and links against libsgx_b200.so; no device is touched."""
+    import subprocess
+
+    from helpers import build_cpp_shim_test
+
+    pkg._lib.load()
+    exe = build_cpp_shim_test()
+    out = subprocess.run([exe, "--link-only"], capture_output=True, text=True, timeout=60)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert out.stdout.strip() == "abi 1"

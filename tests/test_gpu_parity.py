@@ -679,3 +679,20 @@ def test_helmholtz_vector_methods(pkg, ref, torch_cuda, helm_table):
     # a null lambda is an error (SafeMustGet aborts in the reference), not a silent default
     with pytest.raises(pkg.SgxError):
         g._eval(L.P_FROM_RHO_T, rho_d, T_d, out, n, None)
+
+
+# ------------------------------------------------------------------------------------------
+def test_cpp_host_shim(pkg, torch_cuda):
+    """The C++ host side (include/sgx/eos.hpp, closure.hpp): IdealGas golden values of
+    test/test_eos_vector.cpp through the raw-pointer vector overloads, FillEos, the
+    throw-on-error contract, and a 2000-cell PTESolverRhoT batch with the acceptance checks of
+    test/test_pte.cpp:204-262 -- all from a plain g++ program linked against the C ABI."""
+    import subprocess
+
+    from helpers import build_cpp_shim_test
+
+    exe = build_cpp_shim_test()
+    out = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    print(out.stdout)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert out.stdout.strip().endswith("ok")
