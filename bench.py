@@ -247,6 +247,42 @@ def run_ours(args):
         del sie
     del lam
 
+    # ---- config 4: Helmholtz FillEos on the synthetic table (the shipped one is absent) ----
+    if not args.quick:
+        import tempfile
+        tq = pkg.thermalqs
+        hpath = os.path.join(tempfile.gettempdir(), f"sgx_helm_synthetic_{os.getpid()}.dat")
+        pkg.tablegen.write_synthetic_helm_table(hpath)
+        nh = min(n, 1 << 25)
+        h_rho, h_T = W.helm_inputs(nh, rank * nh, xp=torch, device=dev)
+        h_e, h_P, h_cv, h_b = (torch.empty_like(h_rho) for _ in range(4))
+        comp = torch.tensor([[1., 1.], [4., 2.], [12., 6.], [16., 8.], [56., 26.]],
+                            dtype=torch.float64, device=dev)
+        idx = torch.arange(nh, device=dev) % 5
+        lam3 = torch.cat([comp[idx], torch.full((nh, 1), -1.0, dtype=torch.float64, device=dev)],
+                         dim=1).contiguous()
+        helm = pkg.Helmholtz(hpath)
+        mode_i = tq.specific_internal_energy | tq.pressure | tq.specific_heat | tq.bulk_modulus
+        kh = max(3, K // 4)
+        lookup("helmholtz_FillEos_rhoT(e,P,cv,bmod)",
+               lambda: helm.FillEos(h_rho, h_T, h_e, h_P, h_cv, h_b, nh, mode_i, lam3), 72,
+               cells=nh, steps=kh)
+        # mode (ii): (rho,e) -> T,P,cv,bmod, Newton on e(T); Coulomb off (the reference test's
+        # variant: with Coulomb on e(T) is non-monotone on ~6 % of this box), no lT slot
+        helm2 = pkg.Helmholtz(hpath, coul=False, lambda_has_lT_slot=False)
+        helm2.FillEos(h_rho, h_T, h_e, h_P, h_cv, h_b, nh, mode_i, lam3[:, :2].contiguous())
+        lam2 = lam3[:, :2].contiguous()
+        h_T2 = torch.empty_like(h_T)
+        mode_ii = tq.temperature | tq.pressure | tq.specific_heat | tq.bulk_modulus
+        lookup("helmholtz_FillEos_rhoe(T,P,cv,bmod)_newton_coul_off",
+               lambda: helm2.FillEos(h_rho, h_T2, h_e, h_P, h_cv, h_b, nh, mode_ii, lam2), 64,
+               cells=nh, steps=kh)
+        del h_rho, h_T, h_e, h_P, h_cv, h_b, lam3, lam2, h_T2, helm, helm2
+        try:
+            os.remove(hpath)
+        except OSError:
+            pass
+
     # ---- config 5: PTE RhoT -------------------------------------------------------------
     if not args.quick:
         npte = (1 << 27) if args.pte_full else args.pte_cells

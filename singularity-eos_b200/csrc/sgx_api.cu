@@ -13,6 +13,7 @@
 //    persisting access-policy window set at create time).
 #include <cstring>
 #include <new>
+#include <type_traits>
 
 #include "sgx_internal.hpp"
 
@@ -89,6 +90,18 @@ SGX_D double call_method(const EOS &eos, const double a, const double b, double 
   return 0.0;
 }
 
+// Streaming accesses on the cell arrays: read-only, no L1 allocation on loads; evict-first
+// (.cs) on stores so the output stream does not push the tables out of L2.
+struct D4 {
+  double x, y, z, w;
+};
+SGX_D D4 ld_stream4(const double *p) { // 256-bit, needs 32-byte alignment
+  D4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f64 {%0,%1,%2,%3}, [%4];"
+               : "=d"(v.x), "=d"(v.y), "=d"(v.z), "=d"(v.w)
+               : "l"(p));
+  return v;
+}
 SGX_D double2 ld_stream2(const double *p) {
   double2 v;
   asm volatile("ld.global.nc.L1::no_allocate.v2.f64 {%0,%1}, [%2];"
@@ -101,6 +114,12 @@ SGX_D double ld_stream1(const double *p) {
   asm volatile("ld.global.nc.L1::no_allocate.f64 %0, [%1];" : "=d"(v) : "l"(p));
   return v;
 }
+SGX_D void st_stream4(double *p, const double x, const double y, const double z,
+                      const double w) {
+  asm volatile("st.global.cs.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(x), "d"(y), "d"(z),
+               "d"(w)
+               : "memory");
+}
 SGX_D void st_stream2(double *p, const double x, const double y) {
   asm volatile("st.global.cs.v2.f64 [%0], {%1,%2};" ::"l"(p), "d"(x), "d"(y) : "memory");
 }
@@ -108,36 +127,177 @@ SGX_D void st_stream1(double *p, const double x) {
   asm volatile("st.global.cs.f64 [%0], %1;" ::"l"(p), "d"(x) : "memory");
 }
 
+// Does METHOD read the cell's lambda row before (possibly) writing it?  Only then is the row
+// loaded; otherwise it is produced in registers and stored once.
+//  * SpinerRhoT *_FROM_RHO_E read the cached lT as the root-find guess
+//    (eos_spiner_rho_temp.hpp:1218-1223);
+//  * SpinerRhoSie GruneisenParamFromDensityInternalEnergy does not write lambda at all
+//    (eos_spiner_rho_sie.hpp:757-761), so the row must round-trip unchanged.
+template <int METHOD, class EOS>
+struct LambdaTraits {
+  static constexpr bool from_e = METHOD == SGX_T_FROM_RHO_E || METHOD == SGX_P_FROM_RHO_E ||
+                                 METHOD == SGX_CV_FROM_RHO_E || METHOD == SGX_BMOD_FROM_RHO_E ||
+                                 METHOD == SGX_GAMMA_FROM_RHO_E;
+  static constexpr bool load = (std::is_same<EOS, SpinerRhoT>::value && from_e) ||
+                               (std::is_same<EOS, SpinerRhoSie>::value &&
+                                METHOD == SGX_GAMMA_FROM_RHO_E);
+};
+
+// Which (EOS, METHOD) pairs have the two-phase prep()/finish() form (sgx_spiner.cuh)
+template <class EOS, int METHOD>
+struct TwoPhase : std::false_type {};
+template <int METHOD>
+struct TwoPhase<SpinerRhoT, METHOD>
+    : std::integral_constant<bool, SpinerRhoT::two_phase<METHOD>()> {};
+template <int METHOD>
+struct TwoPhase<SpinerRhoSie, METHOD>
+    : std::integral_constant<bool, SpinerRhoSie::two_phase<METHOD>()> {};
+
+// One cell with its lambda row held in registers: NL = EOS::nlambda doubles.
+template <int METHOD, class EOS, int NL>
+SGX_D double eval_cell(const EOS &eos, const double a, const double b, double (&lam)[NL > 0 ? NL : 1],
+                       const bool has_lambda) {
+  return call_method<METHOD>(eos, a, b, (NL > 0 && has_lambda) ? lam : nullptr);
+}
+
 // OUT[i] = eos.METHOD(IN1[i], IN2[i], lambda[i])   (eos_base.hpp:174-183)
-// VEC: arrays are 16-byte aligned -> two cells per thread per trip.
-template <int METHOD, class EOS, bool VEC>
-__global__ void __launch_bounds__(256)
+// VW cells per thread per trip (4: arrays 32-byte aligned -> 256-bit accesses; 2: 16-byte;
+// 1: anything).  The VW evaluations of a trip are independent, so their table gathers overlap
+// (memory-level parallelism: ncu showed this kernel stalled on `long_scoreboard`).
+// PACKED: lambda_stride == EOS::nlambda, rows are contiguous and stored with vector stores.
+// Per-family tuning, each value measured on B200 at 2^24 cells (profiles/r1_tuning.md):
+//  * SpinerRhoT direct lookups: two-phase gathers + input prefetch keep 4 cell records and the
+//    next trip's inputs live -> 128 registers, 2 resident blocks (0.150 ms; capped at 80
+//    registers it spills and takes 0.268 ms);
+//  * SpinerRhoT root finds are issue-bound and divergent: they want warps, not registers ->
+//    4 blocks (<= 64 regs), 2 cells/thread, no prefetch (2.50 ms vs 3.47 ms at 2 blocks);
+//  * SpinerRhoSie lookups are branch-free, so the compiler hoists the 4 gathers by itself:
+//    one-phase, no prefetch, 48 registers, 4 blocks (0.131 ms vs 0.146 ms two-phase);
+//  * analytic models: light, 4 blocks, prefetch on.
+template <int METHOD, class EOS>
+constexpr bool is_iterative() {
+  return std::is_same<EOS, SpinerRhoT>::value && LambdaTraits<METHOD, EOS>::from_e;
+}
+template <int METHOD, class EOS>
+constexpr bool use_two_phase() {
+  return std::is_same<EOS, SpinerRhoT>::value && TwoPhase<EOS, METHOD>::value;
+}
+template <int METHOD, class EOS>
+constexpr bool use_prefetch() {
+  return !is_iterative<METHOD, EOS>() && !std::is_same<EOS, SpinerRhoSie>::value;
+}
+template <int METHOD, class EOS>
+constexpr int min_blocks() {
+  return use_two_phase<METHOD, EOS>() ? 2 : 4;
+}
+
+template <int METHOD, class EOS, int VW, bool PACKED>
+__global__ void __launch_bounds__(256, min_blocks<METHOD, EOS>())
     eval_kernel(const __grid_constant__ EOS eos, const double *__restrict__ in1,
                 const double *__restrict__ in2, double *__restrict__ out, const int64_t n,
                 double *__restrict__ lambda, const int lstride) {
+  constexpr int NL = EOS::nlambda;
+  constexpr int NLA = NL > 0 ? NL : 1;
+  constexpr bool kLoad = LambdaTraits<METHOD, EOS>::load;
+  // root-finding methods are compute-bound and register-hungry: no input prefetch for them
+  constexpr bool kPrefetch = use_prefetch<METHOD, EOS>();
   const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int64_t nthr = (int64_t)gridDim.x * blockDim.x;
-  if constexpr (VEC) {
-    const int64_t npair = n >> 1;
-    for (int64_t p = tid; p < npair; p += nthr) {
-      const int64_t i = p << 1;
-      const double2 a = ld_stream2(in1 + i);
-      const double2 b = ld_stream2(in2 + i);
-      double *l0 = lambda ? lambda + i * lstride : nullptr;
-      double *l1 = lambda ? l0 + lstride : nullptr;
-      const double r0 = call_method<METHOD>(eos, a.x, b.x, l0);
-      const double r1 = call_method<METHOD>(eos, a.y, b.y, l1);
-      st_stream2(out + i, r0, r1);
+  const bool has_lambda = (NL > 0) && lambda != nullptr;
+  const int64_t ngroup = n / VW;
+  auto load_group = [&](const int64_t g, double (&a)[VW], double (&b)[VW]) {
+    const int64_t i = g * VW;
+    if constexpr (VW == 4) {
+      const D4 va = ld_stream4(in1 + i), vb = ld_stream4(in2 + i);
+      a[0] = va.x, a[1] = va.y, a[2] = va.z, a[3] = va.w;
+      b[0] = vb.x, b[1] = vb.y, b[2] = vb.z, b[3] = vb.w;
+    } else if constexpr (VW == 2) {
+      const double2 va = ld_stream2(in1 + i), vb = ld_stream2(in2 + i);
+      a[0] = va.x, a[1] = va.y;
+      b[0] = vb.x, b[1] = vb.y;
+    } else {
+      a[0] = ld_stream1(in1 + i);
+      b[0] = ld_stream1(in2 + i);
     }
-    if ((n & 1) && tid == 0) {
-      const int64_t i = n - 1;
-      out[i] = call_method<METHOD>(eos, in1[i], in2[i], lambda ? lambda + i * lstride : nullptr);
+  };
+  double a[VW], b[VW];
+  int64_t g = tid;
+  if (g < ngroup) load_group(g, a, b);
+  while (g < ngroup) {
+    const int64_t i = g * VW;
+    // software pipeline: the next trip's rho, T leave for HBM before this trip's table gathers
+    // (ncu: the first use of the streamed inputs was the top `long_scoreboard` site)
+    double an[VW], bn[VW];
+    const int64_t gn = g + nthr;
+    if (kPrefetch && gn < ngroup) load_group(gn, an, bn);
+    double r[VW], lam[VW][NLA];
+    if (kLoad && has_lambda) {
+#pragma unroll
+      for (int c = 0; c < VW; ++c)
+#pragma unroll
+        for (int k = 0; k < NL; ++k)
+          lam[c][k] = lambda[(i + c) * lstride + k];
     }
-  } else {
-    for (int64_t i = tid; i < n; i += nthr) {
-      out[i] = call_method<METHOD>(eos, ld_stream1(in1 + i), ld_stream1(in2 + i),
-                                   lambda ? lambda + i * lstride : nullptr);
+    if constexpr (use_two_phase<METHOD, EOS>()) {
+      LookupPrep q[VW];
+#pragma unroll
+      for (int c = 0; c < VW; ++c)
+        eos.template prep<METHOD>(a[c], b[c], q[c]);
+#pragma unroll
+      for (int c = 0; c < VW; ++c)
+        r[c] = eos.template finish<METHOD>(a[c], b[c], q[c], has_lambda ? lam[c] : nullptr);
+    } else {
+#pragma unroll
+      for (int c = 0; c < VW; ++c)
+        r[c] = eval_cell<METHOD, EOS, NL>(eos, a[c], b[c], lam[c], has_lambda);
     }
+    if constexpr (VW == 4) {
+      st_stream4(out + i, r[0], r[1], r[2], r[3]);
+    } else if constexpr (VW == 2) {
+      st_stream2(out + i, r[0], r[1]);
+    } else {
+      st_stream1(out + i, r[0]);
+    }
+    if (has_lambda) {
+      if constexpr (PACKED && NL == 2 && VW == 4) {
+        double *l = lambda + i * 2; // 64 contiguous bytes, 32-byte aligned (checked at launch)
+        st_stream4(l, lam[0][0], lam[0][1], lam[1][0], lam[1][1]);
+        st_stream4(l + 4, lam[2][0], lam[2][1], lam[3][0], lam[3][1]);
+      } else if constexpr (PACKED && NL == 1 && VW == 4) {
+        st_stream4(lambda + i, lam[0][0], lam[1][0], lam[2][0], lam[3][0]);
+      } else if constexpr (PACKED && NL == 2 && VW == 2) {
+        st_stream4(lambda + i * 2, lam[0][0], lam[0][1], lam[1][0], lam[1][1]);
+      } else {
+#pragma unroll
+        for (int c = 0; c < VW; ++c)
+#pragma unroll
+          for (int k = 0; k < NL; ++k)
+            lambda[(i + c) * lstride + k] = lam[c][k];
+      }
+    }
+    g = gn;
+    if constexpr (kPrefetch) {
+#pragma unroll
+      for (int c = 0; c < VW; ++c) {
+        a[c] = an[c];
+        b[c] = bn[c];
+      }
+    } else {
+      if (g < ngroup) load_group(g, a, b);
+    }
+  }
+  // ragged tail: n % VW cells, one per thread
+  const int64_t done = ngroup * VW;
+  if (VW > 1 && tid < n - done) {
+    const int64_t i = done + tid;
+    double lam[NLA];
+    if (kLoad && has_lambda)
+      for (int k = 0; k < NL; ++k)
+        lam[k] = lambda[i * lstride + k];
+    out[i] = eval_cell<METHOD, EOS, NL>(eos, in1[i], in2[i], lam, has_lambda);
+    if (has_lambda)
+      for (int k = 0; k < NL; ++k)
+        lambda[i * lstride + k] = lam[k];
   }
 }
 
@@ -237,16 +397,24 @@ __global__ void solve_kernel(const int n, double *__restrict__ a, double *__rest
 template <int METHOD, class EOS>
 int launch_eval_m(const EOS &eos, const double *in1, const double *in2, double *out, int64_t n,
                   double *lambda, int lstride, cudaStream_t s, int blocks_per_sm) {
-  const bool aligned = ((((uintptr_t)in1) | ((uintptr_t)in2) | ((uintptr_t)out)) & 15) == 0;
-  if (aligned && n >= 2) {
-    const LaunchCfg c = stream_cfg(n / 2, 256, blocks_per_sm);
-    eval_kernel<METHOD, EOS, true><<<c.blocks, c.threads, 0, s>>>(eos, in1, in2, out, n, lambda,
-                                                                   lstride);
+  constexpr int NL = EOS::nlambda;
+  const uintptr_t bits = ((uintptr_t)in1) | ((uintptr_t)in2) | ((uintptr_t)out);
+  // rows are contiguous when the caller's stride equals nlambda(); vector stores on them
+  // additionally need the row array itself 32-byte aligned
+  const bool packed = lambda != nullptr && NL > 0 && lstride == NL &&
+                      (((uintptr_t)lambda) & 31) == 0;
+#define SGX_LAUNCH(VW, PACKED)                                                             do {                                                                                       const LaunchCfg c = stream_cfg(n / VW + (VW - 1), 256, blocks_per_sm);                   eval_kernel<METHOD, EOS, VW, PACKED><<<c.blocks, c.threads, 0, s>>>(eos, in1, in2, out, n,                                                                         lambda, lstride);   } while (0)
+  // Root-finding methods loop a data-dependent number of times per cell: several cells per
+  // thread only stack the divergence and the registers (measured: 4/thread is 40 % slower)
+  constexpr bool kIterative = is_iterative<METHOD, EOS>();
+  if (!kIterative && (bits & 31) == 0 && n >= 4) {
+    if (packed) SGX_LAUNCH(4, true); else SGX_LAUNCH(4, false);
+  } else if ((bits & 15) == 0 && n >= 2) {
+    if (packed) SGX_LAUNCH(2, true); else SGX_LAUNCH(2, false);
   } else {
-    const LaunchCfg c = stream_cfg(n, 256, blocks_per_sm);
-    eval_kernel<METHOD, EOS, false><<<c.blocks, c.threads, 0, s>>>(eos, in1, in2, out, n,
-                                                                    lambda, lstride);
+    SGX_LAUNCH(1, false);
   }
+#undef SGX_LAUNCH
   count_launch();
   SGX_CUDA_OK(cudaGetLastError());
   return SGX_OK;

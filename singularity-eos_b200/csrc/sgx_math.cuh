@@ -108,7 +108,44 @@ constexpr double scale_up = (double)(one << 52);
 constexpr long long mantissa_mask = (one << 52) - one;
 constexpr long long low_mask = (one << 26) - 1;
 
+// floor(n / 3) for 0 <= n < 2^53 with 32-bit pieces.  With n = a 2^32 + b and
+// 2^32 = 3 * 0x55555555 + 1:  n = 3 (a * 0x55555555) + (a + b), so
+// floor(n/3) = a * 0x55555555 + floor((a + b) / 3); when a + b carries out of 32 bits,
+// 2^32 + d = 3 * 0x55555555 + (d + 1).  floor(s/3) for a 32-bit s is umulhi(s, 0xAAAAAAAB) >> 1.
+// (The generic signed 64-bit division the compiler emits for `/ 3` costs ~16 instructions
+// with its sign fix-ups; the numerator in lg() is provably in [0, 2^52).)
+SGX_HD unsigned long long div3_u53(const unsigned long long n) {
+  const unsigned int a = (unsigned int)(n >> 32), b = (unsigned int)n;
+  const unsigned int s = a + b;
+  const bool carry = s < a;
+  const unsigned int t = carry ? s + 1u : s; // cannot wrap: a < 2^21 so s < 2^21 when carrying
+#ifdef __CUDA_ARCH__
+  unsigned int q = __umulhi(t, 0xAAAAAAABu) >> 1;
+#else
+  unsigned int q = (unsigned int)(((unsigned long long)t * 0xAAAAAAABull) >> 33);
+#endif
+  return (unsigned long long)a * 0x55555555ull + (unsigned long long)q +
+         (carry ? 0x55555555ull : 0ull);
+}
+
+// lg_o2_aliased (logs.hpp:188-199), restated on explicit 32-bit pieces.  With
+// f = x_as_int & mantissa_mask in [0, 2^52): fh = f >> 26 and fl = f & low_mask are < 2^26, so
+// fh*fh and fh*fl are single 32x32->64 products, and f - frac_squared is in [0, 2^52)
+// (frac_squared ~ f^2 / 2^52 <= f), so C++'s truncating `/ 3` is floor division.
+// Bit-identical to the literal formula: tests/test_cpu_oracle.py::test_lg_restatement_bits.
 SGX_HD double lg(const double x) {
+  const long long x_as_int = as_int(x) - one_as_int;
+  const unsigned long long frac_as_int = (unsigned long long)(x_as_int & mantissa_mask);
+  const unsigned int frac_high = (unsigned int)(frac_as_int >> 26);
+  const unsigned int frac_low = (unsigned int)frac_as_int & (unsigned int)low_mask;
+  const unsigned long long frac_squared =
+      (unsigned long long)frac_high * frac_high +
+      (((unsigned long long)frac_high * frac_low) >> 25);
+  const long long third = (long long)div3_u53(frac_as_int - frac_squared);
+  return static_cast<double>(x_as_int + third) * scale_down;
+}
+// the literal formula of logs.hpp:188-199, kept for the bit-equality test
+SGX_HD double lg_literal(const double x) {
   const long long x_as_int = as_int(x) - one_as_int;
   const long long frac_as_int = x_as_int & mantissa_mask;
   const long long frac_high = frac_as_int >> 26;
@@ -186,11 +223,35 @@ struct Grid1D {
     }
     return (i - ptot[ig]) * dx[ig] + min[ig];
   }
-  SGX_HD void weights(const double x, int &ix, double &w0, double &w1) const {
-    const int ig = find_grid(x);
-    int i = cvt_int_x86(idx[ig] * (x - min[ig]));
+  // bound(int(v)) of RegularGrid1D::index (regular_grid_1d.hpp:66-74) for a patch of n points.
+  // On x86-64 the conversion yields INT_MIN when v is NaN or out of int range, which the
+  // clamp then maps to 0.  CUDA's cvt.rzi saturates instead: NaN -> 0 and v <= -2^31 ->
+  // INT_MIN both clamp to 0 as well, so only v >= 2^31 (saturates to INT_MAX, would clamp to
+  // n-2) needs an explicit test.
+  SGX_HD static int index_clamped(const double v, const int n) {
+#ifdef __CUDA_ARCH__
+    int i = __double2int_rz(v);
+    if (v >= 2147483648.0) i = 0;
+#else
+    int i = static_cast<int>(v);
+#endif
     if (i < 0) i = 0;
-    if (i >= npoints[ig] - 1) i = npoints[ig] - 2;
+    if (i >= n - 1) i = n - 2;
+    return i;
+  }
+  SGX_HD void weights(const double x, int &ix, double &w0, double &w1) const {
+    if (ngrids == 1) {
+      // single patch (the common case): constant member indices, no patch search, so the
+      // grid metadata stays in uniform registers instead of register-indexed constant loads
+      const int i = index_clamped(idx[0] * (x - min[0]), npoints[0]);
+      const double floor_x = (double)i * dx[0] + min[0];
+      w1 = idx[0] * (x - floor_x);
+      w0 = (1. - w1);
+      ix = i; // pointTotals_[0] == 0
+      return;
+    }
+    const int ig = find_grid(x);
+    const int i = index_clamped(idx[ig] * (x - min[ig]), npoints[ig]);
     const double floor_x = (double)i * dx[ig] + min[ig];
     w1 = idx[ig] * (x - floor_x);
     w0 = (1. - w1);

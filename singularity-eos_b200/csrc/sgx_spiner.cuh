@@ -11,12 +11,26 @@
 #ifndef SGX_SPINER_CUH_
 #define SGX_SPINER_CUH_
 
+#include "../../include/sgx_b200.h" // enum sgx_method
 #include "sgx_analytic.cuh"
 #include "sgx_math.cuh"
 
 namespace sgx {
 
 enum TableStatus { OnTable = 0, OffBottom = 1, OffTop = 2 };
+
+// Two-phase form of the direct (non-root-finding) lookups.  prep() does the NQT logs and grid
+// weights and ISSUES the 256-bit load of the table cell -- unconditionally: weights() clamps the
+// indices, so the address is always a valid cell even for off-table states.  finish() blends and
+// handles the rare off-table branches.  A kernel that runs prep() for several cells before any
+// finish() has all of their gathers in flight together (memory-level parallelism); with the
+// branches inside one scalar method the compiler cannot hoist the loads across cells.
+// Arithmetic and evaluation order are those of the one-phase methods, so results are identical.
+struct LookupPrep {
+  double x2, x1; // lRho and lT (or lE)
+  AxisPos p2, p1;
+  Cell4 cell;
+};
 
 struct SpinerRhoT {
   Grid1D gRho, gT; // gT = range(0) (fastest), gRho = range(1)
@@ -345,6 +359,56 @@ struct SpinerRhoT {
     const double dpde = interp2c(dPdE, numT, pr, AxisPos(gT, lT));
     return ratio(fabs(dpde), fabs(rho));
   }
+  // ---- two-phase (rho,T) lookups: P, sie, Cv, bMod, Gruneisen ---------------------------
+  template <int METHOD>
+  static constexpr bool two_phase() {
+    return METHOD == SGX_P_FROM_RHO_T || METHOD == SGX_E_FROM_RHO_T ||
+           METHOD == SGX_CV_FROM_RHO_T || METHOD == SGX_BMOD_FROM_RHO_T ||
+           METHOD == SGX_GAMMA_FROM_RHO_T;
+  }
+  template <int METHOD>
+  SGX_D const double *table_of() const {
+    if constexpr (METHOD == SGX_P_FROM_RHO_T) return P;
+    if constexpr (METHOD == SGX_E_FROM_RHO_T) return sie;
+    if constexpr (METHOD == SGX_CV_FROM_RHO_T) return dEdT;
+    if constexpr (METHOD == SGX_BMOD_FROM_RHO_T) return bMod;
+    return dPdE;
+  }
+  template <int METHOD>
+  SGX_D void prep(const double rho, const double T, LookupPrep &q) const {
+    q.x2 = lRho_(rho);
+    q.x1 = lT_(T);
+    q.p2 = AxisPos(gRho, q.x2);
+    q.p1 = AxisPos(gT, q.x1);
+    q.cell = ld_cell(table_of<METHOD>(), numT, q.p2.ix, q.p1.ix);
+  }
+  template <int METHOD>
+  SGX_D double finish(const double rho, const double T, const LookupPrep &q,
+                      double *lambda) const {
+    if (lambda) { // getLogsRhoT_ (:1125-1133)
+      lambda[0] = q.x2;
+      lambda[1] = q.x1;
+    }
+    const TableStatus w = locRhoT(q.x2, q.x1);
+    const double tab = blend_cell(q.cell, q.p2.w0, q.p2.w1, q.p1.w0, q.p1.w1);
+    if constexpr (METHOD == SGX_P_FROM_RHO_T) {
+      if (w == OnTable) return tab;
+      return PFromRholRhoTlT(rho, q.p2, T, q.x1, w);
+    } else if constexpr (METHOD == SGX_E_FROM_RHO_T) {
+      if (w == OnTable) return tab;
+      return sieFromlRhoTlT(q.p2, T, q.x1, w);
+    } else if constexpr (METHOD == SGX_CV_FROM_RHO_T) {
+      if (w == OnTable) return tab > kEps ? tab : kEps;
+      return CvFromlRholT(q.p2, q.x1, w);
+    } else if constexpr (METHOD == SGX_BMOD_FROM_RHO_T) {
+      if (w == OnTable) return tab > kEps ? tab : kEps;
+      return bModFromRholRhoTlT(rho, q.p2, T, q.x1, w);
+    } else {
+      if (w == OnTable) return ratio(fabs(tab), fabs(rho));
+      if (w == OffBottom) return ratio(fabs(interp1d(dPdECold, q.p2)), fabs(rho));
+      return interp1d(gm1Max, q.p2);
+    }
+  }
   // FillEos (eos_spiner_rho_temp.hpp:1043-1093)
   __device__ inline bool fill(double &rho, double &temp, double &energy, double &press,
                               double &cv, double &bmod, const unsigned long output,
@@ -473,6 +537,55 @@ struct SpinerRhoSie {
     const double lE = to_log(e, lEOffset);
     const double dpde = interp2c(dPdE_re, gRho, gE, numE, lRho, lE);
     return dpde / rho;
+  }
+  // ---- two-phase lookups: every vector method is one bilinear interpolation ------------
+  template <int METHOD>
+  static constexpr bool two_phase() {
+    return METHOD >= 0 && METHOD < SGX_METHOD_COUNT;
+  }
+  template <int METHOD>
+  static constexpr bool from_e() {
+    return METHOD == SGX_T_FROM_RHO_E || METHOD == SGX_P_FROM_RHO_E ||
+           METHOD == SGX_CV_FROM_RHO_E || METHOD == SGX_BMOD_FROM_RHO_E ||
+           METHOD == SGX_GAMMA_FROM_RHO_E;
+  }
+  template <int METHOD>
+  SGX_D const double *table_of() const {
+    if constexpr (METHOD == SGX_P_FROM_RHO_T) return P;
+    if constexpr (METHOD == SGX_E_FROM_RHO_T) return sie;
+    if constexpr (METHOD == SGX_CV_FROM_RHO_T) return dTdE;
+    if constexpr (METHOD == SGX_BMOD_FROM_RHO_T) return bMod;
+    if constexpr (METHOD == SGX_GAMMA_FROM_RHO_T) return dPdE;
+    if constexpr (METHOD == SGX_T_FROM_RHO_E) return T_re;
+    if constexpr (METHOD == SGX_P_FROM_RHO_E) return P_re;
+    if constexpr (METHOD == SGX_CV_FROM_RHO_E) return dTdE_re;
+    if constexpr (METHOD == SGX_BMOD_FROM_RHO_E) return bMod_re;
+    return dPdE_re;
+  }
+  template <int METHOD>
+  SGX_D void prep(const double rho, const double x, LookupPrep &q) const {
+    q.x2 = to_log(rho, lRhoOffset);
+    q.p2 = AxisPos(gRho, q.x2);
+    if constexpr (from_e<METHOD>()) {
+      q.x1 = to_log(x, lEOffset);
+      q.p1 = AxisPos(gE, q.x1);
+      q.cell = ld_cell(table_of<METHOD>(), numE, q.p2.ix, q.p1.ix);
+    } else {
+      q.x1 = to_log(x, lTOffset);
+      q.p1 = AxisPos(gT, q.x1);
+      q.cell = ld_cell(table_of<METHOD>(), numT, q.p2.ix, q.p1.ix);
+    }
+  }
+  template <int METHOD>
+  SGX_D double finish(const double rho, const double, const LookupPrep &q,
+                      double *lambda) const {
+    // every method but GruneisenParamFromDensityInternalEnergy caches lRho (:915-939,757-761)
+    if (METHOD != SGX_GAMMA_FROM_RHO_E && lambda) lambda[0] = q.x2;
+    const double tab = blend_cell(q.cell, q.p2.w0, q.p2.w1, q.p1.w0, q.p1.w1);
+    if constexpr (METHOD == SGX_CV_FROM_RHO_T || METHOD == SGX_CV_FROM_RHO_E) return 1. / tab;
+    if constexpr (METHOD == SGX_GAMMA_FROM_RHO_T || METHOD == SGX_GAMMA_FROM_RHO_E)
+      return tab / rho;
+    return tab;
   }
   // lRhoFromPlT_ (eos_spiner_rho_sie.hpp:941-986)
   __device__ inline double lRhoFromPlT(const double Pin, const double lT,

@@ -37,6 +37,26 @@ if what in ("rhosie", "all"):
 if what in ("ideal", "all"):
     ig = pkg.IdealGas(0.4, 7.16e6)
     timed("ideal_P", lambda: ig.PressureFromDensityTemperature(rho, T, out, n))
+if what in ("helm", "all"):
+    import tempfile
+    tq = pkg.thermalqs
+    hp = os.path.join(tempfile.gettempdir(), "sgx_helm_prof.dat")
+    pkg.tablegen.write_synthetic_helm_table(hp)
+    nh = 1 << (lg - 2)
+    hr, hT = W.helm_inputs(nh, 0, xp=torch, device=dev)
+    he, hP, hcv, hb = (torch.empty_like(hr) for _ in range(4))
+    lam3 = torch.tensor([4.0, 2.0, -1.0], dtype=torch.float64, device=dev).repeat(nh, 1).contiguous()
+    hm = pkg.Helmholtz(hp)
+    mi = tq.specific_internal_energy | tq.pressure | tq.specific_heat | tq.bulk_modulus
+    n_save = n; n = nh
+    timed("helm_fill_rhoT", lambda: hm.FillEos(hr, hT, he, hP, hcv, hb, nh, mi, lam3))
+    hm2 = pkg.Helmholtz(hp, coul=False, lambda_has_lT_slot=False)
+    lam2 = lam3[:, :2].contiguous()
+    hm2.FillEos(hr, hT, he, hP, hcv, hb, nh, mi, lam2)
+    hT2 = torch.empty_like(hT)
+    mii = tq.temperature | tq.pressure | tq.specific_heat | tq.bulk_modulus
+    timed("helm_fill_rhoe_newton", lambda: hm2.FillEos(hr, hT2, he, hP, hcv, hb, nh, mii, lam2))
+    n = n_save
 if what in ("pte", "all"):
     npte = 1 << (lg - 4)
     g3 = pkg.closure.set_eos_3mat_analytic()

@@ -278,3 +278,60 @@ def test_cpp_shim_compiles_and_links(pkg):
     out = subprocess.run([exe, "--link-only"], capture_output=True, text=True, timeout=60)
     assert out.returncode == 0, out.stdout + out.stderr
     assert out.stdout.strip() == "abi 1"
+
+
+def test_lg_restatement_bits(tmp_path):
+    """fastmath::lg is restated on 32-bit pieces with an explicit floor-division by 3
+    (csrc/sgx_math.cuh); it must equal the literal formula of base/fast-math/logs.hpp:188-199
+    bit for bit.  Host build of the same header, 20 M random doubles over the whole positive
+    range (subnormals included) + mantissa edge cases + the division helper's carry region."""
+    import subprocess
+    import textwrap
+
+    src = tmp_path / "lgtest.cpp"
+    hdr = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
+                       "singularity-eos_b200", "csrc", "sgx_math.cuh")
+    src.write_text(textwrap.dedent('''
+        #include "%s"
+        #include <cstdint>
+        #include <cstdio>
+        #include <initializer_list>
+        int main() {
+          using namespace sgx;
+          long long bad = 0, neg = 0;
+          for (long long i = 0; i < 20000000LL; ++i) {
+            uint64_t z = (uint64_t)i * 0x9E3779B97F4A7C15ull;
+            z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+            z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+            z ^= z >> 31;
+            uint64_t bits = z & 0x7FFFFFFFFFFFFFFFull;
+            if ((bits >> 52) == 0x7FF) bits &= 0x7FEFFFFFFFFFFFFFull;
+            const double x = as_double((long long)bits);
+            if (as_int(fastmath::lg(x)) != as_int(fastmath::lg_literal(x))) ++bad;
+            const long long xi = as_int(x) - fastmath::one_as_int;
+            const long long f = xi & fastmath::mantissa_mask, fh = f >> 26,
+                            fl = f & fastmath::low_mask;
+            if (f - (fh * fh + ((fh * fl) >> 25)) < 0) ++neg;
+          }
+          for (int e = 1; e < 2046; e += 97)
+            for (uint64_t m : {0ull, 1ull, 2ull, 3ull, (1ull << 26) - 1, (1ull << 26),
+                               (1ull << 26) + 1, (1ull << 52) - 3, (1ull << 52) - 2,
+                               (1ull << 52) - 1, (1ull << 51), 0x5555555555555ull,
+                               0xAAAAAAAAAAAAAull, 0xFFFFF00000000ull}) {
+              const double x = as_double((long long)(((uint64_t)e << 52) | m));
+              if (as_int(fastmath::lg(x)) != as_int(fastmath::lg_literal(x))) ++bad;
+            }
+          for (uint64_t a = 0; a < (1u << 21); a += 4099)
+            for (uint64_t b : {0ull, 1ull, 0xFFFFFFFFull, 0xFFFFFFFEull, 0xFFFFFFFFull - a,
+                               0xFFFFFFFFull - a + 1, 0xFFFFFFFFull - a + 2, 0x80000000ull}) {
+              const uint64_t n = (a << 32) | (b & 0xFFFFFFFFull);
+              if (fastmath::div3_u53(n) != n / 3) ++bad;
+            }
+          std::printf("%%lld %%lld\\n", bad, neg);
+          return (bad || neg) ? 1 : 0;
+        }
+    ''' % hdr))
+    exe = tmp_path / "lgtest"
+    subprocess.check_call(["/usr/bin/g++", "-O2", "-std=c++17", "-o", str(exe), str(src)])
+    out = subprocess.run([str(exe)], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0 and out.stdout.split() == ["0", "0"], out.stdout + out.stderr
