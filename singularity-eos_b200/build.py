@@ -12,7 +12,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libsgx_b200.so")
-SOURCES = ["sgx_api.cu", "sgx_spiner_host.cu", "sgx_pte.cu", "sgx_helm.cu"]
+SOURCES = ["sgx_api.cu", "sgx_spiner_host.cu", "sgx_pte.cu", "sgx_pte_rhot.cu", "sgx_helm.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 # -fmad=false: no FMA contraction, so device arithmetic rounds like the reference's x86-64
 # build (parity contract: 1e-12 lookups, 1e-10 PTE states, identical flags).
@@ -23,40 +23,68 @@ FLAGS = [
 ]
 
 
-def _digest():
+def _includes(path, seen):
+    """Transitive closure of the quoted #include files of one source (paths resolved)."""
+    path = os.path.normpath(path)
+    if path in seen or not os.path.exists(path):
+        return
+    seen.add(path)
+    with open(path) as fh:
+        for line in fh:
+            line = line.strip()
+            if line.startswith("#include \""):
+                _includes(os.path.join(os.path.dirname(path), line.split('"')[1]), seen)
+
+
+def _digest(src=None):
+    """Hash of the flags and of one source with the headers it includes (per-object stamp),
+    or of every source (library stamp)."""
+    files = set()
+    for s in ([src] if src else SOURCES):
+        _includes(os.path.join(CSRC, s), files)
     h = hashlib.sha256()
-    for root, _, files in os.walk(CSRC):
-        for f in sorted(files):
-            with open(os.path.join(root, f), "rb") as fh:
-                h.update(f.encode())
-                h.update(fh.read())
-    with open(os.path.join(HERE, "..", "include", "sgx_b200.h"), "rb") as fh:
-        h.update(fh.read())
+    for f in sorted(files):
+        with open(f, "rb") as fh:
+            h.update(os.path.basename(f).encode())
+            h.update(fh.read())
     h.update(" ".join(FLAGS).encode())
     return h.hexdigest()
+
+
+def _read(path):
+    try:
+        with open(path) as fh:
+            return fh.read().strip()
+    except OSError:
+        return ""
 
 
 def build(force=False, verbose=False):
     os.makedirs(LIBDIR, exist_ok=True)
     stamp = os.path.join(LIBDIR, ".stamp")
     dig = _digest()
-    if (not force and os.path.exists(LIB) and os.path.exists(stamp)
-            and open(stamp).read().strip() == dig):
+    if not force and os.path.exists(LIB) and _read(stamp) == dig:
         return LIB
     objs = []
     procs = []
     for src in SOURCES:
         obj = os.path.join(LIBDIR, src.replace(".cu", ".o"))
         objs.append(obj)
+        odig = _digest(src)
+        if not force and os.path.exists(obj) and _read(obj + ".stamp") == odig:
+            continue  # this translation unit and the headers are unchanged
         cmd = [NVCC] + FLAGS + ["-c", os.path.join(CSRC, src), "-o", obj]
         log = open(obj + ".log", "w")
-        procs.append((subprocess.Popen(cmd, stdout=log, stderr=subprocess.STDOUT), cmd, log, obj))
-    for p, cmd, log, obj in procs:
+        procs.append((subprocess.Popen(cmd, stdout=log, stderr=subprocess.STDOUT), cmd, log,
+                      obj, odig))
+    for p, cmd, log, obj, odig in procs:
         rc = p.wait()
         log.close()
         if rc != 0:
             sys.stderr.write(open(obj + ".log").read())
             raise RuntimeError("nvcc failed: " + " ".join(cmd))
+        with open(obj + ".stamp", "w") as fh:
+            fh.write(odig)
         if verbose:
             sys.stdout.write(open(obj + ".log").read())
     cmd = [NVCC, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-cudart", "static",

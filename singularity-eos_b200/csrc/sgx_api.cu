@@ -72,6 +72,13 @@ int ensure_staging(sgx_eos_s *e, size_t pinned_bytes, size_t device_bytes) {
   return SGX_OK;
 }
 
+int ensure_host_streams(sgx_eos_s *e) {
+  for (int k = 0; k < 4; ++k)
+    if (e->host_streams[k] == nullptr)
+      SGX_CUDA_OK(cudaStreamCreateWithFlags(&e->host_streams[k], cudaStreamNonBlocking));
+  return SGX_OK;
+}
+
 // ---------------------------------------------------------------------------------------
 // kernels
 // ---------------------------------------------------------------------------------------
@@ -715,6 +722,8 @@ int sgx_eos_destroy(sgx_eos_t e) {
   if (e->pinned) cudaFreeHost(e->pinned);
   if (e->dscratch) cudaFree(e->dscratch);
   if (e->own_stream) cudaStreamDestroy(e->own_stream);
+  for (int k = 0; k < 4; ++k)
+    if (e->host_streams[k]) cudaStreamDestroy(e->host_streams[k]);
   delete e;
   return SGX_OK;
 }
@@ -891,27 +900,69 @@ int sgx_FillEos(sgx_eos_t e, double *rhos, double *temps, double *energies, doub
 }
 
 // ---- host-pointer forms ---------------------------------------------------------------
+// Which way the lambda rows travel for a vector method: `in` = the kernel reads them (or leaves
+// some slots untouched, so the caller's values must survive the round trip), `out` = it writes.
+static void lambda_io(const sgx_eos_s *e, int method, int ls, bool &in, bool &out) {
+  const bool from_T = method == SGX_E_FROM_RHO_T || (method % 2) == 0;
+  switch (e->kind) {
+  case SGX_EOS_SPINER_RHOT: // (rho,T) lookups only write (lRho,lT); (rho,e) ones read the cache
+    in = !from_T || ls != 2;
+    out = true;
+    break;
+  case SGX_EOS_SPINER_RHOSIE: // lambda[0] = lRho, never read
+    in = ls != 1;
+    out = true;
+    break;
+  case SGX_EOS_HELMHOLTZ: // Abar, Zbar (and lT) in, lT out
+    in = true;
+    out = true;
+    break;
+  default: // analytic models: nlambda == 0
+    in = false;
+    out = false;
+  }
+}
+
+// Host-pointer entry: the cell range is cut into chunks that flow through kHostSlots device
+// slots, each on its own stream (H2D -> kernel -> D2H), so the two PCIe directions and the
+// kernel overlap.  Only the lambda traffic the method needs crosses the bus.
+static constexpr int kHostSlots = 4;
+static constexpr int64_t kHostChunk = 1 << 21; // cells per chunk (16 MiB per array)
+
 int sgx_eos_eval_host(sgx_eos_t e, int method, const double *in1, const double *in2,
                       double *out, int64_t n, double *lambda, int ls) {
   int rc = check_handle(e);
   if (rc) return rc;
   if (n <= 0) return n == 0 ? SGX_OK : fail(SGX_ERR_INVALID, "negative n");
   if (!in1 || !in2 || !out) return fail(SGX_ERR_INVALID, "null array");
-  const size_t nb = (size_t)n * sizeof(double);
-  const size_t lb = lambda ? nb * ls : 0;
-  rc = ensure_staging(e, 0, 3 * nb + lb);
+  bool lam_in = false, lam_out = false;
+  if (lambda) lambda_io(e, method, ls, lam_in, lam_out);
+  const int64_t chunk = n < kHostChunk ? n : kHostChunk;
+  const size_t per_cell = (size_t)(3 + (lambda ? ls : 0)) * sizeof(double);
+  const size_t slot_bytes = ((size_t)chunk * per_cell + 255) & ~size_t(255);
+  rc = ensure_staging(e, 0, kHostSlots * slot_bytes);
   if (rc) return rc;
-  cudaStream_t s = e->own_stream;
-  double *d1 = (double *)e->dscratch, *d2 = d1 + n, *dout = d2 + n;
-  double *dl = lambda ? dout + n : nullptr;
-  SGX_CUDA_OK(cudaMemcpyAsync(d1, in1, nb, cudaMemcpyHostToDevice, s));
-  SGX_CUDA_OK(cudaMemcpyAsync(d2, in2, nb, cudaMemcpyHostToDevice, s));
-  if (lambda) SGX_CUDA_OK(cudaMemcpyAsync(dl, lambda, lb, cudaMemcpyHostToDevice, s));
-  rc = sgx_eos_eval(e, method, d1, d2, dout, n, dl, ls, s);
+  rc = ensure_host_streams(e);
   if (rc) return rc;
-  SGX_CUDA_OK(cudaMemcpyAsync(out, dout, nb, cudaMemcpyDeviceToHost, s));
-  if (lambda) SGX_CUDA_OK(cudaMemcpyAsync(lambda, dl, lb, cudaMemcpyDeviceToHost, s));
-  SGX_CUDA_OK(cudaStreamSynchronize(s));
+  int slot = 0;
+  for (int64_t i0 = 0; i0 < n; i0 += chunk, slot = (slot + 1) % kHostSlots) {
+    const int64_t m = (n - i0) < chunk ? (n - i0) : chunk;
+    const size_t nb = (size_t)m * sizeof(double);
+    cudaStream_t s = e->host_streams[slot];
+    double *d1 = (double *)((char *)e->dscratch + slot * slot_bytes);
+    double *d2 = d1 + chunk, *dout = d2 + chunk;
+    double *dl = lambda ? dout + chunk : nullptr;
+    double *hl = lambda ? lambda + (size_t)i0 * ls : nullptr;
+    SGX_CUDA_OK(cudaMemcpyAsync(d1, in1 + i0, nb, cudaMemcpyHostToDevice, s));
+    SGX_CUDA_OK(cudaMemcpyAsync(d2, in2 + i0, nb, cudaMemcpyHostToDevice, s));
+    if (lam_in) SGX_CUDA_OK(cudaMemcpyAsync(dl, hl, nb * ls, cudaMemcpyHostToDevice, s));
+    rc = sgx_eos_eval(e, method, d1, d2, dout, m, dl, ls, s);
+    if (rc) return rc;
+    SGX_CUDA_OK(cudaMemcpyAsync(out + i0, dout, nb, cudaMemcpyDeviceToHost, s));
+    if (lam_out) SGX_CUDA_OK(cudaMemcpyAsync(hl, dl, nb * ls, cudaMemcpyDeviceToHost, s));
+  }
+  for (int k = 0; k < kHostSlots; ++k)
+    SGX_CUDA_OK(cudaStreamSynchronize(e->host_streams[k]));
   return SGX_OK;
 }
 

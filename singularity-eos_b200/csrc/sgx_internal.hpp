@@ -80,11 +80,13 @@ struct sgx_eos_s {
   void *dscratch = nullptr;
   size_t dscratch_bytes = 0;
   cudaStream_t own_stream = nullptr;
+  cudaStream_t host_streams[4] = {nullptr, nullptr, nullptr, nullptr}; // chunk pipeline
 };
 
 namespace sgx {
 int upload_tables(sgx_eos_s *e);   // cudaMalloc + H2D of e->tables.host, L2 persistence hint
 int ensure_staging(sgx_eos_s *e, size_t pinned_bytes, size_t device_bytes);
+int ensure_host_streams(sgx_eos_s *e);
 int build_spiner_rhot(const sgx_sp5_tables *raw, int reproducible, int pmin_vapor_dome,
                       sgx_eos_s *e);
 int build_spiner_rhosie(const sgx_sp5_tables *raw, int reproducible, int pmin_vapor_dome,
@@ -95,6 +97,11 @@ int launch_helm_fill(sgx_eos_s *e, double *rho, double *T, double *en, double *P
                      int stride, cudaStream_t s);
 int launch_helm_eval(sgx_eos_s *e, int method, const double *in1, const double *in2,
                      double *out, int64_t n, double *lambda, int stride, cudaStream_t s);
+int launch_pte_rhot(const EosSet &set, bool bench_mix, const MixParamsDev &prm, double *rho,
+                    double *vfrac, double *sie, double *temp, double *press,
+                    const double *sie_tot, const double *vfrac_tot, const double *Tguess,
+                    uint64_t *status, double *residual, uint64_t *stats, int64_t ncell,
+                    cudaStream_t s);
 // launch geometry: persistent-ish grid-stride, multiple of the SM count
 struct LaunchCfg {
   int blocks, threads;

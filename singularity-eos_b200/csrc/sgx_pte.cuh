@@ -134,6 +134,13 @@ struct DynEos {
       return;
     }
   }
+  // same, restricted to the models whose PreferredInput() includes pressure (only those
+  // reach it through GetSieCvFromTAndPreferred, :603-612): keeps the solids' nested root
+  // finders out of the RhoT kernels
+  __device__ inline void rho_e_from_P_T_pressure_preferred(int m, double P, double T,
+                                                           double &rho, double &sie) const {
+    if (set.e[m].kind == 0) set.e[m].ideal.rho_e_from_P_T(P, T, nullptr, rho, sie);
+  }
 };
 
 // The benchmark mixture of test/pte_test_3mat_analytic.hpp:38-50 with the material types
@@ -181,6 +188,7 @@ struct Mix3GrDrDp {
       set.e[2].dp.rho_e_from_P_T(P, T, nullptr, rho, sie);
     }
   }
+  SGX_D void rho_e_from_P_T_pressure_preferred(int, double, double, double &, double &) const {}
 #undef SGX_MIX3
 };
 
@@ -694,6 +702,10 @@ struct RhoT : public Base<NM, NM, Eos> {
       dpdT[m] = ratio((p_pert - press[m]), dT);
       dedT_sum += ratio(rhobar[m] * ratio(e_pert, uscale) - u[m], dT);
     }
+    AssembleJacobian(dedT_sum);
+  }
+  // Fill the reduced (T, alpha_{m != ms}) system from dpdv/dedv/dpdT (:1083-1104)
+  SGX_D void AssembleJacobian(const double dedT_sum) {
 #pragma unroll
     for (int i = 0; i < NM * NM; ++i)
       jacobian[i] = 0.0;

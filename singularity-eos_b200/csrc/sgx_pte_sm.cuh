@@ -1,0 +1,599 @@
+// PTESolverRhoT as a per-lane state machine ("lane refill" kernel).
+//
+// Why: the straight transcription in sgx_pte.cuh (one thread walks one cell through
+// Init / Jacobian / TestUpdate) inlines the materials' EOS code at ~12 call sites -- 484 KB of
+// SASS, instruction-fetch bound (profiles/r1a_pte_details.txt: 13.7 `no_instruction` stall
+// cycles per issue) -- and a warp waits for its slowest cell (14.8 of 32 lanes active).
+//
+// Here every lane still owns one cell and executes exactly the reference's sequence of
+// floating-point operations for it (closure/mixed_cell_models.hpp:329-1193, 2188-2291), but the
+// solver is cut at each point where it needs the materials' EOS:
+//
+//   * all EOS work of all phases goes through ONE warp-converged call site, eval_round():
+//     "for each material m: e = e(rho_q[m], T_q), then P(rho_q[m], e) or cv";
+//   * between two rounds a lane runs its own phase handler (cheap scalar algebra: Jacobian
+//     assembly, the 3x3 solve, ScaleDx, line-search bookkeeping);
+//   * a lane whose cell is finished stores it and takes the next cell of its warp's contiguous
+//     cell range at once, so iteration-count differences between cells no longer idle lanes.
+//
+// Evaluation points, in the order a cell visits them (reference line numbers):
+//   A_LO / A_HI / A_BIS  ApproxTemperatureFromRhoMatU  :790-847   (e only)
+//   G_NEWTON             GetTguess newton_step         :547-560   (e and cv)
+//   INIT_EP              InitBase                      :627-662   (e and P)
+//   J1, J2               PTESolverRhoT::Jacobian       :1042-1105 (dv- and dT-perturbed e, P)
+//   TU                   PTESolverRhoT::TestUpdate     :1155-1187 (e, then P from sie=u/rhobar)
+#ifndef SGX_PTE_SM_CUH_
+#define SGX_PTE_SM_CUH_
+
+#include "sgx_pte.cuh"
+
+namespace sgx {
+namespace mix {
+
+#ifdef __CUDACC__
+
+enum SmPhase : int {
+  PH_IDLE = 0,
+  // phases entered with eval_round() results ready
+  PH_A_LO,
+  PH_A_HI,
+  PH_A_BIS,
+  PH_G_NEWTON,
+  PH_INIT_EP,
+  PH_J1,
+  PH_J2,
+  PH_TU,
+  // pure-compute phases (run back to back inside advance())
+  PH_A_CHECK,
+  PH_INIT0,
+  PH_G_BEGIN,
+  PH_G_AFTER,
+  PH_NEWTON_TOP,
+  PH_AFTER_LS,
+  PH_FINISH
+};
+
+enum SmMode : int { MODE_E = 0, MODE_EP = 1, MODE_ECV = 2, MODE_TU = 3 };
+
+// The one place the materials' EOS code is instantiated.
+//   MODE_E   e = e(rho,T)
+//   MODE_EP  e, then GetPressureFromPreferred(m, rho, T, e, false)          (:583-597)
+//   MODE_ECV GetSieCvFromTAndPreferred (both branches)                      (:601-620)
+//   MODE_TU  TestUpdate: sie = ratio(rhobar*e, rhobar), P from that sie     (:1175-1184)
+template <int NM, class Eos>
+__device__ __forceinline__ void eval_round(const Eos &eos, const int mode, const double Tq,
+                                           const double (&rq)[NM], const double (&rb)[NM],
+                                           const double (&press_in)[NM], double (&eq)[NM],
+                                           double (&pq)[NM]) {
+#pragma unroll
+  for (int m = 0; m < NM; ++m) {
+    if (mode == MODE_ECV && (eos.preferred(m) & TQ_PRESSURE)) {
+      // GetSieCvFromTAndPreferred, pressure-preferring branch (:603-612)
+      const double Pmin = eos.MinimumPressure(m);
+      const double Pmax = eos.MaximumPressureAtTemperature(m, Tq);
+      const double P = press_in[m];
+      double Pguess;
+      if (bad_value(P)) {
+        Pguess = 0.5 * (Pmin + Pmax);
+      } else {
+        Pguess = stdmax(Pmin, stdmin(Pmax, P));
+      }
+      double rho_ = rq[m], sie_ = 0.0;
+      eos.rho_e_from_P_T_pressure_preferred(m, Pguess, Tq, rho_, sie_);
+      eq[m] = sie_;
+      pq[m] = eos.cv_from_rho_e(m, rho_, sie_);
+      continue;
+    }
+    const double e = eos.e_from_rho_T(m, rq[m], Tq);
+    eq[m] = e;
+    if (mode == MODE_ECV) {
+      pq[m] = eos.cv_from_rho_T(m, rq[m], Tq);
+    } else if (mode != MODE_E) {
+      double sie_for_p = e;
+      if (mode == MODE_TU) sie_for_p = ratio(rb[m] * e, rb[m]);
+      if (eos.preferred(m) & TQ_SIE) {
+        pq[m] = eos.P_from_rho_e(m, rq[m], sie_for_p);
+      } else {
+        pq[m] = eos.P_from_rho_T(m, rq[m], Tq);
+      }
+    }
+  }
+}
+
+// One lane's cell: the reference solver object plus the program counter and the few locals
+// of PTESolver() / GetTguess() / ApproxTemperatureFromRhoMatU() that live across a cut.
+template <int NM, class Eos>
+struct RhoTLane {
+  RhoT<NM, Eos> s;
+  SolverStatusDev st;
+  int phase = PH_IDLE;
+  int mode = MODE_E;
+  double Tq = 0.0;
+  double rq[NM];
+  // ApproxTemperatureFromRhoMatU locals
+  double u_tot, lTlo, lThi, ulo, uhi, alT;
+  int aiter;
+  // GetTguess locals
+  double Tguess;
+  int gi;
+  // PTESolver locals
+  double err, err_old, gradfdx, scale, err_first;
+  bool close_enough;
+  int tu_kind; // 0: full step, 1: half step, 2: line-search candidates
+  unsigned long long line_iter, pte_max_iter;
+
+  __device__ RhoTLane(const Eos &e, const MixParamsDev &p) : s(e, p) {}
+
+  // ---- requests ----------------------------------------------------------------------
+  SGX_D void request(const int mode_, const double T, const int next_phase) {
+    mode = mode_;
+    Tq = T;
+    phase = next_phase;
+  }
+  SGX_D void request_state_rho(const int mode_, const double T, const int next_phase) {
+#pragma unroll
+    for (int m = 0; m < NM; ++m)
+      rq[m] = s.rho[m];
+    request(mode_, T, next_phase);
+  }
+  // first half of TestUpdate (:1155-1174): new T and volume fractions, densities to evaluate
+  SGX_D void prepare_test_update(const double scale_, const bool cache_state) {
+    if (cache_state) {
+      s.Ttemp = s.Tequil;
+#pragma unroll
+      for (int m = 0; m < NM; ++m)
+        s.vtemp[m] = s.vfrac[m];
+    }
+    s.Tequil = s.Ttemp + scale_ * s.dx[0];
+    int idx = 1;
+#pragma unroll
+    for (int m = 0; m < NM; ++m) {
+      if (s.ms == m) continue;
+      s.vfrac[m] = s.vtemp[m] + scale_ * s.dx[idx++];
+    }
+    const double vsum_others = sum_neumaier(s.vfrac, NM, 0, s.ms);
+#pragma unroll
+    for (int m = 0; m < NM; ++m)
+      if (m == s.ms) s.vfrac[m] = 1 - vsum_others;
+#pragma unroll
+    for (int m = 0; m < NM; ++m)
+      s.rho[m] = ratio(s.rhobar[m], s.vfrac[m]);
+    request_state_rho(MODE_TU, s.Tnorm * s.Tequil, PH_TU);
+  }
+
+  // ---- cell entry (test/test_pte.cpp:188-198) ------------------------------------------
+  // State arrays are already loaded into s.rho .. s.press by the kernel.
+  SGX_D void begin(const double sie_tot_in, const bool have_sie_tot, const double vfrac_tot,
+                   const double Tguess_in, const bool have_Tguess) {
+    st = SolverStatusDev();
+    s.niter = 0;
+    double sie_tot = 0.0, rho_tot = 0.0;
+#pragma unroll
+    for (int m = 0; m < NM; m++) {
+      const double rhobar = s.rho[m] * s.vfrac[m];
+      rho_tot += rhobar;
+      sie_tot += rhobar * s.sie[m];
+    }
+    sie_tot /= rho_tot;
+    if (have_sie_tot) sie_tot = sie_tot_in;
+    s.sie_total = sie_tot;
+    s.vfrac_total = vfrac_tot;
+    if (have_Tguess) {
+      s.Tnorm = Tguess_in;
+      phase = PH_INIT0;
+    } else {
+      u_tot = rho_tot * sie_tot;
+      request_state_rho(MODE_E, 1.e-9, PH_A_LO);
+    }
+  }
+  SGX_D bool wants_eval() const { return phase != PH_IDLE && phase < PH_A_CHECK; }
+
+  // plain left-to-right sum of rho*vfrac*e (the ufunc lambda, :801-808)
+  SGX_D double approx_usum(const double (&eq)[NM]) const {
+    double usum = 0.0;
+#pragma unroll
+    for (int m = 0; m < NM; m++)
+      usum += s.rho[m] * s.vfrac[m] * eq[m];
+    return usum;
+  }
+
+  // ---- the solver, cut at its evaluation points -----------------------------------------
+  // Called after eval_round() (eq/pq hold the results for a lane in a result phase); runs
+  // this lane's handlers until the next evaluation request or the end of the cell.
+  __device__ __forceinline__ void advance(const double (&eq)[NM], const double (&pq)[NM]) {
+    const MixParamsDev &params = s.params_;
+    while (true) {
+      switch (phase) {
+      // ===== ApproxTemperatureFromRhoMatU (:790-847), Tguess = 0 ========================
+      case PH_A_LO: {
+        ulo = approx_usum(eq);
+        if (u_tot < ulo) {
+          s.Tnorm = 1.e-9;
+          phase = PH_INIT0;
+        } else {
+          request(MODE_E, 1.e9, PH_A_HI); // rq still holds the input densities
+        }
+      } break;
+      case PH_A_HI: {
+        uhi = approx_usum(eq);
+        if (u_tot > uhi) {
+          s.Tnorm = 1.e9;
+          phase = PH_INIT0;
+        } else {
+          lTlo = fastmath::lg(1.e-9);
+          lThi = fastmath::lg(1.e9);
+          aiter = 0;
+          phase = PH_A_CHECK;
+        }
+      } break;
+      case PH_A_BIS: {
+        const double uT = approx_usum(eq);
+        if (uT < u_tot) {
+          lTlo = alT;
+          ulo = uT;
+        } else {
+          lThi = alT;
+          uhi = uT;
+        }
+        aiter++;
+        phase = PH_A_CHECK;
+      } break;
+      case PH_A_CHECK: {
+        if (lThi - lTlo > 0.01 && aiter < 10) {
+          alT = 0.5 * (lTlo + lThi);
+          request(MODE_E, fastmath::pow2(alT), PH_A_BIS);
+        } else {
+          const double alpha = ratio((u_tot - ulo), (uhi - ulo));
+          s.Tnorm = fastmath::pow2((1.0 - alpha) * lTlo + alpha * lThi);
+          phase = PH_INIT0;
+        }
+      } break;
+      // ===== InitBase (:627-662) up to GetTguess ========================================
+      case PH_INIT0: {
+        s.InitRhoBarandRho();
+        const double utotal = s.rho_total * s.sie_total;
+        s.uscale = stdmax(fabs(utotal), 1.0e-14);
+        s.utotal_scale = ratio(utotal, s.uscale);
+        // GetTguess (:500-581)
+        if (s.Tnorm > 0.0) {
+          Tguess = s.Tnorm;
+        } else {
+          Tguess = params.default_tguess;
+#pragma unroll
+          for (int m = 0; m < NM; ++m)
+            Tguess = stdmax(Tguess, s.temp[m]);
+        }
+        gi = 0;
+        phase = PH_G_BEGIN;
+      } break;
+      case PH_G_BEGIN: {
+        if (params.iterate_t_guess) {
+#pragma unroll
+          for (int m = 0; m < NM; ++m)
+            rq[m] = stdmin(s.rho[m], s.eos.MaximumDensity(m));
+          request(MODE_ECV, Tguess, PH_G_NEWTON);
+        } else {
+          phase = PH_G_AFTER;
+        }
+      } break;
+      case PH_G_NEWTON: { // newton_step (:547-560)
+        double dudt = 0;
+        double usum = 0;
+#pragma unroll
+        for (int m = 0; m < NM; ++m) {
+          usum += s.rhobar[m] * eq[m];
+          dudt += s.rhobar[m] * pq[m];
+        }
+        const double Tnew = Tguess - ratio((usum - s.utotal_scale * s.uscale), dudt);
+        Tguess = stdmin(params.temperature_limit, stdmax(Tguess, Tnew));
+        phase = PH_G_AFTER;
+      } break;
+      case PH_G_AFTER: { // rest of one pass of the `for (i < 3)` loop (:565-580)
+#pragma unroll
+        for (int m = 0; m < NM; ++m)
+          Tguess = stdmax(s.eos.MinimumTemperature(m), Tguess);
+        bool bad_vfrac_guess = s.SetVfracFromT(Tguess);
+        if (!bad_vfrac_guess) {
+#pragma unroll
+          for (int m = 0; m < NM; ++m)
+            s.rho[m] = ratio(s.rhobar[m], s.vfrac[m]);
+          for (int m = 0; m < NM; ++m) {
+            const double rho_min = s.eos.RhoPmin(m, Tguess);
+            if (s.rho[m] < rho_min) {
+              bad_vfrac_guess = true;
+              break;
+            }
+          }
+        }
+        if (bad_vfrac_guess) {
+          Tguess *= 10.0;
+          gi++;
+        }
+        if (bad_vfrac_guess && gi < 3) {
+          phase = PH_G_BEGIN;
+        } else {
+          s.Tnorm = Tguess;
+          request_state_rho(MODE_EP, Tguess, PH_INIT_EP);
+        }
+      } break;
+      // ===== rest of InitBase + PTESolverRhoT::Init (:947-984) =========================
+      case PH_INIT_EP: {
+#pragma unroll
+        for (int m = 0; m < NM; m++) {
+          s.temp[m] = 1.0;
+          s.sie[m] = eq[m];
+          if ((s.eos.preferred(m) & TQ_PRESSURE) && !bad_value(s.press[m])) {
+            s.press[m] = ratio(s.press[m], s.uscale); // input pressure is the guess (:646-649)
+          } else {
+            s.press[m] = ratio(pq[m], s.uscale);
+          }
+        }
+#pragma unroll
+        for (int m = 0; m < NM; ++m)
+          s.u[m] = s.sie[m] * ratio(s.rhobar[m], s.uscale);
+        if (params.pte_reduced_system_exclude_idx >= 0) {
+          s.ms = (int)params.pte_reduced_system_exclude_idx;
+        } else {
+          s.ms = 0;
+          double xmax = 0;
+#pragma unroll
+          for (int m = 0; m < NM; ++m) {
+            const double x = ratio(s.rhobar[m], s.rho_total);
+            if (x > xmax) {
+              xmax = x;
+              s.ms = m;
+            }
+          }
+        }
+        s.Residual();
+        s.Tequil = s.temp[0];
+        err = s.ResidualNorm();
+        // PTESolver prologue (:2188-2203)
+        st.converged = false;
+        close_enough = false;
+        pte_max_iter = (unsigned long long)NM * params.pte_max_iter_per_mat;
+        s.niter = 0;
+        phase = PH_NEWTON_TOP;
+      } break;
+      // ===== PTESolver loop head (:2204-2211) ==========================================
+      case PH_NEWTON_TOP: {
+        if ((unsigned long long)s.niter >= pte_max_iter) {
+          phase = PH_FINISH;
+          break;
+        }
+        st.max_niter =
+            st.max_niter > (unsigned long long)s.niter ? st.max_niter : s.niter;
+        s.CheckPTE(st.converged, close_enough);
+        if (st.converged) {
+          phase = PH_FINISH;
+          break;
+        }
+        // Jacobian, volume-fraction perturbation (:1046-1054)
+#pragma unroll
+        for (int m = 0; m < NM; m++) {
+          const double dv =
+              (s.vfrac[m] < 0.5 ? 1.0 : -1.0) * s.vfrac[m] * params.derivative_eps;
+          const double vf_pert = s.vfrac[m] + dv;
+          rq[m] = ratio(s.rhobar[m], vf_pert);
+        }
+        request(MODE_EP, s.Tnorm * s.Tequil, PH_J1);
+      } break;
+      case PH_J1: { // :1055-1063
+#pragma unroll
+        for (int m = 0; m < NM; m++) {
+          const double dv =
+              (s.vfrac[m] < 0.5 ? 1.0 : -1.0) * s.vfrac[m] * params.derivative_eps;
+          const double p_pert = ratio(pq[m], s.uscale);
+          s.dpdv[m] = stdmin(ratio((p_pert - s.press[m]), dv), -fabs(params.pte_max_dpdv));
+          s.dedv[m] = ratio(s.rhobar[m] * ratio(eq[m], s.uscale) - s.u[m], dv);
+        }
+        const double dT = s.Tequil * params.derivative_eps;
+        request_state_rho(MODE_EP, s.Tnorm * (s.Tequil + dT), PH_J2);
+      } break;
+      case PH_J2: { // :1064-1105, then Solve / ScaleDx / first TestUpdate (:2212-2226)
+        const double dT = s.Tequil * params.derivative_eps;
+        double dedT_sum = 0.0;
+#pragma unroll
+        for (int m = 0; m < NM; m++) {
+          const double p_pert = ratio(pq[m], s.uscale);
+          s.dpdT[m] = ratio((p_pert - s.press[m]), dT);
+          dedT_sum += ratio(s.rhobar[m] * ratio(eq[m], s.uscale) - s.u[m], dT);
+        }
+        s.AssembleJacobian(dedT_sum);
+        const bool success = s.Solve();
+        if (!success) {
+          st.converged = false;
+          phase = PH_FINISH;
+          break;
+        }
+        scale = stdmin(1.0, s.ScaleDx());
+        if (fabs(scale) < params.pte_small_step_thresh) st.small_step_iters++;
+        if (st.small_step_iters >= params.pte_small_step_tries) {
+          st.converged = false;
+          phase = PH_FINISH;
+          break;
+        }
+        gradfdx = -2.0 * scale * err;
+        scale = 1.0;
+        err_old = err;
+        tu_kind = 0;
+        prepare_test_update(scale, true);
+      } break;
+      // ===== TestUpdate second half (:1175-1187) + line search (:2226-2251) =============
+      case PH_TU: {
+#pragma unroll
+        for (int m = 0; m < NM; ++m) {
+          s.u[m] = s.rhobar[m] * eq[m];
+          s.sie[m] = ratio(s.u[m], s.rhobar[m]);
+          s.u[m] = ratio(s.u[m], s.uscale);
+          s.temp[m] = s.Tequil;
+          s.press[m] = ratio(pq[m], s.uscale);
+        }
+        s.Residual();
+        const double err_new = s.ResidualNorm();
+        if (tu_kind == 0) {
+          err = err_new;
+          if (err > err_old + params.line_search_alpha * gradfdx) {
+            scale = 0.5;
+            tu_kind = 1;
+            prepare_test_update(scale, false);
+          } else {
+            phase = PH_AFTER_LS;
+          }
+        } else if (tu_kind == 1) {
+          const double err_mid = err_new;
+          if (err_mid < err && err_mid < err_old) {
+            scale = 0.75 + 0.5 * ratio(err_mid - err, err - 2.0 * err_mid + err_old);
+          }
+          line_iter = 0;
+          if (line_iter < params.line_search_max_iter) {
+            tu_kind = 2;
+            prepare_test_update(scale, false);
+          } else {
+            phase = PH_AFTER_LS;
+          }
+        } else {
+          err = err_new;
+          if (err < err_old + params.line_search_alpha * scale * gradfdx) {
+            phase = PH_AFTER_LS;
+          } else {
+            scale *= params.line_search_fac;
+            st.max_line_niter = line_iter > st.max_line_niter ? line_iter : st.max_line_niter;
+            line_iter++;
+            if (line_iter < params.line_search_max_iter) {
+              prepare_test_update(scale, false);
+            } else {
+              phase = PH_AFTER_LS;
+            }
+          }
+        }
+      } break;
+      // ===== PTESolver loop tail (:2252-2262) ==========================================
+      case PH_AFTER_LS: {
+        s.Fixup();
+        if (((err > params.pte_slow_convergence_thresh * err_old) ||
+             (unsigned long long)s.niter == pte_max_iter - 1) &&
+            close_enough) {
+          st.converged = true;
+          st.slow_convergence_detected = true;
+          phase = PH_FINISH;
+        } else {
+          ++s.niter;
+          phase = PH_NEWTON_TOP;
+        }
+      } break;
+      case PH_FINISH: { // :2263-2265
+        s.Fixup();
+        s.Finalize();
+        st.residual = err;
+        phase = PH_IDLE;
+      } break;
+      default:
+        break;
+      }
+      if (phase < PH_A_CHECK) break; // IDLE or waiting for an evaluation
+    }
+  }
+};
+
+#endif // __CUDACC__
+} // namespace mix
+
+#ifdef __CUDACC__
+// One lane per cell, one warp per contiguous range of `cells_per_warp` cells; a lane that
+// finishes its cell stores it and pulls the next one of the range.
+template <int NM, class Acc>
+__global__ void __launch_bounds__(128, 2)
+    pte_rhot_sm_kernel(const __grid_constant__ EosSet set,
+                       const __grid_constant__ MixParamsDev prm, double *__restrict__ rho,
+                       double *__restrict__ vfrac, double *__restrict__ sie,
+                       double *__restrict__ temp, double *__restrict__ press,
+                       const double *__restrict__ sie_tot_in,
+                       const double *__restrict__ vfrac_tot_in,
+                       const double *__restrict__ Tguess_in,
+                       unsigned long long *__restrict__ status, double *__restrict__ residual,
+                       unsigned long long *__restrict__ stats, const int64_t ncell,
+                       const int64_t cells_per_warp) {
+  __shared__ unsigned int s_hist[SGX_PTE_NSTATS];
+  if (stats) {
+    for (int k = threadIdx.x; k < SGX_PTE_NSTATS; k += blockDim.x)
+      s_hist[k] = 0;
+    __syncthreads();
+  }
+  const Acc eos(set);
+  mix::RhoTLane<NM, Acc> L(eos, prm);
+  const unsigned lane = threadIdx.x & 31u;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  int64_t next = warp * cells_per_warp;
+  const int64_t end = (next + cells_per_warp < ncell) ? next + cells_per_warp : ncell;
+  int64_t cell = -1;
+  double eq[NM], pq[NM];
+#pragma unroll
+  for (int m = 0; m < NM; ++m) {
+    eq[m] = 0.0;
+    pq[m] = 0.0;
+    L.rq[m] = 1.0;
+    L.s.rhobar[m] = 1.0;
+  }
+  while (true) {
+    const bool idle = (L.phase == mix::PH_IDLE);
+    const unsigned idle_mask = __ballot_sync(0xffffffffu, idle);
+    if (idle_mask) {
+      if (idle) {
+        if (cell >= 0) { // retire the finished cell
+          const int64_t base = cell * NM;
+#pragma unroll
+          for (int m = 0; m < NM; ++m) {
+            rho[base + m] = L.s.rho[m];
+            vfrac[base + m] = L.s.vfrac[m];
+            sie[base + m] = L.s.sie[m];
+            temp[base + m] = L.s.temp[m];
+            press[base + m] = L.s.press[m];
+          }
+          if (status) status[cell] = mix::pack_status(L.st, L.s.niter);
+          if (residual) residual[cell] = L.st.residual;
+          if (stats) {
+            atomicAdd(&s_hist[SGX_PTE_STAT_NCELL], 1u);
+            if (L.st.converged) atomicAdd(&s_hist[SGX_PTE_STAT_CONVERGED], 1u);
+            if (L.st.slow_convergence_detected) atomicAdd(&s_hist[SGX_PTE_STAT_SLOW], 1u);
+            if (!L.st.converged) atomicAdd(&s_hist[SGX_PTE_STAT_FAILED], 1u);
+            const int bin = L.s.niter < 31 ? L.s.niter : 31;
+            atomicAdd(&s_hist[SGX_PTE_STAT_HIST0 + bin], 1u);
+          }
+          cell = -1;
+        }
+        const int64_t mine = next + __popc(idle_mask & ((1u << lane) - 1u));
+        if (mine < end) {
+          cell = mine;
+          const int64_t base = cell * NM;
+#pragma unroll
+          for (int m = 0; m < NM; ++m) {
+            L.s.rho[m] = rho[base + m];
+            L.s.vfrac[m] = vfrac[base + m];
+            L.s.sie[m] = sie[base + m];
+            L.s.temp[m] = temp[base + m];
+            L.s.press[m] = press[base + m];
+          }
+          L.begin(sie_tot_in ? sie_tot_in[cell] : 0.0, sie_tot_in != nullptr,
+                  vfrac_tot_in ? vfrac_tot_in[cell] : 1.0, Tguess_in ? Tguess_in[cell] : 0.0,
+                  Tguess_in != nullptr);
+        }
+      }
+      next += __popc(idle_mask);
+    }
+    if (__ballot_sync(0xffffffffu, L.phase != mix::PH_IDLE) == 0u) break;
+    if (L.wants_eval()) mix::eval_round<NM>(eos, L.mode, L.Tq, L.rq, L.s.rhobar, L.s.press, eq, pq);
+    __syncwarp();
+    if (L.phase != mix::PH_IDLE) L.advance(eq, pq);
+    __syncwarp();
+  }
+  if (stats) {
+    __syncthreads();
+    for (int k = threadIdx.x; k < SGX_PTE_NSTATS; k += blockDim.x)
+      if (s_hist[k]) atomicAdd(&stats[k], (unsigned long long)s_hist[k]);
+  }
+}
+#endif // __CUDACC__
+
+} // namespace sgx
+#endif // SGX_PTE_SM_CUH_

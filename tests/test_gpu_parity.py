@@ -421,6 +421,83 @@ def test_pte_rhot_parity(pkg, ref, torch_cuda, which):
 
 
 @pytest.mark.parametrize("which", ["test_params", "default_params"])
+def test_pte_rhot_state_machine_equals_percell_kernel(pkg, torch_cuda, which, monkeypatch):
+    """The lane-refill state-machine kernel (csrc/sgx_pte_sm.cuh) executes, per cell, the same
+    floating-point operations as the straight per-cell transcription of PTESolver(): states,
+    status words and residuals must be bit-identical, ragged sizes included."""
+    torch = torch_cuda
+    L, W = pkg._lib, pkg.workloads
+    params = pkg.closure.test_pte_params() if which == "test_params" else pkg.closure.MixParams()
+    g3 = pkg.closure.set_eos_3mat_analytic()
+    sie0 = []
+    for m in range(3):
+        o = torch.empty(1, dtype=torch.float64, device="cuda")
+        g3[m].InternalEnergyFromDensityTemperature(dev([W.PTE_RHO[m]]), dev([W.PTE_T]), o, 1)
+        sie0.append(float(o.item()))
+    for n in (1, 31, 33, 4097, (1 << 16) + 5):
+        outs = {}
+        for variant in ("percell", "sm"):
+            monkeypatch.setenv("SGX_PTE_KERNEL", variant)
+            state = W.pte_state_torch(n, sie0, torch.device("cuda"), start=0)
+            status = torch.zeros(n, dtype=torch.int64, device="cuda")
+            resid = torch.zeros(n, dtype=torch.float64, device="cuda")
+            stats = torch.zeros(L.PTE_NSTATS, dtype=torch.int64, device="cuda")
+            pkg.closure.pte_solve(L.PTE_RHOT, g3, *state, params=params, status=status,
+                                  residual=resid, stats=stats)
+            torch.cuda.synchronize()
+            outs[variant] = [a.cpu().numpy() for a in state] + [
+                status.cpu().numpy(), resid.cpu().numpy(), stats.cpu().numpy()]
+        for a, b, nm in zip(outs["percell"], outs["sm"],
+                            ("rho", "vfrac", "sie", "temp", "press", "status", "residual", "stats")):
+            assert a.tobytes() == b.tobytes(), f"n={n} {which}: {nm} differs between kernels"
+
+
+@pytest.mark.parametrize("nmat", [1, 2, 4])
+def test_pte_rhot_generic_mixtures(pkg, ref, torch_cuda, nmat):
+    """Runtime-dispatched mixtures (the Variant path): 1, 2 and 4 materials drawn from ideal
+    gases (test/test_pte_ideal.cpp's family) and the analytic solids, library-default
+    MixParams; SolverStatus identical to the reference, states within 1e-10."""
+    torch = torch_cuda
+    L, W = pkg._lib, pkg.workloads
+    g3, r3 = pkg.closure.set_eos_3mat_analytic(), ref.set_eos_3mat()
+    gi = [pkg.IdealGas(0.4, 7.16e6), pkg.IdealGas(2.0 / 3.0, 1.2e7)]
+    ri = [ref.IdealGas(0.4, 7.16e6), ref.IdealGas(2.0 / 3.0, 1.2e7)]
+    rho_nom = {0: 8.93, 1: 1.89, 2: 2.5, 3: 1.0e-1, 4: 5.0e-2}
+    pick = {1: [3], 2: [3, 4], 4: [0, 3, 2, 4]}[nmat]
+    geos = [(g3 + gi)[k] for k in pick]
+    reos = [(r3 + ri)[k] for k in pick]
+    n = 1 << 13
+    vfrac_h = W.pte_vfracs(n, nmat=nmat)
+    rho_h = np.tile(np.array([rho_nom[k] for k in pick]), (n, 1))
+    temp_h = np.full((n, nmat), 600.0)
+    sie_h = np.stack([reos[m].eval(L.E_FROM_RHO_T, rho_h[:, m].copy(), temp_h[:, m].copy())
+                      for m in range(nmat)], axis=1).copy()
+    # pressures set from the state as test/test_pte_ideal.cpp:93 does: IdealGas prefers
+    # pressure input (eos_ideal.hpp:227-229), so press is a live guess for those materials
+    press_h = np.stack([reos[m].eval(L.P_FROM_RHO_E, rho_h[:, m].copy(), sie_h[:, m].copy())
+                        for m in range(nmat)], axis=1).copy()
+    press_h[: n // 4] = 0.0  # and the degenerate all-zero guess
+    vf_ref = vfrac_h.copy()
+    state_d = [dev(a) for a in (rho_h, vfrac_h, sie_h, temp_h, press_h)]
+    params = pkg.closure.MixParams()
+    st_r, _, _ = ref.pte_solve(L.PTE_RHOT, reos, rho_h, vf_ref, sie_h, temp_h, press_h, params,
+                               nthreads=0)
+    status = torch.zeros(n, dtype=torch.int64, device="cuda")
+    pkg.closure.pte_solve(L.PTE_RHOT, geos, *state_d, params=params, status=status)
+    torch.cuda.synchronize()
+    dg = pkg.closure.decode_status(status.cpu().numpy().view(np.uint64))
+    dr = pkg.closure.decode_status(st_r)
+    for k in ("converged", "slow_convergence_detected", "niter", "max_line_niter"):
+        assert (dg[k] == dr[k]).all(), f"nmat={nmat}: {k} differs"
+    conv = dr["converged"]
+    assert conv.mean() >= 0.9
+    print(f"nmat={nmat}: niter histogram {np.bincount(dr['niter'].astype(int))}")
+    for got, want, nm in zip(state_d, (rho_h, vf_ref, sie_h, temp_h, press_h),
+                             ("rho", "vfrac", "sie", "temp", "press")):
+        assert_rel(got.cpu().numpy()[conv], want[conv], PTE_TOL, f"nmat={nmat} PTE state {nm}")
+
+
+@pytest.mark.parametrize("which", ["test_params", "default_params"])
 def test_pte_pt_parity(pkg, ref, torch_cuda, which):
     """PTESolverPT inverts every material with regula_falsi at xtol = ytol = 1e-8
     (eos_gruneisen.hpp:521, eos_davis.hpp:488,574), so every state update carries ~1e-8 of

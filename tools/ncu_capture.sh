@@ -14,7 +14,7 @@ for t in $TARGETS; do
     root)   KRE='eval_kernel'; LG=24;;
     rhosie) KRE='eval_kernel'; LG=24;;
     ideal)  KRE='eval_kernel'; LG=24;;
-    pte)    KRE='pte_kernel'; LG=22;;
+    pte)    KRE='pte_'; LG=22;;
     helm)   KRE='helm_'; LG=22;;
   esac
   python tests/prof_driver.py $t $LG > $OUT/prof_${t}_${TAG}_plain.log 2>&1 || { echo "plain run of $t failed"; tail -5 $OUT/prof_${t}_${TAG}_plain.log; continue; }
