@@ -22,9 +22,9 @@ static int launch_sm(const EosSet &set, const MixParamsDev &prm, double *rho, do
                      double *sie, double *temp, double *press, const double *sie_tot,
                      const double *vfrac_tot, const double *Tguess, uint64_t *status,
                      double *residual, uint64_t *stats, int64_t ncell, cudaStream_t s) {
-  // 2 blocks x 4 warps per SM resident; each warp owns a contiguous range of >= 32 cells
-  const int threads = 128;
-  int64_t warps = (int64_t)sm_count() * 2 * (threads / 32);
+  // one block of kSmThreads per SM; each warp owns a contiguous range of >= 32 cells
+  const int threads = kSmThreads;
+  int64_t warps = (int64_t)sm_count() * (threads / 32);
   const int64_t min_warps = (ncell + 31) / 32;
   if (warps > min_warps) warps = min_warps;
   const int64_t blocks = (warps + threads / 32 - 1) / (threads / 32);

@@ -502,8 +502,19 @@ struct RhoTLane {
 #ifdef __CUDACC__
 // One lane per cell, one warp per contiguous range of `cells_per_warp` cells; a lane that
 // finishes its cell stores it and pulls the next one of the range.
+//
+// Rounds are block-synchronous (one barrier per round) and the Newton cycle is aligned to
+// the block's round counter r: the dv-perturbed Jacobian evaluation happens when r % 3 == 0,
+// the dT-perturbed one when r % 3 == 1, the full-step TestUpdate when r % 3 == 2.  A lane
+// entering the Newton loop out of step (fresh from Init, or after line-search rounds) skips
+// at most two rounds.  So in any round nearly all lanes of ALL warps of the SM run the same
+// handler: the handlers execute with full warps, and the 16 warps walk the same stretch of
+// SASS at the same time, which is what lets a 160 KB loop body live with the instruction
+// cache (profiles/r1e: unaligned, 75 % of stall samples were instruction fetch and the
+// handlers ran with 5 of 32 lanes).
+constexpr int kSmThreads = 512;
 template <int NM, class Acc>
-__global__ void __launch_bounds__(128, 2)
+__global__ void __launch_bounds__(kSmThreads, 1)
     pte_rhot_sm_kernel(const __grid_constant__ EosSet set,
                        const __grid_constant__ MixParamsDev prm, double *__restrict__ rho,
                        double *__restrict__ vfrac, double *__restrict__ sie,
@@ -535,7 +546,7 @@ __global__ void __launch_bounds__(128, 2)
     L.rq[m] = 1.0;
     L.s.rhobar[m] = 1.0;
   }
-  while (true) {
+  for (unsigned r = 0;; ++r) {
     const bool idle = (L.phase == mix::PH_IDLE);
     const unsigned idle_mask = __ballot_sync(0xffffffffu, idle);
     if (idle_mask) {
@@ -581,10 +592,13 @@ __global__ void __launch_bounds__(128, 2)
       }
       next += __popc(idle_mask);
     }
-    if (__ballot_sync(0xffffffffu, L.phase != mix::PH_IDLE) == 0u) break;
-    if (L.wants_eval()) mix::eval_round<NM>(eos, L.mode, L.Tq, L.rq, L.s.rhobar, L.s.press, eq, pq);
+    // block-wide round barrier; also the termination vote
+    if (!__syncthreads_or(L.phase != mix::PH_IDLE)) break;
+    const bool hold = (L.phase == mix::PH_J1) && (r % 3u != 0u); // wait for the Newton beat
+    if (L.wants_eval() && !hold)
+      mix::eval_round<NM>(eos, L.mode, L.Tq, L.rq, L.s.rhobar, L.s.press, eq, pq);
     __syncwarp();
-    if (L.phase != mix::PH_IDLE) L.advance(eq, pq);
+    if (L.phase != mix::PH_IDLE && !hold) L.advance(eq, pq);
     __syncwarp();
   }
   if (stats) {
