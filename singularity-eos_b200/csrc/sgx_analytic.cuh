@@ -25,6 +25,16 @@ constexpr unsigned long TQ_BMOD = 1ul << 5;
 
 #define SGX_MYMAX(a, b) ((a) > (b) ? (a) : (b)) // eos_ideal.hpp:32
 
+// The density-only terms of a Mie-Grueneisen-form model, e(rho,T) = Es + f(T, Ts) and
+// P(rho,e) = Ps + rho*Gamma*(e - Es).  The PTE kernels evaluate several temperatures at one
+// density (Jacobian dT column, the T-guess bisection); staging the evaluation as
+// rho_part() + *_from_part() lets them reuse these terms.  The staged form performs exactly
+// the operations of the one-shot functions in the same order, so results
+// are bit-identical whichever way a value is obtained.
+struct RhoPart {
+  double Ts, Es, Ps, rG; // reference temperature / energy / pressure curves, rho*Gamma
+};
+
 // ---------------------------------------------------------------------------------------
 struct IdealGas {
   double Cv, gm1;
@@ -79,6 +89,17 @@ struct IdealGas {
     if (output & TQ_CV) cv = cv_from_rho_e(rho, sie);
     return true;
   }
+  // staged form (no density-only terms)
+  SGX_HD void rho_part(double, RhoPart &p) const { p.Ts = p.Es = p.Ps = p.rG = 0.0; }
+  SGX_HD double e_from_part(const RhoPart &, double rho, double T) const {
+    return e_from_rho_T(rho, T);
+  }
+  SGX_HD double P_from_part(const RhoPart &, double rho, double sie) const {
+    return P_from_rho_e(rho, sie);
+  }
+  SGX_HD double cv_from_part(const RhoPart &, double rho, double sie) const {
+    return cv_from_rho_e(rho, sie);
+  }
   // bounds used by the PTE solvers (EosBase defaults)
   SGX_HD double MinimumDensity() const { return 0; }
   SGX_HD double MinimumTemperature() const { return 0; }
@@ -105,8 +126,8 @@ struct Gruneisen {
   SGX_D double e_from_rho_T(double, double temp, double * = nullptr) const {
     return Cv * (temp - T0);
   }
-  // eos_gruneisen.hpp:353-371
-  SGX_D double P_from_rho_e(const double rho_in, const double sie, double * = nullptr) const {
+  // eos_gruneisen.hpp:353-371, staged: Hugoniot reference curves, then the thermal term
+  SGX_D void rho_part(const double rho_in, RhoPart &p) const {
     const double rho = stdmin(rho_in, rho_max);
     double P_H, E_H;
     if (rho >= rho0) {
@@ -118,7 +139,22 @@ struct Gruneisen {
       P_H = P0 + pow2i(C0) * (rho - rho0);
       E_H = 0.;
     }
-    return P_H + Gamma(rho) * rho * (sie - E_H);
+    p.Ps = P_H;
+    p.Es = E_H;
+    p.rG = Gamma(rho) * rho;
+    p.Ts = T0;
+  }
+  SGX_D double e_from_part(const RhoPart &, double, const double temp) const {
+    return Cv * (temp - T0);
+  }
+  SGX_D double P_from_part(const RhoPart &p, double, const double sie) const {
+    return p.Ps + p.rG * (sie - p.Es);
+  }
+  SGX_D double cv_from_part(const RhoPart &, double, double) const { return Cv; }
+  SGX_D double P_from_rho_e(const double rho_in, const double sie, double * = nullptr) const {
+    RhoPart p;
+    rho_part(rho_in, p);
+    return P_from_part(p, rho_in, sie);
   }
   SGX_D double P_from_rho_T(const double rho_in, const double temp, double * = nullptr) const {
     const double rho = stdmin(rho_in, rho_max);
@@ -300,6 +336,24 @@ struct DavisReactants {
     const double tmp = pow(power_base, i1pa);
     return Ts(rho) * tmp;
   }
+  // staged form of :76-84 (e), :92-97 (P), :129-139 (cv)
+  SGX_D void rho_part(const double rho, RhoPart &p) const {
+    p.Ts = Ts(rho);
+    p.Es = Es(rho);
+    p.Ps = Ps(rho);
+    p.rG = Gamma(rho) * rho;
+  }
+  SGX_D double e_from_part(const RhoPart &p, double, const double temp) const {
+    return p.Es + Cv0 * p.Ts * i1pa * (pow(ratio(temp, p.Ts), 1.0 + alpha) - 1.0);
+  }
+  SGX_D double P_from_part(const RhoPart &p, double, const double sie) const {
+    return p.Ps + p.rG * (sie - p.Es);
+  }
+  SGX_D double cv_from_part(const RhoPart &p, double, const double sie) const {
+    const double power_base = ratio(1.0 + alpha, p.Ts * Cv0) * (sie - p.Es) + 1.0;
+    if (power_base <= 0) return 0.;
+    return ratio(Cv0, pow(power_base, -alpha * i1pa));
+  }
   SGX_D double e_from_rho_T(const double rho, const double temp, double * = nullptr) const {
     const double t_s = Ts(rho);
     return Es(rho) + Cv0 * t_s * i1pa * (pow(ratio(temp, t_s), 1.0 + alpha) - 1.0);
@@ -382,6 +436,10 @@ struct DavisReactants {
 // ---------------------------------------------------------------------------------------
 struct DavisProducts {
   double a, b, k, n, aon, vc, pc, Cv;
+  // pow(2, -a*b/n) * pc * vc / (Cv*(k-1+a)): the density-independent factor of Ts (:381-391),
+  // evaluated once on the host at create time (the reference evaluates it with the host libm
+  // on every call)
+  double Ts_coef;
   static constexpr unsigned long preferred_input = TQ_DENSITY | TQ_SIE;
   static constexpr int nlambda = 0;
 
@@ -406,7 +464,7 @@ struct DavisProducts {
   SGX_D double Ts(const double rho) const {
     if (rho <= 0) return 0.;
     const double vvc = ratio(1.0, rho * vc);
-    return pow(2.0, -a * ratio(b, n)) * pc * ratio(vc, Cv * (k - 1 + a)) *
+    return Ts_coef *
            ratio(pow(0.5 * (pow(vvc, n) + pow(vvc, -n)), aon * (1 - b)),
                  pow(vvc, k - 1.0 + a * (1 - b)));
   }
@@ -414,6 +472,20 @@ struct DavisProducts {
   SGX_D double T_from_rho_e(const double rho, const double sie, double * = nullptr) const {
     return Ts(rho) + ratio(sie - Es(rho), Cv);
   }
+  // staged form of :235-240 (e), :248-253 (P)
+  SGX_D void rho_part(const double rho, RhoPart &p) const {
+    p.Ts = Ts(rho);
+    p.Es = Es(rho);
+    p.Ps = Ps(rho);
+    p.rG = rho * Gamma(rho);
+  }
+  SGX_D double e_from_part(const RhoPart &p, double, const double temp) const {
+    return Cv * (temp - p.Ts) + p.Es;
+  }
+  SGX_D double P_from_part(const RhoPart &p, double, const double sie) const {
+    return p.Ps + p.rG * (sie - p.Es);
+  }
+  SGX_D double cv_from_part(const RhoPart &, double, double) const { return Cv; }
   SGX_D double e_from_rho_T(const double rho, const double temp, double * = nullptr) const {
     return Cv * (temp - Ts(rho)) + Es(rho);
   }

@@ -658,6 +658,7 @@ int sgx_eos_create_davis_products(double a, double b, double k, double n, double
   d.vc = vc;
   d.pc = pc;
   d.Cv = Cv;
+  d.Ts_coef = std::pow(2.0, -a * ratio(b, n)) * pc * ratio(vc, Cv * (k - 1 + a));
   *out = e;
   return SGX_OK;
 }

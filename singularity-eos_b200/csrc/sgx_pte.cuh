@@ -134,6 +134,32 @@ struct DynEos {
       return;
     }
   }
+  // staged evaluation (sgx_analytic.cuh RhoPart)
+  __device__ inline void rho_part(int m, double rho, RhoPart &p) const {
+    switch (set.e[m].kind) {
+    case 0:
+      set.e[m].ideal.rho_part(rho, p);
+      return;
+    case 1:
+      set.e[m].gr.rho_part(rho, p);
+      return;
+    case 2:
+      set.e[m].dr.rho_part(rho, p);
+      return;
+    default:
+      set.e[m].dp.rho_part(rho, p);
+      return;
+    }
+  }
+  SGX_D double e_from_part(int m, const RhoPart &p, double rho, double T) const {
+    SGX_EOS_DISPATCH(m, e_from_part(p, rho, T))
+  }
+  SGX_D double P_from_part(int m, const RhoPart &p, double rho, double sie) const {
+    SGX_EOS_DISPATCH(m, P_from_part(p, rho, sie))
+  }
+  SGX_D double cv_from_part(int m, const RhoPart &p, double rho, double sie) const {
+    SGX_EOS_DISPATCH(m, cv_from_part(p, rho, sie))
+  }
   // same, restricted to the models whose PreferredInput() includes pressure (only those
   // reach it through GetSieCvFromTAndPreferred, :603-612): keeps the solids' nested root
   // finders out of the RhoT kernels
@@ -189,6 +215,24 @@ struct Mix3GrDrDp {
     }
   }
   SGX_D void rho_e_from_P_T_pressure_preferred(int, double, double, double &, double &) const {}
+  __device__ inline void rho_part(int m, double rho, RhoPart &p) const {
+    if (m == 0) {
+      set.e[0].gr.rho_part(rho, p);
+    } else if (m == 1) {
+      set.e[1].dr.rho_part(rho, p);
+    } else {
+      set.e[2].dp.rho_part(rho, p);
+    }
+  }
+  SGX_D double e_from_part(int m, const RhoPart &p, double rho, double T) const {
+    SGX_MIX3(e_from_part(p, rho, T))
+  }
+  SGX_D double P_from_part(int m, const RhoPart &p, double rho, double sie) const {
+    SGX_MIX3(P_from_part(p, rho, sie))
+  }
+  SGX_D double cv_from_part(int m, const RhoPart &p, double rho, double sie) const {
+    SGX_MIX3(cv_from_part(p, rho, sie))
+  }
 #undef SGX_MIX3
 };
 

@@ -20,7 +20,7 @@
 //   A_LO / A_HI / A_BIS  ApproxTemperatureFromRhoMatU  :790-847   (e only)
 //   G_NEWTON             GetTguess newton_step         :547-560   (e and cv)
 //   INIT_EP              InitBase                      :627-662   (e and P)
-//   J1, J2               PTESolverRhoT::Jacobian       :1042-1105 (dv- and dT-perturbed e, P)
+//   J                    PTESolverRhoT::Jacobian       :1042-1105 (dv- and dT-perturbed e, P)
 //   TU                   PTESolverRhoT::TestUpdate     :1155-1187 (e, then P from sie=u/rhobar)
 #ifndef SGX_PTE_SM_CUH_
 #define SGX_PTE_SM_CUH_
@@ -40,8 +40,7 @@ enum SmPhase : int {
   PH_A_BIS,
   PH_G_NEWTON,
   PH_INIT_EP,
-  PH_J1,
-  PH_J2,
+  PH_J,
   PH_TU,
   // pure-compute phases (run back to back inside advance())
   PH_A_CHECK,
@@ -53,18 +52,28 @@ enum SmPhase : int {
   PH_FINISH
 };
 
-enum SmMode : int { MODE_E = 0, MODE_EP = 1, MODE_ECV = 2, MODE_TU = 3 };
+enum SmMode : int { MODE_E = 0, MODE_EP = 1, MODE_ECV = 2, MODE_TU = 3, MODE_J = 4 };
 
-// The one place the materials' EOS code is instantiated.
+// The one place the materials' EOS code is instantiated.  Evaluation is staged (RhoPart,
+// sgx_analytic.cuh): density-only curves first, then the temperature / energy terms.
 //   MODE_E   e = e(rho,T)
-//   MODE_EP  e, then GetPressureFromPreferred(m, rho, T, e, false)          (:583-597)
+//   MODE_EP  e, then GetPressureFromPreferred(m, rho, T, e, false)          (:583-597);
+//            keeps the density-only terms in `cache` (InitBase: rho is the state density)
 //   MODE_ECV GetSieCvFromTAndPreferred (both branches)                      (:601-620)
-//   MODE_TU  TestUpdate: sie = ratio(rhobar*e, rhobar), P from that sie     (:1175-1184)
+//   MODE_TU  TestUpdate: sie = ratio(rhobar*e, rhobar), P from that sie     (:1175-1184);
+//            keeps the density-only terms in `cache`
+//   MODE_J   Jacobian: (e,P) at the dv-perturbed densities rq and T = Tq, and (e2,P2) at the
+//            state densities rho_c -- whose density-only terms are in `cache` since the last
+//            TestUpdate / InitBase -- and T = Tq2                          (:1042-1075)
+// Every material here has specific internal energy among its preferred inputs, so
+// GetPressureFromPreferred always takes the P(rho, e) branch.
 template <int NM, class Eos>
 __device__ __forceinline__ void eval_round(const Eos &eos, const int mode, const double Tq,
-                                           const double (&rq)[NM], const double (&rb)[NM],
-                                           const double (&press_in)[NM], double (&eq)[NM],
-                                           double (&pq)[NM]) {
+                                           const double Tq2, const double (&rq)[NM],
+                                           const double (&rho_c)[NM], const double (&rb)[NM],
+                                           const double (&press_in)[NM], RhoPart (&cache)[NM],
+                                           double (&eq)[NM], double (&pq)[NM],
+                                           double (&eq2)[NM], double (&pq2)[NM]) {
 #pragma unroll
   for (int m = 0; m < NM; ++m) {
     if (mode == MODE_ECV && (eos.preferred(m) & TQ_PRESSURE)) {
@@ -84,17 +93,22 @@ __device__ __forceinline__ void eval_round(const Eos &eos, const int mode, const
       pq[m] = eos.cv_from_rho_e(m, rho_, sie_);
       continue;
     }
-    const double e = eos.e_from_rho_T(m, rq[m], Tq);
+    RhoPart part;
+    eos.rho_part(m, rq[m], part);
+    const double e = eos.e_from_part(m, part, rq[m], Tq);
     eq[m] = e;
     if (mode == MODE_ECV) {
-      pq[m] = eos.cv_from_rho_T(m, rq[m], Tq);
+      pq[m] = eos.cv_from_part(m, part, rq[m], e);
     } else if (mode != MODE_E) {
       double sie_for_p = e;
       if (mode == MODE_TU) sie_for_p = ratio(rb[m] * e, rb[m]);
-      if (eos.preferred(m) & TQ_SIE) {
-        pq[m] = eos.P_from_rho_e(m, rq[m], sie_for_p);
+      pq[m] = eos.P_from_part(m, part, rq[m], sie_for_p);
+      if (mode == MODE_J) {
+        const double e2 = eos.e_from_part(m, cache[m], rho_c[m], Tq2);
+        eq2[m] = e2;
+        pq2[m] = eos.P_from_part(m, cache[m], rho_c[m], e2);
       } else {
-        pq[m] = eos.P_from_rho_T(m, rq[m], Tq);
+        cache[m] = part;
       }
     }
   }
@@ -108,8 +122,9 @@ struct RhoTLane {
   SolverStatusDev st;
   int phase = PH_IDLE;
   int mode = MODE_E;
-  double Tq = 0.0;
+  double Tq = 0.0, Tq2 = 0.0;
   double rq[NM];
+  RhoPart cache[NM]; // density-only EOS terms at the state densities s.rho
   // ApproxTemperatureFromRhoMatU locals
   double u_tot, lTlo, lThi, ulo, uhi, alT;
   int aiter;
@@ -200,7 +215,9 @@ struct RhoTLane {
   // ---- the solver, cut at its evaluation points -----------------------------------------
   // Called after eval_round() (eq/pq hold the results for a lane in a result phase); runs
   // this lane's handlers until the next evaluation request or the end of the cell.
-  __device__ __forceinline__ void advance(const double (&eq)[NM], const double (&pq)[NM]) {
+  __device__ __forceinline__ void advance(const double (&eq)[NM], const double (&pq)[NM],
+                                          const double (&eq2)[NM],
+                                          const double (&pq2)[NM]) {
     const MixParamsDev &params = s.params_;
     while (true) {
       switch (phase) {
@@ -376,28 +393,22 @@ struct RhoTLane {
           const double vf_pert = s.vfrac[m] + dv;
           rq[m] = ratio(s.rhobar[m], vf_pert);
         }
-        request(MODE_EP, s.Tnorm * s.Tequil, PH_J1);
+        Tq2 = s.Tnorm * (s.Tequil + s.Tequil * params.derivative_eps);
+        request(MODE_J, s.Tnorm * s.Tequil, PH_J);
       } break;
-      case PH_J1: { // :1055-1063
-#pragma unroll
-        for (int m = 0; m < NM; m++) {
-          const double dv =
-              (s.vfrac[m] < 0.5 ? 1.0 : -1.0) * s.vfrac[m] * params.derivative_eps;
-          const double p_pert = ratio(pq[m], s.uscale);
-          s.dpdv[m] = stdmin(ratio((p_pert - s.press[m]), dv), -fabs(params.pte_max_dpdv));
-          s.dedv[m] = ratio(s.rhobar[m] * ratio(eq[m], s.uscale) - s.u[m], dv);
-        }
-        const double dT = s.Tequil * params.derivative_eps;
-        request_state_rho(MODE_EP, s.Tnorm * (s.Tequil + dT), PH_J2);
-      } break;
-      case PH_J2: { // :1064-1105, then Solve / ScaleDx / first TestUpdate (:2212-2226)
+      case PH_J: { // :1055-1105, then Solve / ScaleDx / first TestUpdate (:2212-2226)
         const double dT = s.Tequil * params.derivative_eps;
         double dedT_sum = 0.0;
 #pragma unroll
         for (int m = 0; m < NM; m++) {
-          const double p_pert = ratio(pq[m], s.uscale);
+          const double dv =
+              (s.vfrac[m] < 0.5 ? 1.0 : -1.0) * s.vfrac[m] * params.derivative_eps;
+          double p_pert = ratio(pq[m], s.uscale);
+          s.dpdv[m] = stdmin(ratio((p_pert - s.press[m]), dv), -fabs(params.pte_max_dpdv));
+          s.dedv[m] = ratio(s.rhobar[m] * ratio(eq[m], s.uscale) - s.u[m], dv);
+          p_pert = ratio(pq2[m], s.uscale);
           s.dpdT[m] = ratio((p_pert - s.press[m]), dT);
-          dedT_sum += ratio(s.rhobar[m] * ratio(eq[m], s.uscale) - s.u[m], dT);
+          dedT_sum += ratio(s.rhobar[m] * ratio(eq2[m], s.uscale) - s.u[m], dT);
         }
         s.AssembleJacobian(dedT_sum);
         const bool success = s.Solve();
@@ -504,10 +515,9 @@ struct RhoTLane {
 // finishes its cell stores it and pulls the next one of the range.
 //
 // Rounds are block-synchronous (one barrier per round) and the Newton cycle is aligned to
-// the block's round counter r: the dv-perturbed Jacobian evaluation happens when r % 3 == 0,
-// the dT-perturbed one when r % 3 == 1, the full-step TestUpdate when r % 3 == 2.  A lane
-// entering the Newton loop out of step (fresh from Init, or after line-search rounds) skips
-// at most two rounds.  So in any round nearly all lanes of ALL warps of the SM run the same
+// the block's round counter r: the Jacobian evaluations happen when r % 2 == 0, the
+// full-step TestUpdate when r % 2 == 1.  A lane entering the Newton loop out of step (fresh
+// from Init, or after line-search rounds) skips one round.  So in any round nearly all lanes of ALL warps of the SM run the same
 // handler: the handlers execute with full warps, and the 16 warps walk the same stretch of
 // SASS at the same time, which is what lets a 160 KB loop body live with the instruction
 // cache (profiles/r1e: unaligned, 75 % of stall samples were instruction fetch and the
@@ -538,11 +548,12 @@ __global__ void __launch_bounds__(kSmThreads, 1)
   int64_t next = warp * cells_per_warp;
   const int64_t end = (next + cells_per_warp < ncell) ? next + cells_per_warp : ncell;
   int64_t cell = -1;
-  double eq[NM], pq[NM];
+  double eq[NM], pq[NM], eq2[NM], pq2[NM];
 #pragma unroll
   for (int m = 0; m < NM; ++m) {
-    eq[m] = 0.0;
-    pq[m] = 0.0;
+    eq[m] = pq[m] = eq2[m] = pq2[m] = 0.0;
+    L.s.rho[m] = 1.0;
+    L.cache[m] = RhoPart{1.0, 0.0, 0.0, 0.0};
     L.rq[m] = 1.0;
     L.s.rhobar[m] = 1.0;
   }
@@ -594,11 +605,12 @@ __global__ void __launch_bounds__(kSmThreads, 1)
     }
     // block-wide round barrier; also the termination vote
     if (!__syncthreads_or(L.phase != mix::PH_IDLE)) break;
-    const bool hold = (L.phase == mix::PH_J1) && (r % 3u != 0u); // wait for the Newton beat
+    const bool hold = (L.phase == mix::PH_J) && (r % 2u != 0u); // wait for the Newton beat
     if (L.wants_eval() && !hold)
-      mix::eval_round<NM>(eos, L.mode, L.Tq, L.rq, L.s.rhobar, L.s.press, eq, pq);
+      mix::eval_round<NM>(eos, L.mode, L.Tq, L.Tq2, L.rq, L.s.rho, L.s.rhobar, L.s.press,
+                          L.cache, eq, pq, eq2, pq2);
     __syncwarp();
-    if (L.phase != mix::PH_IDLE && !hold) L.advance(eq, pq);
+    if (L.phase != mix::PH_IDLE && !hold) L.advance(eq, pq, eq2, pq2);
     __syncwarp();
   }
   if (stats) {
