@@ -527,7 +527,8 @@ struct Base {
       } else {
         Pguess = stdmax(Pmin, stdmin(Pmax, P));
       }
-      eos.rho_e_from_P_T(m, Pguess, T, rho_, sie_);
+      // only models whose PreferredInput() includes pressure get here
+      eos.rho_e_from_P_T_pressure_preferred(m, Pguess, T, rho_, sie_);
       cv = eos.cv_from_rho_e(m, rho_, sie_);
     } else {
       sie_ = eos.e_from_rho_T(m, rho_, T);

@@ -17,25 +17,44 @@ static bool percell_variant() {
   return s && strcmp(s, "percell") == 0;
 }
 
+// Cells go through in chunks: init kernel -> scratch record -> state-machine kernel, both on
+// the caller's stream; the scratch is stream-ordered (cudaMallocAsync), (2*NM+1)*8 B/cell.
+static constexpr int64_t kPteChunk = int64_t(1) << 22;
+
 template <int NM, class Acc>
 static int launch_sm(const EosSet &set, const MixParamsDev &prm, double *rho, double *vfrac,
                      double *sie, double *temp, double *press, const double *sie_tot,
                      const double *vfrac_tot, const double *Tguess, uint64_t *status,
                      double *residual, uint64_t *stats, int64_t ncell, cudaStream_t s) {
-  // one block of kSmThreads per SM; each warp owns a contiguous range of >= 32 cells
-  const int threads = kSmThreads;
-  int64_t warps = (int64_t)sm_count() * (threads / 32);
-  const int64_t min_warps = (ncell + 31) / 32;
-  if (warps > min_warps) warps = min_warps;
-  const int64_t blocks = (warps + threads / 32 - 1) / (threads / 32);
-  warps = blocks * (threads / 32);
-  const int64_t cpw = (ncell + warps - 1) / warps;
-  pte_rhot_sm_kernel<NM, Acc><<<(unsigned)blocks, threads, 0, s>>>(
-      set, prm, rho, vfrac, sie, temp, press, sie_tot, vfrac_tot, Tguess,
-      reinterpret_cast<unsigned long long *>(status), residual,
-      reinterpret_cast<unsigned long long *>(stats), ncell, cpw);
-  count_launch();
-  SGX_CUDA_OK(cudaGetLastError());
+  const int64_t chunk = ncell < kPteChunk ? ncell : kPteChunk;
+  double *init = nullptr;
+  SGX_CUDA_OK(cudaMallocAsync(&init, (size_t)chunk * (2 * NM + 1) * sizeof(double), s));
+  for (int64_t c0 = 0; c0 < ncell; c0 += chunk) {
+    const int64_t n = (ncell - c0) < chunk ? (ncell - c0) : chunk;
+    const int64_t o = c0 * NM;
+    const LaunchCfg ci = stream_cfg(n, 256, 4);
+    pte_rhot_init_kernel<NM, Acc><<<ci.blocks, ci.threads, 0, s>>>(
+        set, prm, rho + o, vfrac + o, sie + o, temp + o, press + o,
+        sie_tot ? sie_tot + c0 : nullptr, vfrac_tot ? vfrac_tot + c0 : nullptr,
+        Tguess ? Tguess + c0 : nullptr, init, n);
+    // one block of kSmThreads per SM; each warp owns a contiguous range of >= 32 cells
+    const int threads = kSmThreads;
+    int64_t warps = (int64_t)sm_count() * (threads / 32);
+    const int64_t min_warps = (n + 31) / 32;
+    if (warps > min_warps) warps = min_warps;
+    const int64_t blocks = (warps + threads / 32 - 1) / (threads / 32);
+    warps = blocks * (threads / 32);
+    const int64_t cpw = (n + warps - 1) / warps;
+    pte_rhot_sm_kernel<NM, Acc><<<(unsigned)blocks, threads, 0, s>>>(
+        set, prm, rho + o, vfrac + o, sie + o, temp + o, press + o,
+        sie_tot ? sie_tot + c0 : nullptr, vfrac_tot ? vfrac_tot + c0 : nullptr, init,
+        status ? reinterpret_cast<unsigned long long *>(status) + c0 : nullptr,
+        residual ? residual + c0 : nullptr, reinterpret_cast<unsigned long long *>(stats), n,
+        cpw);
+    count_launch(2);
+    SGX_CUDA_OK(cudaGetLastError());
+  }
+  SGX_CUDA_OK(cudaFreeAsync(init, s));
   return SGX_OK;
 }
 

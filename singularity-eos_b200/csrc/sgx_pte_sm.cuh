@@ -16,9 +16,15 @@
 //   * a lane whose cell is finished stores it and takes the next cell of its warp's contiguous
 //     cell range at once, so iteration-count differences between cells no longer idle lanes.
 //
-// Evaluation points, in the order a cell visits them (reference line numbers):
-//   A_LO / A_HI / A_BIS  ApproxTemperatureFromRhoMatU  :790-847   (e only)
-//   G_NEWTON             GetTguess newton_step         :547-560   (e and cv)
+// The solve is split in two kernels:
+//   pte_rhot_init_kernel  ApproxTemperatureFromRhoMatU (:790-847) and GetTguess (:500-581).
+//                         Every cell takes the same path here (2 + 10 bisection steps, one
+//                         Newton step), so plain thread-per-cell code is already converged;
+//                         the 12 energies of the bisection share one density, so the
+//                         density-only EOS terms are computed once (RhoPart).  Leaves
+//                         Tguess, vfrac[], rho[] in a 2*NM+1 doubles/cell scratch record.
+//   pte_rhot_sm_kernel    everything from InitBase's first EOS call on, as the state machine.
+// Evaluation points of the state machine (reference line numbers):
 //   INIT_EP              InitBase                      :627-662   (e and P)
 //   J                    PTESolverRhoT::Jacobian       :1042-1105 (dv- and dT-perturbed e, P)
 //   TU                   PTESolverRhoT::TestUpdate     :1155-1187 (e, then P from sie=u/rhobar)
@@ -35,31 +41,21 @@ namespace mix {
 enum SmPhase : int {
   PH_IDLE = 0,
   // phases entered with eval_round() results ready
-  PH_A_LO,
-  PH_A_HI,
-  PH_A_BIS,
-  PH_G_NEWTON,
   PH_INIT_EP,
   PH_J,
   PH_TU,
   // pure-compute phases (run back to back inside advance())
-  PH_A_CHECK,
-  PH_INIT0,
-  PH_G_BEGIN,
-  PH_G_AFTER,
   PH_NEWTON_TOP,
   PH_AFTER_LS,
   PH_FINISH
 };
 
-enum SmMode : int { MODE_E = 0, MODE_EP = 1, MODE_ECV = 2, MODE_TU = 3, MODE_J = 4 };
+enum SmMode : int { MODE_EP = 1, MODE_TU = 3, MODE_J = 4 };
 
 // The one place the materials' EOS code is instantiated.  Evaluation is staged (RhoPart,
 // sgx_analytic.cuh): density-only curves first, then the temperature / energy terms.
-//   MODE_E   e = e(rho,T)
 //   MODE_EP  e, then GetPressureFromPreferred(m, rho, T, e, false)          (:583-597);
 //            keeps the density-only terms in `cache` (InitBase: rho is the state density)
-//   MODE_ECV GetSieCvFromTAndPreferred (both branches)                      (:601-620)
 //   MODE_TU  TestUpdate: sie = ratio(rhobar*e, rhobar), P from that sie     (:1175-1184);
 //            keeps the density-only terms in `cache`
 //   MODE_J   Jacobian: (e,P) at the dv-perturbed densities rq and T = Tq, and (e2,P2) at the
@@ -71,47 +67,69 @@ template <int NM, class Eos>
 __device__ __forceinline__ void eval_round(const Eos &eos, const int mode, const double Tq,
                                            const double Tq2, const double (&rq)[NM],
                                            const double (&rho_c)[NM], const double (&rb)[NM],
-                                           const double (&press_in)[NM], RhoPart (&cache)[NM],
-                                           double (&eq)[NM], double (&pq)[NM],
-                                           double (&eq2)[NM], double (&pq2)[NM]) {
+                                           RhoPart (&cache)[NM], double (&eq)[NM],
+                                           double (&pq)[NM], double (&eq2)[NM],
+                                           double (&pq2)[NM]) {
 #pragma unroll
   for (int m = 0; m < NM; ++m) {
-    if (mode == MODE_ECV && (eos.preferred(m) & TQ_PRESSURE)) {
-      // GetSieCvFromTAndPreferred, pressure-preferring branch (:603-612)
-      const double Pmin = eos.MinimumPressure(m);
-      const double Pmax = eos.MaximumPressureAtTemperature(m, Tq);
-      const double P = press_in[m];
-      double Pguess;
-      if (bad_value(P)) {
-        Pguess = 0.5 * (Pmin + Pmax);
-      } else {
-        Pguess = stdmax(Pmin, stdmin(Pmax, P));
-      }
-      double rho_ = rq[m], sie_ = 0.0;
-      eos.rho_e_from_P_T_pressure_preferred(m, Pguess, Tq, rho_, sie_);
-      eq[m] = sie_;
-      pq[m] = eos.cv_from_rho_e(m, rho_, sie_);
-      continue;
-    }
     RhoPart part;
     eos.rho_part(m, rq[m], part);
     const double e = eos.e_from_part(m, part, rq[m], Tq);
     eq[m] = e;
-    if (mode == MODE_ECV) {
-      pq[m] = eos.cv_from_part(m, part, rq[m], e);
-    } else if (mode != MODE_E) {
-      double sie_for_p = e;
-      if (mode == MODE_TU) sie_for_p = ratio(rb[m] * e, rb[m]);
-      pq[m] = eos.P_from_part(m, part, rq[m], sie_for_p);
-      if (mode == MODE_J) {
-        const double e2 = eos.e_from_part(m, cache[m], rho_c[m], Tq2);
-        eq2[m] = e2;
-        pq2[m] = eos.P_from_part(m, cache[m], rho_c[m], e2);
-      } else {
-        cache[m] = part;
-      }
+    double sie_for_p = e;
+    if (mode == MODE_TU) sie_for_p = ratio(rb[m] * e, rb[m]);
+    pq[m] = eos.P_from_part(m, part, rq[m], sie_for_p);
+    if (mode == MODE_J) {
+      const double e2 = eos.e_from_part(m, cache[m], rho_c[m], Tq2);
+      eq2[m] = e2;
+      pq2[m] = eos.P_from_part(m, cache[m], rho_c[m], e2);
+    } else {
+      cache[m] = part;
     }
   }
+}
+
+// ApproxTemperatureFromRhoMatU (:790-847) with the density-only terms hoisted: the same
+// operations as mix::ApproxTemperatureFromRhoMatU (sgx_pte.cuh), in the same order.
+template <int NM, class Eos>
+__device__ inline double ApproxTemperatureStaged(const Eos &eos, const double u_tot,
+                                                 const double *rho, const double *vfrac) {
+  constexpr double minimum_temperature = 1.e-9;
+  constexpr double maximum_temperature = 1.e9;
+  RhoPart part[NM];
+#pragma unroll
+  for (int m = 0; m < NM; m++)
+    eos.rho_part(m, rho[m], part[m]);
+  auto ufunc = [&](const double T) {
+    double usum = 0.0;
+#pragma unroll
+    for (int m = 0; m < NM; m++) {
+      usum += rho[m] * vfrac[m] * eos.e_from_part(m, part[m], rho[m], T);
+    }
+    return usum;
+  };
+  double ulo = ufunc(minimum_temperature);
+  if (u_tot < ulo) return minimum_temperature;
+  double uhi = ufunc(maximum_temperature);
+  if (u_tot > uhi) return maximum_temperature;
+  double lTlo = fastmath::lg(minimum_temperature);
+  double lThi = fastmath::lg(maximum_temperature);
+  int iter = 0;
+  constexpr int max_iter = 10;
+  while (lThi - lTlo > 0.01 && iter < max_iter) {
+    const double lT = 0.5 * (lTlo + lThi);
+    const double uT = ufunc(fastmath::pow2(lT));
+    if (uT < u_tot) {
+      lTlo = lT;
+      ulo = uT;
+    } else {
+      lThi = lT;
+      uhi = uT;
+    }
+    iter++;
+  }
+  const double alpha = ratio((u_tot - ulo), (uhi - ulo));
+  return fastmath::pow2((1.0 - alpha) * lTlo + alpha * lThi);
 }
 
 // One lane's cell: the reference solver object plus the program counter and the few locals
@@ -121,16 +139,10 @@ struct RhoTLane {
   RhoT<NM, Eos> s;
   SolverStatusDev st;
   int phase = PH_IDLE;
-  int mode = MODE_E;
+  int mode = MODE_EP;
   double Tq = 0.0, Tq2 = 0.0;
   double rq[NM];
   RhoPart cache[NM]; // density-only EOS terms at the state densities s.rho
-  // ApproxTemperatureFromRhoMatU locals
-  double u_tot, lTlo, lThi, ulo, uhi, alT;
-  int aiter;
-  // GetTguess locals
-  double Tguess;
-  int gi;
   // PTESolver locals
   double err, err_old, gradfdx, scale, err_first;
   bool close_enough;
@@ -176,10 +188,14 @@ struct RhoTLane {
     request_state_rho(MODE_TU, s.Tnorm * s.Tequil, PH_TU);
   }
 
-  // ---- cell entry (test/test_pte.cpp:188-198) ------------------------------------------
-  // State arrays are already loaded into s.rho .. s.press by the kernel.
+  // ---- cell entry ------------------------------------------------------------------------
+  // The kernel has loaded the caller's state into s.rho .. s.press.  The init kernel
+  // (pte_rhot_init_kernel below) already ran ApproxTemperatureFromRhoMatU and GetTguess for
+  // this cell and left Tguess and the volume fractions / densities GetTguess settled on;
+  // here: the cell totals (test/test_pte.cpp:188-195) and the scalings of InitBase (:627-640).
   SGX_D void begin(const double sie_tot_in, const bool have_sie_tot, const double vfrac_tot,
-                   const double Tguess_in, const bool have_Tguess) {
+                   const double Tguess, const double (&vfrac_init)[NM],
+                   const double (&rho_init)[NM]) {
     st = SolverStatusDev();
     s.niter = 0;
     double sie_tot = 0.0, rho_tot = 0.0;
@@ -193,24 +209,19 @@ struct RhoTLane {
     if (have_sie_tot) sie_tot = sie_tot_in;
     s.sie_total = sie_tot;
     s.vfrac_total = vfrac_tot;
-    if (have_Tguess) {
-      s.Tnorm = Tguess_in;
-      phase = PH_INIT0;
-    } else {
-      u_tot = rho_tot * sie_tot;
-      request_state_rho(MODE_E, 1.e-9, PH_A_LO);
-    }
-  }
-  SGX_D bool wants_eval() const { return phase != PH_IDLE && phase < PH_A_CHECK; }
-
-  // plain left-to-right sum of rho*vfrac*e (the ufunc lambda, :801-808)
-  SGX_D double approx_usum(const double (&eq)[NM]) const {
-    double usum = 0.0;
+    s.InitRhoBarandRho();
+    const double utotal = s.rho_total * s.sie_total;
+    s.uscale = stdmax(fabs(utotal), 1.0e-14);
+    s.utotal_scale = ratio(utotal, s.uscale);
 #pragma unroll
-    for (int m = 0; m < NM; m++)
-      usum += s.rho[m] * s.vfrac[m] * eq[m];
-    return usum;
+    for (int m = 0; m < NM; ++m) {
+      s.vfrac[m] = vfrac_init[m];
+      s.rho[m] = rho_init[m];
+    }
+    s.Tnorm = Tguess;
+    request_state_rho(MODE_EP, Tguess, PH_INIT_EP);
   }
+  SGX_D bool wants_eval() const { return phase != PH_IDLE && phase < PH_NEWTON_TOP; }
 
   // ---- the solver, cut at its evaluation points -----------------------------------------
   // Called after eval_round() (eq/pq hold the results for a lane in a result phase); runs
@@ -221,118 +232,6 @@ struct RhoTLane {
     const MixParamsDev &params = s.params_;
     while (true) {
       switch (phase) {
-      // ===== ApproxTemperatureFromRhoMatU (:790-847), Tguess = 0 ========================
-      case PH_A_LO: {
-        ulo = approx_usum(eq);
-        if (u_tot < ulo) {
-          s.Tnorm = 1.e-9;
-          phase = PH_INIT0;
-        } else {
-          request(MODE_E, 1.e9, PH_A_HI); // rq still holds the input densities
-        }
-      } break;
-      case PH_A_HI: {
-        uhi = approx_usum(eq);
-        if (u_tot > uhi) {
-          s.Tnorm = 1.e9;
-          phase = PH_INIT0;
-        } else {
-          lTlo = fastmath::lg(1.e-9);
-          lThi = fastmath::lg(1.e9);
-          aiter = 0;
-          phase = PH_A_CHECK;
-        }
-      } break;
-      case PH_A_BIS: {
-        const double uT = approx_usum(eq);
-        if (uT < u_tot) {
-          lTlo = alT;
-          ulo = uT;
-        } else {
-          lThi = alT;
-          uhi = uT;
-        }
-        aiter++;
-        phase = PH_A_CHECK;
-      } break;
-      case PH_A_CHECK: {
-        if (lThi - lTlo > 0.01 && aiter < 10) {
-          alT = 0.5 * (lTlo + lThi);
-          request(MODE_E, fastmath::pow2(alT), PH_A_BIS);
-        } else {
-          const double alpha = ratio((u_tot - ulo), (uhi - ulo));
-          s.Tnorm = fastmath::pow2((1.0 - alpha) * lTlo + alpha * lThi);
-          phase = PH_INIT0;
-        }
-      } break;
-      // ===== InitBase (:627-662) up to GetTguess ========================================
-      case PH_INIT0: {
-        s.InitRhoBarandRho();
-        const double utotal = s.rho_total * s.sie_total;
-        s.uscale = stdmax(fabs(utotal), 1.0e-14);
-        s.utotal_scale = ratio(utotal, s.uscale);
-        // GetTguess (:500-581)
-        if (s.Tnorm > 0.0) {
-          Tguess = s.Tnorm;
-        } else {
-          Tguess = params.default_tguess;
-#pragma unroll
-          for (int m = 0; m < NM; ++m)
-            Tguess = stdmax(Tguess, s.temp[m]);
-        }
-        gi = 0;
-        phase = PH_G_BEGIN;
-      } break;
-      case PH_G_BEGIN: {
-        if (params.iterate_t_guess) {
-#pragma unroll
-          for (int m = 0; m < NM; ++m)
-            rq[m] = stdmin(s.rho[m], s.eos.MaximumDensity(m));
-          request(MODE_ECV, Tguess, PH_G_NEWTON);
-        } else {
-          phase = PH_G_AFTER;
-        }
-      } break;
-      case PH_G_NEWTON: { // newton_step (:547-560)
-        double dudt = 0;
-        double usum = 0;
-#pragma unroll
-        for (int m = 0; m < NM; ++m) {
-          usum += s.rhobar[m] * eq[m];
-          dudt += s.rhobar[m] * pq[m];
-        }
-        const double Tnew = Tguess - ratio((usum - s.utotal_scale * s.uscale), dudt);
-        Tguess = stdmin(params.temperature_limit, stdmax(Tguess, Tnew));
-        phase = PH_G_AFTER;
-      } break;
-      case PH_G_AFTER: { // rest of one pass of the `for (i < 3)` loop (:565-580)
-#pragma unroll
-        for (int m = 0; m < NM; ++m)
-          Tguess = stdmax(s.eos.MinimumTemperature(m), Tguess);
-        bool bad_vfrac_guess = s.SetVfracFromT(Tguess);
-        if (!bad_vfrac_guess) {
-#pragma unroll
-          for (int m = 0; m < NM; ++m)
-            s.rho[m] = ratio(s.rhobar[m], s.vfrac[m]);
-          for (int m = 0; m < NM; ++m) {
-            const double rho_min = s.eos.RhoPmin(m, Tguess);
-            if (s.rho[m] < rho_min) {
-              bad_vfrac_guess = true;
-              break;
-            }
-          }
-        }
-        if (bad_vfrac_guess) {
-          Tguess *= 10.0;
-          gi++;
-        }
-        if (bad_vfrac_guess && gi < 3) {
-          phase = PH_G_BEGIN;
-        } else {
-          s.Tnorm = Tguess;
-          request_state_rho(MODE_EP, Tguess, PH_INIT_EP);
-        }
-      } break;
       // ===== rest of InitBase + PTESolverRhoT::Init (:947-984) =========================
       case PH_INIT_EP: {
 #pragma unroll
@@ -502,7 +401,7 @@ struct RhoTLane {
       default:
         break;
       }
-      if (phase < PH_A_CHECK) break; // IDLE or waiting for an evaluation
+      if (phase < PH_NEWTON_TOP) break; // IDLE or waiting for an evaluation
     }
   }
 };
@@ -511,6 +410,66 @@ struct RhoTLane {
 } // namespace mix
 
 #ifdef __CUDACC__
+// Init kernel: one thread per cell, every lane on the same path.  test/test_pte.cpp:188-198
+// (cell totals, Tguess = ApproxTemperatureFromRhoMatU unless the caller supplies one), then
+// InitBase up to and including GetTguess (:627-640, :500-581).  The caller's arrays are only
+// read; the record {Tguess, vfrac[NM], rho[NM]} goes to `init`.
+template <int NM, class Acc>
+__global__ void __launch_bounds__(256)
+    pte_rhot_init_kernel(const __grid_constant__ EosSet set,
+                         const __grid_constant__ MixParamsDev prm,
+                         const double *__restrict__ rho, const double *__restrict__ vfrac,
+                         const double *__restrict__ sie, const double *__restrict__ temp,
+                         const double *__restrict__ press,
+                         const double *__restrict__ sie_tot_in,
+                         const double *__restrict__ vfrac_tot_in,
+                         const double *__restrict__ Tguess_in, double *__restrict__ init,
+                         const int64_t ncell) {
+  const Acc eos(set);
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t nthr = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t t = tid; t < ncell; t += nthr) {
+    mix::Base<NM, NM, Acc> s(eos, prm);
+    const int64_t base = t * NM;
+#pragma unroll
+    for (int m = 0; m < NM; ++m) {
+      s.rho[m] = rho[base + m];
+      s.vfrac[m] = vfrac[base + m];
+      s.sie[m] = sie[base + m];
+      s.temp[m] = temp[base + m];
+      s.press[m] = press[base + m];
+    }
+    double sie_tot = 0.0, rho_tot = 0.0;
+#pragma unroll
+    for (int m = 0; m < NM; m++) {
+      const double rhobar = s.rho[m] * s.vfrac[m];
+      rho_tot += rhobar;
+      sie_tot += rhobar * s.sie[m];
+    }
+    sie_tot /= rho_tot;
+    if (sie_tot_in) sie_tot = sie_tot_in[t];
+    s.sie_total = sie_tot;
+    s.vfrac_total = vfrac_tot_in ? vfrac_tot_in[t] : 1.0;
+    if (Tguess_in) {
+      s.Tnorm = Tguess_in[t];
+    } else {
+      s.Tnorm = mix::ApproxTemperatureStaged<NM>(eos, rho_tot * sie_tot, s.rho, s.vfrac);
+    }
+    s.InitRhoBarandRho();
+    const double utotal = s.rho_total * s.sie_total;
+    s.uscale = stdmax(fabs(utotal), 1.0e-14);
+    s.utotal_scale = ratio(utotal, s.uscale);
+    const double Tguess = s.GetTguess();
+    double *rec = init + t * (2 * NM + 1);
+    rec[0] = Tguess;
+#pragma unroll
+    for (int m = 0; m < NM; ++m) {
+      rec[1 + m] = s.vfrac[m];
+      rec[1 + NM + m] = s.rho[m];
+    }
+  }
+}
+
 // One lane per cell, one warp per contiguous range of `cells_per_warp` cells; a lane that
 // finishes its cell stores it and pulls the next one of the range.
 //
@@ -531,7 +490,7 @@ __global__ void __launch_bounds__(kSmThreads, 1)
                        double *__restrict__ temp, double *__restrict__ press,
                        const double *__restrict__ sie_tot_in,
                        const double *__restrict__ vfrac_tot_in,
-                       const double *__restrict__ Tguess_in,
+                       const double *__restrict__ init,
                        unsigned long long *__restrict__ status, double *__restrict__ residual,
                        unsigned long long *__restrict__ stats, const int64_t ncell,
                        const int64_t cells_per_warp) {
@@ -596,9 +555,15 @@ __global__ void __launch_bounds__(kSmThreads, 1)
             L.s.temp[m] = temp[base + m];
             L.s.press[m] = press[base + m];
           }
+          const double *rec = init + cell * (2 * NM + 1);
+          double vfrac_init[NM], rho_init[NM];
+#pragma unroll
+          for (int m = 0; m < NM; ++m) {
+            vfrac_init[m] = rec[1 + m];
+            rho_init[m] = rec[1 + NM + m];
+          }
           L.begin(sie_tot_in ? sie_tot_in[cell] : 0.0, sie_tot_in != nullptr,
-                  vfrac_tot_in ? vfrac_tot_in[cell] : 1.0, Tguess_in ? Tguess_in[cell] : 0.0,
-                  Tguess_in != nullptr);
+                  vfrac_tot_in ? vfrac_tot_in[cell] : 1.0, rec[0], vfrac_init, rho_init);
         }
       }
       next += __popc(idle_mask);
@@ -607,8 +572,8 @@ __global__ void __launch_bounds__(kSmThreads, 1)
     if (!__syncthreads_or(L.phase != mix::PH_IDLE)) break;
     const bool hold = (L.phase == mix::PH_J) && (r % 2u != 0u); // wait for the Newton beat
     if (L.wants_eval() && !hold)
-      mix::eval_round<NM>(eos, L.mode, L.Tq, L.Tq2, L.rq, L.s.rho, L.s.rhobar, L.s.press,
-                          L.cache, eq, pq, eq2, pq2);
+      mix::eval_round<NM>(eos, L.mode, L.Tq, L.Tq2, L.rq, L.s.rho, L.s.rhobar, L.cache, eq,
+                          pq, eq2, pq2);
     __syncwarp();
     if (L.phase != mix::PH_IDLE && !hold) L.advance(eq, pq, eq2, pq2);
     __syncwarp();
