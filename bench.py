@@ -38,8 +38,9 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cells", type=int, default=N_LOOKUP, help="cells per GPU for lookup configs")
-    ap.add_argument("--pte-cells", type=int, default=1 << 24, help="PTE cells per GPU")
-    ap.add_argument("--pte-full", action="store_true", help="PTE at 2^27 cells per GPU")
+    ap.add_argument("--pte-cells", type=int, default=1 << 27,
+                    help="PTE cells per GPU (BASELINE.json configs[4]: 2^27)")
+    ap.add_argument("--pte-full", action="store_true", help="(default now) PTE at 2^27 cells")
     ap.add_argument("--quick", action="store_true", help="headline config only")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     return ap.parse_args()
@@ -47,51 +48,79 @@ def parse():
 
 # ------------------------------------------------------------------------------------------
 class ClockSampler:
-    """nvidia-smi clocks + throttle reasons DURING the timed region."""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    """SM clock + clock-event (throttle) reasons sampled DURING the timed region through NVML
+    (nvidia_ml_py, ~2 ms period: the headline region is only K x 0.5 ms long); summary() cuts
+    the stream into time windows.  Same quantities as the nvidia-smi clocks line of
+    B200_PROFILING.md."""
 
     def __init__(self, gpu_index):
         self.idx = gpu_index
-        self.rows = []
+        self.rows = []  # (t, sm_mhz, reasons bitmask)
+        self.max_mhz = None
         self._stop = threading.Event()
         self._t = None
+        self.nv = None
 
     def _run(self):
+        nv = self.nv
+        h = nv.nvmlDeviceGetHandleByIndex(self.idx)
+        try:
+            self.max_mhz = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+        except Exception:
+            pass
+        get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or \
+            getattr(nv, "nvmlDeviceGetCurrentClocksThrottleReasons")
         while not self._stop.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q,
-                                      "--format=csv,noheader,nounits"], capture_output=True,
-                                     text=True, timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([c.strip() for c in out.split(",")])
+                self.rows.append((time.perf_counter(),
+                                  float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)),
+                                  int(get_reasons(h))))
             except Exception:
                 pass
-            self._stop.wait(0.2)
+            self._stop.wait(0.002)
 
     def start(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            self.nv = nv
+        except Exception:
+            return
         self._t = threading.Thread(target=self._run, daemon=True)
         self._t.start()
 
     def stop(self):
         self._stop.set()
         if self._t:
-            self._t.join(timeout=6)
-        sm, mx, reasons = [], [], set()
-        for r in self.rows:
-            try:
-                sm.append(float(r[1]))
-                mx.append(float(r[2]))
-            except Exception:
+            self._t.join(timeout=5)
+
+    def summary(self, t0=None, t1=None):
+        # NVML clocks-event-reason bits (nvml.h)
+        bits = {"sw_power_cap": 0x4, "hw_slowdown": 0x8, "sw_thermal_slowdown": 0x20,
+                "hw_thermal_slowdown": 0x40}
+        sm, reasons = [], set()
+        for t, mhz, mask in self.rows:
+            if (t0 is not None and t < t0) or (t1 is not None and t > t1):
                 continue
-            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown",
-                                "sw_power_cap"), r[4:8]):
-                if v.lower().startswith("active"):
+            sm.append(mhz)
+            for name, bit in bits.items():
+                if mask & bit:
                     reasons.add(name)
-        return {"sm_mhz": float(np.median(sm)) if sm else None,
-                "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
-                "samples": len(sm)}
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def headline_traffic(cells):
+    """DRAM bytes per launch of the headline kernel from the committed `ncu --set full`
+    capture (profiles/headline_traffic.json), if it was taken at this launch size."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "headline_traffic.json")) as fh:
+            t = json.load(fh)
+        if int(t["cells"]) == int(cells):
+            return float(t["dram_bytes_read"]) + float(t["dram_bytes_write"])
+    except Exception:
+        pass
+    return None
 
 
 def measured_peak_gbs():
@@ -166,19 +195,22 @@ def run_ours(args):
 
     # ---- headline: config 2, P(rho,T) with (lRho,lT) lambda write-back: 40 B/cell ------
     sampler = ClockSampler(local)
-    launches0 = lib.sgx_launch_count()
     if rank == 0:
         sampler.start()
+        time.sleep(0.1)
+    launches0 = lib.sgx_launch_count()
+    t_head0 = time.perf_counter()
     secs = time_steps(torch, lambda: eos_rt.PressureFromDensityTemperature(rho, T, out, n, lam),
                       K, Wu, dist)
-    clocks = sampler.stop() if rank == 0 else None
+    t_head1 = time.perf_counter()
     launches = lib.sgx_launch_count() - launches0 - Wu
     cells_total = n * world * K
     value = cells_total / secs / 1e9
     bytes_per_cell = 40
     achieved = n * bytes_per_cell / (secs / K) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "frac": achieved / peak, "traffic": headline_traffic(n),
+                "algorithmic_bytes_per_launch": n * bytes_per_cell, "peak_source": peak_src,
                 "kernel": "eval_kernel<P_FROM_RHO_T, SpinerRhoT, VEC>",
                 "algorithmic_bytes_per_cell": bytes_per_cell}
     results["spiner_rhot_P_rhoT_lambda"] = {"Gcells_per_s": value, "GBps_per_gpu": achieved,
@@ -285,7 +317,7 @@ def run_ours(args):
 
     # ---- config 5: PTE RhoT -------------------------------------------------------------
     if not args.quick:
-        npte = (1 << 27) if args.pte_full else args.pte_cells
+        npte = args.pte_cells
         g3 = pkg.closure.set_eos_3mat_analytic()
         sie0 = []
         for m in range(3):
@@ -312,9 +344,33 @@ def run_ours(args):
         st = stats.cpu().numpy()
         results["pte_rhot_3mat"] = {
             "cell_solves_per_s": npte * world * ks / s, "cells_per_gpu": npte,
+            "mix_params": "test/test_pte.cpp:164-175 (tolerances 1e-16)",
             "converged_frac": float(st[1]) / max(1, float(st[0])),
             "niter_hist": [int(x) for x in st[8:24]],
+            "algorithmic_bytes_per_cell": 224,
             "note": "includes the 5-array state reset copy each step (in-place solver)"}
+        # secondary: library-default MixParams, and PTESolverPT, on a 2^22-cell slice
+        nsec = min(npte, 1 << 22)
+        sec0 = [a[:nsec] for a in state0]
+        sec = [a[:nsec] for a in state]
+        prm_def = pkg.closure.MixParams()
+
+        def pte_def():
+            for a, b in zip(sec, sec0):
+                a.copy_(b)
+            pkg.closure.PTESolverRhoT(g3, *sec, params=prm_def)
+        s = time_steps(torch, pte_def, ks, 1, dist)
+        results["pte_rhot_3mat_default_mixparams"] = {
+            "cell_solves_per_s": nsec * world * ks / s, "cells_per_gpu": nsec}
+        npt = min(npte, 1 << 18)
+
+        def pte_pt():
+            for a, b in zip(sec, sec0):
+                a[:npt].copy_(b[:npt])
+            pkg.closure.PTESolverPT(g3, *[a[:npt] for a in sec], params=prm_def)
+        s = time_steps(torch, pte_pt, 2, 1, dist)
+        results["pte_pt_3mat_default_mixparams"] = {
+            "cell_solves_per_s": npt * world * 2 / s, "cells_per_gpu": npt}
         del state, state0, status
 
     # ---- e2e: host buffers through the C ABI (_host entry), H2D + D2H inside the timing --
@@ -343,6 +399,11 @@ def run_ours(args):
            "cells_per_step_per_gpu": ne,
            "api": "sgx_eos_eval_host(P_FROM_RHO_T) with pinned host arrays"}
 
+    clocks = None
+    if rank == 0:
+        sampler.stop()
+        clocks = sampler.summary(t_head0, t_head1)  # warm-up + timed region of the headline
+        clocks["all_configs"] = sampler.summary()
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K,
         "warmup": Wu, "ms_per_step": secs / K * 1e3, "higher_is_better": True,
@@ -385,9 +446,25 @@ def cpu_baseline(pkg, raw, sample, reps):
         t0 = time.perf_counter()
         eos.eval(L.P_FROM_RHO_T, rho, T, lam, nthreads=0)
         best = min(best, time.perf_counter() - t0)
-    return {"value": sample / best / 1e9, "unit": UNIT, "cores": cores, "kind": "reference",
-            "sample": f"{sample} cells of the headline workload, best of {reps}, OpenMP over the "
-                      "reference vector API (PORTABILITY_STRATEGY_NONE), g++ -O2"}
+    out = {"value": sample / best / 1e9, "unit": UNIT, "cores": cores, "kind": "reference",
+           "sample": f"{sample} cells of the headline workload, best of {reps}, OpenMP over the "
+                     "reference vector API (PORTABILITY_STRATEGY_NONE), g++ -O2"}
+    # config 5 beside it: the reference PTESolverRhoT on 2^17 cells of the same workload
+    try:
+        W = pkg.workloads
+        r3 = ref.set_eos_3mat()
+        sie0 = [r3[m].eval(L.E_FROM_RHO_T, [W.PTE_RHO[m]], [W.PTE_T])[0] for m in range(3)]
+        npte = 1 << 17
+        st0 = W.pte_state_np(npte, sie0)
+        t0 = time.perf_counter()
+        ref.pte_solve(L.PTE_RHOT, r3, *[a.copy() for a in st0], pkg.closure.test_pte_params(),
+                      nthreads=0)
+        dt = time.perf_counter() - t0
+        out["pte_rhot_cell_solves_per_s"] = npte / dt
+        out["pte_sample"] = f"{npte} cells, one pass, {cores} threads"
+    except Exception as exc:  # the headline baseline stands on its own
+        out["pte_error"] = repr(exc)
+    return out
 
 
 def run_reference(args):
