@@ -174,6 +174,8 @@ def run_ours(args):
     if world > 1:
         import torch.distributed as dist_mod
 
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"  # keep NCCL's version banner off stdout
         dist_mod.init_process_group("nccl", device_id=torch.device("cuda", local))
         dist = dist_mod
     pkg = g.load_package()
@@ -426,6 +428,15 @@ def run_ours(args):
 
 
 # ------------------------------------------------------------------------------------------
+def host_threads():
+    """Threads for the CPU legs: every core this process may run on (torchrun exports
+    OMP_NUM_THREADS=1, which would otherwise cap the OpenMP baseline at one thread)."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
 def cpu_baseline(pkg, raw, sample, reps):
     """The reference's own code (oracle/_ref) on the host cores, bounded sample of the headline
     workload.  This is the checker being *timed*, never part of the product path."""
@@ -439,12 +450,12 @@ def cpu_baseline(pkg, raw, sample, reps):
     eos = ref.SpinerRhoT(raw)
     rho, T = pkg.workloads.spiner_inputs(sample)
     lam = np.full((sample, 2), np.nan)
-    cores = ref.num_threads()
-    eos.eval(L.P_FROM_RHO_T, rho, T, lam, nthreads=0)
+    cores = host_threads()
+    eos.eval(L.P_FROM_RHO_T, rho, T, lam, nthreads=cores)
     best = 1e30
     for _ in range(reps):
         t0 = time.perf_counter()
-        eos.eval(L.P_FROM_RHO_T, rho, T, lam, nthreads=0)
+        eos.eval(L.P_FROM_RHO_T, rho, T, lam, nthreads=cores)
         best = min(best, time.perf_counter() - t0)
     out = {"value": sample / best / 1e9, "unit": UNIT, "cores": cores, "kind": "reference",
            "sample": f"{sample} cells of the headline workload, best of {reps}, OpenMP over the "
@@ -458,7 +469,7 @@ def cpu_baseline(pkg, raw, sample, reps):
         st0 = W.pte_state_np(npte, sie0)
         t0 = time.perf_counter()
         ref.pte_solve(L.PTE_RHOT, r3, *[a.copy() for a in st0], pkg.closure.test_pte_params(),
-                      nthreads=0)
+                      nthreads=cores)
         dt = time.perf_counter() - t0
         out["pte_rhot_cell_solves_per_s"] = npte / dt
         out["pte_sample"] = f"{npte} cells, one pass, {cores} threads"
@@ -489,14 +500,14 @@ def run_reference(args):
     rho, T = pkg.workloads.spiner_inputs(sample)
     lam = np.full((sample, 2), np.nan)
     K, Wu = args.steps, max(args.warmup, 1)
+    cores = host_threads()
     for _ in range(Wu):
-        eos.eval(L.P_FROM_RHO_T, rho, T, lam, nthreads=0)
+        eos.eval(L.P_FROM_RHO_T, rho, T, lam, nthreads=cores)
     t0 = time.perf_counter()
     for _ in range(K):
-        eos.eval(L.P_FROM_RHO_T, rho, T, lam, nthreads=0)
+        eos.eval(L.P_FROM_RHO_T, rho, T, lam, nthreads=cores)
     secs = time.perf_counter() - t0
     value = sample * K / secs / 1e9
-    cores = ref.num_threads()
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT,
         "n_gpus": args.gpus, "steps": K, "warmup": Wu, "ms_per_step": secs / K * 1e3,
