@@ -255,6 +255,7 @@ SGX_D double sum_neumaier(const double *data, const int n, const int offset, con
                           const Op &op) {
   double sum = 0;
   double c = 0;
+#pragma unroll
   for (int i = 0; i < n; ++i) {
     if (iskip >= 0 && i == iskip) continue;
     const double x = op(data[i + offset]);
@@ -274,115 +275,159 @@ SGX_D double sum_neumaier(const double *data, const int n, const int offset = 0,
 }
 
 // Column-pivoted Householder QR solve for n >= 3 (the reference delegates to Eigen's
-// colPivHouseholderQr, :266-273).  a is row-major n x n (destroyed), b -> x.
-template <int NMAX>
-__device__ inline void qr_solve(const int n, double *a, double *b) {
-  int perm[NMAX];
-  double cn[NMAX];
-  for (int j = 0; j < n; ++j) {
+// colPivHouseholderQr, :266-273).  a is row-major N x N (destroyed), b -> x.
+// N is a compile-time constant and every loop is unrolled with static indices: the pivot
+// column is brought to position k by predicated swaps, never by a[i*n + piv], so the
+// matrix stays in registers (a dynamically indexed member would push the whole solver
+// object into local memory).  Arithmetic and its order are unchanged.
+template <int N>
+__device__ __forceinline__ void qr_solve_static(double *a, double *b) {
+  int perm[N];
+#pragma unroll
+  for (int j = 0; j < N; ++j)
     perm[j] = j;
-    double s = 0;
-    for (int i = 0; i < n; ++i)
-      s += a[i * n + j] * a[i * n + j];
-    cn[j] = s;
-  }
-  for (int k = 0; k < n; ++k) {
-    // pivot: largest remaining column norm (recomputed: n is tiny)
+#pragma unroll
+  for (int k = 0; k < N; ++k) {
+    // pivot: largest remaining column norm (recomputed: N is tiny)
     int piv = k;
     double best = -1;
-    for (int j = k; j < n; ++j) {
+#pragma unroll
+    for (int j = k; j < N; ++j) {
       double s = 0;
-      for (int i = k; i < n; ++i)
-        s += a[i * n + j] * a[i * n + j];
-      cn[j] = s;
+#pragma unroll
+      for (int i = k; i < N; ++i)
+        s += a[i * N + j] * a[i * N + j];
       if (s > best) {
         best = s;
         piv = j;
       }
     }
-    if (piv != k) {
-      for (int i = 0; i < n; ++i) {
-        const double t = a[i * n + k];
-        a[i * n + k] = a[i * n + piv];
-        a[i * n + piv] = t;
+#pragma unroll
+    for (int j = k + 1; j < N; ++j) {
+      if (piv == j) {
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+          const double t = a[i * N + k];
+          a[i * N + k] = a[i * N + j];
+          a[i * N + j] = t;
+        }
+        const int tp = perm[k];
+        perm[k] = perm[j];
+        perm[j] = tp;
       }
-      const int tp = perm[k];
-      perm[k] = perm[piv];
-      perm[piv] = tp;
     }
-    // Householder vector for column k, rows k..n-1
-    const double c0 = a[k * n + k];
+    // Householder vector for column k, rows k..N-1
+    const double c0 = a[k * N + k];
     double tail = 0;
-    for (int i = k + 1; i < n; ++i)
-      tail += a[i * n + k] * a[i * n + k];
-    if (tail == 0.0) continue; // already triangular in this column
-    double beta = sqrt(c0 * c0 + tail);
-    if (c0 >= 0) beta = -beta;
-    const double tau = (beta - c0) / beta;
-    const double inv = 1.0 / (c0 - beta);
-    // v = [1, a[k+1..]/ (c0-beta)]
-    for (int i = k + 1; i < n; ++i)
-      a[i * n + k] *= inv;
-    a[k * n + k] = beta;
-    // apply H = I - tau v v^T to the trailing columns and to b
-    for (int j = k + 1; j < n; ++j) {
-      double s = a[k * n + j];
-      for (int i = k + 1; i < n; ++i)
-        s += a[i * n + k] * a[i * n + j];
+#pragma unroll
+    for (int i = k + 1; i < N; ++i)
+      tail += a[i * N + k] * a[i * N + k];
+    if (tail != 0.0) { // else already triangular in this column
+      double beta = sqrt(c0 * c0 + tail);
+      if (c0 >= 0) beta = -beta;
+      const double tau = (beta - c0) / beta;
+      const double inv = 1.0 / (c0 - beta);
+      // v = [1, a[k+1..]/ (c0-beta)]
+#pragma unroll
+      for (int i = k + 1; i < N; ++i)
+        a[i * N + k] *= inv;
+      a[k * N + k] = beta;
+      // apply H = I - tau v v^T to the trailing columns and to b
+#pragma unroll
+      for (int j = k + 1; j < N; ++j) {
+        double s = a[k * N + j];
+#pragma unroll
+        for (int i = k + 1; i < N; ++i)
+          s += a[i * N + k] * a[i * N + j];
+        s *= tau;
+        a[k * N + j] -= s;
+#pragma unroll
+        for (int i = k + 1; i < N; ++i)
+          a[i * N + j] -= s * a[i * N + k];
+      }
+      double s = b[k];
+#pragma unroll
+      for (int i = k + 1; i < N; ++i)
+        s += a[i * N + k] * b[i];
       s *= tau;
-      a[k * n + j] -= s;
-      for (int i = k + 1; i < n; ++i)
-        a[i * n + j] -= s * a[i * n + k];
+      b[k] -= s;
+#pragma unroll
+      for (int i = k + 1; i < N; ++i)
+        b[i] -= s * a[i * N + k];
     }
-    double s = b[k];
-    for (int i = k + 1; i < n; ++i)
-      s += a[i * n + k] * b[i];
-    s *= tau;
-    b[k] -= s;
-    for (int i = k + 1; i < n; ++i)
-      b[i] -= s * a[i * n + k];
   }
   // back substitution R y = Q^T b
-  double y[NMAX];
-  for (int i = n - 1; i >= 0; --i) {
+  double y[N];
+#pragma unroll
+  for (int i = N - 1; i >= 0; --i) {
     double s = b[i];
-    for (int j = i + 1; j < n; ++j)
-      s -= a[i * n + j] * y[j];
-    y[i] = s / a[i * n + i];
+#pragma unroll
+    for (int j = i + 1; j < N; ++j)
+      s -= a[i * N + j] * y[j];
+    y[i] = s / a[i * N + i];
   }
-  for (int j = 0; j < n; ++j)
-    b[perm[j]] = y[j];
+  // x[perm[j]] = y[j]
+#pragma unroll
+  for (int i = 0; i < N; ++i) {
+    double x = 0.0;
+#pragma unroll
+    for (int j = 0; j < N; ++j)
+      if (perm[j] == i) x = y[j];
+    b[i] = x;
+  }
 }
 
-// solve_Ax_b_wscr (:176-278)
-template <int NMAX>
-__device__ inline bool solve_Ax_b(const int n, double *a, double *b) {
-  for (int row = 0; row < n; ++row) {
-    double maxabs = 0;
-    for (int column = 0; column < n; ++column) {
-      maxabs = stdmax(fabs(a[row * n + column]), maxabs);
+// solve_Ax_b_wscr (:176-278), N a compile-time constant
+template <int N>
+__device__ __forceinline__ bool solve_Ax_b_static(double *a, double *b) {
+  bool nonzero_rows = true;
+#pragma unroll
+  for (int row = 0; row < N; ++row) {
+    if (nonzero_rows) { // the reference returns at the first all-zero row
+      double maxabs = 0;
+#pragma unroll
+      for (int column = 0; column < N; ++column) {
+        maxabs = stdmax(fabs(a[row * N + column]), maxabs);
+      }
+      if (maxabs == 0) {
+        nonzero_rows = false;
+      } else {
+#pragma unroll
+        for (int column = 0; column < N; ++column) {
+          a[row * N + column] /= maxabs;
+        }
+        b[row] /= maxabs;
+      }
     }
-    if (maxabs == 0) return false;
-    for (int column = 0; column < n; ++column) {
-      a[row * n + column] /= maxabs;
-    }
-    b[row] /= maxabs;
   }
-  if (n == 1) {
+  if (!nonzero_rows) return false;
+  if constexpr (N == 1) {
     b[0] = ratio(b[0], a[0]);
-  } else if (n == 2) {
+  } else if constexpr (N == 2) {
     const double det = a[0] * a[3] - a[1] * a[2];
     const double x0 = ratio(a[3] * b[0] - a[1] * b[1], det);
     const double x1 = ratio(a[0] * b[1] - a[2] * b[0], det);
     b[0] = x0;
     b[1] = x1;
   } else {
-    qr_solve<NMAX>(n, a, b);
+    qr_solve_static<N>(a, b);
   }
   bool retval = true;
-  for (int i = 0; i < n; ++i)
+#pragma unroll
+  for (int i = 0; i < N; ++i)
     if (!isfinite_ref(b[i])) retval = false;
   return retval;
+}
+
+// runtime-n front end (building-block entry sgx_solve_Ax_b)
+template <int NMAX>
+__device__ inline bool solve_Ax_b(const int n, double *a, double *b) {
+  if (n == 1) return solve_Ax_b_static<1>(a, b);
+  if (n == 2) return solve_Ax_b_static<2>(a, b);
+  if constexpr (NMAX >= 4) {
+    if (n == 4) return solve_Ax_b_static<4>(a, b);
+  }
+  return solve_Ax_b_static<3>(a, b);
 }
 
 // ApproxTemperatureFromRhoMatU (:790-847); lambdas are NullIndexer here.
@@ -619,7 +664,7 @@ struct Base {
 #pragma unroll
     for (int m = 0; m < NEQ; m++)
       dx[m] = residual[m];
-    return solve_Ax_b<NEQ>(NEQ, jacobian, dx);
+    return solve_Ax_b_static<NEQ>(jacobian, dx);
   }
 };
 
@@ -695,13 +740,14 @@ struct RhoT : public Base<NM, NM, Eos> {
   SGX_D void Residual() {
     const double esum = sum_neumaier(u, NM);
     residual[0] = utotal_scale - esum;
-    int ires = 1;
+    // residual[k], k = 1..NM-1, belongs to the k-th material other than ms (static indices:
+    // a runtime ires++ would force the solver object into local memory)
 #pragma unroll
-    for (int m = 0; m < NM; ++m) {
-      if (m == ms) continue;
-      residual[ires++] = press_at(ms) - press[m];
-    }
+    for (int k = 1; k < NM; ++k)
+      residual[k] = press_at(ms) - press_at(other(k));
   }
+  // the material of unknown / equation k >= 1 of the reduced system
+  SGX_D int other(const int k) const { return (k - 1 < ms) ? k - 1 : k; }
   SGX_D double press_at(const int i) const {
     double v = press[0];
 #pragma unroll
@@ -756,25 +802,16 @@ struct RhoT : public Base<NM, NM, Eos> {
       jacobian[i] = 0.0;
     const double dedv_s = pick(dedv, ms), dpdT_s = pick(dpdT, ms), dpdv_s = pick(dpdv, ms);
     jacobian[0] = dedT_sum;
-    int col = 1;
 #pragma unroll
-    for (int m = 0; m < NM; ++m) {
-      if (m == ms) continue;
-      jacobian[col++] = dedv[m] - dedv_s;
-    }
-    int row = 1;
+    for (int k = 1; k < NM; ++k)
+      jacobian[k] = pick(dedv, other(k)) - dedv_s;
 #pragma unroll
-    for (int m = 0; m < NM; m++) {
-      if (m == ms) continue;
-      jacobian[row * NM + 0] = dpdT[m] - dpdT_s;
-      int c = 1;
+    for (int row = 1; row < NM; ++row) {
+      const int m = other(row);
+      jacobian[row * NM + 0] = pick(dpdT, m) - dpdT_s;
 #pragma unroll
-      for (int mm = 0; mm < NM; ++mm) {
-        if (mm == ms) continue;
-        jacobian[row * NM + c] = (mm == m) ? dpdv[m] + dpdv_s : dpdv_s;
-        c++;
-      }
-      row++;
+      for (int c = 1; c < NM; ++c)
+        jacobian[row * NM + c] = (c == row) ? pick(dpdv, m) + dpdv_s : dpdv_s;
     }
   }
   SGX_D static double pick(const double *a, const int i) {
@@ -790,7 +827,7 @@ struct RhoT : public Base<NM, NM, Eos> {
     int idx = 1;
 #pragma unroll
     for (int m = 0; m < NM; ++m) {
-      const double mydx = (m == ms) ? dalphaskip : dx[idx++];
+      const double mydx = (m == ms) ? dalphaskip : pick(dx, idx++);
       if (scale * mydx < -params_.vfrac_safety_fac * vfrac[m]) {
         scale = stdmin(scale, fabs(params_.vfrac_safety_fac * ratio(vfrac[m], mydx)));
       }
@@ -803,7 +840,7 @@ struct RhoT : public Base<NM, NM, Eos> {
           stdmax(eos.RhoPmin(m, Tnorm * Tequil), eos.RhoPmin(m, Tnorm * Tnew));
       const double alpha_max = stdmin(1.0, ratio(rhobar[m], rho_min));
       if (alpha_max < vfrac[m]) continue; // NB: skips idx++ exactly like the reference
-      const double mydx = (m == ms) ? dalphaskip : dx[idx++];
+      const double mydx = (m == ms) ? dalphaskip : pick(dx, idx++);
       if (scale * mydx > 0.5 * (alpha_max - vfrac[m])) {
         scale = stdmin(ratio(0.5 * (alpha_max - vfrac[m]), mydx), scale);
       }
@@ -828,7 +865,7 @@ struct RhoT : public Base<NM, NM, Eos> {
 #pragma unroll
     for (int m = 0; m < NM; ++m) {
       if (ms == m) continue;
-      vfrac[m] = vtemp[m] + scale * dx[idx++];
+      vfrac[m] = vtemp[m] + scale * pick(dx, idx++);
     }
     const double vsum_others = sum_neumaier(vfrac, NM, 0, ms);
 #pragma unroll

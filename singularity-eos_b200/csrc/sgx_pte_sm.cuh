@@ -176,7 +176,7 @@ struct RhoTLane {
 #pragma unroll
     for (int m = 0; m < NM; ++m) {
       if (s.ms == m) continue;
-      s.vfrac[m] = s.vtemp[m] + scale_ * s.dx[idx++];
+      s.vfrac[m] = s.vtemp[m] + scale_ * s.pick(s.dx, idx++);
     }
     const double vsum_others = sum_neumaier(s.vfrac, NM, 0, s.ms);
 #pragma unroll
