@@ -21,7 +21,7 @@ static bool percell_variant() {
 // the caller's stream; the scratch is stream-ordered (cudaMallocAsync), (2*NM+1)*8 B/cell.
 static constexpr int64_t kPteChunk = int64_t(1) << 22;
 
-template <int NM, class Acc>
+template <int NM, class Acc, int THREADS = kSmThreads, int MINB = 1>
 static int launch_sm(const EosSet &set, const MixParamsDev &prm, double *rho, double *vfrac,
                      double *sie, double *temp, double *press, const double *sie_tot,
                      const double *vfrac_tot, const double *Tguess, uint64_t *status,
@@ -38,14 +38,14 @@ static int launch_sm(const EosSet &set, const MixParamsDev &prm, double *rho, do
         sie_tot ? sie_tot + c0 : nullptr, vfrac_tot ? vfrac_tot + c0 : nullptr,
         Tguess ? Tguess + c0 : nullptr, init, n);
     // one block of kSmThreads per SM; each warp owns a contiguous range of >= 32 cells
-    const int threads = kSmThreads;
-    int64_t warps = (int64_t)sm_count() * (threads / 32);
+    const int threads = THREADS;
+    int64_t warps = (int64_t)sm_count() * MINB * (threads / 32);
     const int64_t min_warps = (n + 31) / 32;
     if (warps > min_warps) warps = min_warps;
     const int64_t blocks = (warps + threads / 32 - 1) / (threads / 32);
     warps = blocks * (threads / 32);
     const int64_t cpw = (n + warps - 1) / warps;
-    pte_rhot_sm_kernel<NM, Acc><<<(unsigned)blocks, threads, 0, s>>>(
+    pte_rhot_sm_kernel<NM, Acc, THREADS, MINB><<<(unsigned)blocks, threads, 0, s>>>(
         set, prm, rho + o, vfrac + o, sie + o, temp + o, press + o,
         sie_tot ? sie_tot + c0 : nullptr, vfrac_tot ? vfrac_tot + c0 : nullptr, init,
         status ? reinterpret_cast<unsigned long long *>(status) + c0 : nullptr,

@@ -482,8 +482,8 @@ __global__ void __launch_bounds__(256)
 // cache (profiles/r1e: unaligned, 75 % of stall samples were instruction fetch and the
 // handlers ran with 5 of 32 lanes).
 constexpr int kSmThreads = 512;
-template <int NM, class Acc>
-__global__ void __launch_bounds__(kSmThreads, 1)
+template <int NM, class Acc, int THREADS = kSmThreads, int MINB = 1>
+__global__ void __launch_bounds__(THREADS, MINB)
     pte_rhot_sm_kernel(const __grid_constant__ EosSet set,
                        const __grid_constant__ MixParamsDev prm, double *__restrict__ rho,
                        double *__restrict__ vfrac, double *__restrict__ sie,
