@@ -219,6 +219,28 @@ def test_tablegen_matches_reference_generators(pkg, ref):
     # test/test_eos_vinet.cpp gold: P(rho0, T0) = 0, e(rho0, T0) = E0
     assert abs(rv.eval(L.P_FROM_RHO_T, [8.93], [298.0])[0]) < 1e-3
     assert abs(rv.eval(L.E_FROM_RHO_T, [8.93], [298.0])[0]) < 1e-3
+    # the full gold arrays of test/test_eos_vinet.cpp:80-107 (rho-sie lookups, tolerance 1e-12
+    # via array_compare, test/eos_unit_test_helpers.hpp:66-81)
+    rho0, T0, B0, A0, Cv0 = 8.93, 298.0, 1.3448466e12, 5.19245e-05, 0.383e7
+    dens = np.array([8.0, 8.5, 9.0, 8.93])
+    ener = np.array([2.0e8, 4.6e9, 4.7e9, 0.0])
+    gold = {
+        L.T_FROM_RHO_E: [6.638294350641033e+1, 1.42266691572769e+03, 1.52867838544081e+03, T0],
+        L.P_FROM_RHO_E: [-1.283459624233147e+11, 1.98538351697004e+10, 9.66446220551959e+10,
+                         0.0],
+        L.CV_FROM_RHO_E: [Cv0] * 4,
+        L.BMOD_FROM_RHO_E: [7.44411028807209e+11, 1.254880120063067e+12,
+                            1.613822819346433e+12, B0 + B0 * B0 * A0 * A0 / Cv0 / rho0 * T0],
+        L.GAMMA_FROM_RHO_E: [B0 * A0 / Cv0 / 8.0, B0 * A0 / Cv0 / 8.5, B0 * A0 / Cv0 / 9.0,
+                             B0 * A0 / Cv0 / rho0],
+    }
+    for method, want in gold.items():
+        got = rv.eval(method, dens, ener)
+        want = np.asarray(want)
+        # array_compare: |a-b| <= 1e-12 * max(|a|,|b|), with P(rho0, e0) = 0 compared absolutely
+        # against the pressure scale B0
+        scale = np.maximum(np.maximum(np.abs(got), np.abs(want)), 1e-3 * B0 * (want == 0))
+        assert (np.abs(got - want) <= 1e-12 * scale).all(), (L.METHOD_NAMES[method], got, want)
 
 
 def test_ref_spiner_classes_load_and_invert(pkg, ref):
