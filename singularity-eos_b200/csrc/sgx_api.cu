@@ -11,6 +11,7 @@
 //  * grid = (#SMs × resident blocks) so every SM streams from the first wave;
 //  * table gathers go through the read-only path and stay L2-resident (≤ 5 MiB per EOS,
 //    persisting access-policy window set at create time).
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <type_traits>
@@ -786,6 +787,13 @@ int sgx_eos_get_scalar(sgx_eos_t e, const char *name, double *out) {
   return SGX_OK;
 }
 
+// The one-thread-per-cell root find is the default; SGX_ROOT_KERNEL=flow selects the
+// warp-level flow kernel of sgx_spiner_root.cu (bit-identical, measured no faster)
+static bool per_thread_root_kernel() {
+  const char *v = getenv("SGX_ROOT_KERNEL");
+  return !(v && strcmp(v, "flow") == 0);
+}
+
 int sgx_eos_eval(sgx_eos_t e, int method, const double *in1, const double *in2, double *out,
                  int64_t n, double *lambda, int lambda_stride, sgx_stream_t stream) {
   int rc = check_handle(e);
@@ -807,6 +815,8 @@ int sgx_eos_eval(sgx_eos_t e, int method, const double *in1, const double *in2, 
   case SGX_EOS_DAVIS_PRODUCTS:
     return launch_eval(e->analytic.dp, method, in1, in2, out, n, nullptr, 0, s, 8);
   case SGX_EOS_SPINER_RHOT:
+    if (method == SGX_T_FROM_RHO_E && !per_thread_root_kernel())
+      return launch_rhot_T_from_rho_e_flow(e->rhot, in1, in2, out, n, lambda, lambda_stride, s);
     return launch_eval(e->rhot, method, in1, in2, out, n, lambda, lambda_stride, s, 8);
   case SGX_EOS_SPINER_RHOSIE:
     return launch_eval(e->rhosie, method, in1, in2, out, n, lambda, lambda_stride, s, 8);

@@ -30,6 +30,10 @@ if what in ("root", "all"):
     def cold():
         lam.fill_(float("nan")); rt.TemperatureFromDensityInternalEnergy(rho, sie, out, n, lam)
     timed("rhot_T_rhoe_cold", cold)
+    lam_w = lam.clone()  # holds the converged (lRho, lT) of the cold pass
+    def warm():
+        lam.copy_(lam_w); rt.TemperatureFromDensityInternalEnergy(rho, sie, out, n, lam)
+    timed("rhot_T_rhoe_warm", warm)
 if what in ("rhosie", "all"):
     rs = pkg.SpinerEOSDependsRhoSie(raw)
     lam1 = torch.full((n, 1), float("nan"), dtype=torch.float64, device=dev)

@@ -251,6 +251,36 @@ def test_spiner_rhot_root_find(pkg, ref, torch_cuda, raw, guess):
             assert_rel(lam_d.cpu().numpy(), lam_h, LOOKUP_TOL, f"RhoT lambda [{guess}]")
 
 
+@pytest.mark.parametrize("guess", ["nan", "warm", "null"])
+def test_root_flow_equals_per_thread_kernel(pkg, ref, torch_cuda, raw, guess, monkeypatch):
+    """The warp-level flow kernel (csrc/sgx_spiner_root.cu: setup / iterate-with-refill /
+    retire) performs, per cell, the per-thread root find's floating-point operations: T and the
+    lambda write-back must be bit-identical, for ragged sizes, off-table cells, warm and cold
+    starts, and a null lambda."""
+    torch = torch_cuda
+    L = pkg._lib
+    g, r = pkg.SpinerEOSDependsRhoT(raw), ref.SpinerRhoT(raw)
+    for n in (1, 31, 257, 5000, (1 << 17) + 3):
+        rho_h, T_h, sie_h = _rhot_sie_inputs(pkg, r, raw, max(n, 16))
+        rho_h, T_h, sie_h = rho_h[:n].copy(), T_h[:n].copy(), sie_h[:n].copy()
+        lam0 = np.full((n, 2), np.nan)
+        if guess == "warm":
+            r.eval(L.E_FROM_RHO_T, rho_h, T_h, lam0, nthreads=0)
+        outs = {}
+        for variant in ("perthread", "flow"):
+            monkeypatch.setenv("SGX_ROOT_KERNEL", variant)  # default is the per-thread kernel
+            rho_d, sie_d = dev(rho_h), dev(sie_h)
+            out = torch.full_like(rho_d, float("nan"))
+            lam_d = None if guess == "null" else dev(lam0.copy())
+            g._eval(L.T_FROM_RHO_E, rho_d, sie_d, out, n, lam_d)
+            torch.cuda.synchronize()
+            outs[variant] = (out.cpu().numpy(),
+                             None if lam_d is None else lam_d.cpu().numpy())
+        assert_bits(outs["flow"][0], outs["perthread"][0], f"T n={n} [{guess}]")
+        if guess != "null":
+            assert_bits(outs["flow"][1], outs["perthread"][1], f"lambda n={n} [{guess}]")
+
+
 def test_spiner_rhot_fill_eos(pkg, ref, torch_cuda, raw):
     torch = torch_cuda
     tq = pkg.thermalqs

@@ -11,7 +11,7 @@ for t in $TARGETS; do
   case $t in
     # prof_driver launches one e(rho,T) first, then the target kernel 4x: -s 1 skips the former
     lookup) KRE='eval_kernel'; LG=${LOOKUP_LG:-24};;
-    root)   KRE='eval_kernel'; LG=24;;
+    root)   KRE='eval_kernel|rhot_T_from'; LG=24;;
     rhosie) KRE='eval_kernel'; LG=24;;
     ideal)  KRE='eval_kernel'; LG=24;;
     pte)    KRE='pte_'; LG=22;;
