@@ -163,8 +163,8 @@ int build_helmholtz(const char *path, const sgx_helm_options *opt, sgx_eos_s *e)
 // FillEos vector overload (eos_base.hpp:503-518) for Helmholtz.  OUTPUT is a compile-time
 // mask for the two benchmarked modes (dead outputs and their arithmetic are pruned), 0 =
 // run-time mask.
-template <unsigned long OUTPUT>
-__global__ void __launch_bounds__(128)
+template <unsigned long OUTPUT, int MINB = 1>
+__global__ void __launch_bounds__(128, MINB)
     helm_fill_kernel(const __grid_constant__ HelmDev eos, double *__restrict__ rho,
                      double *__restrict__ T, double *__restrict__ en, double *__restrict__ P,
                      double *__restrict__ cv, double *__restrict__ bmod, const int64_t n,
@@ -282,8 +282,9 @@ int launch_helm_fill(sgx_eos_s *e, double *rho, double *T, double *en, double *P
   const LaunchCfg c = stream_cfg(n, 128, 8);
   constexpr unsigned long kModeI = TQ_SIE | TQ_PRESSURE | TQ_CV | TQ_BMOD;
   constexpr unsigned long kModeII = TQ_TEMPERATURE | TQ_PRESSURE | TQ_CV | TQ_BMOD;
+  // mode (i): 128 registers / 4 blocks per SM measured 6 % ahead of 204 registers / 2 blocks
   if (output == kModeI && T && en && P && cv && bmod) {
-    helm_fill_kernel<kModeI><<<c.blocks, c.threads, 0, s>>>(e->helm, rho, T, en, P, cv, bmod, n,
+    helm_fill_kernel<kModeI, 4><<<c.blocks, c.threads, 0, s>>>(e->helm, rho, T, en, P, cv, bmod, n,
                                                             output, lambda, stride, nullptr);
   } else if (output == kModeII && T && en && P && cv && bmod) {
     helm_fill_kernel<kModeII><<<c.blocks, c.threads, 0, s>>>(e->helm, rho, T, en, P, cv, bmod,
