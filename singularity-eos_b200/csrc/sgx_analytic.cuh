@@ -337,11 +337,43 @@ struct DavisReactants {
     return Ts(rho) * tmp;
   }
   // staged form of :76-84 (e), :92-97 (P), :129-139 (cv)
+  // Ps, Es, Ts, Gamma share y = 1 - rho0/rho, 4By and exp(4By); each is evaluated once here
+  // (same operands => same bits as the one-shot forms above, expressions kept literally)
   SGX_D void rho_part(const double rho, RhoPart &p) const {
-    p.Ts = Ts(rho);
-    p.Es = Es(rho);
-    p.Ps = Ps(rho);
-    p.rG = Gamma(rho) * rho;
+    if (rho <= 0) { // the one-shot forms' guards (:402-440); Gamma(rho < rho0) = G0
+      p.Ps = 0;
+      p.Es = 0;
+      p.Ts = T0;
+      p.rG = G0 * rho;
+      return;
+    }
+    const double rho0overrho = ratio(rho0, stdmax(rho, 0.));
+    const double y = 1.0 - rho0overrho;
+    const double phat = 0.25 * A2oB * rho0;
+    const double b4y = 4.0 * B * y;
+    const bool compressed = rho >= rho0;
+    const bool y_pos = y > 0.0;
+    double eb4y = 0.0;
+    if (!compressed || !y_pos) eb4y = exp(b4y);
+    if (compressed) {
+      p.Ps = phat *
+             (b4y + 0.5 * (pow2i(b4y) + onethird * (pow3i(b4y) + C * pow4i(b4y) * 0.25)) +
+              ratio(pow2i(y), pow4i(1 - y)));
+    } else {
+      p.Ps = phat * (eb4y - 1.0);
+    }
+    double e_s;
+    if (y_pos) {
+      const double z = rho * spvol0 - 1;
+      e_s = 0.5 * y * b4y *
+                (1.0 + onethird * b4y * (1.0 + 0.25 * b4y * (1.0 + C * 0.2 * b4y))) +
+            onethird * pow3i(z);
+    } else {
+      e_s = -y - ratio(1.0 - eb4y, 4.0 * B);
+    }
+    p.Es = e0 + P0 * (spvol0 - ratio(1.0, stdmax(rho, 0.))) + phat * spvol0 * e_s;
+    p.Ts = T0 * exp(-Z * y) * pow(rho0overrho, -G0 - Z);
+    p.rG = (compressed ? G0 + Z * y : G0) * rho;
   }
   SGX_D double e_from_part(const RhoPart &p, double, const double temp) const {
     return p.Es + Cv0 * p.Ts * i1pa * (pow(ratio(temp, p.Ts), 1.0 + alpha) - 1.0);
@@ -473,11 +505,26 @@ struct DavisProducts {
     return Ts(rho) + ratio(sie - Es(rho), Cv);
   }
   // staged form of :235-240 (e), :248-253 (P)
+  // Ts, Es, Ps and F share pow(vvc, +-n) and the cosh-like mixture; each distinct pow is
+  // evaluated once here (same function, same operands => same bits as the one-shot forms
+  // above, whose expressions and order are kept literally).
   SGX_D void rho_part(const double rho, RhoPart &p) const {
-    p.Ts = Ts(rho);
-    p.Es = Es(rho);
-    p.Ps = Ps(rho);
-    p.rG = rho * Gamma(rho);
+    if (rho <= 0) { // the one-shot forms' guards
+      p.Ts = 0.;
+      p.Es = 0.;
+      p.Ps = 0.;
+      p.rG = rho * (k - 1.0 + (1.0 - b) * 0.);
+      return;
+    }
+    const double vvc = ratio(1.0, rho * vc);
+    const double mix = 0.5 * (pow(vvc, n) + pow(vvc, -n));
+    const double mix_aon = pow(mix, aon);
+    const double Fv = 2.0 * ratio(a, pow(vvc, 2 * n) + 1.0);
+    p.Ts = Ts_coef * ratio(pow(mix, aon * (1 - b)), pow(vvc, k - 1.0 + a * (1 - b)));
+    const double ec = pc * ratio(vc, k - 1.0 + a);
+    p.Es = ratio(ec * mix_aon, pow(vvc, k - 1.0 + a));
+    p.Ps = pc * ratio(mix_aon, pow(vvc, k + a)) * ratio(k - 1.0 + Fv, k - 1.0 + a);
+    p.rG = rho * (k - 1.0 + (1.0 - b) * Fv);
   }
   SGX_D double e_from_part(const RhoPart &p, double, const double temp) const {
     return Cv * (temp - p.Ts) + p.Es;
