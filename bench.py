@@ -475,6 +475,51 @@ def cpu_baseline(pkg, raw, sample, reps):
         out["pte_sample"] = f"{npte} cells, one pass, {cores} threads"
     except Exception as exc:  # the headline baseline stands on its own
         out["pte_error"] = repr(exc)
+    # the other configs beside it (2^20-cell samples, best of 2), Gcells/s
+    try:
+        import tempfile
+        W, tq = pkg.workloads, pkg.thermalqs
+        ns = 1 << 20
+        other = {}
+
+        def best_of(fn, reps2=2):
+            fn()
+            b = 1e30
+            for _ in range(reps2):
+                t0 = time.perf_counter()
+                fn()
+                b = min(b, time.perf_counter() - t0)
+            return b
+        r1, t1 = W.ideal_inputs(ns)
+        ig = ref.IdealGas(0.4, 7.16e6)
+        other["ideal_P_then_e"] = ns / best_of(lambda: (
+            ig.eval(L.P_FROM_RHO_T, r1, t1, nthreads=cores),
+            ig.eval(L.E_FROM_RHO_T, r1, t1, nthreads=cores))) / 1e9
+        rho_s, T_s = rho[:ns], T[:ns]
+        sie_s = eos.eval(L.E_FROM_RHO_T, rho_s, T_s, nthreads=cores)
+        lam_s = np.full((ns, 2), np.nan)
+
+        def root_cold():
+            lam_s.fill(np.nan)
+            eos.eval(L.T_FROM_RHO_E, rho_s, sie_s, lam_s, nthreads=cores)
+        other["spiner_rhot_T_rhoe_rootfind_cold"] = ns / best_of(root_cold) / 1e9
+        rs = ref.SpinerRhoSie(raw)
+        lam1 = np.full((ns, 1), np.nan)
+        other["spiner_rhosie_T_rhoe"] = ns / best_of(
+            lambda: rs.eval(L.T_FROM_RHO_E, rho_s, sie_s, lam1, nthreads=cores)) / 1e9
+        with tempfile.TemporaryDirectory() as d:
+            hp = pkg.tablegen.write_synthetic_helm_table(os.path.join(d, "helm.dat"))
+            h = ref.Helmholtz(hp, L.HelmOptions(1, 1, 1, 1, 1, 1, 1))
+            nh = 1 << 18
+            hr, hT = W.helm_inputs(nh)
+            lam3 = np.tile(np.array([4.0, 2.0, -1.0]), (nh, 1))
+            he, hP, hcv, hb = (np.zeros(nh) for _ in range(4))
+            mask = tq.specific_internal_energy | tq.pressure | tq.specific_heat | tq.bulk_modulus
+            other["helmholtz_FillEos_rhoT"] = nh / best_of(
+                lambda: h.fill(hr, hT, he, hP, hcv, hb, mask, lam3, nthreads=cores)) / 1e9
+        out["other_configs_Gcells_per_s"] = other
+    except Exception as exc:
+        out["other_configs_error"] = repr(exc)
     return out
 
 
