@@ -94,6 +94,18 @@ inline void PTESolverPT(const std::vector<EosBase> &eos, std::int64_t ncell, Rea
               params, status, residual, stats, stream);
 }
 
+// PTESolverFixedT + PTESolver (closure/mixed_cell_models.hpp:1462-1672): the temperature of
+// every cell is given (T_true [ncell]); unknowns are the volume fractions.
+inline void PTESolverFixedT(const std::vector<EosBase> &eos, std::int64_t ncell,
+                            const Real *T_true, Real *rho, Real *vfrac, Real *sie, Real *temp,
+                            Real *press, const MixParams &params = MixParams(),
+                            std::uint64_t *status = nullptr, const Real *vfrac_tot = nullptr,
+                            Real *residual = nullptr, std::uint64_t *stats = nullptr,
+                            sgx_stream_t stream = nullptr) {
+  detail::pte(SGX_PTE_FIXED_T, eos, ncell, rho, vfrac, sie, temp, press, nullptr, vfrac_tot,
+              T_true, params, status, residual, stats, stream);
+}
+
 // The three materials of test/pte_test_3mat_analytic.hpp:38-50
 inline std::vector<EosBase> set_eos_3mat_analytic() {
   return {Gruneisen(394000.0, 1.489, 0.0, 0.0, 2.02, 0.47, 8.93, 297.0, 1.0e6, 0.383e7),

@@ -616,7 +616,9 @@ int ref_pte_solve(int solver, void **eos_handles, int nmat, int64_t ncell, doubl
   {
     std::vector<EOS> eos_local(eos_vec);
     EosIndexer eos{eos_local.data()};
-    const int nscr = std::max(PTESolverRhoTRequiredScratch(nmat), PTESolverPTRequiredScratch(nmat));
+    const int nscr = (int)std::max<std::size_t>(
+        std::max<std::size_t>(PTESolverRhoTRequiredScratch(nmat), PTESolverPTRequiredScratch(nmat)),
+        PTESolverFixedTRequiredScratch(nmat));
     std::vector<double> scratch(nscr);
 #pragma omp for schedule(dynamic, 256)
     for (int64_t t = 0; t < ncell; ++t) {
@@ -646,6 +648,12 @@ int ref_pte_solve(int solver, void **eos_handles, int nmat, int64_t ncell, doubl
           PTESolverRhoT<EosIndexer, RowIndexer, NullIndexer> method(
               nmat, eos, vfrac_tot, sie_tot, r, vf, e, tp, pr, lambda, scratch.data(), Tguess,
               mp);
+          st = PTESolver(method);
+          niter = method.Niter();
+        } else if (solver == SGX_PTE_FIXED_T) {
+          PTESolverFixedT<EosIndexer, RowIndexer, NullIndexer> method(
+              nmat, eos, vfrac_tot, Tguess /* T_true */, r, vf, e, tp, pr, lambda,
+              scratch.data(), mp);
           st = PTESolver(method);
           niter = method.Niter();
         } else {

@@ -72,6 +72,13 @@ def PTESolverPT(eos_list, rho, vfrac, sie, temp, press, **kw):
     return pte_solve(_lib.PTE_PT, eos_list, rho, vfrac, sie, temp, press, **kw)
 
 
+def PTESolverFixedT(eos_list, T_true, rho, vfrac, sie, temp, press, **kw):
+    """PTESolverFixedT (closure/mixed_cell_models.hpp:1462-1672): the cell temperatures
+    `T_true` [ncell] are given; unknowns are the volume fractions."""
+    return pte_solve(_lib.PTE_FIXED_T, eos_list, rho, vfrac, sie, temp, press, Tguess=T_true,
+                     **kw)
+
+
 def pte_solve_host(solver, eos_list, rho, vfrac, sie, temp, press, params=None, status=None,
                    residual=None, sie_tot=None, vfrac_tot=None, Tguess=None):
     """numpy arrays in host memory; staging happens inside the library."""

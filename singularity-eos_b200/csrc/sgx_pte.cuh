@@ -1026,6 +1026,155 @@ struct PT : public Base<NM, 2, Eos> {
 };
 
 // ---------------------------------------------------------------------------------------
+// PTESolverFixedT (:1462-1672): temperature given, unknowns are the NM volume fractions;
+// equations: volume sum, and pressure equality of consecutive materials.
+// ---------------------------------------------------------------------------------------
+template <int NM, class Eos>
+struct FixedT : public Base<NM, NM, Eos> {
+  using B = Base<NM, NM, Eos>;
+  using B::dx;
+  using B::eos;
+  using B::jacobian;
+  using B::params_;
+  using B::press;
+  using B::residual;
+  using B::rho;
+  using B::rhobar;
+  using B::sie;
+  using B::temp;
+  using B::Tnorm;
+  using B::u;
+  using B::uscale;
+  using B::vfrac;
+  double dpdv[NM], vtemp[NM];
+  double Tequil;
+
+  __device__ FixedT(const Eos &e, const MixParamsDev &p) : B(e, p) {}
+
+  // Init (:1523-1551).  The kernel puts T_true into Tnorm; the constructor (:1498-1510) keeps
+  // it as Tequil and resets Tnorm to 1.
+  __device__ inline double Init() {
+    Tequil = Tnorm;
+    Tnorm = 1.0;
+    B::InitRhoBarandRho();
+    B::SetVfracFromT(Tequil);
+    uscale = 0.0;
+#pragma unroll
+    for (int m = 0; m < NM; m++) {
+      rho[m] = ratio(rhobar[m], vfrac[m]);
+      sie[m] = eos.e_from_rho_T(m, rho[m], Tequil);
+      uscale += fabs(sie[m]) * rho[m];
+      press[m] = eos.P_from_rho_T(m, rho[m], Tequil);
+    }
+    uscale = stdmax(uscale, 1.0e-14);
+#pragma unroll
+    for (int m = 0; m < NM; ++m) {
+      press[m] = ratio(press[m], uscale);
+      u[m] = sie[m] * ratio(rhobar[m], uscale);
+    }
+    Residual();
+    return B::ResidualNorm();
+  }
+  SGX_D void Fixup() {}
+  SGX_D void Finalize() { // base Finalize (:351-357)
+#pragma unroll
+    for (int m = 0; m < NM; m++) {
+      temp[m] *= Tnorm;
+      u[m] *= uscale;
+      press[m] *= uscale;
+    }
+  }
+  SGX_D void Residual() {
+    const double vsum = sum_neumaier(vfrac, NM);
+    residual[0] = B::vfrac_total - vsum;
+#pragma unroll
+    for (int m = 0; m < NM - 1; ++m)
+      residual[1 + m] = press[m] - press[m + 1];
+  }
+  SGX_D void CheckPTE(bool &converged, bool &acceptable) const {
+    double mean_p = vfrac[0] * press[0];
+    double error_p = 0;
+#pragma unroll
+    for (int m = 1; m < NM; ++m) {
+      mean_p += vfrac[m] * press[m];
+      error_p += residual[m] * residual[m];
+    }
+    error_p = sqrt(error_p);
+    const double error_v = fabs(residual[0]);
+    const bool converged_p = (error_p < params_.pte_rel_tolerance_p * fabs(mean_p) ||
+                              error_p < params_.pte_abs_tolerance_p);
+    const bool converged_v = error_v < params_.pte_rel_tolerance_v;
+    const bool acceptable_p =
+        (error_p < params_.pte_rel_tolerance_p_sufficient * fabs(mean_p) ||
+         error_p < params_.pte_abs_tolerance_p_sufficient);
+    const bool acceptable_v = error_v < params_.pte_rel_tolerance_v_sufficient;
+    converged = converged_p && converged_v;
+    acceptable = acceptable_p && acceptable_v;
+  }
+  __device__ inline void Jacobian() {
+#pragma unroll
+    for (int m = 0; m < NM; m++) {
+      const double dv = (vfrac[m] < 0.5 ? 1.0 : -1.0) * vfrac[m] * params_.derivative_eps;
+      const double vf_pert = vfrac[m] + dv;
+      const double rho_pert = ratio(rhobar[m], vf_pert);
+      const double p_pert = ratio(eos.P_from_rho_T(m, rho_pert, Tequil), uscale);
+      dpdv[m] = stdmin(ratio((p_pert - press[m]), dv), -fabs(params_.pte_max_dpdv));
+    }
+#pragma unroll
+    for (int i = 0; i < NM * NM; ++i)
+      jacobian[i] = 0.0;
+#pragma unroll
+    for (int m = 0; m < NM; ++m)
+      jacobian[m] = 1.0;
+#pragma unroll
+    for (int m = 0; m < NM - 1; m++) {
+      jacobian[(m + 1) * NM + m] = -dpdv[m];
+      jacobian[(m + 1) * NM + m + 1] = dpdv[m + 1];
+    }
+  }
+  __device__ inline double ScaleDx() {
+    double scale = 1.0;
+#pragma unroll
+    for (int m = 0; m < NM; ++m) {
+      if (scale * dx[m] < -params_.vfrac_safety_fac * vfrac[m]) {
+        scale = ratio(-params_.vfrac_safety_fac * vfrac[m], dx[m]);
+      }
+    }
+#pragma unroll
+    for (int m = 0; m < NM; m++) {
+      const double rho_min = eos.RhoPmin(m, Tequil);
+      const double alpha_max = ratio(rhobar[m], rho_min);
+      if (alpha_max < vfrac[m]) continue;
+      if (scale * dx[m] > 0.5 * (alpha_max - vfrac[m])) {
+        scale = ratio(0.5 * (alpha_max - vfrac[m]), dx[m]);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < NM; ++i)
+      dx[i] *= scale;
+    return scale;
+  }
+  __device__ inline double TestUpdate(const double scale, const bool cache_state = false) {
+    if (cache_state) {
+#pragma unroll
+      for (int m = 0; m < NM; ++m)
+        vtemp[m] = vfrac[m];
+    }
+#pragma unroll
+    for (int m = 0; m < NM; ++m) {
+      vfrac[m] = vtemp[m] + scale * dx[m];
+      rho[m] = ratio(rhobar[m], vfrac[m]);
+      u[m] = rhobar[m] * eos.e_from_rho_T(m, rho[m], Tequil);
+      sie[m] = ratio(u[m], rhobar[m]);
+      u[m] = ratio(u[m], uscale);
+      press[m] = ratio(eos.P_from_rho_T(m, rho[m], Tequil), uscale);
+    }
+    Residual();
+    return B::ResidualNorm();
+  }
+};
+
+// ---------------------------------------------------------------------------------------
 // PTESolver (:2188-2291)
 // ---------------------------------------------------------------------------------------
 template <class System>

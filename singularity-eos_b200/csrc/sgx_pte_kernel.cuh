@@ -27,8 +27,10 @@ __global__ void __launch_bounds__(128)
   const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int64_t nthr = (int64_t)gridDim.x * blockDim.x;
   for (int64_t t = tid; t < ncell; t += nthr) {
-    using System =
-        typename std::conditional<SOLVER == SGX_PTE_RHOT, mix::RhoT<NM, Acc>, mix::PT<NM, Acc>>::type;
+    using System = typename std::conditional<
+        SOLVER == SGX_PTE_RHOT, mix::RhoT<NM, Acc>,
+        typename std::conditional<SOLVER == SGX_PTE_PT, mix::PT<NM, Acc>,
+                                  mix::FixedT<NM, Acc>>::type>::type;
     System s(eos, prm);
     const int64_t base = t * NM;
 #pragma unroll
@@ -51,7 +53,9 @@ __global__ void __launch_bounds__(128)
     if (sie_tot_in) sie_tot = sie_tot_in[t];
     s.sie_total = sie_tot;
     s.vfrac_total = vfrac_tot_in ? vfrac_tot_in[t] : 1.0;
-    if (Tguess_in) {
+    if constexpr (SOLVER == SGX_PTE_FIXED_T) {
+      s.Tnorm = Tguess_in[t]; // T_true (PTESolverFixedT ctor, :1498-1510)
+    } else if (Tguess_in) {
       s.Tnorm = Tguess_in[t];
     } else {
       s.Tnorm = mix::ApproxTemperatureFromRhoMatU<NM>(eos, rho_tot * sie_tot, s.rho, s.vfrac);

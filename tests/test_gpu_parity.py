@@ -527,6 +527,52 @@ def test_pte_rhot_generic_mixtures(pkg, ref, torch_cuda, nmat):
         assert_rel(got.cpu().numpy()[conv], want[conv], PTE_TOL, f"nmat={nmat} PTE state {nm}")
 
 
+@pytest.mark.parametrize("mix", ["3mat", "ideal+solids"])
+def test_pte_fixed_T_parity(pkg, ref, torch_cuda, mix):
+    """PTESolverFixedT (closure/mixed_cell_models.hpp:1462-1672): temperatures given per cell,
+    volume fractions solved so that the pressures equilibrate.  SolverStatus identical to the
+    reference, states within 1e-10; volume fractions sum to one."""
+    torch = torch_cuda
+    L, W = pkg._lib, pkg.workloads
+    g3, r3 = pkg.closure.set_eos_3mat_analytic(), ref.set_eos_3mat()
+    if mix == "3mat":
+        geos, reos, rho_nom = g3, r3, [8.93, 1.89, 2.5]
+    else:
+        geos = [g3[0], pkg.IdealGas(0.4, 7.16e6), g3[2], pkg.IdealGas(2.0 / 3.0, 1.2e7)]
+        reos = [r3[0], ref.IdealGas(0.4, 7.16e6), r3[2], ref.IdealGas(2.0 / 3.0, 1.2e7)]
+        rho_nom = [8.93, 0.1, 2.5, 0.05]
+    nmat = len(geos)
+    n = 1 << 13
+    vfrac_h = W.pte_vfracs(n, nmat=nmat)
+    rho_h = np.tile(np.array(rho_nom), (n, 1))
+    T_true = 300.0 + 900.0 * pkg.rng.uniform_np(77, 0, n)
+    temp_h = np.repeat(T_true[:, None], nmat, axis=1).copy()
+    sie_h = np.stack([reos[m].eval(L.E_FROM_RHO_T, rho_h[:, m].copy(), temp_h[:, m].copy())
+                      for m in range(nmat)], axis=1).copy()
+    press_h = np.zeros((n, nmat))
+    vf_ref = vfrac_h.copy()
+    state_d = [dev(a) for a in (rho_h, vfrac_h, sie_h, temp_h, press_h)]
+    params = pkg.closure.MixParams()
+    st_r, _, _ = ref.pte_solve(L.PTE_FIXED_T, reos, rho_h, vf_ref, sie_h, temp_h, press_h, params,
+                               Tguess=T_true, nthreads=0)
+    status = torch.zeros(n, dtype=torch.int64, device="cuda")
+    pkg.closure.PTESolverFixedT(geos, dev(T_true), *state_d, params=params, status=status)
+    torch.cuda.synchronize()
+    dg = pkg.closure.decode_status(status.cpu().numpy().view(np.uint64))
+    dr = pkg.closure.decode_status(st_r)
+    for k in ("converged", "slow_convergence_detected", "niter", "max_line_niter"):
+        assert (dg[k] == dr[k]).all(), f"FixedT {mix}: {k} differs"
+    conv = dr["converged"]
+    assert conv.mean() >= 0.9, conv.mean()
+    print(f"FixedT {mix}: converged {conv.sum()}/{n}, niter histogram "
+          f"{np.bincount(dr['niter'].astype(int))}")
+    for got, want, nm in zip(state_d, (rho_h, vf_ref, sie_h, temp_h, press_h),
+                             ("rho", "vfrac", "sie", "temp", "press")):
+        assert_rel(got.cpu().numpy()[conv], want[conv], PTE_TOL, f"FixedT {mix} state {nm}")
+    assert_rel(state_d[1].cpu().numpy()[conv].sum(axis=1), np.ones(conv.sum()), 1e-9,
+               "FixedT volume fractions sum")
+
+
 @pytest.mark.parametrize("which", ["test_params", "default_params"])
 def test_pte_pt_parity(pkg, ref, torch_cuda, which):
     """PTESolverPT inverts every material with regula_falsi at xtol = ytol = 1e-8
