@@ -110,6 +110,28 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def pin_to_gpu_numa(gpu_index):
+    """One process per GPU: run this rank on the CPUs NVML reports as local to its GPU, so the
+    pinned host buffers of the e2e leg are first-touched on that NUMA node and the staging
+    copies do not cross the socket interconnect.  Returns the CPU list, or None."""
+    try:
+        import pynvml as nv
+        nv.nvmlInit()
+        h = nv.nvmlDeviceGetHandleByIndex(gpu_index)
+        ncpu = os.cpu_count() or 1
+        words = nv.nvmlDeviceGetCpuAffinity(h, (ncpu + 63) // 64)
+        cpus = [64 * w + b for w, word in enumerate(words) for b in range(64)
+                if (int(word) >> b) & 1]
+        allowed = os.sched_getaffinity(0)
+        cpus = [c for c in cpus if c in allowed]
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return cpus
+    except Exception:
+        pass
+    return None
+
+
 def headline_traffic(cells):
     """DRAM bytes per launch of the headline kernel from the committed `ncu --set full`
     capture (profiles/headline_traffic.json), if it was taken at this launch size."""
@@ -170,6 +192,8 @@ def run_ours(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py (impl=ours) needs a CUDA device: there is no CPU path")
     torch.cuda.set_device(local)
+    all_cpus = sorted(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else []
+    numa = pin_to_gpu_numa(local) if world > 1 else None
     dist = None
     if world > 1:
         import torch.distributed as dist_mod
@@ -399,7 +423,9 @@ def run_ours(args):
     e2e = {"value": ne * world * ke / t_e2e / 1e9, "unit": UNIT,
            "h2d_bytes_per_step": ne * (8 + 8 + 16), "d2h_bytes_per_step": ne * (8 + 16),
            "cells_per_step_per_gpu": ne,
-           "api": "sgx_eos_eval_host(P_FROM_RHO_T) with pinned host arrays"}
+           "api": "sgx_eos_eval_host(P_FROM_RHO_T) with pinned host arrays",
+           "host_cpus_of_rank0": (f"{len(numa)} CPUs local to the GPU (NVML affinity)"
+                                  if numa else "unrestricted")}
 
     clocks = None
     if rank == 0:
@@ -418,6 +444,8 @@ def run_ours(args):
         "roofline": roofline, "e2e": e2e, "gpu_launches": int(launches),
         "clocks": clocks, "configs": results,
     }
+    if all_cpus:
+        os.sched_setaffinity(0, all_cpus)  # the CPU baseline uses every host core
     if rank == 0 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(pkg, raw, sample=1 << 22, reps=3)
     if dist is not None:
