@@ -421,7 +421,9 @@ def run_ours(args):
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         t_e2e = float(tt.item())
     e2e = {"value": ne * world * ke / t_e2e / 1e9, "unit": UNIT,
-           "h2d_bytes_per_step": ne * (8 + 8 + 16), "d2h_bytes_per_step": ne * (8 + 16),
+           # rho, T in; P and the (lRho, lT) lambda rows out.  The lambda rows are write-only for
+           # a (rho, T) lookup, so the library does not copy them to the device (lambda_io)
+           "h2d_bytes_per_step": ne * (8 + 8), "d2h_bytes_per_step": ne * (8 + 16),
            "cells_per_step_per_gpu": ne,
            "api": "sgx_eos_eval_host(P_FROM_RHO_T) with pinned host arrays",
            "host_cpus_of_rank0": (f"{len(numa)} CPUs local to the GPU (NVML affinity)"
