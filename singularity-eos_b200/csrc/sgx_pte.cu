@@ -168,38 +168,59 @@ int sgx_pte_solve_host(int solver, const sgx_eos_t *eos, int nmat, int64_t ncell
                        const sgx_mix_params *params, uint64_t *status, double *residual) {
   if (!eos || !eos[0]) return fail(SGX_ERR_INVALID, "null EOS array");
   if (ncell <= 0) return ncell == 0 ? SGX_OK : fail(SGX_ERR_INVALID, "negative ncell");
+  if (nmat < 1 || nmat > 4)
+    return fail(SGX_ERR_UNSUPPORTED, "nmat=%d: this build instantiates 1..4 materials", nmat);
   sgx_eos_s *e0 = eos[0];
   cudaError_t err = cudaSetDevice(e0->device);
   if (err != cudaSuccess)
     return fail(SGX_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(err));
-  const size_t nb = (size_t)ncell * nmat * sizeof(double);
-  const size_t cb = (size_t)ncell * sizeof(double);
-  int rc = ensure_staging(e0, 0, 5 * nb + 5 * cb);
+  // Chunks of cells flow through kSlots device slots, each on its own stream
+  // (H2D -> solve -> D2H), so both PCIe directions overlap the solver.
+  constexpr int kSlots = 3;
+  constexpr int64_t kChunk = int64_t(1) << 20;
+  const int64_t chunk = ncell < kChunk ? ncell : kChunk;
+  const size_t nb_max = (size_t)chunk * nmat * sizeof(double);
+  const size_t cb_max = (size_t)chunk * sizeof(double);
+  const size_t slot_bytes = (5 * nb_max + 5 * cb_max + 255) & ~size_t(255);
+  int rc = ensure_staging(e0, 0, kSlots * slot_bytes);
   if (rc) return rc;
-  cudaStream_t s = e0->own_stream;
-  char *base = (char *)e0->dscratch;
-  double *d[5];
+  rc = ensure_host_streams(e0);
+  if (rc) return rc;
   double *h[5] = {rho, vfrac, sie, temp, press};
-  for (int k = 0; k < 5; ++k) {
-    d[k] = (double *)(base + k * nb);
-    SGX_CUDA_OK(cudaMemcpyAsync(d[k], h[k], nb, cudaMemcpyHostToDevice, s));
+  int slot = 0;
+  for (int64_t c0 = 0; c0 < ncell; c0 += chunk, slot = (slot + 1) % kSlots) {
+    const int64_t n = (ncell - c0) < chunk ? (ncell - c0) : chunk;
+    const size_t nb = (size_t)n * nmat * sizeof(double);
+    const size_t cb = (size_t)n * sizeof(double);
+    cudaStream_t s = e0->host_streams[slot];
+    char *base = (char *)e0->dscratch + slot * slot_bytes;
+    double *d[5];
+    for (int k = 0; k < 5; ++k) {
+      d[k] = (double *)(base + k * nb_max);
+      SGX_CUDA_OK(cudaMemcpyAsync(d[k], h[k] + c0 * nmat, nb, cudaMemcpyHostToDevice, s));
+    }
+    double *d_sie_tot = (double *)(base + 5 * nb_max);
+    double *d_vf_tot = d_sie_tot + chunk, *d_Tg = d_vf_tot + chunk, *d_res = d_Tg + chunk;
+    uint64_t *d_status = (uint64_t *)(d_res + chunk);
+    if (sie_tot)
+      SGX_CUDA_OK(cudaMemcpyAsync(d_sie_tot, sie_tot + c0, cb, cudaMemcpyHostToDevice, s));
+    if (vfrac_tot)
+      SGX_CUDA_OK(cudaMemcpyAsync(d_vf_tot, vfrac_tot + c0, cb, cudaMemcpyHostToDevice, s));
+    if (Tguess) SGX_CUDA_OK(cudaMemcpyAsync(d_Tg, Tguess + c0, cb, cudaMemcpyHostToDevice, s));
+    rc = sgx_pte_solve(solver, eos, nmat, n, d[0], d[1], d[2], d[3], d[4],
+                       sie_tot ? d_sie_tot : nullptr, vfrac_tot ? d_vf_tot : nullptr,
+                       Tguess ? d_Tg : nullptr, params, status ? d_status : nullptr,
+                       residual ? d_res : nullptr, nullptr, s);
+    if (rc) return rc;
+    for (int k = 0; k < 5; ++k)
+      SGX_CUDA_OK(cudaMemcpyAsync(h[k] + c0 * nmat, d[k], nb, cudaMemcpyDeviceToHost, s));
+    if (status)
+      SGX_CUDA_OK(cudaMemcpyAsync(status + c0, d_status, cb, cudaMemcpyDeviceToHost, s));
+    if (residual)
+      SGX_CUDA_OK(cudaMemcpyAsync(residual + c0, d_res, cb, cudaMemcpyDeviceToHost, s));
   }
-  double *d_sie_tot = (double *)(base + 5 * nb);
-  double *d_vf_tot = d_sie_tot + ncell, *d_Tg = d_vf_tot + ncell, *d_res = d_Tg + ncell;
-  uint64_t *d_status = (uint64_t *)(d_res + ncell);
-  if (sie_tot) SGX_CUDA_OK(cudaMemcpyAsync(d_sie_tot, sie_tot, cb, cudaMemcpyHostToDevice, s));
-  if (vfrac_tot) SGX_CUDA_OK(cudaMemcpyAsync(d_vf_tot, vfrac_tot, cb, cudaMemcpyHostToDevice, s));
-  if (Tguess) SGX_CUDA_OK(cudaMemcpyAsync(d_Tg, Tguess, cb, cudaMemcpyHostToDevice, s));
-  rc = sgx_pte_solve(solver, eos, nmat, ncell, d[0], d[1], d[2], d[3], d[4],
-                     sie_tot ? d_sie_tot : nullptr, vfrac_tot ? d_vf_tot : nullptr,
-                     Tguess ? d_Tg : nullptr, params, status ? d_status : nullptr,
-                     residual ? d_res : nullptr, nullptr, s);
-  if (rc) return rc;
-  for (int k = 0; k < 5; ++k)
-    SGX_CUDA_OK(cudaMemcpyAsync(h[k], d[k], nb, cudaMemcpyDeviceToHost, s));
-  if (status) SGX_CUDA_OK(cudaMemcpyAsync(status, d_status, cb, cudaMemcpyDeviceToHost, s));
-  if (residual) SGX_CUDA_OK(cudaMemcpyAsync(residual, d_res, cb, cudaMemcpyDeviceToHost, s));
-  SGX_CUDA_OK(cudaStreamSynchronize(s));
+  for (int k = 0; k < kSlots; ++k)
+    SGX_CUDA_OK(cudaStreamSynchronize(e0->host_streams[k]));
   return SGX_OK;
 }
 

@@ -623,6 +623,43 @@ def test_pte_properties_full_path(pkg, torch_cuda):
     assert close(vfrac[c].sum(dim=1), torch.ones_like(vfrac[c, 0]), 1e-12).all()
 
 
+def test_host_entry_points_multi_chunk_equal_device_path(pkg, torch_cuda, raw):
+    """The *_host entry points cut the range into chunks that flow through several streams
+    (csrc/sgx_api.cu sgx_eos_eval_host, csrc/sgx_pte.cu sgx_pte_solve_host): results must equal
+    the device-pointer path bit for bit, for sizes that are not multiples of the chunk."""
+    torch = torch_cuda
+    L, W = pkg._lib, pkg.workloads
+    # lookups: 2 chunks + ragged tail
+    n = (1 << 22) + 4321
+    rho_h, T_h = W.spiner_inputs(n)
+    g = pkg.SpinerEOSDependsRhoT(raw)
+    out_d = torch.empty(n, dtype=torch.float64, device="cuda")
+    lam_d = torch.full((n, 2), float("nan"), dtype=torch.float64, device="cuda")
+    g.PressureFromDensityTemperature(dev(rho_h), dev(T_h), out_d, n, lam_d)
+    out_h, lam_h = np.empty(n), np.full((n, 2), np.nan)
+    g.eval_host(L.P_FROM_RHO_T, rho_h, T_h, out_h, lam_h)
+    assert_bits(out_h, out_d.cpu().numpy(), "eval_host P")
+    assert_bits(lam_h, lam_d.cpu().numpy(), "eval_host lambda")
+    # PTE: 2 chunks + ragged tail
+    n = (1 << 21) + 777
+    g3 = pkg.closure.set_eos_3mat_analytic()
+    sie0 = []
+    for m in range(3):
+        o = torch.empty(1, dtype=torch.float64, device="cuda")
+        g3[m].InternalEnergyFromDensityTemperature(dev([W.PTE_RHO[m]]), dev([W.PTE_T]), o, 1)
+        sie0.append(float(o.item()))
+    st_h = [a.copy() for a in W.pte_state_np(n, sie0)]
+    st_d = [dev(a) for a in st_h]
+    status_d = torch.zeros(n, dtype=torch.int64, device="cuda")
+    pkg.closure.pte_solve(L.PTE_RHOT, g3, *st_d, params=pkg.closure.MixParams(), status=status_d)
+    status_h = np.zeros(n, dtype=np.uint64)
+    pkg.closure.pte_solve_host(L.PTE_RHOT, g3, *st_h, params=pkg.closure.MixParams(),
+                               status=status_h)
+    assert (status_h == status_d.cpu().numpy().view(np.uint64)).all()
+    for a, b, nm in zip(st_h, st_d, ("rho", "vfrac", "sie", "temp", "press")):
+        assert_bits(a, b.cpu().numpy(), "pte_solve_host " + nm)
+
+
 def test_host_pointer_entry_points(pkg, ref, torch_cuda, raw):
     """The *_host C-ABI forms (what a host code without device arrays calls)."""
     L = pkg._lib
