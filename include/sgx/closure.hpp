@@ -94,6 +94,19 @@ inline void PTESolverPT(const std::vector<EosBase> &eos, std::int64_t ncell, Rea
               params, status, residual, stats, stream);
 }
 
+// PTESolverRhoU + PTESolver (closure/mixed_cell_models.hpp:1934-2183); same arguments as
+// PTESolverRhoT
+inline void PTESolverRhoU(const std::vector<EosBase> &eos, std::int64_t ncell, Real *rho,
+                          Real *vfrac, Real *sie, Real *temp, Real *press,
+                          const MixParams &params = MixParams(),
+                          std::uint64_t *status = nullptr, const Real *sie_tot = nullptr,
+                          const Real *vfrac_tot = nullptr, const Real *Tguess = nullptr,
+                          Real *residual = nullptr, std::uint64_t *stats = nullptr,
+                          sgx_stream_t stream = nullptr) {
+  detail::pte(SGX_PTE_RHOU, eos, ncell, rho, vfrac, sie, temp, press, sie_tot, vfrac_tot,
+              Tguess, params, status, residual, stats, stream);
+}
+
 // PTESolverFixedT + PTESolver (closure/mixed_cell_models.hpp:1462-1672): the temperature of
 // every cell is given (T_true [ncell]); unknowns are the volume fractions.
 inline void PTESolverFixedT(const std::vector<EosBase> &eos, std::int64_t ncell,

@@ -618,7 +618,8 @@ int ref_pte_solve(int solver, void **eos_handles, int nmat, int64_t ncell, doubl
     EosIndexer eos{eos_local.data()};
     const int nscr = (int)std::max<std::size_t>(
         std::max<std::size_t>(PTESolverRhoTRequiredScratch(nmat), PTESolverPTRequiredScratch(nmat)),
-        PTESolverFixedTRequiredScratch(nmat));
+        std::max<std::size_t>(PTESolverFixedTRequiredScratch(nmat),
+                              PTESolverRhoURequiredScratch(nmat)));
     std::vector<double> scratch(nscr);
 #pragma omp for schedule(dynamic, 256)
     for (int64_t t = 0; t < ncell; ++t) {
@@ -646,6 +647,12 @@ int ref_pte_solve(int solver, void **eos_handles, int nmat, int64_t ncell, doubl
       int lrc = guarded([&]() {
         if (solver == SGX_PTE_RHOT) {
           PTESolverRhoT<EosIndexer, RowIndexer, NullIndexer> method(
+              nmat, eos, vfrac_tot, sie_tot, r, vf, e, tp, pr, lambda, scratch.data(), Tguess,
+              mp);
+          st = PTESolver(method);
+          niter = method.Niter();
+        } else if (solver == SGX_PTE_RHOU) {
+          PTESolverRhoU<EosIndexer, RowIndexer, NullIndexer> method(
               nmat, eos, vfrac_tot, sie_tot, r, vf, e, tp, pr, lambda, scratch.data(), Tguess,
               mp);
           st = PTESolver(method);

@@ -90,7 +90,7 @@ METHOD_NAMES = {
     GAMMA_FROM_RHO_T: "GruneisenParamFromDensityTemperature",
     GAMMA_FROM_RHO_E: "GruneisenParamFromDensityInternalEnergy",
 }
-PTE_RHOT, PTE_PT, PTE_FIXED_T = 0, 1, 2
+PTE_RHOT, PTE_PT, PTE_FIXED_T, PTE_RHOU = 0, 1, 2, 3
 PTE_NSTATS = 64
 
 

@@ -72,6 +72,11 @@ def PTESolverPT(eos_list, rho, vfrac, sie, temp, press, **kw):
     return pte_solve(_lib.PTE_PT, eos_list, rho, vfrac, sie, temp, press, **kw)
 
 
+def PTESolverRhoU(eos_list, rho, vfrac, sie, temp, press, **kw):
+    """PTESolverRhoU (closure/mixed_cell_models.hpp:1934-2183)."""
+    return pte_solve(_lib.PTE_RHOU, eos_list, rho, vfrac, sie, temp, press, **kw)
+
+
 def PTESolverFixedT(eos_list, T_true, rho, vfrac, sie, temp, press, **kw):
     """PTESolverFixedT (closure/mixed_cell_models.hpp:1462-1672): the cell temperatures
     `T_true` [ncell] are given; unknowns are the volume fractions."""

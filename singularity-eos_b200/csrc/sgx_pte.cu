@@ -93,6 +93,7 @@ void sgx_mix_params_default(sgx_mix_params *p) {
 int sgx_pte_required_scratch(int solver, int nmat) {
   if (solver == SGX_PTE_RHOT) return nmat * nmat + 4 * nmat + 6 * nmat; // :873-878
   if (solver == SGX_PTE_FIXED_T) return nmat * nmat + 4 * nmat + 4 * nmat; // :1450-1456
+  if (solver == SGX_PTE_RHOU) return 4 * nmat * nmat + 8 * nmat + 8 * nmat; // :1924-1929
   return 2 * 2 + 4 * 2 + 2 * nmat;                                       // :1198-1203
 }
 
@@ -102,8 +103,12 @@ int sgx_pte_solve(int solver, const sgx_eos_t *eos, int nmat, int64_t ncell, dou
                   const sgx_mix_params *params, uint64_t *status, double *residual,
                   uint64_t *stats, sgx_stream_t stream) {
   if (!eos) return fail(SGX_ERR_INVALID, "null EOS array");
-  if (solver != SGX_PTE_RHOT && solver != SGX_PTE_PT && solver != SGX_PTE_FIXED_T)
+  if (solver != SGX_PTE_RHOT && solver != SGX_PTE_PT && solver != SGX_PTE_FIXED_T &&
+      solver != SGX_PTE_RHOU)
     return fail(SGX_ERR_INVALID, "unknown PTE solver %d", solver);
+  if (solver == SGX_PTE_RHOU && (nmat < 2 || nmat > 3))
+    return fail(SGX_ERR_UNSUPPORTED, "PTESolverRhoU: nmat=%d, this build instantiates 2..3",
+                nmat);
   if (solver == SGX_PTE_FIXED_T && !Tguess)
     return fail(SGX_ERR_INVALID, "PTESolverFixedT needs the temperature array (Tguess)");
   if (nmat < 1 || nmat > 4)
@@ -135,6 +140,11 @@ int sgx_pte_solve(int solver, const sgx_eos_t *eos, int nmat, int64_t ncell, dou
       stats, ncell, s
   if (solver == SGX_PTE_RHOT) return launch_pte_rhot(set, is_bench_mix, prm, rho, vfrac, sie, temp, press, sie_tot,
                            vfrac_tot, Tguess, status, residual, stats, ncell, s);
+  if (solver == SGX_PTE_RHOU) {
+    if (is_bench_mix) return launch_pte_percell<3, Mix3GrDrDp, SGX_PTE_RHOU>(SGX_PTE_ARGS);
+    if (nmat == 2) return launch_pte_percell<2, DynEos, SGX_PTE_RHOU>(SGX_PTE_ARGS);
+    return launch_pte_percell<3, DynEos, SGX_PTE_RHOU>(SGX_PTE_ARGS);
+  }
   if (solver == SGX_PTE_FIXED_T) {
     if (is_bench_mix) return launch_pte_percell<3, Mix3GrDrDp, SGX_PTE_FIXED_T>(SGX_PTE_ARGS);
     switch (nmat) {

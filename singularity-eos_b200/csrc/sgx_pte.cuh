@@ -101,6 +101,9 @@ struct DynEos {
   SGX_D double P_from_rho_e(int m, double rho, double e) const {
     SGX_EOS_DISPATCH(m, P_from_rho_e(rho, e))
   }
+  SGX_D double T_from_rho_e(int m, double rho, double e) const {
+    SGX_EOS_DISPATCH(m, T_from_rho_e(rho, e))
+  }
   SGX_D double P_from_rho_T(int m, double rho, double T) const {
     SGX_EOS_DISPATCH(m, P_from_rho_T(rho, T))
   }
@@ -185,6 +188,9 @@ struct Mix3GrDrDp {
   }
   SGX_D double P_from_rho_e(int m, double rho, double e) const {
     SGX_MIX3(P_from_rho_e(rho, e))
+  }
+  SGX_D double T_from_rho_e(int m, double rho, double e) const {
+    SGX_MIX3(T_from_rho_e(rho, e))
   }
   SGX_D double P_from_rho_T(int m, double rho, double T) const {
     SGX_MIX3(P_from_rho_T(rho, T))
@@ -1168,6 +1174,263 @@ struct FixedT : public Base<NM, NM, Eos> {
       sie[m] = ratio(u[m], rhobar[m]);
       u[m] = ratio(u[m], uscale);
       press[m] = ratio(eos.P_from_rho_T(m, rho[m], Tequil), uscale);
+    }
+    Residual();
+    return B::ResidualNorm();
+  }
+};
+
+// ---------------------------------------------------------------------------------------
+// PTESolverRhoU (:1934-2183): unknowns are the NM volume fractions and the NM energy
+// densities; equations: volume sum, energy sum, pressure and temperature equality of
+// consecutive materials.  Init tries the ideal-gas PTE guess (TryIdealPTE, :692-763).
+// ---------------------------------------------------------------------------------------
+template <int NM, class Eos>
+struct RhoU : public Base<NM, 2 * NM, Eos> {
+  static constexpr int NEQ = 2 * NM;
+  using B = Base<NM, 2 * NM, Eos>;
+  using B::dx;
+  using B::eos;
+  using B::jacobian;
+  using B::params_;
+  using B::press;
+  using B::residual;
+  using B::rho;
+  using B::rhobar;
+  using B::sie;
+  using B::temp;
+  using B::Tnorm;
+  using B::u;
+  using B::uscale;
+  using B::utotal_scale;
+  using B::vfrac;
+  double dpdv[NM], dtdv[NM], dpde[NM], dtde[NM], vtemp[NM], utemp[NM];
+
+  __device__ RhoU(const Eos &e, const MixParamsDev &p) : B(e, p) {}
+
+  __device__ inline double Init() {
+    B::InitBase();
+    Residual();
+    TryIdealPTE();
+    return B::ResidualNorm();
+  }
+  SGX_D void Fixup() {}
+  SGX_D void Finalize() { // base Finalize (:351-357)
+#pragma unroll
+    for (int m = 0; m < NM; m++) {
+      temp[m] *= Tnorm;
+      u[m] *= uscale;
+      press[m] *= uscale;
+    }
+  }
+  SGX_D void Residual() {
+    const double vsum = sum_neumaier(vfrac, NM);
+    const double esum = sum_neumaier(u, NM);
+    residual[0] = B::vfrac_total - vsum;
+    residual[1] = utotal_scale - esum;
+#pragma unroll
+    for (int m = 0; m < NM - 1; ++m)
+      residual[2 + m] = press[m + 1] - press[m];
+#pragma unroll
+    for (int m = NM + 1; m < NEQ; m++)
+      residual[m] = temp[m - NM] - temp[m - NM - 1];
+  }
+  // GetIdealPTE (:676-688) + TryIdealPTE (:692-763)
+  __device__ inline void TryIdealPTE() {
+    double rhoBsum = 0.0;
+    double Asum = 0.0;
+#pragma unroll
+    for (int m = 0; m < NM; m++) {
+      Asum += vfrac[m] * ratio(press[m], temp[m]);
+      rhoBsum += rho[m] * vfrac[m] * ratio(sie[m], temp[m]);
+    }
+    Asum *= uscale / Tnorm;
+    rhoBsum /= Tnorm;
+    const double Tideal = uscale / rhoBsum / Tnorm;
+    const double Pideal = ratio(Tnorm * Tideal * Asum, uscale * B::vfrac_total);
+    double etemp[NM], ptemp[NM], vsave[NM], rtemp[NM], res[NEQ];
+#pragma unroll
+    for (int m = 0; m < NM; ++m) {
+      etemp[m] = u[m];
+      ptemp[m] = press[m];
+      vsave[m] = vfrac[m];
+      rtemp[m] = rho[m];
+    }
+    double res_norm_old = 0.0;
+#pragma unroll
+    for (int m = 0; m < NEQ; ++m) {
+      res[m] = residual[m];
+      res_norm_old += res[m] * res[m];
+    }
+    const double alpha = ratio(Pideal, Tideal);
+    bool aborted = false;
+#pragma unroll
+    for (int m = 0; m < NM; ++m) {
+      if (!aborted) {
+        vfrac[m] *= ratio(press[m], (temp[m] * alpha));
+        if (Tnorm * Tideal < 0 ||
+            ratio(rhobar[m], vfrac[m]) < eos.RhoPmin(m, Tnorm * Tideal)) {
+#pragma unroll
+          for (int n = 0; n < NM; n++)
+            if (n <= m) vfrac[n] = vsave[n];
+          aborted = true;
+        }
+      }
+    }
+    if (aborted) return;
+#pragma unroll
+    for (int m = 0; m < NM; ++m) {
+      rho[m] = ratio(rhobar[m], vfrac[m]);
+      const double sie_m = eos.e_from_rho_T(m, rho[m], Tnorm * Tideal);
+      u[m] = rhobar[m] * ratio(sie_m, uscale);
+      press[m] =
+          ratio(B::GetPressureFromPreferred(m, rho[m], Tnorm * Tideal, sie_m, false), uscale);
+    }
+    Residual();
+    double res_norm_new = 0.0;
+#pragma unroll
+    for (int m = 0; m < NEQ; m++)
+      res_norm_new += residual[m] * residual[m];
+    if (res_norm_new > res_norm_old) {
+#pragma unroll
+      for (int m = 0; m < NM; ++m) {
+        vfrac[m] = vsave[m];
+        rho[m] = rtemp[m];
+        u[m] = etemp[m];
+        press[m] = ptemp[m];
+      }
+#pragma unroll
+      for (int m = 0; m < NEQ; ++m)
+        residual[m] = res[m];
+    } else {
+#pragma unroll
+      for (int m = 0; m < NM; ++m) {
+        temp[m] = Tideal;
+        sie[m] = uscale * ratio(u[m], rhobar[m]);
+      }
+    }
+  }
+  SGX_D void CheckPTE(bool &converged, bool &acceptable) const {
+    double mean_p = vfrac[0] * press[0];
+    double mean_t = rhobar[0] * temp[0];
+    double error_p = 0.0;
+    double error_t = 0.0;
+#pragma unroll
+    for (int m = 1; m < NM; ++m) {
+      mean_p += vfrac[m] * press[m];
+      mean_t += rhobar[m] * temp[m];
+      error_p += residual[m + 1] * residual[m + 1];
+      error_t += residual[m + NM] * residual[m + NM];
+    }
+    mean_t = ratio(mean_t, B::rho_total);
+    error_p = sqrt(error_p);
+    error_t = sqrt(error_t);
+    const bool converged_p = (error_p < params_.pte_rel_tolerance_p * fabs(mean_p) ||
+                              error_p < params_.pte_abs_tolerance_p);
+    const bool converged_t = (error_t < params_.pte_rel_tolerance_t * mean_t ||
+                              error_t < params_.pte_abs_tolerance_t);
+    const bool acceptable_p =
+        (error_p < params_.pte_rel_tolerance_p_sufficient * fabs(mean_p) ||
+         error_p < params_.pte_abs_tolerance_p_sufficient);
+    const bool acceptable_t = (error_t < params_.pte_rel_tolerance_t_sufficient * mean_t ||
+                               error_t < params_.pte_abs_tolerance_t_sufficient);
+    converged = converged_p && converged_t;
+    acceptable = acceptable_p && acceptable_t;
+  }
+  __device__ inline void Jacobian() {
+#pragma unroll
+    for (int m = 0; m < NM; m++) {
+      const double dv = (vfrac[m] < 0.5 ? 1.0 : -1.0) * vfrac[m] * params_.derivative_eps;
+      const double vf_pert = vfrac[m] + dv;
+      const double rho_pert = ratio(rhobar[m], vf_pert);
+      double t_pert = ratio(eos.T_from_rho_e(m, rho_pert, sie[m]), Tnorm);
+      double p_pert = ratio(
+          B::GetPressureFromPreferred(m, rho_pert, Tnorm * t_pert, sie[m], false), uscale);
+      dpdv[m] = stdmin(ratio(p_pert - press[m], dv), -fabs(params_.pte_max_dpdv));
+      dtdv[m] = ratio(t_pert - temp[m], dv);
+      const double de = fabs(u[m]) * params_.derivative_eps;
+      const double e_pert = ratio(u[m] + de, rhobar[m]);
+      t_pert = ratio(eos.T_from_rho_e(m, rho[m], uscale * e_pert), Tnorm);
+      p_pert = ratio(
+          B::GetPressureFromPreferred(m, rho[m], Tnorm * t_pert, uscale * e_pert, false),
+          uscale);
+      dpde[m] = ratio(p_pert - press[m], de);
+      dtde[m] = ratio(t_pert - temp[m], de);
+      if (fabs(dtde[m]) < params_.min_dtde) dtde[m] = params_.derivative_eps;
+    }
+#pragma unroll
+    for (int i = 0; i < NEQ * NEQ; ++i)
+      jacobian[i] = 0.0;
+#pragma unroll
+    for (int m = 0; m < NM; ++m) {
+      jacobian[m] = 1.0;
+      jacobian[2 * NM + NM + m] = 1.0;
+    }
+    // the reference writes these eight entries unconditionally (:2076-2083); for NM == 1 they
+    // index rows 2 and 3 of a 2 x 2 matrix, i.e. past the Jacobian, so they are guarded here
+    if constexpr (NM > 1) {
+      jacobian[2 * 2 * NM] = dpdv[0];
+      jacobian[NM * 2 * NM + NM - 1] = -dpdv[NM - 1];
+      jacobian[(NM + 1) * 2 * NM] = dtdv[0];
+      jacobian[(2 * NM - 1) * 2 * NM + NM - 1] = -dtdv[NM - 1];
+      jacobian[2 * 2 * NM + NM] = dpde[0];
+      jacobian[NM * 2 * NM + 2 * NM - 1] = -dpde[NM - 1];
+      jacobian[(NM + 1) * 2 * NM + NM] = dtde[0];
+      jacobian[(2 * NM - 1) * 2 * NM + 2 * NM - 1] = -dtde[NM - 1];
+    }
+#pragma unroll
+    for (int m = 1; m < NM - 1; ++m) {
+      jacobian[(1 + m) * 2 * NM + m] = -dpdv[m];
+      jacobian[(2 + m) * 2 * NM + m] = dpdv[m];
+      jacobian[(NM + m) * 2 * NM + m] = -dtdv[m];
+      jacobian[(NM + m + 1) * 2 * NM + m] = dtdv[m];
+      jacobian[(1 + m) * 2 * NM + NM + m] = -dpde[m];
+      jacobian[(2 + m) * 2 * NM + NM + m] = dpde[m];
+      jacobian[(NM + m) * 2 * NM + NM + m] = -dtde[m];
+      jacobian[(NM + m + 1) * 2 * NM + NM + m] = dtde[m];
+    }
+  }
+  __device__ inline double ScaleDx() {
+    double scale = 1.0;
+#pragma unroll
+    for (int m = 0; m < NM; ++m) {
+      if (scale * dx[m] < -0.1 * vfrac[m]) {
+        scale = -0.1 * ratio(vfrac[m], dx[m]);
+      }
+      const double dt = (dtdv[m] * dx[m] + dtde[m] * dx[m + NM]);
+      if (scale * dt < -0.1 * temp[m]) {
+        scale = -0.1 * ratio(temp[m], dt);
+      }
+      const double tt = temp[m] + scale * dt;
+      const double rho_min = stdmax(eos.RhoPmin(m, Tnorm * temp[m]), eos.RhoPmin(m, Tnorm * tt));
+      const double alpha_max = ratio(rhobar[m], rho_min);
+      if (alpha_max < vfrac[m]) continue;
+      if (scale * dx[m] > 0.5 * (alpha_max - vfrac[m])) {
+        scale = 0.5 * ratio(alpha_max - vfrac[m], dx[m]);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < NEQ; ++i)
+      dx[i] *= scale;
+    return scale;
+  }
+  __device__ inline double TestUpdate(const double scale, const bool cache_state = false) {
+    if (cache_state) {
+#pragma unroll
+      for (int m = 0; m < NM; ++m) {
+        vtemp[m] = vfrac[m];
+        utemp[m] = u[m];
+      }
+    }
+#pragma unroll
+    for (int m = 0; m < NM; ++m) {
+      vfrac[m] = vtemp[m] + scale * dx[m];
+      rho[m] = ratio(rhobar[m], vfrac[m]);
+      u[m] = utemp[m] + scale * dx[NM + m];
+      sie[m] = uscale * ratio(u[m], rhobar[m]);
+      temp[m] = ratio(eos.T_from_rho_e(m, rho[m], sie[m]), Tnorm);
+      press[m] = ratio(
+          B::GetPressureFromPreferred(m, rho[m], Tnorm * temp[m], sie[m], false), uscale);
     }
     Residual();
     return B::ResidualNorm();

@@ -29,8 +29,10 @@ __global__ void __launch_bounds__(128)
   for (int64_t t = tid; t < ncell; t += nthr) {
     using System = typename std::conditional<
         SOLVER == SGX_PTE_RHOT, mix::RhoT<NM, Acc>,
-        typename std::conditional<SOLVER == SGX_PTE_PT, mix::PT<NM, Acc>,
-                                  mix::FixedT<NM, Acc>>::type>::type;
+        typename std::conditional<
+            SOLVER == SGX_PTE_PT, mix::PT<NM, Acc>,
+            typename std::conditional<SOLVER == SGX_PTE_FIXED_T, mix::FixedT<NM, Acc>,
+                                      mix::RhoU<NM, Acc>>::type>::type>::type;
     System s(eos, prm);
     const int64_t base = t * NM;
 #pragma unroll

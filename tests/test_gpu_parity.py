@@ -527,6 +527,22 @@ def test_pte_rhot_generic_mixtures(pkg, ref, torch_cuda, nmat):
         assert_rel(got.cpu().numpy()[conv], want[conv], PTE_TOL, f"nmat={nmat} PTE state {nm}")
 
 
+@pytest.mark.parametrize("which", ["test_params", "default_params"])
+def test_pte_rhou_parity(pkg, ref, torch_cuda, which):
+    """PTESolverRhoU (closure/mixed_cell_models.hpp:1934-2183, incl. TryIdealPTE :692-763) on
+    the test/test_pte.cpp mixture: identical `converged`, states within 1e-10 under the library
+    defaults; under the 1e-16 test tolerances the iteration ends in round-off noise like RhoT
+    (see test_pte_rhot_parity) and the flags other than `converged` are reported."""
+    n = 1 << 13
+    vf = pkg.workloads.pte_vfracs(n)
+    if which == "test_params":
+        _pte_compare(pkg, ref, torch_cuda, pkg._lib.PTE_RHOU, vf, pkg.closure.test_pte_params(),
+                     what="RhoU/test_params", strict_flags=False)
+    else:
+        _pte_compare(pkg, ref, torch_cuda, pkg._lib.PTE_RHOU, vf, pkg.closure.MixParams(),
+                     what="RhoU/default_params", strict_flags=True)
+
+
 @pytest.mark.parametrize("mix", ["3mat", "ideal+solids"])
 def test_pte_fixed_T_parity(pkg, ref, torch_cuda, mix):
     """PTESolverFixedT (closure/mixed_cell_models.hpp:1462-1672): temperatures given per cell,
