@@ -156,6 +156,11 @@ PROTOTYPES = {
                            [C.POINTER(MixParams), _VP, _VP]),
     "sgx_fastmath_eval": (C.c_int, [C.c_int, _VP, _VP, _I64, _VP]),
     "sgx_solve_Ax_b": (C.c_int, [C.c_int, _VP, _VP, _VP, _I64, _VP]),
+    "sgx_comm_unique_id": (C.c_int, [C.c_char_p]),
+    "sgx_comm_create": (C.c_int, [C.c_char_p, C.c_int, C.c_int, C.POINTER(_VP)]),
+    "sgx_comm_from_nccl": (C.c_int, [_VP, C.POINTER(_VP)]),
+    "sgx_comm_destroy": (C.c_int, [_VP]),
+    "sgx_stats_allreduce": (C.c_int, [_VP, _VP, C.c_int, _VP]),
 }
 
 _lib = None

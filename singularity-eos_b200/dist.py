@@ -42,3 +42,44 @@ def max_over_ranks(seconds, device):
     t = torch.tensor([seconds], dtype=torch.float64, device=device)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return float(t.item())
+
+
+class StatsComm:
+    """The C ABI's own communicator for `sgx_stats_allreduce` (NCCL bound at run time inside
+    the library).  Rank 0 makes the id; `exchange` ships 128 bytes to the other ranks (any
+    transport: torch.distributed object broadcast here, MPI_Bcast in a host code)."""
+
+    def __init__(self, rank, world, exchange=None):
+        import ctypes as C
+
+        from . import _lib
+
+        self._lib = _lib
+        lib = _lib.load()
+        buf = C.create_string_buffer(128)
+        if rank == 0:
+            _lib.check(lib.sgx_comm_unique_id(buf))
+        raw = bytes(buf.raw)
+        if world > 1:
+            if exchange is None:
+                import torch.distributed as dist
+
+                box = [raw]
+                dist.broadcast_object_list(box, src=0)
+                raw = box[0]
+            else:
+                raw = exchange(raw)
+        self.h = C.c_void_p()
+        _lib.check(lib.sgx_comm_create(C.create_string_buffer(raw, 128), world, rank,
+                                       C.byref(self.h)))
+
+    def allreduce(self, stats, stream=None):
+        """In-place sum of a device int64/uint64 tensor over the ranks."""
+        self._lib.check(self._lib.load().sgx_stats_allreduce(self.h, stats.data_ptr(),
+                                                             stats.numel(), stream))
+        return stats
+
+    def close(self):
+        if self.h:
+            self._lib.load().sgx_comm_destroy(self.h)
+            self.h = None

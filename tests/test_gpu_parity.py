@@ -902,3 +902,18 @@ def test_cpp_host_shim(pkg, torch_cuda):
     print(out.stdout)
     assert out.returncode == 0, out.stdout + out.stderr
     assert out.stdout.strip().endswith("ok")
+
+
+def test_stats_allreduce_single_rank(pkg, torch_cuda):
+    """sgx_stats_allreduce through the C ABI's own NCCL communicator (one rank here; the
+    multi-rank run is tests/run_stats_allreduce.py under torchrun)."""
+    import os
+    import subprocess
+    import sys
+
+    script = os.path.join(os.path.dirname(os.path.abspath(__file__)), "run_stats_allreduce.py")
+    env = dict(os.environ, RANK="0", WORLD_SIZE="1", LOCAL_RANK="0")
+    out = subprocess.run([sys.executable, script], env=env, capture_output=True, text=True,
+                         timeout=600)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert "OK" in out.stdout
