@@ -983,28 +983,40 @@ int sgx_FillEos_host(sgx_eos_t e, double *rhos, double *temps, double *energies,
   int rc = check_handle(e);
   if (rc) return rc;
   if (n <= 0) return n == 0 ? SGX_OK : fail(SGX_ERR_INVALID, "negative n");
-  const size_t nb = (size_t)n * sizeof(double);
-  const size_t lb = lambda ? nb * ls : 0;
-  rc = ensure_staging(e, 0, 6 * nb + lb);
+  // same chunk pipeline as sgx_eos_eval_host: kHostSlots device slots, one stream each
+  const int64_t chunk = n < kHostChunk ? n : kHostChunk;
+  const size_t per_cell = (size_t)(6 + (lambda ? ls : 0)) * sizeof(double);
+  const size_t slot_bytes = ((size_t)chunk * per_cell + 255) & ~size_t(255);
+  rc = ensure_staging(e, 0, kHostSlots * slot_bytes);
   if (rc) return rc;
-  cudaStream_t s = e->own_stream;
+  rc = ensure_host_streams(e);
+  if (rc) return rc;
   double *h[6] = {rhos, temps, energies, presses, cvs, bmods};
   const unsigned long bits[6] = {TQ_DENSITY, TQ_TEMPERATURE, TQ_SIE, TQ_PRESSURE, TQ_CV, TQ_BMOD};
-  double *d[6];
-  for (int k = 0; k < 6; ++k)
-    d[k] = h[k] ? (double *)e->dscratch + (size_t)k * n : nullptr;
-  double *dl = lambda ? (double *)e->dscratch + 6 * (size_t)n : nullptr;
-  for (int k = 0; k < 4; ++k) // cv / bmod are never inputs
-    if (h[k] && !(output & bits[k]))
-      SGX_CUDA_OK(cudaMemcpyAsync(d[k], h[k], nb, cudaMemcpyHostToDevice, s));
-  if (lambda) SGX_CUDA_OK(cudaMemcpyAsync(dl, lambda, lb, cudaMemcpyHostToDevice, s));
-  rc = sgx_FillEos(e, d[0], d[1], d[2], d[3], d[4], d[5], n, output, dl, ls, s);
-  if (rc) return rc;
-  for (int k = 0; k < 6; ++k)
-    if (h[k] && (output & bits[k]))
-      SGX_CUDA_OK(cudaMemcpyAsync(h[k], d[k], nb, cudaMemcpyDeviceToHost, s));
-  if (lambda) SGX_CUDA_OK(cudaMemcpyAsync(lambda, dl, lb, cudaMemcpyDeviceToHost, s));
-  SGX_CUDA_OK(cudaStreamSynchronize(s));
+  int slot = 0;
+  for (int64_t i0 = 0; i0 < n; i0 += chunk, slot = (slot + 1) % kHostSlots) {
+    const int64_t m = (n - i0) < chunk ? (n - i0) : chunk;
+    const size_t nb = (size_t)m * sizeof(double);
+    cudaStream_t s = e->host_streams[slot];
+    double *base = (double *)((char *)e->dscratch + slot * slot_bytes);
+    double *d[6];
+    for (int k = 0; k < 6; ++k)
+      d[k] = h[k] ? base + (size_t)k * chunk : nullptr;
+    double *dl = lambda ? base + 6 * (size_t)chunk : nullptr;
+    double *hl = lambda ? lambda + (size_t)i0 * ls : nullptr;
+    for (int k = 0; k < 4; ++k) // cv / bmod are never inputs
+      if (h[k] && !(output & bits[k]))
+        SGX_CUDA_OK(cudaMemcpyAsync(d[k], h[k] + i0, nb, cudaMemcpyHostToDevice, s));
+    if (lambda) SGX_CUDA_OK(cudaMemcpyAsync(dl, hl, nb * ls, cudaMemcpyHostToDevice, s));
+    rc = sgx_FillEos(e, d[0], d[1], d[2], d[3], d[4], d[5], m, output, dl, ls, s);
+    if (rc) return rc;
+    for (int k = 0; k < 6; ++k)
+      if (h[k] && (output & bits[k]))
+        SGX_CUDA_OK(cudaMemcpyAsync(h[k] + i0, d[k], nb, cudaMemcpyDeviceToHost, s));
+    if (lambda) SGX_CUDA_OK(cudaMemcpyAsync(hl, dl, nb * ls, cudaMemcpyDeviceToHost, s));
+  }
+  for (int k = 0; k < kHostSlots; ++k)
+    SGX_CUDA_OK(cudaStreamSynchronize(e->host_streams[k]));
   return SGX_OK;
 }
 

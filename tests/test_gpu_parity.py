@@ -656,6 +656,18 @@ def test_host_entry_points_multi_chunk_equal_device_path(pkg, torch_cuda, raw):
     g.eval_host(L.P_FROM_RHO_T, rho_h, T_h, out_h, lam_h)
     assert_bits(out_h, out_d.cpu().numpy(), "eval_host P")
     assert_bits(lam_h, lam_d.cpu().numpy(), "eval_host lambda")
+    # FillEos (rho, T) -> e, P, cv, bmod over the same ragged range
+    tq = pkg.thermalqs
+    mask = tq.specific_internal_energy | tq.pressure | tq.specific_heat | tq.bulk_modulus
+    outs_d = [torch.zeros(n, dtype=torch.float64, device="cuda") for _ in range(4)]
+    lam_d.fill_(float("nan"))
+    g.FillEos(dev(rho_h), dev(T_h), *outs_d, n, mask, lam_d)
+    outs_h = [np.zeros(n) for _ in range(4)]
+    lam_h = np.full((n, 2), np.nan)
+    g.FillEos_host(rho_h.copy(), T_h.copy(), *outs_h, mask, lam_h)
+    for a, b, nm in zip(outs_h, outs_d, ("e", "P", "cv", "bmod")):
+        assert_bits(a, b.cpu().numpy(), "FillEos_host " + nm)
+    assert_bits(lam_h, lam_d.cpu().numpy(), "FillEos_host lambda")
     # PTE: 2 chunks + ragged tail
     n = (1 << 21) + 777
     g3 = pkg.closure.set_eos_3mat_analytic()
