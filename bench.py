@@ -462,6 +462,16 @@ def run_ours(args):
         sampler.stop()
         clocks = sampler.summary(t_head0, t_head1)  # warm-up + timed region of the headline
         clocks["all_configs"] = sampler.summary()
+    # FP64 pipe peak of this GPU, for the FP64-bound configs (3a, 4, 5); pipe utilisation of
+    # those kernels comes from the committed ncu captures (profiles/r1h_*_details.txt)
+    import ctypes
+    fp64 = {}
+    for name, fused in (("dfma_tflops", 1), ("dmul_dadd_tflops", 0)):
+        v = ctypes.c_double(0.0)
+        if lib.sgx_microbench_fp64(fused, ctypes.byref(v)) == 0:
+            fp64[name] = v.value
+    fp64["ncu_pipe_fp64_pct"] = {"pte_rhot_sm_kernel": 30.0, "rootfind eval_kernel": 44.4,
+                                 "helm_fill_kernel": 42.3}
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K,
         "warmup": Wu, "ms_per_step": secs / K * 1e3, "higher_is_better": True,
@@ -472,7 +482,7 @@ def run_ours(args):
                    "l2_policy": "inputs (1 GiB/GPU) larger than L2; no flush needed",
                    "parallelism": f"cells sharded contiguously over {world} GPU(s), tables replicated"},
         "roofline": roofline, "e2e": e2e, "gpu_launches": int(launches),
-        "clocks": clocks, "configs": results,
+        "clocks": clocks, "fp64_peak": fp64, "configs": results,
     }
     if all_cpus:
         os.sched_setaffinity(0, all_cpus)  # the CPU baseline uses every host core

@@ -161,6 +161,7 @@ PROTOTYPES = {
     "sgx_comm_from_nccl": (C.c_int, [_VP, C.POINTER(_VP)]),
     "sgx_comm_destroy": (C.c_int, [_VP]),
     "sgx_stats_allreduce": (C.c_int, [_VP, _VP, C.c_int, _VP]),
+    "sgx_microbench_fp64": (C.c_int, [C.c_int, C.POINTER(C.c_double)]),
 }
 
 _lib = None

@@ -59,6 +59,33 @@ struct sgx_comm_s {
 
 using namespace sgx;
 
+// ---- FP64 pipe peak: the denominator for the FP64-bound kernels ---------
+// 8 independent accumulators per thread; fused = DFMA chain, else DMUL + DADD pairs (the
+// library is compiled with -fmad=false, so its kernels run on the non-fused rate for a*b+c).
+template <int FUSED>
+__global__ void __launch_bounds__(256) fp64_peak_kernel(double *out, const int iters,
+                                                       const double a, const double b) {
+  double x[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k)
+    x[k] = threadIdx.x * 1e-3 + k;
+  for (int i = 0; i < iters; ++i) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      if (FUSED) {
+        x[k] = __fma_rn(x[k], a, b);
+      } else {
+        x[k] = __dadd_rn(__dmul_rn(x[k], a), b);
+      }
+    }
+  }
+  double s = 0;
+#pragma unroll
+  for (int k = 0; k < 8; ++k)
+    s += x[k];
+  if (s == 12345.678) out[0] = s; // keep the chain alive
+}
+
 extern "C" {
 
 int sgx_comm_unique_id(char id[SGX_COMM_ID_BYTES]) {
@@ -115,6 +142,38 @@ int sgx_stats_allreduce(sgx_comm_t c, uint64_t *stats, int n, sgx_stream_t strea
   const int rc = nccl().AllReduce(stats, stats, (size_t)n, kNcclUint64, kNcclSum, c->comm,
                                   (cudaStream_t)stream);
   if (rc != kNcclSuccess) return nccl_fail("ncclAllReduce", rc);
+  return SGX_OK;
+}
+
+int sgx_microbench_fp64(int fused, double *tflops) {
+  if (!tflops) return fail(SGX_ERR_INVALID, "null result");
+  double *d = nullptr;
+  SGX_CUDA_OK(cudaMalloc(&d, sizeof(double)));
+  const int iters = 4096, threads = 256;
+  const int blocks = sm_count() * 8;
+  cudaEvent_t e0, e1;
+  SGX_CUDA_OK(cudaEventCreate(&e0));
+  SGX_CUDA_OK(cudaEventCreate(&e1));
+  float best = 1e30f;
+  for (int rep = 0; rep < 4; ++rep) {
+    SGX_CUDA_OK(cudaEventRecord(e0));
+    if (fused) {
+      fp64_peak_kernel<1><<<blocks, threads>>>(d, iters, 1.0000001, 1e-9);
+    } else {
+      fp64_peak_kernel<0><<<blocks, threads>>>(d, iters, 1.0000001, 1e-9);
+    }
+    SGX_CUDA_OK(cudaEventRecord(e1));
+    SGX_CUDA_OK(cudaEventSynchronize(e1));
+    float ms = 0;
+    SGX_CUDA_OK(cudaEventElapsedTime(&ms, e0, e1));
+    if (rep > 0 && ms < best) best = ms;
+  }
+  count_launch(4);
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaFree(d);
+  // 2 flops per element-iteration either way (one multiply and one add)
+  *tflops = 2.0 * 8 * iters * (double)threads * blocks / (best * 1e-3) / 1e12;
   return SGX_OK;
 }
 
