@@ -102,6 +102,16 @@ int launch_pte_rhot(const EosSet &set, bool bench_mix, const MixParamsDev &prm, 
                     const double *sie_tot, const double *vfrac_tot, const double *Tguess,
                     uint64_t *status, double *residual, uint64_t *stats, int64_t ncell,
                     cudaStream_t s);
+int launch_pte_fixedt(const EosSet &set, bool bench_mix, const MixParamsDev &prm, double *rho,
+                      double *vfrac, double *sie, double *temp, double *press,
+                      const double *sie_tot, const double *vfrac_tot, const double *Tguess,
+                      uint64_t *status, double *residual, uint64_t *stats, int64_t ncell,
+                      cudaStream_t s);
+int launch_pte_rhou(const EosSet &set, bool bench_mix, const MixParamsDev &prm, double *rho,
+                    double *vfrac, double *sie, double *temp, double *press,
+                    const double *sie_tot, const double *vfrac_tot, const double *Tguess,
+                    uint64_t *status, double *residual, uint64_t *stats, int64_t ncell,
+                    cudaStream_t s);
 // SpinerRhoT T(rho, e) root find as a warp-level flow kernel (sgx_spiner_root.cu)
 int launch_rhot_T_from_rho_e_flow(const SpinerRhoT &eos, const double *rho, const double *sie,
                                   double *out, int64_t n, double *lambda, int ls,

@@ -135,29 +135,16 @@ int sgx_pte_solve(int solver, const sgx_eos_t *eos, int nmat, int64_t ncell, dou
   const bool is_bench_mix = nmat == 3 && set.e[0].kind == SGX_EOS_GRUNEISEN &&
                             set.e[1].kind == SGX_EOS_DAVIS_REACTANTS &&
                             set.e[2].kind == SGX_EOS_DAVIS_PRODUCTS;
+#define SGX_PTE_TAIL                                                                     \
+  prm, rho, vfrac, sie, temp, press, sie_tot, vfrac_tot, Tguess, status, residual, stats,  \
+      ncell, s
 #define SGX_PTE_ARGS                                                                     \
   set, prm, rho, vfrac, sie, temp, press, sie_tot, vfrac_tot, Tguess, status, residual,   \
       stats, ncell, s
   if (solver == SGX_PTE_RHOT) return launch_pte_rhot(set, is_bench_mix, prm, rho, vfrac, sie, temp, press, sie_tot,
                            vfrac_tot, Tguess, status, residual, stats, ncell, s);
-  if (solver == SGX_PTE_RHOU) {
-    if (is_bench_mix) return launch_pte_percell<3, Mix3GrDrDp, SGX_PTE_RHOU>(SGX_PTE_ARGS);
-    if (nmat == 2) return launch_pte_percell<2, DynEos, SGX_PTE_RHOU>(SGX_PTE_ARGS);
-    return launch_pte_percell<3, DynEos, SGX_PTE_RHOU>(SGX_PTE_ARGS);
-  }
-  if (solver == SGX_PTE_FIXED_T) {
-    if (is_bench_mix) return launch_pte_percell<3, Mix3GrDrDp, SGX_PTE_FIXED_T>(SGX_PTE_ARGS);
-    switch (nmat) {
-    case 1:
-      return launch_pte_percell<1, DynEos, SGX_PTE_FIXED_T>(SGX_PTE_ARGS);
-    case 2:
-      return launch_pte_percell<2, DynEos, SGX_PTE_FIXED_T>(SGX_PTE_ARGS);
-    case 3:
-      return launch_pte_percell<3, DynEos, SGX_PTE_FIXED_T>(SGX_PTE_ARGS);
-    default:
-      return launch_pte_percell<4, DynEos, SGX_PTE_FIXED_T>(SGX_PTE_ARGS);
-    }
-  }
+  if (solver == SGX_PTE_RHOU) return launch_pte_rhou(set, is_bench_mix, SGX_PTE_TAIL);
+  if (solver == SGX_PTE_FIXED_T) return launch_pte_fixedt(set, is_bench_mix, SGX_PTE_TAIL);
   if (is_bench_mix) return launch_pte_percell<3, Mix3GrDrDp, SGX_PTE_PT>(SGX_PTE_ARGS);
   switch (nmat) {
   case 1:
@@ -170,6 +157,7 @@ int sgx_pte_solve(int solver, const sgx_eos_t *eos, int nmat, int64_t ncell, dou
     return launch_pte_percell<4, DynEos, SGX_PTE_PT>(SGX_PTE_ARGS);
   }
 #undef SGX_PTE_ARGS
+#undef SGX_PTE_TAIL
 }
 
 int sgx_pte_solve_host(int solver, const sgx_eos_t *eos, int nmat, int64_t ncell,
