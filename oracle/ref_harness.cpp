@@ -252,6 +252,13 @@ int ref_solve_Ax_b(int n, double *a, double *b) {
   double scr[16];
   return mix_impl::solve_Ax_b_wscr(n, a, b, scr) ? 1 : 0;
 }
+// batch form for the bit-equality test of the device linear solver (a, b as in the C ABI's
+// sgx_solve_Ax_b: [batch][n*n] row-major and [batch][n], both overwritten)
+void ref_solve_Ax_b_batch(int n, double *a, double *b, int *ok, long batch) {
+  double scr[16];
+  for (long i = 0; i < batch; ++i)
+    ok[i] = mix_impl::solve_Ax_b_wscr(n, a + i * n * n, b + i * n, scr) ? 1 : 0;
+}
 double ref_sum_neumaier(const double *x, int n) { return mix_impl::sum_neumaier(x, n); }
 
 // ---- EOS handles ----------------------------------------------------------------

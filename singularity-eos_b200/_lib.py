@@ -155,6 +155,7 @@ PROTOTYPES = {
     "sgx_pte_solve_host": (C.c_int, [C.c_int, C.POINTER(_VP), C.c_int, _I64] + [_VP] * 8 +
                            [C.POINTER(MixParams), _VP, _VP]),
     "sgx_fastmath_eval": (C.c_int, [C.c_int, _VP, _VP, _I64, _VP]),
+    "sgx_libm_eval": (C.c_int, [C.c_int, _VP, _VP, _VP, _I64, _VP]),
     "sgx_solve_Ax_b": (C.c_int, [C.c_int, _VP, _VP, _VP, _I64, _VP]),
     "sgx_comm_unique_id": (C.c_int, [C.c_char_p]),
     "sgx_comm_create": (C.c_int, [C.c_char_p, C.c_int, C.c_int, C.POINTER(_VP)]),

@@ -291,7 +291,7 @@ struct DavisReactants {
              (b4y + 0.5 * (pow2i(b4y) + onethird * (pow3i(b4y) + C * pow4i(b4y) * 0.25)) +
               ratio(pow2i(y), pow4i(1 - y)));
     } else {
-      return phat * (exp(b4y) - 1.0);
+      return phat * (xexp(b4y) - 1.0);
     }
   }
   // eos_davis.hpp:418-434
@@ -307,7 +307,7 @@ struct DavisReactants {
                 (1.0 + onethird * b4y * (1.0 + 0.25 * b4y * (1.0 + C * 0.2 * b4y))) +
             onethird * pow3i(z);
     } else {
-      e_s = -y - ratio(1.0 - exp(b4y), 4.0 * B);
+      e_s = -y - ratio(1.0 - xexp(b4y), 4.0 * B);
     }
     return e0 + P0 * (spvol0 - ratio(1.0, stdmax(rho, 0.))) + phat * spvol0 * e_s;
   }
@@ -316,7 +316,7 @@ struct DavisReactants {
     if (rho <= 0) return T0;
     const double rho0overrho = ratio(rho0, stdmax(rho, 0.));
     const double y = 1 - rho0overrho;
-    return T0 * exp(-Z * y) * pow(rho0overrho, -G0 - Z);
+    return T0 * xexp(-Z * y) * xpow(rho0overrho, -G0 - Z);
   }
   // eos_davis.hpp:441-448
   SGX_D double Gamma(const double rho) const {
@@ -333,7 +333,7 @@ struct DavisReactants {
   SGX_D double T_from_rho_e(const double rho, const double sie, double * = nullptr) const {
     const double power_base = DimlessEdiff(rho, sie);
     if (power_base <= 0) return 0.;
-    const double tmp = pow(power_base, i1pa);
+    const double tmp = xpow(power_base, i1pa);
     return Ts(rho) * tmp;
   }
   // staged form of :76-84 (e), :92-97 (P), :129-139 (cv)
@@ -354,7 +354,7 @@ struct DavisReactants {
     const bool compressed = rho >= rho0;
     const bool y_pos = y > 0.0;
     double eb4y = 0.0;
-    if (!compressed || !y_pos) eb4y = exp(b4y);
+    if (!compressed || !y_pos) eb4y = xexp(b4y);
     if (compressed) {
       p.Ps = phat *
              (b4y + 0.5 * (pow2i(b4y) + onethird * (pow3i(b4y) + C * pow4i(b4y) * 0.25)) +
@@ -372,11 +372,11 @@ struct DavisReactants {
       e_s = -y - ratio(1.0 - eb4y, 4.0 * B);
     }
     p.Es = e0 + P0 * (spvol0 - ratio(1.0, stdmax(rho, 0.))) + phat * spvol0 * e_s;
-    p.Ts = T0 * exp(-Z * y) * pow(rho0overrho, -G0 - Z);
+    p.Ts = T0 * xexp(-Z * y) * xpow(rho0overrho, -G0 - Z);
     p.rG = (compressed ? G0 + Z * y : G0) * rho;
   }
   SGX_D double e_from_part(const RhoPart &p, double, const double temp) const {
-    return p.Es + Cv0 * p.Ts * i1pa * (pow(ratio(temp, p.Ts), 1.0 + alpha) - 1.0);
+    return p.Es + Cv0 * p.Ts * i1pa * (xpow(ratio(temp, p.Ts), 1.0 + alpha) - 1.0);
   }
   SGX_D double P_from_part(const RhoPart &p, double, const double sie) const {
     return p.Ps + p.rG * (sie - p.Es);
@@ -384,11 +384,11 @@ struct DavisReactants {
   SGX_D double cv_from_part(const RhoPart &p, double, const double sie) const {
     const double power_base = ratio(1.0 + alpha, p.Ts * Cv0) * (sie - p.Es) + 1.0;
     if (power_base <= 0) return 0.;
-    return ratio(Cv0, pow(power_base, -alpha * i1pa));
+    return ratio(Cv0, xpow(power_base, -alpha * i1pa));
   }
   SGX_D double e_from_rho_T(const double rho, const double temp, double * = nullptr) const {
     const double t_s = Ts(rho);
-    return Es(rho) + Cv0 * t_s * i1pa * (pow(ratio(temp, t_s), 1.0 + alpha) - 1.0);
+    return Es(rho) + Cv0 * t_s * i1pa * (xpow(ratio(temp, t_s), 1.0 + alpha) - 1.0);
   }
   SGX_D double P_from_rho_e(const double rho, const double sie, double * = nullptr) const {
     return Ps(rho) + Gamma(rho) * rho * (sie - Es(rho));
@@ -400,7 +400,7 @@ struct DavisReactants {
   SGX_D double cv_from_rho_e(const double rho, const double sie, double * = nullptr) const {
     const double power_base = DimlessEdiff(rho, sie);
     if (power_base <= 0) return 0.;
-    return ratio(Cv0, pow(power_base, -alpha * i1pa));
+    return ratio(Cv0, xpow(power_base, -alpha * i1pa));
   }
   SGX_D double cv_from_rho_T(const double rho, const double temp, double * = nullptr) const {
     return cv_from_rho_e(rho, e_from_rho_T(rho, temp));
@@ -417,7 +417,7 @@ struct DavisReactants {
             ? -phat * rho0 *
                   (4 * B * (1 + b4y + 0.5 * (pow2i(b4y) + onethird * C * pow3i(b4y))) +
                    3 * ratio(y, pow4i(1 - y)) + 4 * ratio(pow2i(y), pow5i(1 - y)))
-            : -phat * 4 * B * rho0 * exp(b4y);
+            : -phat * 4 * B * rho0 * xexp(b4y);
     const double gammav = (rho >= rho0) ? -Z * rho0 : 0.0;
     const double es = Es(rho);
     const double numerator =
@@ -442,7 +442,7 @@ struct DavisReactants {
                                         double &rho, double &sie) const {
     auto PofRatT = [&](const double r) {
       return (Ps(r) + Gamma(r) * r * Cv0 * Ts(r) * i1pa *
-                          (pow(ratio(temp, Ts(r)), 1 + alpha) - 1.0));
+                          (xpow(ratio(temp, Ts(r)), 1 + alpha) - 1.0));
     };
     root::regula_falsi(PofRatT, press, rho0, 1.0e-5, 1.0e3, 1.0e-8, 1.0e-8, rho);
     rho = stdmax(0., rho);
@@ -479,26 +479,26 @@ struct DavisProducts {
   SGX_D double F(const double rho) const {
     if (rho <= 0) return 0.;
     const double vvc = ratio(1.0, rho * vc);
-    return 2.0 * ratio(a, pow(vvc, 2 * n) + 1.0);
+    return 2.0 * ratio(a, xpow(vvc, 2 * n) + 1.0);
   }
   SGX_D double Ps(const double rho) const {
     if (rho <= 0) return 0.;
     const double vvc = ratio(1, rho * vc);
-    return pc * ratio(pow(0.5 * (pow(vvc, n) + pow(vvc, -n)), aon), pow(vvc, k + a)) *
+    return pc * ratio(xpow(0.5 * (xpow(vvc, n) + xpow(vvc, -n)), aon), xpow(vvc, k + a)) *
            ratio(k - 1.0 + F(rho), k - 1.0 + a);
   }
   SGX_D double Es(const double rho) const {
     if (rho <= 0) return 0.;
     const double vvc = ratio(1.0, rho * vc);
     const double ec = pc * ratio(vc, k - 1.0 + a);
-    return ratio(ec * pow(0.5 * (pow(vvc, n) + pow(vvc, -n)), aon), pow(vvc, k - 1.0 + a));
+    return ratio(ec * xpow(0.5 * (xpow(vvc, n) + xpow(vvc, -n)), aon), xpow(vvc, k - 1.0 + a));
   }
   SGX_D double Ts(const double rho) const {
     if (rho <= 0) return 0.;
     const double vvc = ratio(1.0, rho * vc);
     return Ts_coef *
-           ratio(pow(0.5 * (pow(vvc, n) + pow(vvc, -n)), aon * (1 - b)),
-                 pow(vvc, k - 1.0 + a * (1 - b)));
+           ratio(xpow(0.5 * (xpow(vvc, n) + xpow(vvc, -n)), aon * (1 - b)),
+                 xpow(vvc, k - 1.0 + a * (1 - b)));
   }
   SGX_D double Gamma(const double rho) const { return k - 1.0 + (1.0 - b) * F(rho); }
   SGX_D double T_from_rho_e(const double rho, const double sie, double * = nullptr) const {
@@ -517,13 +517,13 @@ struct DavisProducts {
       return;
     }
     const double vvc = ratio(1.0, rho * vc);
-    const double mix = 0.5 * (pow(vvc, n) + pow(vvc, -n));
-    const double mix_aon = pow(mix, aon);
-    const double Fv = 2.0 * ratio(a, pow(vvc, 2 * n) + 1.0);
-    p.Ts = Ts_coef * ratio(pow(mix, aon * (1 - b)), pow(vvc, k - 1.0 + a * (1 - b)));
+    const double mix = 0.5 * (xpow(vvc, n) + xpow(vvc, -n));
+    const double mix_aon = xpow(mix, aon);
+    const double Fv = 2.0 * ratio(a, xpow(vvc, 2 * n) + 1.0);
+    p.Ts = Ts_coef * ratio(xpow(mix, aon * (1 - b)), xpow(vvc, k - 1.0 + a * (1 - b)));
     const double ec = pc * ratio(vc, k - 1.0 + a);
-    p.Es = ratio(ec * mix_aon, pow(vvc, k - 1.0 + a));
-    p.Ps = pc * ratio(mix_aon, pow(vvc, k + a)) * ratio(k - 1.0 + Fv, k - 1.0 + a);
+    p.Es = ratio(ec * mix_aon, xpow(vvc, k - 1.0 + a));
+    p.Ps = pc * ratio(mix_aon, xpow(vvc, k + a)) * ratio(k - 1.0 + Fv, k - 1.0 + a);
     p.rG = rho * (k - 1.0 + (1.0 - b) * Fv);
   }
   SGX_D double e_from_part(const RhoPart &p, double, const double temp) const {
@@ -548,11 +548,11 @@ struct DavisProducts {
   SGX_D double bmod_from_rho_e(const double rho, const double sie, double * = nullptr) const {
     if (rho <= 0) return 0.;
     const double vvc = ratio(1.0, rho * vc);
-    const double Fx = -4 * a * n * ratio(pow(vvc, 2 * n - 1), pow2i(1 + pow(vvc, 2 * n)));
-    const double tmp = ratio(pow(0.5 * (pow(vvc, n) + pow(vvc, -n)), aon), pow(vvc, k + a));
+    const double Fx = -4 * a * n * ratio(xpow(vvc, 2 * n - 1), pow2i(1 + xpow(vvc, 2 * n)));
+    const double tmp = ratio(xpow(0.5 * (xpow(vvc, n) + xpow(vvc, -n)), aon), xpow(vvc, k + a));
     const double tmp_x =
-        0.5 * a * (pow(vvc, n - 1) - pow(vvc, -n - 1)) *
-            ratio(pow(0.5 * (pow(vvc, n) + pow(vvc, -n)), aon - 1), pow(vvc, k + a)) -
+        0.5 * a * (xpow(vvc, n - 1) - xpow(vvc, -n - 1)) *
+            ratio(xpow(0.5 * (xpow(vvc, n) + xpow(vvc, -n)), aon - 1), xpow(vvc, k + a)) -
         (k + a) * ratio(tmp, vvc);
     const double psv =
         ratio(pc, k - 1 + a) * ratio(tmp * Fx + (k - 1 + F(rho)) * tmp_x, vc);

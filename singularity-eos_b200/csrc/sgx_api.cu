@@ -386,12 +386,12 @@ __global__ void solve_kernel(const int n, double *__restrict__ a, double *__rest
                              int *__restrict__ ok, const int64_t batch) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= batch) return;
-  double la[9], lb[3];
+  double la[36], lb[6];
   for (int k = 0; k < n * n; ++k)
     la[k] = a[i * n * n + k];
   for (int k = 0; k < n; ++k)
     lb[k] = b[i * n + k];
-  const bool good = mix::solve_Ax_b<3>(n, la, lb);
+  const bool good = mix::solve_Ax_b<6>(n, la, lb);
   for (int k = 0; k < n * n; ++k)
     a[i * n * n + k] = la[k];
   for (int k = 0; k < n; ++k)
@@ -1031,7 +1031,7 @@ int sgx_fastmath_eval(int which, const double *x, double *y, int64_t n, sgx_stre
   return SGX_OK;
 }
 int sgx_solve_Ax_b(int n, double *a, double *b, int *ok, int64_t batch, sgx_stream_t stream) {
-  if (n < 1 || n > 3) return fail(SGX_ERR_INVALID, "n must be 1..3");
+  if (n < 1 || n > 6 || n == 5) return fail(SGX_ERR_INVALID, "n must be 1..4 or 6");
   if (batch <= 0) return batch == 0 ? SGX_OK : fail(SGX_ERR_INVALID, "negative batch");
   const int threads = 128;
   const int blocks = (int)((batch + threads - 1) / threads);

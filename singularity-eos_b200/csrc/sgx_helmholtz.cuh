@@ -59,7 +59,7 @@ struct HelmDev {
   int use_newton_raphson, lambda_has_lT_slot;
 
 #ifdef __CUDACC__
-  SGX_D static double pow10(const double x) { return exp(helm::LN10 * x); }
+  SGX_D static double pow10(const double x) { return xexp(helm::LN10 * x); }
   // hermite basis (base/hermite.hpp:24-56, 74-82)
   SGX_D static double psi0(double z) { return z * z * z * (z * (-6.0 * z + 15.0) - 10.0) + 1.0; }
   SGX_D static double dpsi0(double z) { return z * z * (z * (-30.0 * z + 60.0) - 30.0); }
@@ -382,7 +382,7 @@ struct HelmDev {
     const double dsda = ftpi * dxnida;
     constexpr double one_third = 1.0 / 3.0;
     const double si = ratio(1.0, s);
-    const double lami = ratio(1.0, cbrt(s));
+    const double lami = ratio(1.0, xcbrt(s));
     const double lamidd = -lami * one_third * dsdd * si;
     const double lamida = -lami * one_third * dsda * si;
     const double plasg = pow2i(ELECTRON_CHARGE_ESU * zbar) / (kbT * lami);
@@ -398,7 +398,7 @@ struct HelmDev {
       const double c1_o_x = ratio(c1, x);
       ecoul[VAL] = y * temp * (a1 * plasg + b1 * x + c1_o_x + d1);
       pcoul[VAL] = one_third * rho * ecoul[0];
-      scoul[VAL] = -y * (3.0 * b1 * x - 5.0 * c1_o_x + d1 * (log(plasg) - 1.0) - e1);
+      scoul[VAL] = -y * (3.0 * b1 * x - 5.0 * c1_o_x + d1 * (xlog(plasg) - 1.0) - e1);
       y = KBNA * temp * ytot * (a1 + ratio(0.25, plasg) * (b1 * x - c1_o_x));
       ecoul[DDR] = y * plasgdd;
       ecoul[DDT] = y * plasgdt + ratio(ecoul[0], temp);
@@ -416,7 +416,7 @@ struct HelmDev {
       scoul[DDZ] = y * plasgdz;
     } else {
       const double x = plasg * sqrt(fabs(plasg));
-      const double y = pow(plasg, b2);
+      const double y = xpow(plasg, b2);
       const double z = c2 * x - one_third * a2 * y;
       const double plasgi = ratio(1., plasg);
       const double rhoi = ratio(1.0, rho);
@@ -440,8 +440,8 @@ struct HelmDev {
       scoul[DDZ] = s * plasgdz;
     }
     double g_r, dgdf_r, g_t, dgdf_t;
-    butterworth12(log10(temp) - 4.5, 3.0, g_r, dgdf_r);
-    butterworth12(log10(rho) + 1.0, 6.0, g_t, dgdf_t);
+    butterworth12(xlog10(temp) - 4.5, 3.0, g_r, dgdf_r);
+    butterworth12(xlog10(rho) + 1.0, 6.0, g_t, dgdf_t);
     const double gain = (1.0 - g_t * g_r);
     const double dgaindt = -ratio(g_r * dgdf_t, temp * LN10);
     const double dgaindd = -ratio(g_t * dgdf_r, rho * LN10);
@@ -472,9 +472,9 @@ struct HelmDev {
     c.zbar = zbar;
     c.ytot = ratio(1.0, abar);
     c.ye = zbar * c.ytot;
-    c.ywot = log(ratio(abar * abar * sqrt(abar), rho * helm::NA));
+    c.ywot = xlog(ratio(abar * abar * sqrt(abar), rho * helm::NA));
     c.De = rho * c.ye;
-    c.lDe = log10(c.De);
+    c.lDe = xlog10(c.De);
     return c;
   }
   SGX_D static void mass_fractions(const double rho, const double ytot, double &xni,
@@ -495,7 +495,7 @@ struct HelmDev {
 #pragma unroll
     for (int i = 0; i < 5; ++i)
       etaele[i] = nep[i] = 0;
-    const double lT = log10(T);
+    const double lT = xlog10(T);
     const double lnT = lT / log10e;
     if (enable_rad) rad(rho, T, prad, erad, srad);
     if (enable_gas) {
@@ -508,7 +508,7 @@ struct HelmDev {
       } else {
         const double abar_ion = ratio(c.abar, c.zbar + 1);
         const double ytot_ion = ratio(1.0, abar_ion);
-        const double ywot_ion = ratio(log(abar_ion * abar_ion * sqrt(abar_ion)), rho * NA);
+        const double ywot_ion = ratio(xlog(abar_ion * abar_ion * sqrt(abar_ion)), rho * NA);
         const double y_ion = ywot_ion + LSWOT15 * lnT;
         double xni, dxnidd, dxnida;
         mass_fractions(rho, ytot_ion, xni, dxnidd, dxnida);
@@ -537,7 +537,7 @@ struct HelmDev {
 
   SGX_D static double lTAnalytic(const double rho, const double e, const double ni,
                                  const double ne) {
-    return log10((2.0 / 3.0) * ratio(e * rho, ni + ne) * helm::KBi);
+    return xlog10((2.0 / 3.0) * ratio(e * rho, ni + ne) * helm::KBi);
   }
 
   // lTFromRhoSie_ (:867-960).  `lambda` is the cell's lambda row (Abar, Zbar[, lT]).
@@ -592,7 +592,7 @@ struct HelmDev {
       lT = lTAnalytic(rho, e, ni, gas_ionized * ne);
       T = pow10(lT);
     }
-    lT = log10(T);
+    lT = xlog10(T);
     if (lT < lTMin) lT = lTMin;
     if (lT > lTMax) lT = lTMax;
     // :958 SafeGet (sic): with an lT slot the computed value is overwritten by the cache
@@ -629,7 +629,7 @@ struct HelmDev {
       lT = lTFromRhoSie(rho, energy, c, lambda);
       temp = pow10(lT);
     } else {
-      lT = log10(temp);
+      lT = xlog10(temp);
       if (lambda_has_lT_slot) lambda[2] = lT;
     }
     double p[NDERIV], e[NDERIV], s[NDERIV], etaele[NDERIV], nep[NDERIV];

@@ -32,7 +32,28 @@
 #include <cmath>
 #include <cstring>
 
+#include "sgx_libm.cuh"
+
 namespace sgx {
+
+// ---------------------------------------------------------------------------------------
+// The reference's std::exp / log / pow / log10 / cbrt.  Host code calls the host libm (the
+// one the reference links); device code runs the same glibc algorithm bit for bit
+// (sgx_libm.cuh), so both sides of the parity contract see identical transcendental values.
+// ---------------------------------------------------------------------------------------
+#ifdef __CUDA_ARCH__
+SGX_HD double xexp(const double x) { return libm::exp(x); }
+SGX_HD double xlog(const double x) { return libm::log(x); }
+SGX_HD double xpow(const double x, const double y) { return libm::pow(x, y); }
+SGX_HD double xlog10(const double x) { return libm::log10(x); }
+SGX_HD double xcbrt(const double x) { return libm::cbrt(x); }
+#else
+SGX_HD double xexp(const double x) { return std::exp(x); }
+SGX_HD double xlog(const double x) { return std::log(x); }
+SGX_HD double xpow(const double x, const double y) { return std::pow(x, y); }
+SGX_HD double xlog10(const double x) { return std::log10(x); }
+SGX_HD double xcbrt(const double x) { return std::cbrt(x); }
+#endif
 
 // ---------------------------------------------------------------------------------------
 // robust utils

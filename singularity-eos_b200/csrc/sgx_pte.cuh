@@ -15,6 +15,7 @@
 #define SGX_PTE_CUH_
 
 #include "sgx_analytic.cuh"
+#include "sgx_linsolve.cuh"
 #include "sgx_math.cuh"
 
 namespace sgx {
@@ -243,198 +244,6 @@ struct Mix3GrDrDp {
 };
 
 namespace mix {
-
-// error_utils::bad_value == !is_normal_or_zero (base/error_utils.hpp:31-76)
-SGX_D bool is_normal(const double v) {
-  const double a = fabs(v);
-  return (a >= DBL_MIN) && (a <= DBL_MAX); // excludes 0, subnormal, inf, NaN
-}
-SGX_D bool bad_value(const double v) {
-  const bool good = (v == 0.0) || (is_normal(1.0e10 * v) && is_normal(v));
-  return !good;
-}
-SGX_D bool isfinite_ref(const double a) { return (a == a) && ((a == 0) || (a != 2 * a)); }
-
-// sum_neumaier (:287-305)
-template <typename Op>
-SGX_D double sum_neumaier(const double *data, const int n, const int offset, const int iskip,
-                          const Op &op) {
-  double sum = 0;
-  double c = 0;
-#pragma unroll
-  for (int i = 0; i < n; ++i) {
-    if (iskip >= 0 && i == iskip) continue;
-    const double x = op(data[i + offset]);
-    const double t = sum + x;
-    if (fabs(sum) >= fabs(x)) {
-      c += (sum - t) + x;
-    } else {
-      c += (x - t) + sum;
-    }
-    sum = t;
-  }
-  return sum + c;
-}
-SGX_D double sum_neumaier(const double *data, const int n, const int offset = 0,
-                          const int iskip = -1) {
-  return sum_neumaier(data, n, offset, iskip, [](const double x) { return x; });
-}
-
-// Column-pivoted Householder QR solve for n >= 3 (the reference delegates to Eigen's
-// colPivHouseholderQr, :266-273).  a is row-major N x N (destroyed), b -> x.
-// N is a compile-time constant and every loop is unrolled with static indices: the pivot
-// column is brought to position k by predicated swaps, never by a[i*n + piv], so the
-// matrix stays in registers (a dynamically indexed member would push the whole solver
-// object into local memory).  Arithmetic and its order are unchanged.
-template <int N>
-__device__ __forceinline__ void qr_solve_static(double *a, double *b) {
-  int perm[N];
-#pragma unroll
-  for (int j = 0; j < N; ++j)
-    perm[j] = j;
-#pragma unroll
-  for (int k = 0; k < N; ++k) {
-    // pivot: largest remaining column norm (recomputed: N is tiny)
-    int piv = k;
-    double best = -1;
-#pragma unroll
-    for (int j = k; j < N; ++j) {
-      double s = 0;
-#pragma unroll
-      for (int i = k; i < N; ++i)
-        s += a[i * N + j] * a[i * N + j];
-      if (s > best) {
-        best = s;
-        piv = j;
-      }
-    }
-#pragma unroll
-    for (int j = k + 1; j < N; ++j) {
-      if (piv == j) {
-#pragma unroll
-        for (int i = 0; i < N; ++i) {
-          const double t = a[i * N + k];
-          a[i * N + k] = a[i * N + j];
-          a[i * N + j] = t;
-        }
-        const int tp = perm[k];
-        perm[k] = perm[j];
-        perm[j] = tp;
-      }
-    }
-    // Householder vector for column k, rows k..N-1
-    const double c0 = a[k * N + k];
-    double tail = 0;
-#pragma unroll
-    for (int i = k + 1; i < N; ++i)
-      tail += a[i * N + k] * a[i * N + k];
-    if (tail != 0.0) { // else already triangular in this column
-      double beta = sqrt(c0 * c0 + tail);
-      if (c0 >= 0) beta = -beta;
-      const double tau = (beta - c0) / beta;
-      const double inv = 1.0 / (c0 - beta);
-      // v = [1, a[k+1..]/ (c0-beta)]
-#pragma unroll
-      for (int i = k + 1; i < N; ++i)
-        a[i * N + k] *= inv;
-      a[k * N + k] = beta;
-      // apply H = I - tau v v^T to the trailing columns and to b
-#pragma unroll
-      for (int j = k + 1; j < N; ++j) {
-        double s = a[k * N + j];
-#pragma unroll
-        for (int i = k + 1; i < N; ++i)
-          s += a[i * N + k] * a[i * N + j];
-        s *= tau;
-        a[k * N + j] -= s;
-#pragma unroll
-        for (int i = k + 1; i < N; ++i)
-          a[i * N + j] -= s * a[i * N + k];
-      }
-      double s = b[k];
-#pragma unroll
-      for (int i = k + 1; i < N; ++i)
-        s += a[i * N + k] * b[i];
-      s *= tau;
-      b[k] -= s;
-#pragma unroll
-      for (int i = k + 1; i < N; ++i)
-        b[i] -= s * a[i * N + k];
-    }
-  }
-  // back substitution R y = Q^T b
-  double y[N];
-#pragma unroll
-  for (int i = N - 1; i >= 0; --i) {
-    double s = b[i];
-#pragma unroll
-    for (int j = i + 1; j < N; ++j)
-      s -= a[i * N + j] * y[j];
-    y[i] = s / a[i * N + i];
-  }
-  // x[perm[j]] = y[j]
-#pragma unroll
-  for (int i = 0; i < N; ++i) {
-    double x = 0.0;
-#pragma unroll
-    for (int j = 0; j < N; ++j)
-      if (perm[j] == i) x = y[j];
-    b[i] = x;
-  }
-}
-
-// solve_Ax_b_wscr (:176-278), N a compile-time constant
-template <int N>
-__device__ __forceinline__ bool solve_Ax_b_static(double *a, double *b) {
-  bool nonzero_rows = true;
-#pragma unroll
-  for (int row = 0; row < N; ++row) {
-    if (nonzero_rows) { // the reference returns at the first all-zero row
-      double maxabs = 0;
-#pragma unroll
-      for (int column = 0; column < N; ++column) {
-        maxabs = stdmax(fabs(a[row * N + column]), maxabs);
-      }
-      if (maxabs == 0) {
-        nonzero_rows = false;
-      } else {
-#pragma unroll
-        for (int column = 0; column < N; ++column) {
-          a[row * N + column] /= maxabs;
-        }
-        b[row] /= maxabs;
-      }
-    }
-  }
-  if (!nonzero_rows) return false;
-  if constexpr (N == 1) {
-    b[0] = ratio(b[0], a[0]);
-  } else if constexpr (N == 2) {
-    const double det = a[0] * a[3] - a[1] * a[2];
-    const double x0 = ratio(a[3] * b[0] - a[1] * b[1], det);
-    const double x1 = ratio(a[0] * b[1] - a[2] * b[0], det);
-    b[0] = x0;
-    b[1] = x1;
-  } else {
-    qr_solve_static<N>(a, b);
-  }
-  bool retval = true;
-#pragma unroll
-  for (int i = 0; i < N; ++i)
-    if (!isfinite_ref(b[i])) retval = false;
-  return retval;
-}
-
-// runtime-n front end (building-block entry sgx_solve_Ax_b)
-template <int NMAX>
-__device__ inline bool solve_Ax_b(const int n, double *a, double *b) {
-  if (n == 1) return solve_Ax_b_static<1>(a, b);
-  if (n == 2) return solve_Ax_b_static<2>(a, b);
-  if constexpr (NMAX >= 4) {
-    if (n == 4) return solve_Ax_b_static<4>(a, b);
-  }
-  return solve_Ax_b_static<3>(a, b);
-}
 
 // ApproxTemperatureFromRhoMatU (:790-847); lambdas are NullIndexer here.
 template <int NM, class Eos>

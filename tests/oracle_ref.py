@@ -34,6 +34,7 @@ def load():
         "ref_regula_falsi_table": (C.c_int, [_VP, C.c_int, _D, _D, _D, _D, _D, _D, _D, _D,
                                              C.POINTER(_D)]),
         "ref_solve_Ax_b": (C.c_int, [C.c_int, _VP, _VP]),
+        "ref_solve_Ax_b_batch": (None, [C.c_int, _VP, _VP, _VP, C.c_long]),
         "ref_sum_neumaier": (_D, [_VP, C.c_int]),
         "ref_eos_ideal": (_VP, [_D, _D]),
         "ref_eos_gruneisen": (_VP, [_D] * 11),
@@ -143,6 +144,14 @@ class Ref:
         a = np.array(a, dtype=np.float64).copy()
         b = np.array(b, dtype=np.float64).copy()
         ok = self.lib.ref_solve_Ax_b(b.size, _p(a), _p(b))
+        return ok, b
+
+    def solve_Ax_b_batch(self, n, a, b):
+        """a [batch][n*n], b [batch][n] (copies); returns (ok[batch], x[batch][n])."""
+        a = np.array(a, dtype=np.float64).copy()
+        b = np.array(b, dtype=np.float64).copy()
+        ok = np.zeros(b.shape[0], dtype=np.int32)
+        self.lib.ref_solve_Ax_b_batch(n, _p(a), _p(b), ok.ctypes.data_as(_VP), b.shape[0])
         return ok, b
 
     def sum_neumaier(self, x):
