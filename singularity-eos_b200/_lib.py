@@ -156,6 +156,7 @@ PROTOTYPES = {
                            [C.POINTER(MixParams), _VP, _VP]),
     "sgx_fastmath_eval": (C.c_int, [C.c_int, _VP, _VP, _I64, _VP]),
     "sgx_libm_eval": (C.c_int, [C.c_int, _VP, _VP, _VP, _I64, _VP]),
+    "sgx_eos_root_stats": (C.c_int, [_VP, C.POINTER(C.c_uint64), C.c_int]),
     "sgx_solve_Ax_b": (C.c_int, [C.c_int, _VP, _VP, _VP, _I64, _VP]),
     "sgx_comm_unique_id": (C.c_int, [C.c_char_p]),
     "sgx_comm_create": (C.c_int, [C.c_char_p, C.c_int, C.c_int, C.POINTER(_VP)]),

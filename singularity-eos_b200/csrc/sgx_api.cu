@@ -9,8 +9,10 @@
 //    on the cell arrays, (ρ,T)→(lRho,lT) lambda write-back as one 16-byte store when
 //    lambda_stride == 2;
 //  * grid = (#SMs × resident blocks) so every SM streams from the first wave;
-//  * table gathers go through the read-only path and stay L2-resident (≤ 5 MiB per EOS,
-//    persisting access-policy window set at create time).
+//  * table gathers go through the read-only path (ld.global.nc); the packed tables are
+//    <= 18 MiB per EOS and stay L2-resident on their own against the .cs / no_allocate cell
+//    streams (measured: 99.9 % of table sectors hit L2, profiles/r1h_lookup_details.txt), so
+//    no persisting access-policy window is set.
 #include <cstdlib>
 #include <cstring>
 #include <new>
@@ -71,6 +73,24 @@ int ensure_staging(sgx_eos_s *e, size_t pinned_bytes, size_t device_bytes) {
     e->dscratch_bytes = device_bytes;
   }
   return SGX_OK;
+}
+
+HostPin::HostPin(const void *p, size_t bytes) {
+  static const bool enabled = [] {
+    const char *v = getenv("SGX_HOST_PIN");
+    return !(v && strcmp(v, "none") == 0);
+  }();
+  if (!enabled || !p || bytes < (size_t(1) << 20)) return; // small ranges: not worth a syscall
+  cudaPointerAttributes attr;
+  if (cudaPointerGetAttributes(&attr, p) != cudaSuccess) {
+    cudaGetLastError();
+    return;
+  }
+  if (attr.type != cudaMemoryTypeUnregistered) return; // already pinned / managed / device
+  if (cudaHostRegister(const_cast<void *>(p), bytes, cudaHostRegisterDefault) == cudaSuccess)
+    ptr = const_cast<void *>(p);
+  else
+    cudaGetLastError(); // clear; the copies still work from pageable memory
 }
 
 int ensure_host_streams(sgx_eos_s *e) {
@@ -451,10 +471,48 @@ int launch_eval(const EOS &eos, int method, const double *in1, const double *in2
   }
 }
 
+// Output masks the reference's scalar FillEos rejects (UNDEFINED_ERROR / EOS_ERROR aborts):
+// checked on the host so the call fails loudly instead of skipping cells.
+//   IdealGas   eos_ideal.hpp:236-262      Gruneisen  eos_gruneisen.hpp:527-548
+//   SpinerRhoT eos_spiner_rho_temp.hpp:1043-1093   SpinerRhoSie eos_spiner_rho_sie.hpp:842-900
+static const char *fill_mask_error(int kind, unsigned long output) {
+  const unsigned long in = ~output;
+  const bool oR = output & TQ_DENSITY, oT = output & TQ_TEMPERATURE, oE = output & TQ_SIE,
+             oP = output & TQ_PRESSURE;
+  switch (kind) {
+  case SGX_EOS_IDEAL:
+    if (oR && oE && (oP || oT)) return "IdealGas::FillEos: density and energy outputs need P and T inputs";
+    if (oP && oE && (oR || oT)) return "IdealGas::FillEos: pressure and energy outputs need rho and T inputs";
+    return nullptr;
+  case SGX_EOS_GRUNEISEN:
+    if (!((in & TQ_TEMPERATURE) && (in & TQ_PRESSURE)) && (oR || oE))
+      return "Gruneisen::FillEos: density and energy must be inputs unless P and T are given";
+    return nullptr;
+  case SGX_EOS_SPINER_RHOT:
+    if (oR && !((in & TQ_PRESSURE) && (in & TQ_TEMPERATURE)))
+      return "SpinerEOSDependsRhoT::FillEos: density output needs P and T inputs";
+    if (oT && !((in & TQ_DENSITY) && ((in & TQ_SIE) || (in & TQ_PRESSURE))))
+      return "SpinerEOSDependsRhoT::FillEos: temperature output needs rho and (sie or P) inputs";
+    return nullptr;
+  case SGX_EOS_SPINER_RHOSIE:
+    if (oT && oE) return "SpinerEOSDependsRhoSie::FillEos: T and sie cannot both be outputs";
+    if (oR && (oP || oT)) return "SpinerEOSDependsRhoSie::FillEos: density output needs P and T inputs";
+    return nullptr;
+  default:
+    return nullptr;
+  }
+}
+
 template <class EOS>
 int launch_fill(sgx_eos_s *h, const EOS &eos, double *rho, double *T, double *en, double *P,
                 double *cv, double *bmod, int64_t n, unsigned long output, double *lambda,
                 int lstride, cudaStream_t s) {
+  if (const char *why = fill_mask_error(h->kind, output)) return fail(SGX_ERR_UNSUPPORTED, "%s", why);
+  // every quantity the mask names -- input or output -- needs its array
+  double *arr[6] = {rho, T, en, P, cv, bmod};
+  const unsigned long bit[6] = {TQ_DENSITY, TQ_TEMPERATURE, TQ_SIE, TQ_PRESSURE, TQ_CV, TQ_BMOD};
+  for (int k = 0; k < 6; ++k)
+    if ((output & bit[k]) && !arr[k]) return fail(SGX_ERR_INVALID, "FillEos: null output array %d", k);
   const LaunchCfg c = stream_cfg(n, 256, 8);
   fill_kernel<EOS><<<c.blocks, c.threads, 0, s>>>(eos, rho, T, en, P, cv, bmod, n, output,
                                                   lambda, lstride, nullptr);
@@ -719,10 +777,12 @@ int sgx_eos_create_helmholtz(const char *table_path, const sgx_helm_options *opt
 
 int sgx_eos_destroy(sgx_eos_t e) {
   if (!e) return SGX_OK;
+  DeviceGuard guard;
   cudaSetDevice(e->device);
   if (e->tables.dev) cudaFree(e->tables.dev);
   if (e->pinned) cudaFreeHost(e->pinned);
   if (e->dscratch) cudaFree(e->dscratch);
+  if (e->root_stats) cudaFree(e->root_stats);
   if (e->own_stream) cudaStreamDestroy(e->own_stream);
   for (int k = 0; k < 4; ++k)
     if (e->host_streams[k]) cudaStreamDestroy(e->host_streams[k]);
@@ -772,6 +832,7 @@ int64_t sgx_eos_get_table(sgx_eos_t e, const char *name, double *out, int64_t ca
   if (!out) return n;
   const int64_t m = n < cap ? n : cap;
   // read back from the DEVICE copy: this is what the kernels see
+  DeviceGuard guard;
   if (check_handle(e)) return SGX_ERR_CUDA;
   cudaError_t err = cudaMemcpy(out, e->tables.dev + it->second.first, m * sizeof(double),
                                cudaMemcpyDeviceToHost);
@@ -787,15 +848,9 @@ int sgx_eos_get_scalar(sgx_eos_t e, const char *name, double *out) {
   return SGX_OK;
 }
 
-// The one-thread-per-cell root find is the default; SGX_ROOT_KERNEL=flow selects the
-// warp-level flow kernel of sgx_spiner_root.cu (bit-identical, measured no faster)
-static bool per_thread_root_kernel() {
-  const char *v = getenv("SGX_ROOT_KERNEL");
-  return !(v && strcmp(v, "flow") == 0);
-}
-
 int sgx_eos_eval(sgx_eos_t e, int method, const double *in1, const double *in2, double *out,
                  int64_t n, double *lambda, int lambda_stride, sgx_stream_t stream) {
+  DeviceGuard guard;
   int rc = check_handle(e);
   if (rc) return rc;
   if (n < 0) return fail(SGX_ERR_INVALID, "negative n");
@@ -815,8 +870,11 @@ int sgx_eos_eval(sgx_eos_t e, int method, const double *in1, const double *in2, 
   case SGX_EOS_DAVIS_PRODUCTS:
     return launch_eval(e->analytic.dp, method, in1, in2, out, n, nullptr, 0, s, 8);
   case SGX_EOS_SPINER_RHOT:
-    if (method == SGX_T_FROM_RHO_E && !per_thread_root_kernel())
-      return launch_rhot_T_from_rho_e_flow(e->rhot, in1, in2, out, n, lambda, lambda_stride, s);
+    // config 3a: direct inversion where it provably matches the reference iterate, the iterate
+    // itself elsewhere (sgx_spiner_root.cu); SGX_ROOT_MODE=exact keeps the iterate for all cells
+    if (method == SGX_T_FROM_RHO_E && root_mode() != 1)
+      return launch_rhot_T_from_rho_e_hybrid(e, root_mode() == 0, in1, in2, out, n, lambda,
+                                             lambda_stride, s);
     return launch_eval(e->rhot, method, in1, in2, out, n, lambda, lambda_stride, s, 8);
   case SGX_EOS_SPINER_RHOSIE:
     return launch_eval(e->rhosie, method, in1, in2, out, n, lambda, lambda_stride, s, 8);
@@ -852,10 +910,13 @@ int sgx_PressureEnergyFromDensityTemperature(sgx_eos_t e, const double *rhos,
                                              const double *temps, double *P, double *E,
                                              int64_t n, double *lambda, int ls,
                                              sgx_stream_t stream) {
+  DeviceGuard guard;
   int rc = check_handle(e);
   if (rc) return rc;
   if (n <= 0) return n == 0 ? SGX_OK : fail(SGX_ERR_INVALID, "negative n");
   if (!rhos || !temps || !P || !E) return fail(SGX_ERR_INVALID, "null array");
+  if (lambda && ls < sgx_eos_nlambda(e))
+    return fail(SGX_ERR_INVALID, "lambda_stride %d < nlambda %d", ls, sgx_eos_nlambda(e));
   cudaStream_t s = (cudaStream_t)stream;
   switch (e->kind) {
   case SGX_EOS_IDEAL:
@@ -878,10 +939,13 @@ int sgx_PressureEnergyFromDensityTemperature(sgx_eos_t e, const double *rhos,
 int sgx_FillEos(sgx_eos_t e, double *rhos, double *temps, double *energies, double *presses,
                 double *cvs, double *bmods, int64_t n, unsigned long output, double *lambda,
                 int ls, sgx_stream_t stream) {
+  DeviceGuard guard;
   int rc = check_handle(e);
   if (rc) return rc;
   if (n <= 0) return n == 0 ? SGX_OK : fail(SGX_ERR_INVALID, "negative n");
   if (output == 0) return fail(SGX_ERR_UNSUPPORTED, "FillEos: output == thermalqs::none");
+  if (lambda && ls < sgx_eos_nlambda(e))
+    return fail(SGX_ERR_INVALID, "lambda_stride %d < nlambda %d", ls, sgx_eos_nlambda(e));
   cudaStream_t s = (cudaStream_t)stream;
   switch (e->kind) {
   case SGX_EOS_IDEAL:
@@ -914,15 +978,27 @@ int sgx_FillEos(sgx_eos_t e, double *rhos, double *temps, double *energies, doub
 // Which way the lambda rows travel for a vector method: `in` = the kernel reads them (or leaves
 // some slots untouched, so the caller's values must survive the round trip), `out` = it writes.
 static void lambda_io(const sgx_eos_s *e, int method, int ls, bool &in, bool &out) {
-  const bool from_T = method == SGX_E_FROM_RHO_T || (method % 2) == 0;
+  const bool from_T = method == SGX_P_FROM_RHO_T || method == SGX_E_FROM_RHO_T ||
+                      method == SGX_CV_FROM_RHO_T || method == SGX_BMOD_FROM_RHO_T ||
+                      method == SGX_GAMMA_FROM_RHO_T;
   switch (e->kind) {
-  case SGX_EOS_SPINER_RHOT: // (rho,T) lookups only write (lRho,lT); (rho,e) ones read the cache
+  case SGX_EOS_SPINER_RHOT:
+    // (rho,T) lookups only write (lRho,lT); every *_FROM_RHO_E method reads lambda[1] as the
+    // root-find guess (eos_spiner_rho_temp.hpp:1218-1223) before writing both slots.  Slots past
+    // nlambda are never touched by the kernel, so a wider row must make the round trip.
     in = !from_T || ls != 2;
     out = true;
     break;
-  case SGX_EOS_SPINER_RHOSIE: // lambda[0] = lRho, never read
-    in = ls != 1;
-    out = true;
+  case SGX_EOS_SPINER_RHOSIE:
+    // lambda[0] = lRho is written, never read -- except GruneisenParamFromDensityInternalEnergy,
+    // which does not touch lambda at all (eos_spiner_rho_sie.hpp:757-761): nothing crosses the bus
+    // and the caller's rows stay as they are.
+    if (method == SGX_GAMMA_FROM_RHO_E) {
+      in = out = false;
+    } else {
+      in = ls != 1;
+      out = true;
+    }
     break;
   case SGX_EOS_HELMHOLTZ: // Abar, Zbar (and lT) in, lT out
     in = true;
@@ -940,49 +1016,82 @@ static void lambda_io(const sgx_eos_s *e, int method, int ls, bool &in, bool &ou
 static constexpr int kHostSlots = 4;
 static constexpr int64_t kHostChunk = 1 << 21; // cells per chunk (16 MiB per array)
 
+// On any failure inside a chunk loop the slot streams are drained before the error is returned,
+// so no asynchronous copy into the caller's buffers is still pending when the call comes back.
+#define SGX_PIPE_TRY(expr)                                                                 \
+  do {                                                                                     \
+    cudaError_t err__ = (expr);                                                            \
+    if (err__ != cudaSuccess) {                                                            \
+      rc = fail(SGX_ERR_CUDA, "%s: %s", #expr, cudaGetErrorString(err__));                 \
+      goto drain;                                                                          \
+    }                                                                                      \
+  } while (0)
+
+static int drain_host_streams(sgx_eos_s *e, int rc) {
+  for (int k = 0; k < kHostSlots; ++k) {
+    if (!e->host_streams[k]) continue;
+    cudaError_t err = cudaStreamSynchronize(e->host_streams[k]);
+    if (err != cudaSuccess && rc == SGX_OK)
+      rc = fail(SGX_ERR_CUDA, "cudaStreamSynchronize: %s", cudaGetErrorString(err));
+  }
+  return rc;
+}
+
 int sgx_eos_eval_host(sgx_eos_t e, int method, const double *in1, const double *in2,
                       double *out, int64_t n, double *lambda, int ls) {
+  DeviceGuard guard;
   int rc = check_handle(e);
   if (rc) return rc;
   if (n <= 0) return n == 0 ? SGX_OK : fail(SGX_ERR_INVALID, "negative n");
   if (!in1 || !in2 || !out) return fail(SGX_ERR_INVALID, "null array");
+  if (lambda && ls < sgx_eos_nlambda(e))
+    return fail(SGX_ERR_INVALID, "lambda_stride %d < nlambda %d", ls, sgx_eos_nlambda(e));
   bool lam_in = false, lam_out = false;
   if (lambda) lambda_io(e, method, ls, lam_in, lam_out);
+  const bool lam_dev = lam_in || lam_out; // rows that never cross the bus are not given to the kernel
   const int64_t chunk = n < kHostChunk ? n : kHostChunk;
-  const size_t per_cell = (size_t)(3 + (lambda ? ls : 0)) * sizeof(double);
+  const size_t per_cell = (size_t)(3 + (lam_dev ? ls : 0)) * sizeof(double);
   const size_t slot_bytes = ((size_t)chunk * per_cell + 255) & ~size_t(255);
   rc = ensure_staging(e, 0, kHostSlots * slot_bytes);
   if (rc) return rc;
   rc = ensure_host_streams(e);
   if (rc) return rc;
-  int slot = 0;
-  for (int64_t i0 = 0; i0 < n; i0 += chunk, slot = (slot + 1) % kHostSlots) {
-    const int64_t m = (n - i0) < chunk ? (n - i0) : chunk;
-    const size_t nb = (size_t)m * sizeof(double);
-    cudaStream_t s = e->host_streams[slot];
-    double *d1 = (double *)((char *)e->dscratch + slot * slot_bytes);
-    double *d2 = d1 + chunk, *dout = d2 + chunk;
-    double *dl = lambda ? dout + chunk : nullptr;
-    double *hl = lambda ? lambda + (size_t)i0 * ls : nullptr;
-    SGX_CUDA_OK(cudaMemcpyAsync(d1, in1 + i0, nb, cudaMemcpyHostToDevice, s));
-    SGX_CUDA_OK(cudaMemcpyAsync(d2, in2 + i0, nb, cudaMemcpyHostToDevice, s));
-    if (lam_in) SGX_CUDA_OK(cudaMemcpyAsync(dl, hl, nb * ls, cudaMemcpyHostToDevice, s));
-    rc = sgx_eos_eval(e, method, d1, d2, dout, m, dl, ls, s);
-    if (rc) return rc;
-    SGX_CUDA_OK(cudaMemcpyAsync(out + i0, dout, nb, cudaMemcpyDeviceToHost, s));
-    if (lam_out) SGX_CUDA_OK(cudaMemcpyAsync(hl, dl, nb * ls, cudaMemcpyDeviceToHost, s));
+  {
+    HostPin pin_in1(in1, (size_t)n * sizeof(double)), pin_in2(in2, (size_t)n * sizeof(double)),
+        pin_out(out, (size_t)n * sizeof(double)),
+        pin_lam(lam_dev ? lambda : nullptr, (size_t)n * ls * sizeof(double));
+    int slot = 0;
+    for (int64_t i0 = 0; i0 < n; i0 += chunk, slot = (slot + 1) % kHostSlots) {
+      const int64_t m = (n - i0) < chunk ? (n - i0) : chunk;
+      const size_t nb = (size_t)m * sizeof(double);
+      cudaStream_t s = e->host_streams[slot];
+      double *d1 = (double *)((char *)e->dscratch + slot * slot_bytes);
+      double *d2 = d1 + chunk, *dout = d2 + chunk;
+      double *dl = lam_dev ? dout + chunk : nullptr;
+      double *hl = lam_dev ? lambda + (size_t)i0 * ls : nullptr;
+      SGX_PIPE_TRY(cudaMemcpyAsync(d1, in1 + i0, nb, cudaMemcpyHostToDevice, s));
+      SGX_PIPE_TRY(cudaMemcpyAsync(d2, in2 + i0, nb, cudaMemcpyHostToDevice, s));
+      if (lam_in) SGX_PIPE_TRY(cudaMemcpyAsync(dl, hl, nb * ls, cudaMemcpyHostToDevice, s));
+      rc = sgx_eos_eval(e, method, d1, d2, dout, m, dl, ls, s);
+      if (rc) goto drain;
+      SGX_PIPE_TRY(cudaMemcpyAsync(out + i0, dout, nb, cudaMemcpyDeviceToHost, s));
+      if (lam_out) SGX_PIPE_TRY(cudaMemcpyAsync(hl, dl, nb * ls, cudaMemcpyDeviceToHost, s));
+    }
+  drain:
+    rc = drain_host_streams(e, rc);
   }
-  for (int k = 0; k < kHostSlots; ++k)
-    SGX_CUDA_OK(cudaStreamSynchronize(e->host_streams[k]));
-  return SGX_OK;
+  return rc;
 }
 
 int sgx_FillEos_host(sgx_eos_t e, double *rhos, double *temps, double *energies,
                      double *presses, double *cvs, double *bmods, int64_t n,
                      unsigned long output, double *lambda, int ls) {
+  DeviceGuard guard;
   int rc = check_handle(e);
   if (rc) return rc;
   if (n <= 0) return n == 0 ? SGX_OK : fail(SGX_ERR_INVALID, "negative n");
+  if (lambda && ls < sgx_eos_nlambda(e))
+    return fail(SGX_ERR_INVALID, "lambda_stride %d < nlambda %d", ls, sgx_eos_nlambda(e));
   // same chunk pipeline as sgx_eos_eval_host: kHostSlots device slots, one stream each
   const int64_t chunk = n < kHostChunk ? n : kHostChunk;
   const size_t per_cell = (size_t)(6 + (lambda ? ls : 0)) * sizeof(double);
@@ -993,30 +1102,49 @@ int sgx_FillEos_host(sgx_eos_t e, double *rhos, double *temps, double *energies,
   if (rc) return rc;
   double *h[6] = {rhos, temps, energies, presses, cvs, bmods};
   const unsigned long bits[6] = {TQ_DENSITY, TQ_TEMPERATURE, TQ_SIE, TQ_PRESSURE, TQ_CV, TQ_BMOD};
-  int slot = 0;
-  for (int64_t i0 = 0; i0 < n; i0 += chunk, slot = (slot + 1) % kHostSlots) {
-    const int64_t m = (n - i0) < chunk ? (n - i0) : chunk;
-    const size_t nb = (size_t)m * sizeof(double);
-    cudaStream_t s = e->host_streams[slot];
-    double *base = (double *)((char *)e->dscratch + slot * slot_bytes);
-    double *d[6];
-    for (int k = 0; k < 6; ++k)
-      d[k] = h[k] ? base + (size_t)k * chunk : nullptr;
-    double *dl = lambda ? base + 6 * (size_t)chunk : nullptr;
-    double *hl = lambda ? lambda + (size_t)i0 * ls : nullptr;
-    for (int k = 0; k < 4; ++k) // cv / bmod are never inputs
-      if (h[k] && !(output & bits[k]))
-        SGX_CUDA_OK(cudaMemcpyAsync(d[k], h[k] + i0, nb, cudaMemcpyHostToDevice, s));
-    if (lambda) SGX_CUDA_OK(cudaMemcpyAsync(dl, hl, nb * ls, cudaMemcpyHostToDevice, s));
-    rc = sgx_FillEos(e, d[0], d[1], d[2], d[3], d[4], d[5], m, output, dl, ls, s);
-    if (rc) return rc;
-    for (int k = 0; k < 6; ++k)
-      if (h[k] && (output & bits[k]))
-        SGX_CUDA_OK(cudaMemcpyAsync(h[k] + i0, d[k], nb, cudaMemcpyDeviceToHost, s));
-    if (lambda) SGX_CUDA_OK(cudaMemcpyAsync(hl, dl, nb * ls, cudaMemcpyDeviceToHost, s));
+  {
+    HostPin pins[6] = {HostPin(h[0], (size_t)n * 8), HostPin(h[1], (size_t)n * 8),
+                       HostPin(h[2], (size_t)n * 8), HostPin(h[3], (size_t)n * 8),
+                       HostPin(h[4], (size_t)n * 8), HostPin(h[5], (size_t)n * 8)};
+    HostPin pin_lam(lambda, (size_t)n * ls * sizeof(double));
+    int slot = 0;
+    for (int64_t i0 = 0; i0 < n; i0 += chunk, slot = (slot + 1) % kHostSlots) {
+      const int64_t m = (n - i0) < chunk ? (n - i0) : chunk;
+      const size_t nb = (size_t)m * sizeof(double);
+      cudaStream_t s = e->host_streams[slot];
+      double *base = (double *)((char *)e->dscratch + slot * slot_bytes);
+      double *d[6];
+      for (int k = 0; k < 6; ++k)
+        d[k] = h[k] ? base + (size_t)k * chunk : nullptr;
+      double *dl = lambda ? base + 6 * (size_t)chunk : nullptr;
+      double *hl = lambda ? lambda + (size_t)i0 * ls : nullptr;
+      for (int k = 0; k < 4; ++k) // cv / bmod are never inputs
+        if (h[k] && !(output & bits[k]))
+          SGX_PIPE_TRY(cudaMemcpyAsync(d[k], h[k] + i0, nb, cudaMemcpyHostToDevice, s));
+      if (lambda) SGX_PIPE_TRY(cudaMemcpyAsync(dl, hl, nb * ls, cudaMemcpyHostToDevice, s));
+      rc = sgx_FillEos(e, d[0], d[1], d[2], d[3], d[4], d[5], m, output, dl, ls, s);
+      if (rc) goto drain;
+      for (int k = 0; k < 6; ++k)
+        if (h[k] && (output & bits[k]))
+          SGX_PIPE_TRY(cudaMemcpyAsync(h[k] + i0, d[k], nb, cudaMemcpyDeviceToHost, s));
+      if (lambda) SGX_PIPE_TRY(cudaMemcpyAsync(hl, dl, nb * ls, cudaMemcpyDeviceToHost, s));
+    }
+  drain:
+    rc = drain_host_streams(e, rc);
   }
-  for (int k = 0; k < kHostSlots; ++k)
-    SGX_CUDA_OK(cudaStreamSynchronize(e->host_streams[k]));
+  return rc;
+}
+#undef SGX_PIPE_TRY
+
+int sgx_eos_root_stats(sgx_eos_t e, uint64_t out[2], int reset) {
+  if (!e || !out) return fail(SGX_ERR_INVALID, "null argument");
+  out[0] = out[1] = 0;
+  if (!e->root_stats) return SGX_OK;
+  DeviceGuard guard;
+  int rc = check_handle(e);
+  if (rc) return rc;
+  SGX_CUDA_OK(cudaMemcpy(out, e->root_stats, 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+  if (reset) SGX_CUDA_OK(cudaMemset(e->root_stats, 0, 2 * sizeof(uint64_t)));
   return SGX_OK;
 }
 

@@ -42,6 +42,38 @@ inline int fail(int code, const char *fmt, ...) {
                        cudaGetErrorString(_e), __FILE__, __LINE__);                      \
   } while (0)
 
+// Entry points switch to the handle's device (tables are per device); the caller's current
+// device is put back when the call returns, so a single-process multi-GPU host sees no side effect.
+struct DeviceGuard {
+  int saved = -1;
+  DeviceGuard() {
+    if (cudaGetDevice(&saved) != cudaSuccess) saved = -1;
+  }
+  ~DeviceGuard() {
+    int now = -1;
+    if (saved >= 0 && cudaGetDevice(&now) == cudaSuccess && now != saved) cudaSetDevice(saved);
+  }
+  DeviceGuard(const DeviceGuard &) = delete;
+  DeviceGuard &operator=(const DeviceGuard &) = delete;
+};
+
+// A caller's host range for the duration of one *_host call.  Pageable memory makes
+// cudaMemcpyAsync synchronous and staged by the driver, which serialises the chunk pipeline;
+// ranges the caller has not pinned are page-locked here (cudaHostRegister) and released when the
+// call returns.  SGX_HOST_PIN=none disables it (the copies then run at pageable speed); a failed
+// registration (locked-memory limit) silently falls back to the same.
+struct HostPin {
+  void *ptr = nullptr;
+  HostPin() {}
+  HostPin(const void *p, size_t bytes);
+  ~HostPin() {
+    if (ptr) cudaHostUnregister(ptr);
+  }
+  HostPin(HostPin &&o) noexcept : ptr(o.ptr) { o.ptr = nullptr; }
+  HostPin(const HostPin &) = delete;
+  HostPin &operator=(const HostPin &) = delete;
+};
+
 extern std::atomic<unsigned long long> g_launches;
 inline void count_launch(int n = 1) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
@@ -81,10 +113,12 @@ struct sgx_eos_s {
   size_t dscratch_bytes = 0;
   cudaStream_t own_stream = nullptr;
   cudaStream_t host_streams[4] = {nullptr, nullptr, nullptr, nullptr}; // chunk pipeline
+  // SpinerRhoT T(rho,sie): device uint64[2] = {cells seen, cells sent to the reference iterate}
+  void *root_stats = nullptr;
 };
 
 namespace sgx {
-int upload_tables(sgx_eos_s *e);   // cudaMalloc + H2D of e->tables.host, L2 persistence hint
+int upload_tables(sgx_eos_s *e);   // cudaMalloc + H2D of e->tables.host
 int ensure_staging(sgx_eos_s *e, size_t pinned_bytes, size_t device_bytes);
 int ensure_host_streams(sgx_eos_s *e);
 int build_spiner_rhot(const sgx_sp5_tables *raw, int reproducible, int pmin_vapor_dome,
@@ -112,10 +146,12 @@ int launch_pte_rhou(const EosSet &set, bool bench_mix, const MixParamsDev &prm, 
                     const double *sie_tot, const double *vfrac_tot, const double *Tguess,
                     uint64_t *status, double *residual, uint64_t *stats, int64_t ncell,
                     cudaStream_t s);
-// SpinerRhoT T(rho, e) root find as a warp-level flow kernel (sgx_spiner_root.cu)
-int launch_rhot_T_from_rho_e_flow(const SpinerRhoT &eos, const double *rho, const double *sie,
-                                  double *out, int64_t n, double *lambda, int ls,
-                                  cudaStream_t s);
+// SpinerRhoT T(rho, e): direct inversion + reference iterate for the listed cells
+// (sgx_spiner_root.cu).  root_mode(): 0 hybrid (default), 1 exact, 2 direct (SGX_ROOT_MODE).
+int root_mode();
+int launch_rhot_T_from_rho_e_hybrid(sgx_eos_s *e, bool bounded, const double *rho,
+                                    const double *sie, double *out, int64_t n, double *lambda,
+                                    int ls, cudaStream_t s);
 // launch geometry: persistent-ish grid-stride, multiple of the SM count
 struct LaunchCfg {
   int blocks, threads;

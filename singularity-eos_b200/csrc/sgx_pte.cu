@@ -102,6 +102,7 @@ int sgx_pte_solve(int solver, const sgx_eos_t *eos, int nmat, int64_t ncell, dou
                   const double *sie_tot, const double *vfrac_tot, const double *Tguess,
                   const sgx_mix_params *params, uint64_t *status, double *residual,
                   uint64_t *stats, sgx_stream_t stream) {
+  DeviceGuard guard;
   if (!eos) return fail(SGX_ERR_INVALID, "null EOS array");
   if (solver != SGX_PTE_RHOT && solver != SGX_PTE_PT && solver != SGX_PTE_FIXED_T &&
       solver != SGX_PTE_RHOU)
@@ -169,6 +170,7 @@ int sgx_pte_solve_host(int solver, const sgx_eos_t *eos, int nmat, int64_t ncell
   if (nmat < 1 || nmat > 4)
     return fail(SGX_ERR_UNSUPPORTED, "nmat=%d: this build instantiates 1..4 materials", nmat);
   sgx_eos_s *e0 = eos[0];
+  DeviceGuard guard;
   cudaError_t err = cudaSetDevice(e0->device);
   if (err != cudaSuccess)
     return fail(SGX_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(err));
@@ -185,41 +187,63 @@ int sgx_pte_solve_host(int solver, const sgx_eos_t *eos, int nmat, int64_t ncell
   rc = ensure_host_streams(e0);
   if (rc) return rc;
   double *h[5] = {rho, vfrac, sie, temp, press};
-  int slot = 0;
-  for (int64_t c0 = 0; c0 < ncell; c0 += chunk, slot = (slot + 1) % kSlots) {
-    const int64_t n = (ncell - c0) < chunk ? (ncell - c0) : chunk;
-    const size_t nb = (size_t)n * nmat * sizeof(double);
-    const size_t cb = (size_t)n * sizeof(double);
-    cudaStream_t s = e0->host_streams[slot];
-    char *base = (char *)e0->dscratch + slot * slot_bytes;
-    double *d[5];
-    for (int k = 0; k < 5; ++k) {
-      d[k] = (double *)(base + k * nb_max);
-      SGX_CUDA_OK(cudaMemcpyAsync(d[k], h[k] + c0 * nmat, nb, cudaMemcpyHostToDevice, s));
+  // any failure drains the slot streams before returning (no copy into the caller's buffers
+  // may still be pending when the call comes back)
+#define SGX_PIPE_TRY(expr)                                                                 \
+  do {                                                                                     \
+    cudaError_t err__ = (expr);                                                            \
+    if (err__ != cudaSuccess) {                                                            \
+      rc = fail(SGX_ERR_CUDA, "%s: %s", #expr, cudaGetErrorString(err__));                 \
+      goto drain;                                                                          \
+    }                                                                                      \
+  } while (0)
+  {
+    const size_t tot = (size_t)ncell * nmat * sizeof(double), tc = (size_t)ncell * sizeof(double);
+    HostPin pins[5] = {HostPin(h[0], tot), HostPin(h[1], tot), HostPin(h[2], tot),
+                       HostPin(h[3], tot), HostPin(h[4], tot)};
+    HostPin p_st(sie_tot, tc), p_vt(vfrac_tot, tc), p_tg(Tguess, tc), p_status(status, tc),
+        p_res(residual, tc);
+    int slot = 0;
+    for (int64_t c0 = 0; c0 < ncell; c0 += chunk, slot = (slot + 1) % kSlots) {
+      const int64_t n = (ncell - c0) < chunk ? (ncell - c0) : chunk;
+      const size_t nb = (size_t)n * nmat * sizeof(double);
+      const size_t cb = (size_t)n * sizeof(double);
+      cudaStream_t s = e0->host_streams[slot];
+      char *base = (char *)e0->dscratch + slot * slot_bytes;
+      double *d[5];
+      for (int k = 0; k < 5; ++k) {
+        d[k] = (double *)(base + k * nb_max);
+        SGX_PIPE_TRY(cudaMemcpyAsync(d[k], h[k] + c0 * nmat, nb, cudaMemcpyHostToDevice, s));
+      }
+      double *d_sie_tot = (double *)(base + 5 * nb_max);
+      double *d_vf_tot = d_sie_tot + chunk, *d_Tg = d_vf_tot + chunk, *d_res = d_Tg + chunk;
+      uint64_t *d_status = (uint64_t *)(d_res + chunk);
+      if (sie_tot)
+        SGX_PIPE_TRY(cudaMemcpyAsync(d_sie_tot, sie_tot + c0, cb, cudaMemcpyHostToDevice, s));
+      if (vfrac_tot)
+        SGX_PIPE_TRY(cudaMemcpyAsync(d_vf_tot, vfrac_tot + c0, cb, cudaMemcpyHostToDevice, s));
+      if (Tguess) SGX_PIPE_TRY(cudaMemcpyAsync(d_Tg, Tguess + c0, cb, cudaMemcpyHostToDevice, s));
+      rc = sgx_pte_solve(solver, eos, nmat, n, d[0], d[1], d[2], d[3], d[4],
+                         sie_tot ? d_sie_tot : nullptr, vfrac_tot ? d_vf_tot : nullptr,
+                         Tguess ? d_Tg : nullptr, params, status ? d_status : nullptr,
+                         residual ? d_res : nullptr, nullptr, s);
+      if (rc) goto drain;
+      for (int k = 0; k < 5; ++k)
+        SGX_PIPE_TRY(cudaMemcpyAsync(h[k] + c0 * nmat, d[k], nb, cudaMemcpyDeviceToHost, s));
+      if (status)
+        SGX_PIPE_TRY(cudaMemcpyAsync(status + c0, d_status, cb, cudaMemcpyDeviceToHost, s));
+      if (residual)
+        SGX_PIPE_TRY(cudaMemcpyAsync(residual + c0, d_res, cb, cudaMemcpyDeviceToHost, s));
     }
-    double *d_sie_tot = (double *)(base + 5 * nb_max);
-    double *d_vf_tot = d_sie_tot + chunk, *d_Tg = d_vf_tot + chunk, *d_res = d_Tg + chunk;
-    uint64_t *d_status = (uint64_t *)(d_res + chunk);
-    if (sie_tot)
-      SGX_CUDA_OK(cudaMemcpyAsync(d_sie_tot, sie_tot + c0, cb, cudaMemcpyHostToDevice, s));
-    if (vfrac_tot)
-      SGX_CUDA_OK(cudaMemcpyAsync(d_vf_tot, vfrac_tot + c0, cb, cudaMemcpyHostToDevice, s));
-    if (Tguess) SGX_CUDA_OK(cudaMemcpyAsync(d_Tg, Tguess + c0, cb, cudaMemcpyHostToDevice, s));
-    rc = sgx_pte_solve(solver, eos, nmat, n, d[0], d[1], d[2], d[3], d[4],
-                       sie_tot ? d_sie_tot : nullptr, vfrac_tot ? d_vf_tot : nullptr,
-                       Tguess ? d_Tg : nullptr, params, status ? d_status : nullptr,
-                       residual ? d_res : nullptr, nullptr, s);
-    if (rc) return rc;
-    for (int k = 0; k < 5; ++k)
-      SGX_CUDA_OK(cudaMemcpyAsync(h[k] + c0 * nmat, d[k], nb, cudaMemcpyDeviceToHost, s));
-    if (status)
-      SGX_CUDA_OK(cudaMemcpyAsync(status + c0, d_status, cb, cudaMemcpyDeviceToHost, s));
-    if (residual)
-      SGX_CUDA_OK(cudaMemcpyAsync(residual + c0, d_res, cb, cudaMemcpyDeviceToHost, s));
+  drain:
+    for (int k = 0; k < kSlots; ++k) {
+      cudaError_t e2 = cudaStreamSynchronize(e0->host_streams[k]);
+      if (e2 != cudaSuccess && rc == SGX_OK)
+        rc = fail(SGX_ERR_CUDA, "cudaStreamSynchronize: %s", cudaGetErrorString(e2));
+    }
   }
-  for (int k = 0; k < kSlots; ++k)
-    SGX_CUDA_OK(cudaStreamSynchronize(e0->host_streams[k]));
-  return SGX_OK;
+#undef SGX_PIPE_TRY
+  return rc;
 }
 
 } // extern "C"

@@ -52,7 +52,11 @@ static int launch_sm(const EosSet &set, const MixParamsDev &prm, double *rho, do
         residual ? residual + c0 : nullptr, reinterpret_cast<unsigned long long *>(stats), n,
         cpw);
     count_launch(2);
-    SGX_CUDA_OK(cudaGetLastError());
+    const cudaError_t err = cudaGetLastError();
+    if (err != cudaSuccess) { // the stream-ordered scratch is released on every exit path
+      cudaFreeAsync(init, s);
+      return fail(SGX_ERR_CUDA, "PTE RhoT launch failed: %s", cudaGetErrorString(err));
+    }
   }
   SGX_CUDA_OK(cudaFreeAsync(init, s));
   return SGX_OK;

@@ -290,8 +290,28 @@ int build_spiner_rhot(const sgx_sp5_tables *raw, int reproducible, int pmin_vapo
   static const char *k2d[] = {"P", "sie", "bMod", "dPdRho", "dPdE", "dTdRho", "dTdE", "dEdRho",
                               "dEdT"};
   for (const char *nm : k2d) add_packed(ts, nm, numRho, numT);
+  // Row pairs (j, j+1) of sie whose every T-segment rises strictly (junction nodes of a piecewise
+  // grid are stored twice and may repeat): there the blend of the two rows is strictly monotone
+  // in lT and the direct T(rho,sie) inversion of sgx_spiner_root.cu has a unique root.
+  {
+    std::vector<char> junction(numT, 0);
+    for (int g = 1; g < s.gT.ngrids; ++g) junction[s.gT.ptot[g] - 1] = 1;
+    std::vector<char> rising(numRho, 1);
+    const double *sie_h = ts.h("sie");
+    for (int j = 0; j < numRho; ++j)
+      for (int i = 0; i + 1 < numT; ++i) {
+        const double a = sie_h[(size_t)j * numT + i], b = sie_h[(size_t)j * numT + i + 1];
+        if (!(b > a || (junction[i] && b == a))) rising[j] = 0;
+      }
+    std::vector<double> mono(numRho > 1 ? numRho - 1 : 1, 0.0);
+    for (int j = 0; j + 1 < numRho; ++j) mono[j] = (rising[j] && rising[j + 1]) ? 1.0 : 0.0;
+    ts.add("sie#mono", mono.data(), mono.size());
+  }
   int rc = upload_tables(e);
   if (rc) return rc;
+  if (cudaMalloc(&e->root_stats, 2 * sizeof(uint64_t)) != cudaSuccess ||
+      cudaMemset(e->root_stats, 0, 2 * sizeof(uint64_t)) != cudaSuccess)
+    return fail(SGX_ERR_CUDA, "root statistics buffer: %s", cudaGetErrorString(cudaGetLastError()));
   s.P = ts.d("P#cells");
   s.sie = ts.d("sie#cells");
   s.bMod = ts.d("bMod#cells");

@@ -1,30 +1,38 @@
 // SpinerEOSDependsRhoT::TemperatureFromDensityInternalEnergy over an array of cells
 // (eos/eos_spiner_rho_temp.hpp:777-784 -> lTFromlRhoSie_ :1192-1250 -> regula_falsi,
-// base/root-finding-1d/root_finding.hpp:154-240) as a warp-level flow kernel.
+// base/root-finding-1d/root_finding.hpp:154-240): direct inversion where it provably agrees with
+// the reference iterate, the reference iterate itself everywhere else.
 //
-// Why not one thread per cell (eval_kernel<T_FROM_RHO_E, SpinerRhoT>): the regula-falsi trip
-// count is data dependent, so a warp waits for its slowest cell -- profiles/r1h_root_details:
-// 13.3 of 32 lanes active, issue slots 70 % busy, FP64 pipe 44 %.  The trip count cannot be
-// changed (the iterate is the parity contract), the idling can:
+// At fixed lRho the inverted function is the reference's four-corner blend with (ix2, w2)
+// frozen: piecewise linear in lT.  SURVEY.md 9-K2 allows replacing the root find by a segment
+// search + linear solve where the two agree to 1e-12.  Measured against the reference on the
+// config-3a workload (2^18 cells, /tmp prototype recorded in profiles/r2_root_direct_study.md):
+// they do NOT agree everywhere -- 1.1 % of cells differ by more than 1e-12 (max 1.1e-11).  The
+// cause is conditioning, not a bug: the reference iterate stops at a sign change of the
+// *rounded* blend, which wanders by ~4 ulp(sie) / slope around the exact root, so wherever
+// |sie| / |h(i+1) - h(i)| is large (cold, compressed states: the energy is dominated by the cold
+// curve and barely moves with T) the reference's own answer is only defined to ~1e-11, and
+// which value it lands on depends on every rounding of its path.  That path cannot be
+// shortened; it can only be walked.  Hence two kernels:
 //
-//   * each warp owns a contiguous cell range and runs three kinds of steps on it;
-//   * SETUP, a full-warp batch of 32 fresh cells: logs, density-axis weights, table location,
-//     bracket selection (2-3 function evaluations).  Off-table cells are finished here; the
-//     others become 72-byte iteration records in a per-warp shared-memory ready queue;
-//   * ITERATE, one regula-falsi step per live lane.  A lane whose root is found appends
-//     (cell, lT) to the warp's done queue and takes the next record from the ready queue in
-//     the same round, so all lanes keep iterating whatever their trip counts;
-//   * RETIRE, a full-warp batch of 32 finished cells: T = 10^lT - offset, stores, lambda.
+//  1. rhot_T_direct_kernel, every cell: NQT logs, density-axis weights, table location exactly
+//     as the reference; for on-table cells a bisection over the row pair's cells (<= 8 probes,
+//     one 32-byte record each, no data-dependent trip counts beyond that) and a linear solve in
+//     the bracketing cell.  The result is kept when an a-priori bound on its distance from ANY
+//     value the reference iterate can return,
+//         4 ulp * max|corner| / |h1 - h0| * dx * ln10   (relative error of T),
+//     is below 1e-12 (measured worst case inside the bound: 3.9e-13).  Otherwise -- and for
+//     non-monotone row pairs, density extrapolation and energies outside the row's range, where
+//     the reference's bracket logic or its FAIL -> guess path decides the answer -- the cell's
+//     index is appended to a list (warp-aggregated atomic).
+//  2. rhot_T_list_kernel, the listed cells only: the reference iterate, operation for
+//     operation (SpinerRhoT::T_from_rho_e, the code the per-thread eval_kernel runs), reading the
+//     cached guess from lambda like the reference.  Its lanes are dense in hard cells.
 //
-// MEASURED (B200, 2^24 cells, profiles/r1_tuning.md): lanes active 13.3 -> 24.7, but the step
-// chain (weights -> 32-byte gather from L2 -> blend -> FP64 divide) is latency-bound, the
-// queues take L1 capacity and ~65 bookkeeping instructions per round, and the kernel ends up
-// level with the per-thread one on cold starts (2.59 vs 2.49 ms) and behind it on warm starts
-// (0.89 vs 0.61 ms).  It is therefore NOT the default: SGX_ROOT_KERNEL=flow selects it.
-//
-// Every cell executes exactly the floating-point operations of the per-thread path (same
-// bracket logic, same secant / Illinois updates, same loop condition), so results are
-// bit-identical to it (tests/test_gpu_parity.py::test_root_flow_equals_per_thread_kernel).
+// SGX_ROOT_MODE selects: "hybrid" (default, above), "exact" (reference iterate for every cell:
+// eval_kernel<T_FROM_RHO_E, SpinerRhoT>, bit-identical lambda), "direct" (kernel 1 keeps every
+// well-posed cell whatever the bound: closer to the exact root than the reference, but up to
+// ~1e-11 away from the reference's value; opt-in, not a parity mode).
 #include <cstdlib>
 #include <cstring>
 
@@ -34,282 +42,181 @@ namespace sgx {
 
 namespace {
 
-constexpr int kWarpsPerBlock = 8;
-constexpr int kBlocksPerSM = 3;
-constexpr int kReadyCap = 64; // iteration records per warp (power of two)
-constexpr int kDoneCap = 128; // finished cells per warp (power of two)
-constexpr int kMaxIter = 1000; // SECANT_NITER_MAX
-constexpr int kStepsPerRound = 4; // regula-falsi steps between two rounds of queue bookkeeping
+constexpr int64_t kRootChunk = int64_t(1) << 24; // cells per kernel pair (list scratch 64 MiB)
 
-// per-warp queues in shared memory, structure of arrays (bank-conflict free per field)
-struct WarpQueues {
-  double a[kReadyCap], b[kReadyCap], ya[kReadyCap], yb[kReadyCap];
-  double tgt[kReadyCap], w21[kReadyCap], guess[kReadyCap]; // w20 = 1 - w21 (weights())
-  int cell[kReadyCap];   // offset of the cell in the warp's range
-  int ixsign[kReadyCap]; // density-axis cell index; bit 30 set when sign = -1
-  double done_lT[kDoneCap];
-  int done_cell[kDoneCap];
-};
+// relative-T error budget of the direct solve against the reference iterate (see header):
+// keep when  kBoundCoef * max|corner| * dx <= |h1 - h0|,
+// kBoundCoef = 4 * 2^-52 * ln(10) / 1e-12
+constexpr double kBoundCoef = 4.0 * 2.220446049250313e-16 * 2.302585092994046 / 1.0e-12;
 
-} // namespace
-
-template <int STEPS, int BPS>
-__global__ void __launch_bounds__(kWarpsPerBlock * 32, BPS)
-    rhot_T_from_rho_e_flow_kernel(const __grid_constant__ SpinerRhoT eos,
-                                  const double *__restrict__ rho_in,
-                                  const double *__restrict__ sie_in, double *__restrict__ T_out,
-                                  const int64_t n, double *__restrict__ lambda, const int ls,
-                                  const int64_t cells_per_warp) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  WarpQueues &q = reinterpret_cast<WarpQueues *>(smem_raw)[threadIdx.x >> 5];
-  const unsigned lane = threadIdx.x & 31u;
-  const unsigned lt_mask = (1u << lane) - 1u;
-  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int64_t begin = warp * cells_per_warp;
-  const int ncells = (int)((begin + cells_per_warp < n ? begin + cells_per_warp : n) - begin);
-  if (ncells <= 0) return; // whole warp
-  const double *__restrict__ tab = eos.sie;
-  const int n1 = eos.numT;
-  const double xtol = SpinerRhoT::ROOT_THRESH, ytol = SpinerRhoT::ROOT_THRESH;
-
-  // f(x) - ytarget on the density row fixed by (ix2, w20, w21): the reference's four-corner
-  // blend (databox.hpp:471-474) with the rho-axis weights hoisted
-  auto func = [&](const double x, const int ix2, const double w20, const double w21,
-                  const double tgt) {
-    int ix1;
-    double w10, w11;
-    eos.gT.weights(x, ix1, w10, w11);
-    return blend2c(tab, n1, ix2, w20, w21, ix1, w10, w11) - tgt;
-  };
-
-  int next = 0;                        // next fresh cell of the range (warp-uniform)
-  unsigned rhead = 0, rtail = 0;       // ready queue (monotonic, slot = idx & (cap-1))
-  unsigned dhead = 0, dtail = 0;       // done queue
-  // this lane's live iteration
-  bool live = false;
-  double a = 0, b = 0, ya = 0, yb = 0, tgt = 0, w20 = 0, w21 = 0, guess = 0, sign = 1;
-  int ix2 = 0, cell = 0, b1 = 0, b2 = 0, it = 0;
-
+// One on-table cell.  Returns false when the reference iterate must decide.
+template <bool BOUNDED>
+SGX_D bool lT_direct(const SpinerRhoT &eos, const double *__restrict__ mono, const AxisPos &pr,
+                     const double sie, double &lT) {
+  // interpolation (not extrapolation) between two rows that both rise strictly with T: the
+  // blend then rises strictly too and the root is unique
+  if (!(pr.w1 >= 0.0 && pr.w1 <= 1.0) || ldg(mono + pr.ix) == 0.0) return false;
+  int lo = 0, hi = eos.numT - 2; // candidate table cells along T
+  Cell4 c;
+  double h0, h1;
+  int mid;
   while (true) {
-    // ---- SETUP: keep at least 32 records ahead of the iterating lanes ---------------------
-    while (next < ncells && (rtail - rhead) <= (unsigned)(kReadyCap - 32) &&
-           (dtail - dhead) < 32u) {
-      const int c = next + (int)lane;
-      const bool have = c < ncells;
-      bool to_ready = false, to_done = false;
-      double s_a = 0, s_b = 0, s_ya = 0, s_yb = 0, s_tgt = 0, s_w21 = 0, s_guess = 0,
-             s_lT = 0;
-      int s_ixsign = 0;
-      if (have) {
-        const double rho = ldg(rho_in + begin + c);
-        const double sie = ldg(sie_in + begin + c);
-        const double lRho = eos.lRho_(rho);
-        const AxisPos pr(eos.gRho, lRho);
-        const TableStatus w = eos.locRhoSie(pr, sie);
-        double *lam = lambda ? lambda + (begin + c) * ls : nullptr;
-        if (w == OffBottom) {
-          s_lT = eos.lTMin;
-          to_done = true;
-        } else if (w == OffTop) {
-          const double Cv = interp1d(eos.dEdTMax, pr);
-          const double e0 = interp1d(eos.sielTMax, pr);
-          const double T = eos.TMax + ratio(sie - e0, Cv);
-          s_lT = eos.lT_(T);
-          to_done = true;
-        } else {
-          double lTGuess = eos.reproducible ? eos.lTMin : 0.5 * (eos.lTMin + eos.lTMax);
-          if (lam) {
-            const double lT_cache = lam[1];
-            if ((eos.lTMin <= lT_cache) && (lT_cache <= eos.lTMax)) lTGuess = lT_cache;
-          }
-          // regula_falsi prologue (root_finding.hpp:163-188)
-          s_a = eos.lTMin;
-          s_b = eos.lTMax;
-          s_ya = func(s_a, pr.ix, pr.w0, pr.w1, sie);
-          const double yg = func(lTGuess, pr.ix, pr.w0, pr.w1, sie);
-          bool bracketed = true;
-          if (root::check_bracket(s_ya, yg)) {
-            s_b = lTGuess;
-            s_yb = yg;
-          } else {
-            s_yb = func(s_b, pr.ix, pr.w0, pr.w1, sie);
-            if (root::check_bracket(yg, s_yb)) {
-              s_a = lTGuess;
-              s_ya = yg;
-            } else {
-              auto f1 = [&](const double x) { return func(x, pr.ix, pr.w0, pr.w1, sie); };
-              bracketed = root::set_bracket(f1, s_a, lTGuess, s_b, s_ya, yg, s_yb);
-            }
-          }
-          if (!bracketed) { // Status::FAIL -> lT = guess (:1241)
-            s_lT = eos.reproducible ? eos.lTMin : lTGuess;
-            to_done = true;
-          } else {
-            const bool neg = !(s_ya < 0); // sign = (ya < 0 ? 1.0 : -1.0)
-            const double sg = neg ? -1.0 : 1.0;
-            s_ya *= sg;
-            s_yb *= sg;
-            s_tgt = sie;
-            s_w21 = pr.w1;
-            s_guess = lTGuess;
-            s_ixsign = pr.ix | (neg ? (1 << 30) : 0);
-            to_ready = true;
-          }
-        }
-        if (lam) lam[0] = lRho; // lambda[1] = lT follows at retire
-      }
-      const unsigned rmask = __ballot_sync(0xffffffffu, to_ready);
-      const unsigned dmask = __ballot_sync(0xffffffffu, to_done);
-      if (to_ready) {
-        const unsigned slot = (rtail + __popc(rmask & lt_mask)) & (kReadyCap - 1);
-        q.a[slot] = s_a;
-        q.b[slot] = s_b;
-        q.ya[slot] = s_ya;
-        q.yb[slot] = s_yb;
-        q.tgt[slot] = s_tgt;
-        q.w21[slot] = s_w21;
-        q.guess[slot] = s_guess;
-        q.cell[slot] = c;
-        q.ixsign[slot] = s_ixsign;
-      }
-      if (to_done) {
-        const unsigned slot = (dtail + __popc(dmask & lt_mask)) & (kDoneCap - 1);
-        q.done_lT[slot] = s_lT;
-        q.done_cell[slot] = c;
-      }
-      rtail += __popc(rmask);
-      dtail += __popc(dmask);
-      next += 32;
-      __syncwarp();
+    mid = (lo + hi) >> 1;
+    c = ld_cell(eos.sie, eos.numT, pr.ix, mid);
+    h0 = pr.w0 * c.c00 + pr.w1 * c.c10; // the blend at node mid   (w1 weight 0: exact)
+    h1 = pr.w0 * c.c01 + pr.w1 * c.c11; // the blend at node mid+1
+    if (sie < h0) {
+      hi = mid - 1;
+    } else if (sie >= h1) {
+      lo = mid + 1;
+    } else {
+      break; // h0 <= sie < h1 (never a junction cell of a piecewise grid: there h0 == h1)
     }
-    // ---- REFILL: idle lanes take the next records of the ready queue ----------------------
-    {
-      const unsigned idle_mask = __ballot_sync(0xffffffffu, !live);
-      const unsigned avail = rtail - rhead;
-      const unsigned rank = __popc(idle_mask & lt_mask);
-      if (!live && rank < avail) {
-        const unsigned slot = (rhead + rank) & (kReadyCap - 1);
-        a = q.a[slot];
-        b = q.b[slot];
-        ya = q.ya[slot];
-        yb = q.yb[slot];
-        tgt = q.tgt[slot];
-        w21 = q.w21[slot];
-        w20 = 1. - w21; // as RegularGrid1D::weights computes it (regular_grid_1d.hpp:86)
-        guess = q.guess[slot];
-        cell = q.cell[slot];
-        const int ixs = q.ixsign[slot];
-        ix2 = ixs & ((1 << 30) - 1);
-        sign = (ixs >> 30) ? -1.0 : 1.0;
-        b1 = 0;
-        b2 = 0;
-        it = 0;
-        live = true;
-      }
-      const unsigned taken = __popc(idle_mask);
-      rhead += taken < avail ? taken : avail;
-      __syncwarp();
-    }
-    const bool exhausted =
-        (next >= ncells) && (rtail == rhead) && !__any_sync(0xffffffffu, live);
+    if (lo > hi) return false; // outside the row's range: the reference's bracket logic decides
+  }
+  const Grid1D &g = eos.gT;
+  int ig = 0;
+  if (g.ngrids > 1) ig = (g.ngrids > 2 && mid >= g.ptot[2]) ? 2 : (mid >= g.ptot[1] ? 1 : 0);
+  const double dx = g.dx[ig];
+  const double dh = h1 - h0;
+  if (BOUNDED) {
+    const double mag = fmax(fmax(fabs(c.c00), fabs(c.c01)), fmax(fabs(c.c10), fabs(c.c11)));
+    if (!(kBoundCoef * mag * dx <= dh)) return false;
+  }
+  const double floor_x = (double)(mid - g.ptot[ig]) * dx + g.min[ig];
+  lT = floor_x + ((sie - h0) / dh) * dx;
+  return true;
+}
 
-    // ---- ITERATE: one regula-falsi step per live lane (root_finding.hpp:193-222) ----------
-    bool finished = false;
-    double lT_fin = 0;
-#pragma unroll 1
-    for (int step = 0; step < STEPS; ++step) {
-      if (live) {
-        bool go = b - a > 2.0 * xtol && (fabs(ya) > ytol || fabs(yb) > ytol) && it < kMaxIter;
-        if (go) {
-          const double c = (a * yb - b * ya) / (yb - ya);
-          if (c == a) {
-            b = a; // `continue`: the loop condition then fails on b - a
-          } else if (c == b) {
-            a = b;
+template <bool BOUNDED>
+__global__ void __launch_bounds__(256, 3)
+    rhot_T_direct_kernel(const __grid_constant__ SpinerRhoT eos, const double *__restrict__ mono,
+                         const double *__restrict__ rho_in, const double *__restrict__ sie_in,
+                         double *__restrict__ T_out, const int64_t n, double *__restrict__ lambda,
+                         const int ls, const bool vec_lambda, unsigned int *__restrict__ list,
+                         unsigned int *__restrict__ count) {
+  const unsigned lane = threadIdx.x & 31u;
+  const int64_t nthr = (int64_t)gridDim.x * blockDim.x;
+  // warp-uniform trip count: every lane stays in the loop so the ballots below are full-warp
+  for (int64_t base = (int64_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31u); base < n;
+       base += nthr) {
+    const int64_t i = base + lane;
+    const bool valid = i < n;
+    bool fallback = false;
+    if (valid) {
+      double rho, sie;
+      asm volatile("ld.global.nc.L1::no_allocate.f64 %0, [%1];" : "=d"(rho) : "l"(rho_in + i));
+      asm volatile("ld.global.nc.L1::no_allocate.f64 %0, [%1];" : "=d"(sie) : "l"(sie_in + i));
+      const double lRho = eos.lRho_(rho);
+      const AxisPos pr(eos.gRho, lRho);
+      const TableStatus w = eos.locRhoSie(pr, sie);
+      double lT;
+      if (w == OffBottom) { // eos_spiner_rho_temp.hpp:1204-1206
+        lT = eos.lTMin;
+      } else if (w == OffTop) { // :1207-1212
+        const double Cv = interp1d(eos.dEdTMax, pr);
+        const double e0 = interp1d(eos.sielTMax, pr);
+        lT = eos.lT_(eos.TMax + ratio(sie - e0, Cv));
+      } else {
+        fallback = !lT_direct<BOUNDED>(eos, mono, pr, sie, lT);
+      }
+      if (!fallback) {
+        asm volatile("st.global.cs.f64 [%0], %1;" ::"l"(T_out + i), "d"(eos.T_(lT)) : "memory");
+        if (lambda) { // :1244-1245
+          double *l = lambda + i * ls;
+          if (vec_lambda) { // rows 16-byte aligned (checked at launch)
+            asm volatile("st.global.cs.v2.f64 [%0], {%1,%2};" ::"l"(l), "d"(lRho), "d"(lT)
+                         : "memory");
           } else {
-            const double yc = sign * func(c, ix2, w20, w21, tgt);
-            if (yc > 0.0) {
-              b = c;
-              yb = yc;
-              b1++;
-              ya *= (b1 > 1 ? 0.5 : 1.0);
-              b2 = 0;
-            } else if (yc < 0.0) {
-              a = c;
-              ya = yc;
-              b2++;
-              yb *= (b2 > 1 ? 0.5 : 1.0);
-              b1 = 0;
-            } else {
-              a = c;
-              b = c;
-            }
-            it++;
+            l[0] = lRho;
+            l[1] = lT;
           }
-          go = b - a > 2.0 * xtol && (fabs(ya) > ytol || fabs(yb) > ytol) && it < kMaxIter;
-        }
-        if (!go) {
-          finished = true;
-          // xroot = 0.5*(a+b); FAIL only when the iteration cap was hit (:223-230, :1241)
-          lT_fin = (it == kMaxIter) ? (eos.reproducible ? eos.lTMin : guess) : 0.5 * (a + b);
-          live = false;
         }
       }
     }
-    {
-      const unsigned fmask = __ballot_sync(0xffffffffu, finished);
-      if (finished) {
-        const unsigned slot = (dtail + __popc(fmask & lt_mask)) & (kDoneCap - 1);
-        q.done_lT[slot] = lT_fin;
-        q.done_cell[slot] = cell;
-      }
-      dtail += __popc(fmask);
-      __syncwarp();
+    const unsigned fbm = __ballot_sync(0xffffffffu, fallback);
+    if (fbm) {
+      unsigned pos = 0;
+      if (lane == 0) pos = atomicAdd(count, (unsigned)__popc(fbm));
+      pos = __shfl_sync(0xffffffffu, pos, 0);
+      if (fallback) list[pos + __popc(fbm & ((1u << lane) - 1u))] = (unsigned)i;
     }
-
-    // ---- RETIRE: full-warp batches of finished cells ------------------------------------
-    const bool draining =
-        (next >= ncells) && (rtail == rhead) && !__any_sync(0xffffffffu, live);
-    while ((dtail - dhead) >= 32u || (draining && dtail != dhead)) {
-      const unsigned cnt = dtail - dhead;
-      if (lane < cnt) {
-        const unsigned slot = (dhead + lane) & (kDoneCap - 1);
-        const double lT = q.done_lT[slot];
-        const int64_t c = begin + q.done_cell[slot];
-        T_out[c] = eos.T_(lT);
-        if (lambda) lambda[c * ls + 1] = lT;
-      }
-      dhead += cnt < 32u ? cnt : 32u;
-      __syncwarp();
-    }
-    if (exhausted) break; // nothing was live this round and everything has been retired
   }
 }
 
-template <int STEPS, int BPS>
-static int launch_flow(const SpinerRhoT &eos, const double *rho, const double *sie, double *out,
-                       int64_t n, double *lambda, int ls, cudaStream_t s) {
-  const size_t smem = sizeof(WarpQueues) * kWarpsPerBlock;
-  SGX_CUDA_OK(cudaFuncSetAttribute(rhot_T_from_rho_e_flow_kernel<STEPS, BPS>,
-                                   cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  // BPS blocks of kWarpsPerBlock warps per SM; each warp owns a contiguous range (>= 256 cells)
-  int64_t warps = (int64_t)sm_count() * BPS * kWarpsPerBlock;
-  const int64_t max_warps = (n + 255) / 256;
-  if (warps > max_warps) warps = max_warps;
-  const int64_t blocks = (warps + kWarpsPerBlock - 1) / kWarpsPerBlock;
-  warps = blocks * kWarpsPerBlock;
-  const int64_t cpw = (n + warps - 1) / warps;
-  rhot_T_from_rho_e_flow_kernel<STEPS, BPS><<<(unsigned)blocks, kWarpsPerBlock * 32, smem, s>>>(
-      eos, rho, sie, out, n, lambda, ls, cpw);
-  count_launch();
-  SGX_CUDA_OK(cudaGetLastError());
-  return SGX_OK;
+// The listed cells through the reference iterate (SpinerRhoT::T_from_rho_e)
+__global__ void __launch_bounds__(256, 4)
+    rhot_T_list_kernel(const __grid_constant__ SpinerRhoT eos, const double *__restrict__ rho_in,
+                       const double *__restrict__ sie_in, double *__restrict__ T_out,
+                       double *__restrict__ lambda, const int ls,
+                       const unsigned int *__restrict__ list,
+                       const unsigned int *__restrict__ count,
+                       unsigned long long *__restrict__ stats, const unsigned long long ncell) {
+  const unsigned cnt = *count;
+  const unsigned tid = blockIdx.x * blockDim.x + threadIdx.x;
+  const unsigned nthr = gridDim.x * blockDim.x;
+  if (tid == 0 && stats) {
+    atomicAdd(stats + 0, ncell);
+    atomicAdd(stats + 1, (unsigned long long)cnt);
+  }
+  for (unsigned k = tid; k < cnt; k += nthr) {
+    const int64_t i = list[k];
+    double lam[2];
+    if (lambda) {
+      lam[0] = lambda[i * ls];
+      lam[1] = lambda[i * ls + 1];
+    }
+    T_out[i] = eos.T_from_rho_e(rho_in[i], sie_in[i], lambda ? lam : nullptr);
+    if (lambda) {
+      lambda[i * ls] = lam[0];
+      lambda[i * ls + 1] = lam[1];
+    }
+  }
 }
 
-int launch_rhot_T_from_rho_e_flow(const SpinerRhoT &eos, const double *rho, const double *sie,
-                                  double *out, int64_t n, double *lambda, int ls,
-                                  cudaStream_t s) {
-  return launch_flow<kStepsPerRound, kBlocksPerSM>(eos, rho, sie, out, n, lambda, ls, s);
+} // namespace
+
+int root_mode() {
+  const char *v = getenv("SGX_ROOT_MODE");
+  if (v && strcmp(v, "exact") == 0) return 1;
+  if (v && strcmp(v, "direct") == 0) return 2;
+  return 0;
+}
+
+int launch_rhot_T_from_rho_e_hybrid(sgx_eos_s *e, bool bounded, const double *rho,
+                                    const double *sie, double *out, int64_t n, double *lambda,
+                                    int ls, cudaStream_t s) {
+  const SpinerRhoT &eos = e->rhot;
+  const double *mono = e->tables.d("sie#mono");
+  const int64_t chunk = n < kRootChunk ? n : kRootChunk;
+  unsigned int *scratch = nullptr; // [0] = count, [64...] = list
+  SGX_CUDA_OK(cudaMallocAsync(&scratch, (size_t)(chunk + 64) * sizeof(unsigned int), s));
+  int rc = SGX_OK;
+  for (int64_t c0 = 0; c0 < n && rc == SGX_OK; c0 += chunk) {
+    const int64_t m = (n - c0) < chunk ? (n - c0) : chunk;
+    double *lam = lambda ? lambda + c0 * ls : nullptr;
+    const bool vec_lambda = lam && (ls % 2) == 0 && (((uintptr_t)lam) & 15) == 0;
+    cudaError_t err = cudaMemsetAsync(scratch, 0, sizeof(unsigned int), s);
+    if (err == cudaSuccess) {
+      const LaunchCfg c = stream_cfg(m, 256, 3 * 4);
+      if (bounded)
+        rhot_T_direct_kernel<true><<<c.blocks, c.threads, 0, s>>>(
+            eos, mono, rho + c0, sie + c0, out + c0, m, lam, ls, vec_lambda, scratch + 64, scratch);
+      else
+        rhot_T_direct_kernel<false><<<c.blocks, c.threads, 0, s>>>(
+            eos, mono, rho + c0, sie + c0, out + c0, m, lam, ls, vec_lambda, scratch + 64, scratch);
+      const LaunchCfg c2 = stream_cfg(m, 256, 4);
+      rhot_T_list_kernel<<<c2.blocks, c2.threads, 0, s>>>(
+          eos, rho + c0, sie + c0, out + c0, lam, ls, scratch + 64, scratch,
+          reinterpret_cast<unsigned long long *>(e->root_stats), (unsigned long long)m);
+      count_launch(2);
+      err = cudaGetLastError();
+    }
+    if (err != cudaSuccess)
+      rc = fail(SGX_ERR_CUDA, "T(rho,sie) hybrid launch failed: %s", cudaGetErrorString(err));
+  }
+  cudaFreeAsync(scratch, s); // stream-ordered: released on every exit path
+  return rc;
 }
 
 } // namespace sgx

@@ -73,12 +73,23 @@ class EosBase:
     def scratch_size(self, method, nelements):
         return self._lib.sgx_eos_scratch_bytes(self._h, 0, nelements)
 
+    def _lambda_stride(self, lambdas, n):
+        """Row stride of a lambda array: shape[-1] for [n][stride] arrays; a flat array holds
+        n rows of nlambda() values.  The array must cover n rows."""
+        if lambdas is None:
+            return 0
+        ndim = lambdas.dim() if hasattr(lambdas, "dim") else lambdas.ndim
+        stride = int(lambdas.shape[-1]) if ndim > 1 else max(1, self.nlambda())
+        size = lambdas.numel() if hasattr(lambdas, "numel") else lambdas.size
+        if size < n * stride:
+            raise ValueError(f"lambda array holds {size} values, {n} rows of stride {stride} "
+                             f"need {n * stride}")
+        return stride
+
     def _eval(self, method, in1, in2, out, num, lambdas):
         _require_cuda_f64(in1, in2, out, lambdas)
         n = in1.numel() if num is None else int(num)
-        stride = 0
-        if lambdas is not None:
-            stride = lambdas.shape[-1] if lambdas.dim() > 1 else max(1, self.nlambda())
+        stride = self._lambda_stride(lambdas, n)
         check(self._lib.sgx_eos_eval(self._h, method, _ptr(in1), _ptr(in2), _ptr(out), n,
                                      _ptr(lambdas), stride, _stream()))
         return out
@@ -125,7 +136,7 @@ class EosBase:
         """Fused P(rho,T)+e(rho,T) (one pass; not in the reference, same results)."""
         _require_cuda_f64(rhos, temperatures, pressures, sies, lambdas)
         n = rhos.numel() if num is None else int(num)
-        stride = 0 if lambdas is None else lambdas.shape[-1]
+        stride = self._lambda_stride(lambdas, n)
         check(self._lib.sgx_PressureEnergyFromDensityTemperature(
             self._h, _ptr(rhos), _ptr(temperatures), _ptr(pressures), _ptr(sies), n,
             _ptr(lambdas), stride, _stream()))
@@ -133,7 +144,7 @@ class EosBase:
     def FillEos(self, rhos, temps, energies, presses, cvs, bmods, num, output, lambdas=None):
         """eos/eos_base.hpp:503-531; `output` is a thermalqs bitmask."""
         _require_cuda_f64(rhos, temps, energies, presses, cvs, bmods, lambdas)
-        stride = 0 if lambdas is None else lambdas.shape[-1]
+        stride = self._lambda_stride(lambdas, int(num))
         check(self._lib.sgx_FillEos(self._h, _ptr(rhos), _ptr(temps), _ptr(energies),
                                     _ptr(presses), _ptr(cvs), _ptr(bmods), int(num),
                                     int(output), _ptr(lambdas), stride, _stream()))
@@ -144,7 +155,7 @@ class EosBase:
 
         for a in (in1, in2, out):
             assert isinstance(a, np.ndarray) and a.dtype == np.float64 and a.flags.c_contiguous
-        stride = 0 if lambdas is None else lambdas.shape[-1]
+        stride = self._lambda_stride(lambdas, in1.size)
         check(self._lib.sgx_eos_eval_host(
             self._h, method, in1.ctypes.data, in2.ctypes.data, out.ctypes.data, in1.size,
             None if lambdas is None else lambdas.ctypes.data, stride))
@@ -155,7 +166,7 @@ class EosBase:
             return None if a is None else a.ctypes.data
 
         n = next(a for a in (rhos, temps, energies, presses) if a is not None).size
-        stride = 0 if lambdas is None else lambdas.shape[-1]
+        stride = self._lambda_stride(lambdas, n)
         check(self._lib.sgx_FillEos_host(self._h, p(rhos), p(temps), p(energies), p(presses),
                                          p(cvs), p(bmods), n, int(output), p(lambdas), stride))
 
@@ -212,6 +223,13 @@ class DavisProducts(EosBase):
 
 class SpinerEOSDependsRhoT(EosBase):
     """Constructed from raw .sp5 contents (tablegen.Sp5Raw) instead of a file name."""
+
+    def root_stats(self, reset=False):
+        """(cells through TemperatureFromDensityInternalEnergy, cells among them that needed the
+        reference's regula-falsi iterate) since creation / the last reset."""
+        out = (C.c_uint64 * 2)()
+        check(self._lib.sgx_eos_root_stats(self._h, out, int(reset)))
+        return int(out[0]), int(out[1])
 
     def __init__(self, raw, reproducibility_mode=False, pmin_vapor_dome=False):
         lib = _lib.load()

@@ -79,6 +79,34 @@ def log_bounds(xmin, xmax, n):
     return g, offset, nodes
 
 
+def piecewise_log_bounds(xmin, xmax, npoints=(48, 160, 48), breaks=(0.3, 0.7)):
+    """Multi-patch axis = Spiner::PiecewiseGrid1D (utils/spiner/spiner/piecewise_grid_1d.hpp:
+    47-68): RegularGrid1D patches that meet at exactly one point, so the junction node is stored
+    twice and every table carries sum(npoints) entries per axis.  This is the coarse-fine-coarse
+    shape sesame2spiner writes (base/spiner_table_utils.hpp:72-135).  `breaks` are the patch
+    junctions as fractions of the log range.  Returns (Grid1D, offset, nodes)."""
+    eps = np.finfo(np.float64).eps
+    offset = 0.0
+    if xmin <= 0:
+        offset = 1.1 * abs(xmin) + 10 * eps
+    lmin = float(fast_log10(np.abs(np.float64(xmin + offset))))
+    lmax = float(fast_log10(np.abs(np.float64(xmax + offset))))
+    edges = [lmin] + [lmin + f * (lmax - lmin) for f in breaks] + [lmax]
+    assert len(npoints) == len(edges) - 1 <= 3
+    g = _lib.Grid1D()
+    g.ngrids = len(npoints)
+    lnodes = []
+    for k, n in enumerate(npoints):
+        lo, hi = edges[k], edges[k + 1]
+        dx = (hi - lo) / float(n - 1)
+        g.npoints[k] = n
+        g.min[k], g.max[k], g.dx[k] = lo, hi, dx
+        lnodes.append(np.arange(n, dtype=np.float64) * dx + lo)  # RegularGrid1D::x
+    lnodes = np.concatenate(lnodes)
+    nodes = np.minimum(xmax, np.maximum(xmin, fast_pow10(lnodes) - offset))
+    return g, offset, nodes
+
+
 # ---------------------------------------------------------------------------------------
 # Vinet (eos/eos_vinet.hpp:204-292)
 # ---------------------------------------------------------------------------------------
@@ -168,12 +196,18 @@ def _derived(rho, e, P, dpdrho_T, dpdt, cv, dedrho_T):
 
 
 def vinet_sp5_tables(nrho=256, nT=256, nE=256, rho_min=1.0, rho_max=30.0, T_min=1.0,
-                     T_max=1.0e5, vinet=None):
-    """Vinet copper on 256x256 single-patch NQT-log grids."""
+                     T_max=1.0e5, vinet=None, piecewise=False):
+    """Vinet copper on 256x256 single-patch NQT-log grids, or
+    (`piecewise=True`) on 3-patch PiecewiseGrid1D axes with the same node totals."""
     v = vinet or Vinet()
     raw = Sp5Raw()
-    gR, offR, rho_n = log_bounds(rho_min, rho_max, nrho)
-    gT, offT, T_n = log_bounds(T_min, T_max, nT)
+    if piecewise:
+        split = lambda n: (n // 4 - 16, n - 2 * (n // 4 - 16), n // 4 - 16)
+        gR, offR, rho_n = piecewise_log_bounds(rho_min, rho_max, split(nrho), (0.25, 0.6))
+        gT, offT, T_n = piecewise_log_bounds(T_min, T_max, split(nT), (0.3, 0.7))
+    else:
+        gR, offR, rho_n = log_bounds(rho_min, rho_max, nrho)
+        gT, offT, T_n = log_bounds(T_min, T_max, nT)
     R, TT = np.meshgrid(rho_n, T_n, indexing="ij")  # [nrho][nT], T fastest
     e, P, dpdr, dpdt, cv, dedr = v.eval(R, TT)
     der = _derived(R, e, P, dpdr, dpdt, cv, dedr)
@@ -189,7 +223,11 @@ def vinet_sp5_tables(nrho=256, nT=256, nE=256, rho_min=1.0, rho_max=30.0, T_min=
     raw.set("bModCold", der0["bMod"])
     raw.set("dPdRhoCold", der0["dPdRho"])
     # (rho, sie) set
-    gE, offE, e_n = log_bounds(float(e.min()), float(e.max()), nE)
+    if piecewise:
+        gE, offE, e_n = piecewise_log_bounds(float(e.min()), float(e.max()), split(nE),
+                                             (0.35, 0.65))
+    else:
+        gE, offE, e_n = log_bounds(float(e.min()), float(e.max()), nE)
     R2, EE = np.meshgrid(rho_n, e_n, indexing="ij")
     T2 = v.T_from_rho_e(R2, EE)
     e2, P2, dpdr2, dpdt2, cv2, dedr2 = v.eval(R2, T2)

@@ -7,7 +7,7 @@ import re
 import numpy as np
 import pytest
 
-from helpers import assert_bits, assert_rel
+from helpers import assert_bits, assert_rel, is_close
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
@@ -139,17 +139,57 @@ def test_two_rank_sharding_and_stats_allreduce_gloo(pkg):
 
 # ---- the oracle pinned to the reference's golden vectors ---------------------------------
 def test_ref_ideal_gas_golden(pkg, ref):
-    """test/test_eos_vector.cpp:53-57,139-143,309-313 (IdealGas gm1=0.4, Cv=5)."""
+    """test/test_eos_vector.cpp:41-42,53-57,123-143,296-313, verbatim: IdealGas gm1=0.4, Cv=5,
+    density {1,2,5}, energy {5,10,15}, temperature {50,100,150}."""
     L = pkg._lib
     e = ref.IdealGas(0.4, 5.0)
-    rho, sie = np.array([1.0, 2.0, 3.0]), np.array([5.0, 10.0, 15.0])
+    rho, sie = np.array([1.0, 2.0, 5.0]), np.array([5.0, 10.0, 15.0])
     assert_rel(e.eval(L.T_FROM_RHO_E, rho, sie), [1.0, 2.0, 3.0], 1e-12)
-    assert_rel(e.eval(L.P_FROM_RHO_E, rho, sie), [2.0, 8.0, 18.0], 1e-12)
-    assert_rel(e.eval(L.BMOD_FROM_RHO_E, rho, sie), [2.8, 11.2, 25.2], 1e-12)
+    assert_rel(e.eval(L.P_FROM_RHO_E, rho, sie), [2.0, 8.0, 30.0], 1e-12)
+    assert_rel(e.eval(L.BMOD_FROM_RHO_E, rho, sie), [2.8, 11.2, 42.0], 1e-12)
     T = np.array([50.0, 100.0, 150.0])
     assert_rel(e.eval(L.E_FROM_RHO_T, rho, T), [250.0, 500.0, 750.0], 1e-12)
-    assert_rel(e.eval(L.P_FROM_RHO_T, rho, T), [100.0, 400.0, 900.0], 1e-12)
-    assert_rel(e.eval(L.BMOD_FROM_RHO_T, rho, T), [140.0, 560.0, 1260.0], 1e-12)
+    assert_rel(e.eval(L.P_FROM_RHO_T, rho, T), [100.0, 400.0, 1500.0], 1e-12)
+    assert_rel(e.eval(L.BMOD_FROM_RHO_T, rho, T), [140.0, 560.0, 2100.0], 1e-12)
+
+
+# test/test_eos_gruneisen.cpp:70-84 (copper), :103-110 (inputs), :124-133 (gold arrays), verbatim
+GRUN_CU = dict(C0=0.394 * 1.0 / 1e-06, S1=1.489, S2=0.0, S3=0.0, G0=2.02, b=0.47, rho0=8.93,
+               T0=298.0, P0=0.0, Cv=0.383e-05 * 1e12)
+GRUN_RHO = [8.0, 9.0, 9.5, 0.0]
+GRUN_SIE = [1.0e9, 5.0e8, 1.0e8, 0.0]
+GRUN_GOLD = {
+    "P_FROM_RHO_E": [-1.282094800000000e+11, 1.998504088912181e+10, 9.595823319513451e+10,
+                     0.0 - (0.394e6) * (0.394e6) * 8.93],
+    "BMOD_FROM_RHO_E": [9.990648504000005e+11, 1.460692677162573e+12, 1.851227213843747e+12,
+                        2.02 * (0.0 - (0.394e6) * (0.394e6) * 8.93)],
+    "T_FROM_RHO_E": [5.590966057441253e+02, 4.285483028720627e+02, 3.241096605744125e+02, 298.0],
+    "GAMMA_FROM_RHO_E": [2.02, 2.007944444444444e+00, 1.927000000000000e+00, 2.02],
+}
+
+
+def gruneisen_cu_args():
+    g = GRUN_CU
+    return (g["C0"], g["S1"], g["S2"], g["S3"], g["G0"], g["b"], g["rho0"], g["T0"], g["P0"],
+            g["Cv"])
+
+
+def test_ref_gruneisen_golden(pkg, ref):
+    """The oracle pinned to test/test_eos_gruneisen.cpp:124-133 (P, bmod, T, Gruneisen parameter
+    from (rho, sie); tolerance 1e-12 as array_compare, test/eos_unit_test_helpers.hpp:66-81)."""
+    L = pkg._lib
+    e = ref.Gruneisen(*gruneisen_cu_args())
+    rho, sie = np.array(GRUN_RHO), np.array(GRUN_SIE)
+    for name, gold in GRUN_GOLD.items():
+        assert_rel(e.eval(getattr(L, name), rho, sie), gold, 1e-12, "Gruneisen " + name)
+    # rho_max of the linear / quadratic Hugoniot fits (:585-612): eta_max = 1/S1 and the
+    # smaller root of 1 - S1 eta - S2 eta^2
+    lin = ref.Gruneisen(GRUN_CU["C0"], 1.34, 0.0, 0.0, 2.02, 0.47, 8.93, 298.0, 0.0, GRUN_CU["Cv"])
+    assert_rel([lin.MaximumDensity()], [0.99 * 8.93 / (1 - 1 / 1.34)], 1e-12)
+    s1, s2 = 2.0, 0.1
+    eta = (-s1 + np.sqrt(s1 * s1 + 4 * s2)) / (2 * s2)
+    quad = ref.Gruneisen(GRUN_CU["C0"], s1, s2, 0.0, 2.02, 0.47, 8.93, 298.0, 0.0, GRUN_CU["Cv"])
+    assert_rel([quad.MaximumDensity()], [0.99 * 8.93 / (1 - eta)], 1e-12)
 
 
 def test_ref_nqt_logs(pkg, ref):
@@ -171,7 +211,9 @@ def test_ref_solver_utils_known_answers(ref):
     delta = 1e-10
     A = np.ones((3, 3)) + delta * np.eye(3)
     ok, x = ref.solve_Ax_b(A.reshape(-1), [1.0, 1.0, 2.0])
-    assert ok and np.linalg.norm(A @ x - [1.0, 1.0, 2.0]) < np.sqrt(delta)
+    denom = delta * (3 + delta)  # test/test_solver_utils.cpp:93-97,118-123
+    want = [(delta - 1) / denom, (delta - 1) / denom, 2 * (1 + delta) / denom]
+    assert ok and is_close(x, want, np.sqrt(delta)).all()
 
 
 def test_ref_regula_falsi(ref):

@@ -8,7 +8,7 @@ import ctypes as C
 import numpy as np
 import pytest
 
-from helpers import assert_bits, assert_rel, dev
+from helpers import assert_bits, assert_rel, dev, is_close
 
 pytestmark = pytest.mark.gpu
 
@@ -25,8 +25,17 @@ def torch_cuda():
     return torch
 
 
+@pytest.fixture(scope="module", params=["single_patch", "three_patch"])
+def raw(pkg, request):
+    """Every Spiner parity test runs on the single-patch 256x256 table of configs 2/3 and on a
+    3-patch PiecewiseGrid1D table of the same size (what sesame2spiner writes;
+    utils/spiner/spiner/piecewise_grid_1d.hpp:73-126 findGridFromPosition / weights)."""
+    return pkg.tablegen.vinet_sp5_tables(piecewise=(request.param == "three_patch"))
+
+
 @pytest.fixture(scope="module")
-def raw(pkg):
+def raw1(pkg):
+    """The single-patch table of configs 2/3 only (host-pointer pipelines: layout-independent)."""
     return pkg.tablegen.vinet_sp5_tables()
 
 
@@ -51,20 +60,22 @@ def test_ideal_gas_golden_and_bits(pkg, ref, torch_cuda):
     torch = torch_cuda
     L = pkg._lib
     eos = pkg.IdealGas(0.4, 5.0)
-    rho = dev(np.array([1.0, 2.0, 3.0]))
+    rho = dev(np.array([1.0, 2.0, 5.0]))  # test/test_eos_vector.cpp:41,123,296
     sie = dev(np.array([5.0, 10.0, 15.0]))
     out = torch.empty_like(rho)
     eos.TemperatureFromDensityInternalEnergy(rho, sie, out, 3)
     assert_rel(out.cpu().numpy(), [1.0, 2.0, 3.0], 1e-12, "T")
     eos.PressureFromDensityInternalEnergy(rho, sie, out, 3)
-    assert_rel(out.cpu().numpy(), [2.0, 8.0, 18.0], 1e-12, "P(rho,e)")
+    assert_rel(out.cpu().numpy(), [2.0, 8.0, 30.0], 1e-12, "P(rho,e)")
+    eos.BulkModulusFromDensityInternalEnergy(rho, sie, out, 3)
+    assert_rel(out.cpu().numpy(), [2.8, 11.2, 42.0], 1e-12, "bmod(rho,e)")
     T = dev(np.array([50.0, 100.0, 150.0]))
     eos.InternalEnergyFromDensityTemperature(rho, T, out, 3)
     assert_rel(out.cpu().numpy(), [250.0, 500.0, 750.0], 1e-12, "e")
     eos.PressureFromDensityTemperature(rho, T, out, 3)
-    assert_rel(out.cpu().numpy(), [100.0, 400.0, 900.0], 1e-12, "P(rho,T)")
+    assert_rel(out.cpu().numpy(), [100.0, 400.0, 1500.0], 1e-12, "P(rho,T)")
     eos.BulkModulusFromDensityTemperature(rho, T, out, 3)
-    assert_rel(out.cpu().numpy(), [140.0, 560.0, 1260.0], 1e-12, "bmod")
+    assert_rel(out.cpu().numpy(), [140.0, 560.0, 2100.0], 1e-12, "bmod")
 
     n = 1 << 20
     rho_h, T_h = pkg.workloads.ideal_inputs(n)
@@ -140,6 +151,27 @@ def test_analytic_pte_materials(pkg, ref, torch_cuda, kind):
         # looser on derived quantities; cancellation costs a few digits here
         t = 1e-9 if m in (L.BMOD_FROM_RHO_E, L.BMOD_FROM_RHO_T) else tol
         assert_rel(out.cpu().numpy(), want, t, kind + " " + L.METHOD_NAMES[m])
+
+
+def test_gruneisen_reference_golden(pkg, torch_cuda):
+    """test/test_eos_gruneisen.cpp:70-84,103-110,124-133: copper, P / bmod / T / Gruneisen
+    parameter from (rho, sie) against the reference's own gold arrays (tolerance 1e-12), incl.
+    the rho = 0 cell; ComputeRhoMax for the linear and quadratic Hugoniot fits (:585-612)."""
+    from test_cpu_oracle import GRUN_CU, GRUN_GOLD, GRUN_RHO, GRUN_SIE, gruneisen_cu_args
+    torch = torch_cuda
+    L = pkg._lib
+    eos = pkg.Gruneisen(*gruneisen_cu_args())
+    rho, sie = dev(np.array(GRUN_RHO)), dev(np.array(GRUN_SIE))
+    out = torch.empty_like(rho)
+    for name, gold in GRUN_GOLD.items():
+        eos._eval(getattr(L, name), rho, sie, out, 4, None)
+        assert_rel(out.cpu().numpy(), gold, 1e-12, "Gruneisen " + name)
+    lin = pkg.Gruneisen(GRUN_CU["C0"], 1.34, 0.0, 0.0, 2.02, 0.47, 8.93, 298.0, 0.0, GRUN_CU["Cv"])
+    assert_rel([lin.MaximumDensity()], [0.99 * 8.93 / (1 - 1 / 1.34)], 1e-12)
+    s1, s2 = 2.0, 0.1
+    eta = (-s1 + np.sqrt(s1 * s1 + 4 * s2)) / (2 * s2)
+    quad = pkg.Gruneisen(GRUN_CU["C0"], s1, s2, 0.0, 2.02, 0.47, 8.93, 298.0, 0.0, GRUN_CU["Cv"])
+    assert_rel([quad.MaximumDensity()], [0.99 * 8.93 / (1 - eta)], 1e-12)
 
 
 # ------------------------------------------------------------------------------------------
@@ -247,16 +279,25 @@ def test_spiner_rhot_root_find(pkg, ref, torch_cuda, raw, guess):
         g._eval(m, rho_d, sie_d, out, n, lam_d)
         want = r.eval(m, rho_h, sie_h, lam_h, nthreads=0)
         assert_rel(out.cpu().numpy(), want, LOOKUP_TOL, f"RhoT {L.METHOD_NAMES[m]} [{guess}]")
-        if lam_d is not None:
+        if lam_d is not None and m == L.T_FROM_RHO_E:
+            # hybrid direct/iterate path (test_root_modes): lRho identical, lT to 1e-12 absolute
+            lam_g = lam_d.cpu().numpy()
+            assert_bits(lam_g[:, 0], lam_h[:, 0], f"RhoT lambda lRho [{guess}]")
+            assert np.abs(lam_g[:, 1] - lam_h[:, 1]).max() <= 1e-12
+        elif lam_d is not None:
             assert_rel(lam_d.cpu().numpy(), lam_h, LOOKUP_TOL, f"RhoT lambda [{guess}]")
 
 
 @pytest.mark.parametrize("guess", ["nan", "warm", "null"])
-def test_root_flow_equals_per_thread_kernel(pkg, ref, torch_cuda, raw, guess, monkeypatch):
-    """The warp-level flow kernel (csrc/sgx_spiner_root.cu: setup / iterate-with-refill /
-    retire) performs, per cell, the per-thread root find's floating-point operations: T and the
-    lambda write-back must be bit-identical, for ragged sizes, off-table cells, warm and cold
-    starts, and a null lambda."""
+def test_root_modes(pkg, ref, torch_cuda, raw, guess, monkeypatch):
+    """TemperatureFromDensityInternalEnergy, csrc/sgx_spiner_root.cu.  SGX_ROOT_MODE=exact is the
+    reference iterate for every cell: T and the lambda write-back are compared BIT FOR BIT with
+    the oracle.  The default hybrid (direct inversion where an a-priori bound puts it within
+    1e-12 of anything the iterate can return, the iterate elsewhere) must agree with the oracle
+    to 1e-12 on T and to 1e-12 absolute on the cached lT = log10 T (a logarithm: lT passes
+    through 0 at T = 1, so a relative bar is meaningless there), for ragged sizes, off-table
+    cells, soft-threshold cells, warm and cold starts and a null lambda.  `direct` (opt-in, not
+    a parity mode) is held to the measured 5e-11."""
     torch = torch_cuda
     L = pkg._lib
     g, r = pkg.SpinerEOSDependsRhoT(raw), ref.SpinerRhoT(raw)
@@ -266,19 +307,74 @@ def test_root_flow_equals_per_thread_kernel(pkg, ref, torch_cuda, raw, guess, mo
         lam0 = np.full((n, 2), np.nan)
         if guess == "warm":
             r.eval(L.E_FROM_RHO_T, rho_h, T_h, lam0, nthreads=0)
-        outs = {}
-        for variant in ("perthread", "flow"):
-            monkeypatch.setenv("SGX_ROOT_KERNEL", variant)  # default is the per-thread kernel
+        lam_r = lam0.copy()  # the oracle always gets a lambda (NaN = no cache; SURVEY 7 part 3)
+        T_r = r.eval(L.T_FROM_RHO_E, rho_h, sie_h, lam_r, nthreads=0)
+        for mode in ("exact", "hybrid", "direct"):
+            monkeypatch.setenv("SGX_ROOT_MODE", mode)
             rho_d, sie_d = dev(rho_h), dev(sie_h)
             out = torch.full_like(rho_d, float("nan"))
             lam_d = None if guess == "null" else dev(lam0.copy())
+            g.root_stats(reset=True)
             g._eval(L.T_FROM_RHO_E, rho_d, sie_d, out, n, lam_d)
             torch.cuda.synchronize()
-            outs[variant] = (out.cpu().numpy(),
-                             None if lam_d is None else lam_d.cpu().numpy())
-        assert_bits(outs["flow"][0], outs["perthread"][0], f"T n={n} [{guess}]")
-        if guess != "null":
-            assert_bits(outs["flow"][1], outs["perthread"][1], f"lambda n={n} [{guess}]")
+            T_g = out.cpu().numpy()
+            what = f"T(rho,sie) n={n} [{guess}/{mode}]"
+            if mode == "exact":
+                assert_bits(T_g, T_r, what)
+                if lam_d is not None:
+                    assert_bits(lam_d.cpu().numpy(), lam_r, what + " lambda")
+                continue
+            seen, listed = g.root_stats()
+            assert seen == n and 0 <= listed <= n
+            assert_rel(T_g, T_r, LOOKUP_TOL if mode == "hybrid" else 5e-11, what)
+            if lam_d is not None:
+                lam_g = lam_d.cpu().numpy()
+                assert_bits(lam_g[:, 0], lam_r[:, 0], what + " lambda lRho")
+                dl = np.abs(lam_g[:, 1] - lam_r[:, 1])
+                assert dl.max() <= (1e-12 if mode == "hybrid" else 5e-11), (what, dl.max())
+
+
+def test_root_hybrid_full_size(pkg, torch_cuda):
+    """Config 3a at BASELINE.json's full size (2^26 on-table cells), size-independent properties:
+    hybrid vs the exact reference iterate run on the same device arrays -- T within 1e-12 on every
+    cell, cached lT within 1e-12 absolute, lRho identical -- and the round trip
+    e(rho, T(rho, e)) = e to the table's own resolution.  (The exact mode is pinned bit for bit
+    to the oracle by test_root_modes.)"""
+    import os
+    torch = torch_cuda
+    L, W = pkg._lib, pkg.workloads
+    g = pkg.SpinerEOSDependsRhoT(pkg.tablegen.vinet_sp5_tables())
+    n = 1 << 26
+    rho, T = W.spiner_inputs(n, xp=torch, device="cuda", seeds=(W.SEED_ROOT_RHO, W.SEED_ROOT_T))
+    sie = torch.empty_like(rho)
+    g._eval(L.E_FROM_RHO_T, rho, T, sie, n, None)
+    del T
+    res = {}
+    for mode in ("exact", "hybrid"):
+        os.environ["SGX_ROOT_MODE"] = mode
+        try:
+            out = torch.empty_like(rho)
+            lam = torch.full((n, 2), float("nan"), dtype=torch.float64, device="cuda")
+            g.root_stats(reset=True)
+            g._eval(L.T_FROM_RHO_E, rho, sie, out, n, lam)
+            torch.cuda.synchronize()
+            res[mode] = (out, lam)
+        finally:
+            os.environ.pop("SGX_ROOT_MODE", None)
+    seen, listed = g.root_stats()
+    print(f"hybrid: {listed}/{seen} = {100.0 * listed / seen:.2f}% of cells through the reference iterate")
+    Te, le = res["exact"]
+    Th, lh = res["hybrid"]
+    rel = ((Th - Te).abs() / Te.abs()).max().item()
+    assert rel <= LOOKUP_TOL, f"hybrid vs exact T: max rel {rel:.3e}"
+    assert torch.equal(lh[:, 0], le[:, 0])
+    dl = (lh[:, 1] - le[:, 1]).abs().max().item()
+    assert dl <= 1e-12, f"hybrid vs exact lT: max abs {dl:.3e}"
+    del Te, le, lh
+    back = torch.empty_like(rho)
+    g._eval(L.E_FROM_RHO_T, rho, Th, back, n, None)
+    rt = ((back - sie).abs() / sie.abs().clamp_min(1.0)).max().item()
+    assert rt <= 1e-9, f"e(rho, T(rho, e)) round trip: {rt:.3e}"
 
 
 def test_spiner_rhot_fill_eos(pkg, ref, torch_cuda, raw):
@@ -368,11 +464,13 @@ def test_solve_Ax_b_known_answers(pkg, ref, torch_cuda):
         # the device solve is the reference's arithmetic (Cramer for 2x2, Eigen's
         # colPivHouseholderQr for 3x3): identical bits, and the residual the reference reaches
         assert_bits(x, x_r, "solve")
-        assert_rel(np.linalg.norm(A @ x - b) + 1.0, 1.0, 1e-6 if n == 3 and A is A3 else 1e-7,
-                   "residual")
+        if A is not A3:  # (the near-singular system's residual is dominated by |x| ~ 3e9)
+            assert_rel(np.linalg.norm(A @ x - b) + 1.0, 1.0, 1e-7, "residual")
         if A is A3:
-            # test/test_solver_utils.cpp:90-133: x = {0, 0, 1} + O(sqrt(delta))
-            assert_rel(x + 1.0, np.array([1.0, 1.0, 2.0]), np.sqrt(delta), "3x3 near-singular")
+            # test/test_solver_utils.cpp:93-97,118-123: the exact solution, isClose(.., sqrt(delta))
+            denom = delta * (3 + delta)
+            want = [(delta - 1) / denom, (delta - 1) / denom, 2 * (1 + delta) / denom]
+            assert is_close(x, want, np.sqrt(delta)).all(), ("3x3 near-singular", x, want)
 
 
 @pytest.mark.parametrize("n", [3, 4, 6])
@@ -674,10 +772,11 @@ def test_pte_properties_full_path(pkg, torch_cuda):
     assert close(vfrac[c].sum(dim=1), torch.ones_like(vfrac[c, 0]), 1e-12).all()
 
 
-def test_host_entry_points_multi_chunk_equal_device_path(pkg, torch_cuda, raw):
+def test_host_entry_points_multi_chunk_equal_device_path(pkg, torch_cuda, raw1):
     """The *_host entry points cut the range into chunks that flow through several streams
     (csrc/sgx_api.cu sgx_eos_eval_host, csrc/sgx_pte.cu sgx_pte_solve_host): results must equal
     the device-pointer path bit for bit, for sizes that are not multiples of the chunk."""
+    raw = raw1
     torch = torch_cuda
     L, W = pkg._lib, pkg.workloads
     # lookups: 2 chunks + ragged tail
@@ -723,8 +822,9 @@ def test_host_entry_points_multi_chunk_equal_device_path(pkg, torch_cuda, raw):
         assert_bits(a, b.cpu().numpy(), "pte_solve_host " + nm)
 
 
-def test_host_pointer_entry_points(pkg, ref, torch_cuda, raw):
+def test_host_pointer_entry_points(pkg, ref, torch_cuda, raw1):
     """The *_host C-ABI forms (what a host code without device arrays calls)."""
+    raw = raw1
     L = pkg._lib
     g, r = pkg.SpinerEOSDependsRhoT(raw), ref.SpinerRhoT(raw)
     n = 10007
@@ -751,18 +851,10 @@ def test_host_pointer_entry_points(pkg, ref, torch_cuda, raw):
         assert_rel(a, b, PTE_TOL, "pte_solve_host state")
 
 
-# ------------------------------------------------------------------------------------------
-# Helmholtz (config 4).  The shipped helm_table.dat is absent from the reference checkout, so
-# both sides read the SAME synthetic table (tablegen.write_synthetic_helm_table); parity is
-# against the reference's own Helmholtz class run as oracle, not against shipped gold numbers.
-#
-# Tolerances.  e and P: 1e-12.  cv = T (-d2f/dT2) Ye and bmod are second derivatives of the
-# tabulated free energy: the 36-term biquintic sum cancels by up to ~1e10 where the cold term
-# dominates f, so a 1-ulp difference in log10(T) / exp() between glibc and CUDA's libm moves
-# them by ~1e-7 -- and moves the REFERENCE's own answer by as much.  The bar for those is
-# therefore self-calibrating: |gpu - ref(T)| <= 1e-12 |ref| + 8 max|ref(T+-) - ref(T)| with T+-
-# one ulp of lT = log10(T) away (the EOS works from lT, and a 1-ulp change of T usually leaves
-# lT unchanged), i.e. within the oracle's own response to a last-bit change of its input.
+# Helmholtz.  The device exp / log / log10 / cbrt / pow are glibc's algorithms bit for bit
+# (csrc/sgx_libm.cuh, tests/test_libm_parity.py), so every output -- including cv, bmod and the
+# Grueneisen parameter, second derivatives of the tabulated free energy whose 36-term biquintic
+# sum cancels by up to ~1e10 -- is held to north_star's 1e-12 (measured: bit-identical).
 HELM_TOL = 1e-12
 HELM_COMPOSITIONS = ((1.0, 1.0), (4.0, 2.0), (12.0, 6.0), (16.0, 8.0), (56.0, 26.0))
 HELM_OUT_RT = None  # set lazily (needs pkg.thermalqs)
@@ -781,34 +873,6 @@ def _helm_lambda(n, ncol, lT=-1.0):
     if ncol > 2:
         lam[:, 2] = lT
     return lam
-
-
-def _assert_within_sensitivity(got, want, neighbours, what, floor=HELM_TOL, k=8.0):
-    got, want = np.asarray(got), np.asarray(want)
-    sens = np.zeros_like(want)
-    for nb in neighbours:
-        d = np.abs(nb - want)
-        sens = np.maximum(sens, np.where(np.isfinite(d), d, 0.0))
-    bound = floor * np.abs(want) + k * sens
-    err = np.abs(got - want)
-    ok = (err <= bound) | (np.isnan(got) & np.isnan(want)) | (got == want)
-    if not ok.all():
-        i = int(np.argmax(np.where(ok, 0.0, err / np.maximum(bound, 1e-300))))
-        raise AssertionError(f"{what}: {int((~ok).sum())}/{ok.size} cells outside the oracle's "
-                             f"1-ulp sensitivity; worst at {i}: got {got[i]!r} want {want[i]!r} "
-                             f"bound {bound[i]:.3e}")
-    tight = (err <= floor * np.abs(want)) | (got == want)
-    print(f"{what}: {100 * tight.mean():.2f}% of cells within {floor:g}, rest within the oracle's "
-          f"own 1-ulp input sensitivity")
-
-
-def _lT_ulp_neighbours(T, kmax=3):
-    """T shifted by +-1..kmax ulps of log10(T): T (1 +- k ln10 ulp(lT)).  Several probes are
-    needed because the oracle's cv is not smooth at this scale: it jumps by ~1e-11 relative
-    from one ulp of lT to the next (cancellation noise of the 36-term sum), so a single pair
-    can land on a flat spot."""
-    d = np.log(10.0) * np.spacing(np.abs(np.log10(T))) * T
-    return [T + k * d for k in range(-kmax, kmax + 1) if k != 0]
 
 
 def _ref_fill_rho_T(pkg, r, rho, T, ncol=3):
@@ -835,7 +899,6 @@ def test_helmholtz_fill_rho_T(pkg, ref, torch_cuda, helm_table, coul):
     rho_h[:4] = [1e-12, 1e15, 1e-13, 2e15]
     T_h[4:8] = [1e3, 1e13, 5e2, 3e13]
     e_r, P_r, cv_r, b_r, lam_h = _ref_fill_rho_T(pkg, r, rho_h, T_h)
-    nbs = [_ref_fill_rho_T(pkg, r, rho_h, Tx) for Tx in _lT_ulp_neighbours(T_h)]
     out = tq.specific_internal_energy | tq.pressure | tq.specific_heat | tq.bulk_modulus
     lam_d = dev(_helm_lambda(n, 3))
     e, P, cv, b = (torch.zeros(n, dtype=torch.float64, device="cuda") for _ in range(4))
@@ -843,19 +906,16 @@ def test_helmholtz_fill_rho_T(pkg, ref, torch_cuda, helm_table, coul):
     torch.cuda.synchronize()
     assert_rel(e.cpu().numpy(), e_r, HELM_TOL, f"Helmholtz FillEos(rho,T) e coul={coul}")
     assert_rel(P.cpu().numpy(), P_r, HELM_TOL, f"Helmholtz FillEos(rho,T) P coul={coul}")
-    _assert_within_sensitivity(cv.cpu().numpy(), cv_r, [x[2] for x in nbs],
-                               f"Helmholtz FillEos(rho,T) cv coul={coul}")
-    _assert_within_sensitivity(b.cpu().numpy(), b_r, [x[3] for x in nbs],
-                               f"Helmholtz FillEos(rho,T) bmod coul={coul}")
+    assert_rel(cv.cpu().numpy(), cv_r, HELM_TOL, f"Helmholtz FillEos(rho,T) cv coul={coul}")
+    assert_rel(b.cpu().numpy(), b_r, HELM_TOL, f"Helmholtz FillEos(rho,T) bmod coul={coul}")
     assert_rel(lam_d.cpu().numpy(), lam_h, 1e-15, "Helmholtz lambda lT write-back")
 
 
 def test_helmholtz_fill_rho_e(pkg, ref, torch_cuda, helm_table):
     """Mode (ii): FillEos(rho,e) -> T,P,cv,bmod through newton_raphson on e(T), with the
     type-indexed {Abar,Zbar} lambda (no lT slot: SURVEY 0 finding 6).  Coulomb off, as in
-    test/test_eos_helmholtz.cpp:44, so e(T) is monotone.  Newton stops at
-    |e(T) - e| < 1e-10 |e| (HELM_EOS_EPS), so T is defined to 1e-10 |e| / (cv T): that is the
-    tolerance, floor 1e-9; P, cv, bmod are then compared at the oracle's own T sensitivity."""
+    test/test_eos_helmholtz.cpp:44, so e(T) is monotone.  The Newton iterates are the
+    reference's bit for bit (same libm, same arithmetic), so T, P, cv, bmod are held to 1e-12."""
     torch = torch_cuda
     L, tq = pkg._lib, pkg.thermalqs
     g = pkg.Helmholtz(helm_table, coul=False, lambda_has_lT_slot=False)
@@ -870,20 +930,8 @@ def test_helmholtz_fill_rho_e(pkg, ref, torch_cuda, helm_table):
     T2, P2, cv2, b2 = (torch.zeros(n, dtype=torch.float64, device="cuda") for _ in range(4))
     g.FillEos(dev(rho_h), T2, dev(e_h), P2, cv2, b2, n, out, dev(_helm_lambda(n, 2)))
     torch.cuda.synchronize()
-    T_g = T2.cpu().numpy()
-    tolT = np.maximum(1e-9, 4e-10 * np.abs(e_h) / (np.abs(cv_h) * T_h))
-    errT = np.abs(T_g - T_r) / np.abs(T_r)
-    bad = ~((errT <= tolT) | (np.isnan(T_g) & np.isnan(T_r)))
-    assert not bad.any(), (f"Helmholtz FillEos(rho,e) T: {int(bad.sum())} cells outside the "
-                           f"Newton stopping tolerance; worst rel err {errT[bad].max():.3e}")
-    print(f"Helmholtz T(rho,e): {100 * (errT <= 1e-12).mean():.2f}% of cells within 1e-12, "
-          f"{100 * (errT <= 1e-9).mean():.2f}% within 1e-9, max {np.nanmax(errT):.2e}")
-    # derived outputs at the oracle's T and at T (1 +- tolT): the GPU must lie inside
-    ups = _ref_fill_rho_T(pkg, r, rho_h, T_r * (1 + tolT))
-    dns = _ref_fill_rho_T(pkg, r, rho_h, T_r * (1 - tolT))
-    for got, want, k, nm in ((P2, P_r, 1, "P"), (cv2, cv_r, 2, "cv"), (b2, b_r, 3, "bmod")):
-        _assert_within_sensitivity(got.cpu().numpy(), want, (ups[k], dns[k]),
-                                   "Helmholtz FillEos(rho,e) " + nm, floor=1e-9)
+    for got, want, nm in ((T2, T_r, "T"), (P2, P_r, "P"), (cv2, cv_r, "cv"), (b2, b_r, "bmod")):
+        assert_rel(got.cpu().numpy(), want, HELM_TOL, "Helmholtz FillEos(rho,e) " + nm)
 
 
 def test_helmholtz_lT_slot_overwrite_quirk(pkg, ref, torch_cuda, helm_table):
@@ -918,17 +966,11 @@ def test_helmholtz_vector_methods(pkg, ref, torch_cuda, helm_table):
     rho_h, T_h = pkg.workloads.helm_inputs(n)
     rho_d, T_d = dev(rho_h), dev(T_h)
     out = torch.empty(n, dtype=torch.float64, device="cuda")
-    T_nb = _lT_ulp_neighbours(T_h)
     for m in (L.P_FROM_RHO_T, L.E_FROM_RHO_T, L.CV_FROM_RHO_T, L.BMOD_FROM_RHO_T,
               L.GAMMA_FROM_RHO_T):
         want = r.eval(m, rho_h, T_h, _helm_lambda(n, 3), nthreads=0)
         g._eval(m, rho_d, T_d, out, n, dev(_helm_lambda(n, 3)))
-        if m in (L.P_FROM_RHO_T, L.E_FROM_RHO_T):
-            assert_rel(out.cpu().numpy(), want, HELM_TOL, "Helmholtz " + L.METHOD_NAMES[m])
-        else:
-            nb = [r.eval(m, rho_h, Tx, _helm_lambda(n, 3), nthreads=0) for Tx in T_nb]
-            _assert_within_sensitivity(out.cpu().numpy(), want, nb,
-                                       "Helmholtz " + L.METHOD_NAMES[m])
+        assert_rel(out.cpu().numpy(), want, HELM_TOL, "Helmholtz " + L.METHOD_NAMES[m])
     # a null lambda is an error (SafeMustGet aborts in the reference), not a silent default
     with pytest.raises(pkg.SgxError):
         g._eval(L.P_FROM_RHO_T, rho_d, T_d, out, n, None)
