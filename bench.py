@@ -265,8 +265,19 @@ def run_ours(args):
             lam.copy_(lam_warm)
             eos_rt.TemperatureFromDensityInternalEnergy(rho, sie, out, n, lam)
         ks = max(3, K // 4)
+        eos_rt.root_stats(reset=True)
         lookup("spiner_rhot_T_rhoe_rootfind_cold(+lambda refill)", cold, 40, steps=ks)
+        seen, listed = eos_rt.root_stats(reset=True)
+        results["spiner_rhot_T_rhoe_rootfind_cold(+lambda refill)"].update({
+            "root_mode": os.environ.get("SGX_ROOT_MODE", "hybrid"),
+            "cells_through_reference_iterate_frac": listed / max(1, seen)})
         lookup("spiner_rhot_T_rhoe_rootfind_warm(+lambda refill)", warm, 40, steps=ks)
+        # the reference iterate for every cell (SGX_ROOT_MODE=exact), same inputs
+        os.environ["SGX_ROOT_MODE"] = "exact"
+        try:
+            lookup("spiner_rhot_T_rhoe_rootfind_cold_exact_iterate", cold, 40, steps=3)
+        finally:
+            os.environ.pop("SGX_ROOT_MODE", None)
         # config 3b: RhoSie direct lookup
         eos_rs = pkg.SpinerEOSDependsRhoSie(raw)
         lam1 = torch.full((n, 1), float("nan"), dtype=torch.float64, device=dev)
@@ -311,7 +322,7 @@ def run_ours(args):
         tq = pkg.thermalqs
         hpath = os.path.join(tempfile.gettempdir(), f"sgx_helm_synthetic_{os.getpid()}.dat")
         pkg.tablegen.write_synthetic_helm_table(hpath)
-        nh = min(n, 1 << 25)
+        nh = n  # BASELINE.json configs[3]: 2^26 cells
         h_rho, h_T = W.helm_inputs(nh, rank * nh, xp=torch, device=dev)
         h_e, h_P, h_cv, h_b = (torch.empty_like(h_rho) for _ in range(4))
         comp = torch.tensor([[1., 1.], [4., 2.], [12., 6.], [16., 8.], [56., 26.]],
@@ -363,8 +374,9 @@ def run_ours(args):
                 a.copy_(b)
             pkg.closure.PTESolverRhoT(g3, *state, params=prm, status=status, stats=stats)
         ks = 3
+        s = time_steps(torch, pte, 1, 2, dist)  # warm-up passes (allocator pools, clocks)
         stats.zero_()
-        s = time_steps(torch, pte, ks, 1, dist)
+        s = time_steps(torch, pte, ks, 0, dist)
         if dist is not None:
             dist.all_reduce(stats)  # the optional convergence-statistics all-reduce (NCCL)
         st = stats.cpu().numpy()
@@ -388,15 +400,40 @@ def run_ours(args):
         s = time_steps(torch, pte_def, ks, 1, dist)
         results["pte_rhot_3mat_default_mixparams"] = {
             "cell_solves_per_s": nsec * world * ks / s, "cells_per_gpu": nsec}
-        npt = min(npte, 1 << 18)
+        npt = min(npte, 1 << 24)  # PTESolverPT at 2^24 cells
 
         def pte_pt():
-            for a, b in zip(sec, sec0):
+            for a, b in zip(state, state0):
                 a[:npt].copy_(b[:npt])
-            pkg.closure.PTESolverPT(g3, *[a[:npt] for a in sec], params=prm_def)
+            pkg.closure.PTESolverPT(g3, *[a[:npt] for a in state], params=prm_def)
         s = time_steps(torch, pte_pt, 2, 1, dist)
         results["pte_pt_3mat_default_mixparams"] = {
             "cell_solves_per_s": npt * world * 2 / s, "cells_per_gpu": npt}
+        # the runtime-dispatched (Variant-like, DynEos) path: 2 and 4 materials, 2^22 cells
+        for nm, mats in ((2, (0, 2)), (4, (0, 1, 2, 0))):
+            ng = min(npte, 1 << 22)
+            eos_g = [g3[m] for m in mats]
+            vf = W.pte_vfracs(ng, start=rank * ng, xp=torch, device=dev, nmat=nm)
+            rho_g = torch.tensor([W.PTE_RHO[m] for m in mats], dtype=torch.float64,
+                                 device=dev).repeat(ng, 1).contiguous()
+            sie_g = torch.tensor([sie0[m] for m in mats], dtype=torch.float64,
+                                 device=dev).repeat(ng, 1).contiguous()
+            tmp_g = torch.full((ng, nm), W.PTE_T, dtype=torch.float64, device=dev)
+            prs_g = torch.zeros((ng, nm), dtype=torch.float64, device=dev)
+            g0 = [rho_g, vf, sie_g, tmp_g, prs_g]
+            gs = [a.clone() for a in g0]
+            stg = torch.zeros(ng, dtype=torch.int64, device=dev)
+
+            def pte_gen():
+                for a, b in zip(gs, g0):
+                    a.copy_(b)
+                pkg.closure.PTESolverRhoT(eos_g, *gs, params=prm_def, status=stg)
+            s = time_steps(torch, pte_gen, ks, 1, dist)
+            results[f"pte_rhot_{nm}mat_generic_default_mixparams"] = {
+                "cell_solves_per_s": ng * world * ks / s, "cells_per_gpu": ng,
+                "converged_frac": float((stg & 1).double().mean().item()),
+                "materials": [type(e).__name__ for e in eos_g]}
+            del g0, gs, stg
         # e2e for config 5: host buffers through sgx_pte_solve_host (chunked, 3 streams)
         npe = min(npte, 1 << 22)
         hst0 = [a[:npe].cpu() for a in state0]
@@ -409,45 +446,57 @@ def run_ours(args):
             pkg.closure.pte_solve_host(L.PTE_RHOT, g3, *[a.numpy() for a in hst], params=prm,
                                        status=hstatus.numpy().view(np.uint64))
         pte_host()
-        t_host = 0.0
-        for _ in range(2):
+        pte_host()
+        t_pass = []
+        for _ in range(5):
             for a, b in zip(hst, hst0):
                 a.copy_(b)
+            if dist is not None:
+                dist.barrier()
             t0 = time.perf_counter()
             pkg.closure.pte_solve_host(L.PTE_RHOT, g3, *[a.numpy() for a in hst], params=prm,
                                        status=hstatus.numpy().view(np.uint64))
-            t_host += time.perf_counter() - t0
-        if dist is not None:
-            tt = torch.tensor([t_host], dtype=torch.float64, device=dev)
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-            t_host = float(tt.item())
+            dt = time.perf_counter() - t0
+            if dist is not None:
+                tt = torch.tensor([dt], dtype=torch.float64, device=dev)
+                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+                dt = float(tt.item())
+            t_pass.append(dt)
         results["pte_rhot_3mat_e2e_host"] = {
-            "cell_solves_per_s": npe * world * 2 / t_host, "cells_per_gpu": npe,
+            "cell_solves_per_s": npe * world / float(np.median(t_pass)), "cells_per_gpu": npe,
+            "passes": len(t_pass), "statistic": "median pass, max over ranks",
             "h2d_bytes_per_cell": 120, "d2h_bytes_per_cell": 128,
             "api": "sgx_pte_solve_host with pinned host arrays"}
         del state, state0, status, hst, hst0
 
     # ---- e2e: host buffers through the C ABI (_host entry), H2D + D2H inside the timing --
-    ne = min(n, 1 << 24)
+    # The headline workload itself: 2^26 cells per step per GPU, from the caller's host arrays.
+    ne = n
     rho_h, T_h = W.spiner_inputs(ne, start)
     rho_p = torch.from_numpy(rho_h).pin_memory().numpy()
     T_p = torch.from_numpy(T_h).pin_memory().numpy()
     out_p = torch.empty(ne, dtype=torch.float64).pin_memory().numpy()
     lam_p = torch.full((ne, 2), float("nan"), dtype=torch.float64).pin_memory().numpy()
-    for _ in range(2):
-        eos_rt.eval_host(L.P_FROM_RHO_T, rho_p, T_p, out_p, lam_p)
-    torch.cuda.synchronize()
-    if dist is not None:
-        dist.barrier()
-    t0 = time.perf_counter()
+
+    def timed_host(fn, reps):
+        for _ in range(2):
+            fn()
+        torch.cuda.synchronize()
+        ts = []
+        for _ in range(reps):
+            if dist is not None:
+                dist.barrier()
+            t0 = time.perf_counter()
+            fn()
+            dt = time.perf_counter() - t0
+            if dist is not None:
+                tt = torch.tensor([dt], dtype=torch.float64, device=dev)
+                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+                dt = float(tt.item())
+            ts.append(dt)
+        return float(np.sum(ts))
     ke = 5
-    for _ in range(ke):
-        eos_rt.eval_host(L.P_FROM_RHO_T, rho_p, T_p, out_p, lam_p)
-    t_e2e = time.perf_counter() - t0
-    if dist is not None:
-        tt = torch.tensor([t_e2e], dtype=torch.float64, device=dev)
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        t_e2e = float(tt.item())
+    t_e2e = timed_host(lambda: eos_rt.eval_host(L.P_FROM_RHO_T, rho_p, T_p, out_p, lam_p), ke)
     e2e = {"value": ne * world * ke / t_e2e / 1e9, "unit": UNIT,
            # rho, T in; P and the (lRho, lT) lambda rows out.  The lambda rows are write-only for
            # a (rho, T) lookup, so the library does not copy them to the device (lambda_io)
@@ -456,6 +505,19 @@ def run_ours(args):
            "api": "sgx_eos_eval_host(P_FROM_RHO_T) with pinned host arrays",
            "host_cpus_of_rank0": (f"{len(numa)} CPUs local to the GPU (NVML affinity)"
                                   if numa else "unrestricted")}
+    if not args.quick:
+        # what a host code with ordinary (pageable) arrays sees: the library page-locks the
+        # caller's ranges for the duration of the call (cudaHostRegister, HostPin in
+        # csrc/sgx_internal.hpp); SGX_HOST_PIN=none is read once per process, so only the
+        # default is timed here
+        del rho_p, T_p, out_p, lam_p
+        out_g = np.empty(ne)
+        lam_g = np.full((ne, 2), np.nan)
+        t_pg = timed_host(lambda: eos_rt.eval_host(L.P_FROM_RHO_T, rho_h, T_h, out_g, lam_g), 3)
+        e2e["pageable_host_arrays_Gcells_per_s"] = ne * world * 3 / t_pg / 1e9
+        e2e["pageable_note"] = ("numpy (pageable) arrays; cudaHostRegister + unregister of all "
+                                "four ranges inside every timed call")
+        del out_g, lam_g
 
     clocks = None
     if rank == 0:
@@ -470,8 +532,11 @@ def run_ours(args):
         v = ctypes.c_double(0.0)
         if lib.sgx_microbench_fp64(fused, ctypes.byref(v)) == 0:
             fp64[name] = v.value
-    fp64["ncu_pipe_fp64_pct"] = {"pte_rhot_sm_kernel": 30.0, "rootfind eval_kernel": 44.4,
-                                 "helm_fill_kernel": 42.3}
+    try:  # FP64-pipe utilisation: only what a committed ncu capture says, named with its file
+        with open(os.path.join(ROOT, "profiles", "fp64_pipe_from_ncu.json")) as fh:
+            fp64["ncu_pipe_fp64_pct"] = json.load(fh)
+    except Exception:
+        pass
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K,
         "warmup": Wu, "ms_per_step": secs / K * 1e3, "higher_is_better": True,
@@ -487,7 +552,7 @@ def run_ours(args):
     if all_cpus:
         os.sched_setaffinity(0, all_cpus)  # the CPU baseline uses every host core
     if rank == 0 and not args.no_cpu:
-        line["cpu_baseline"] = cpu_baseline(pkg, raw, sample=1 << 22, reps=3)
+        line["cpu_baseline"] = cpu_baseline(pkg, raw, sample=1 << 24, reps=5)
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
@@ -505,42 +570,68 @@ def host_threads():
         return max(1, os.cpu_count() or 1)
 
 
+def baseline_ref():
+    """The library the CPU legs time: the Kokkos-OpenMP build of the reference harness when it
+    exists (oracle/_ref/libsgref_kokkos.so), else the serial-portableFor + OpenMP-chunk build."""
+    import oracle_ref
+
+    ref = oracle_ref.load_kokkos()
+    if ref is not None:
+        return ref, ("reference vector API under PORTABILITY_STRATEGY_KOKKOS, vendored Kokkos 4.4 "
+                     "OpenMP backend, g++ -O3 -DNDEBUG, OMP_PROC_BIND=%s OMP_PLACES=%s; PTE 3x3 "
+                     "solves through Eigen" % (os.environ.get("OMP_PROC_BIND"),
+                                               os.environ.get("OMP_PLACES")))
+    ref = oracle_ref.load()
+    return ref, ("OpenMP chunks over the reference vector API (PORTABILITY_STRATEGY_NONE), "
+                 "g++ -O2; PTE 3x3 solves through Eigen")
+
+
 def cpu_baseline(pkg, raw, sample, reps):
     """The reference's own code (oracle/_ref) on the host cores, bounded sample of the headline
     workload.  This is the checker being *timed*, never part of the product path."""
-    import oracle_ref
-
-    ref = oracle_ref.load()
+    cores = host_threads()
+    os.environ["OMP_NUM_THREADS"] = str(cores)
+    ref, how = baseline_ref()
     if ref is None:
         return {"value": None, "unit": UNIT, "cores": 0, "kind": "reference",
-                "sample": "oracle/_ref/libsgref.so not present"}
+                "sample": "oracle/_ref/libsgref*.so not present"}
     L = pkg._lib
     eos = ref.SpinerRhoT(raw)
     rho, T = pkg.workloads.spiner_inputs(sample)
     lam = np.full((sample, 2), np.nan)
-    cores = host_threads()
-    eos.eval(L.P_FROM_RHO_T, rho, T, lam, nthreads=cores)
-    best = 1e30
+    for _ in range(2):
+        eos.eval(L.P_FROM_RHO_T, rho, T, lam, nthreads=cores)
+    ts = []
     for _ in range(reps):
         t0 = time.perf_counter()
         eos.eval(L.P_FROM_RHO_T, rho, T, lam, nthreads=cores)
-        best = min(best, time.perf_counter() - t0)
-    out = {"value": sample / best / 1e9, "unit": UNIT, "cores": cores, "kind": "reference",
-           "sample": f"{sample} cells of the headline workload, best of {reps}, OpenMP over the "
-                     "reference vector API (PORTABILITY_STRATEGY_NONE), g++ -O2"}
-    # config 5 beside it: the reference PTESolverRhoT on 2^17 cells of the same workload
+        ts.append(time.perf_counter() - t0)
+    out = {"value": sample / float(np.median(ts)) / 1e9, "unit": UNIT, "cores": cores,
+           "kind": "reference",
+           "sample": f"{sample} cells of the headline workload, 2 warm-up + {reps} timed calls, "
+                     f"median; {how}"}
+    # config 5 beside it (BASELINE.md 3): the reference PTESolverRhoT on 2^22 cells of the same
+    # workload, 3 warm-up + up to 10 timed passes (stopping after ~60 s), median
     try:
         W = pkg.workloads
         r3 = ref.set_eos_3mat()
-        sie0 = [r3[m].eval(L.E_FROM_RHO_T, [W.PTE_RHO[m]], [W.PTE_T])[0] for m in range(3)]
-        npte = 1 << 17
+        sie0 = [r3[m].eval(L.E_FROM_RHO_T, [W.PTE_RHO[m]], [W.PTE_T], nthreads=1)[0]
+                for m in range(3)]
+        npte = 1 << 22
         st0 = W.pte_state_np(npte, sie0)
-        t0 = time.perf_counter()
-        ref.pte_solve(L.PTE_RHOT, r3, *[a.copy() for a in st0], pkg.closure.test_pte_params(),
-                      nthreads=cores)
-        dt = time.perf_counter() - t0
-        out["pte_rhot_cell_solves_per_s"] = npte / dt
-        out["pte_sample"] = f"{npte} cells, one pass, {cores} threads"
+        prm = pkg.closure.test_pte_params()
+        tp, t_begin = [], time.perf_counter()
+        for k in range(13):
+            st = [a.copy() for a in st0]
+            t0 = time.perf_counter()
+            ref.pte_solve(L.PTE_RHOT, r3, *st, prm, nthreads=cores)
+            if k >= 3:
+                tp.append(time.perf_counter() - t0)
+            if time.perf_counter() - t_begin > 60.0 and len(tp) >= 3:
+                break
+        out["pte_rhot_cell_solves_per_s"] = npte / float(np.median(tp))
+        out["pte_sample"] = (f"{npte} cells, 3 warm-up + {len(tp)} timed passes, median, "
+                             f"{cores} threads")
     except Exception as exc:  # the headline baseline stands on its own
         out["pte_error"] = repr(exc)
     # the other configs beside it (2^20-cell samples, best of 2), Gcells/s
@@ -592,35 +683,37 @@ def cpu_baseline(pkg, raw, sample, reps):
 
 
 def run_reference(args):
-    """--impl reference: the reference's CPU implementation of the headline path on all host
-    threads; each step is a bounded sample of the workload.  Rank 0 only."""
+    """--impl reference: the reference's own CPU implementation of the headline path (its
+    Kokkos-OpenMP build) on all host threads, on the GPU arm's configuration: every step is the
+    full 2^26-cell workload.  Rank 0 only."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     import __graft_entry__ as g
-    import oracle_ref
 
     pkg = g.load_package()
-    ref = oracle_ref.load()
+    cores = host_threads()
+    os.environ["OMP_NUM_THREADS"] = str(cores)
+    ref, how = baseline_ref()
     if ref is None:
         print(json.dumps({"impl": "reference",
-                          "unavailable": "oracle/_ref/libsgref.so not built"}), flush=True)
+                          "unavailable": "oracle/_ref/libsgref*.so not built"}), flush=True)
         return
     L = pkg._lib
     raw = pkg.tablegen.vinet_sp5_tables()
     eos = ref.SpinerRhoT(raw)
-    sample = 1 << 23
-    rho, T = pkg.workloads.spiner_inputs(sample)
-    lam = np.full((sample, 2), np.nan)
+    n = args.cells
+    rho, T = pkg.workloads.spiner_inputs(n)
+    lam = np.full((n, 2), np.nan)
     K, Wu = args.steps, max(args.warmup, 1)
-    cores = host_threads()
     for _ in range(Wu):
         eos.eval(L.P_FROM_RHO_T, rho, T, lam, nthreads=cores)
     t0 = time.perf_counter()
     for _ in range(K):
         eos.eval(L.P_FROM_RHO_T, rho, T, lam, nthreads=cores)
     secs = time.perf_counter() - t0
-    value = sample * K / secs / 1e9
+    value = n * K / secs / 1e9
+    world = args.gpus
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT,
         "n_gpus": args.gpus, "steps": K, "warmup": Wu, "ms_per_step": secs / K * 1e3,
@@ -628,9 +721,12 @@ def run_reference(args):
         "data": "synthetic",
         "config": {"workload": "SpinerEOSDependsRhoT PressureFromDensityTemperature, 256x256 "
                                "NQT-log table from analytic Vinet, lambda (lRho,lT) write-back",
-                   "cells_per_step": sample, "note": "bounded sample of the 2^26-cell workload"},
+                   "cells_per_gpu": n, "global_cells": n * world,
+                   "l2_policy": "inputs (1 GiB/GPU) larger than L2; no flush needed",
+                   "parallelism": f"cells sharded contiguously over {world} GPU(s), tables replicated"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference",
-                         "sample": f"{sample} cells per step"},
+                         "sample": f"{n} cells per step (one GPU's full shard of the workload) "
+                                   f"on the host: {how}"},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }

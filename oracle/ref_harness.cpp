@@ -47,7 +47,17 @@
 #include <omp.h>
 #endif
 
+// Second build of this file: oracle/_ref/libsgref_kokkos.so, -O3 -DNDEBUG with
+// PORTABILITY_STRATEGY_KOKKOS against the vendored Kokkos (utils/kokkos, OpenMP backend).  There
+// portableFor IS Kokkos::parallel_for (utils/ports-of-call/ports-of-call/portability.hpp:228-236),
+// so the timed baselines below hand the whole array to ONE reference vector call / ONE
+// portableFor over cells: the reference's Kokkos-OpenMP CPU path, not a loop of ours.
+#ifdef SGREF_KOKKOS
+#include <Kokkos_Core.hpp>
+#endif
+
 #include "../include/sgx_b200.h" // POD layouts only (sgx_sp5_tables, sgx_mix_params, enums)
+#include "sp5_tree.hpp"
 
 using namespace singularity;
 using DataBox = spiner_common::DataBox;
@@ -74,6 +84,19 @@ struct StridedAZLambda {
   }
 };
 
+#ifdef SGREF_KOKKOS
+void kokkos_init_once(int nthreads) {
+  if (Kokkos::is_initialized()) return;
+  Kokkos::InitializationSettings st;
+  if (nthreads > 0) st.set_num_threads(nthreads);
+  st.set_disable_warnings(true);
+  Kokkos::initialize(st);
+  std::atexit([] {
+    if (Kokkos::is_initialized() && !Kokkos::is_finalized()) Kokkos::finalize();
+  });
+}
+#endif
+
 int nthreads_for(int requested) {
 #ifdef _OPENMP
   return requested > 0 ? requested : omp_get_max_threads();
@@ -83,106 +106,7 @@ int nthreads_for(int requested) {
 #endif
 }
 
-// ---- .sp5 tree builder ------------------------------------------------------------
-void put_grid(h5shim::Node *grids, int axis_k /*1-based*/, const sgx_grid1d &g) {
-  const std::string name = "grid_[" + std::to_string(axis_k) + "]";
-  auto put_regular = [](h5shim::Node *parent, const std::string &nm, double mn, double mx,
-                        double dx, int np) {
-    const double range[3] = {mn, mx, dx};
-    h5shim::set_dataset(parent, nm, range, 3);
-    h5shim::set_attr_int(parent->child(nm, false), "npoints", {np});
-  };
-  if (g.ngrids == 1) {
-    put_regular(grids, name, g.min[0], g.max[0], g.dx[0], g.npoints[0]);
-  } else {
-    h5shim::Node *grp = grids->child(name, true);
-    h5shim::set_attr_int(grp, "ngrids", {g.ngrids});
-    for (int p = 0; p < g.ngrids; ++p) {
-      put_regular(grp, "patch_[" + std::to_string(p + 1) + "]", g.min[p], g.max[p], g.dx[p],
-                  g.npoints[p]);
-    }
-  }
-}
-int grid_total(const sgx_grid1d &g) {
-  int n = 0;
-  for (int p = 0; p < g.ngrids; ++p)
-    n += g.npoints[p];
-  return n;
-}
-// rank-2 databox: dims (fastest first) = {n_fast, n_slow}
-void put_db2(h5shim::Node *parent, const char *name, const double *data,
-             const sgx_grid1d &fast, const sgx_grid1d &slow) {
-  if (data == nullptr) return;
-  h5shim::Node *db = parent->child(name, true);
-  const int nf = grid_total(fast), ns = grid_total(slow);
-  h5shim::set_attr_int(db, "rank", {2});
-  h5shim::set_attr_int(db, "dims", {nf, ns});
-  h5shim::set_attr_int(db, "index_types", {0, 0});
-  h5shim::set_dataset(db, "data", data, static_cast<std::size_t>(nf) * ns);
-  h5shim::Node *grids = db->child("grids", true);
-  put_grid(grids, 1, fast);
-  put_grid(grids, 2, slow);
-}
-void put_db1(h5shim::Node *parent, const char *name, const double *data,
-             const sgx_grid1d &g) {
-  if (data == nullptr) return;
-  h5shim::Node *db = parent->child(name, true);
-  const int n = grid_total(g);
-  h5shim::set_attr_int(db, "rank", {1});
-  h5shim::set_attr_int(db, "dims", {n});
-  h5shim::set_attr_int(db, "index_types", {0});
-  h5shim::set_dataset(db, "data", data, n);
-  h5shim::Node *grids = db->child("grids", true);
-  put_grid(grids, 1, g);
-}
-
-int g_file_counter = 0;
-
-std::string build_sp5(const sgx_sp5_tables *raw, int matid) {
-  // the constructors insist the path exists on disk (eos_spiner_common.hpp:128-134)
-  std::string fname = "/tmp/sgx_oracle_" + std::to_string(::getpid()) + "_" +
-                      std::to_string(g_file_counter++) + ".sp5";
-  { std::ofstream touch(fname); }
-  h5shim::drop_file(fname);
-  h5shim::Node *root = h5shim::file_root(fname, true);
-  h5shim::set_attr_int(root, SP5::logType, {static_cast<int>(FastMath::Settings::log_type)});
-  h5shim::Node *mat = root->child(std::to_string(matid), true);
-  h5shim::set_attr_double(mat, SP5::Offsets::rho, raw->rho_offset);
-  h5shim::set_attr_double(mat, SP5::Offsets::T, raw->T_offset);
-  h5shim::set_attr_double(mat, SP5::Offsets::sie, raw->sie_offset);
-  h5shim::set_attr_double(mat, SP5::Material::normalDensity, raw->normal_density);
-  h5shim::set_attr_double(mat, SP5::Material::meanAtomicMass, raw->mean_atomic_mass);
-  h5shim::set_attr_double(mat, SP5::Material::meanAtomicNumber, raw->mean_atomic_number);
-  h5shim::set_attr_int(mat, SP5::Material::matid, {matid});
-
-  h5shim::Node *lT = mat->child(SP5::Depends::logRhoLogT, true);
-  put_db2(lT, SP5::Fields::P, raw->P, raw->lT, raw->lrho);
-  put_db2(lT, SP5::Fields::sie, raw->sie, raw->lT, raw->lrho);
-  put_db2(lT, SP5::Fields::bMod, raw->bMod, raw->lT, raw->lrho);
-  put_db2(lT, SP5::Fields::dPdRho, raw->dPdRho, raw->lT, raw->lrho);
-  put_db2(lT, SP5::Fields::dPdE, raw->dPdE, raw->lT, raw->lrho);
-  put_db2(lT, SP5::Fields::dTdRho, raw->dTdRho, raw->lT, raw->lrho);
-  put_db2(lT, SP5::Fields::dTdE, raw->dTdE, raw->lT, raw->lrho);
-  put_db2(lT, SP5::Fields::dEdRho, raw->dEdRho, raw->lT, raw->lrho);
-  put_db2(lT, SP5::Fields::dEdT, raw->dEdT, raw->lT, raw->lrho);
-
-  h5shim::Node *lE = mat->child(SP5::Depends::logRhoLogSie, true);
-  put_db2(lE, SP5::Fields::T, raw->T_re, raw->lE, raw->lrho);
-  put_db2(lE, SP5::Fields::P, raw->P_re, raw->lE, raw->lrho);
-  put_db2(lE, SP5::Fields::bMod, raw->bMod_re, raw->lE, raw->lrho);
-  put_db2(lE, SP5::Fields::dPdRho, raw->dPdRho_re, raw->lE, raw->lrho);
-  put_db2(lE, SP5::Fields::dPdE, raw->dPdE_re, raw->lE, raw->lrho);
-  put_db2(lE, SP5::Fields::dTdRho, raw->dTdRho_re, raw->lE, raw->lrho);
-  put_db2(lE, SP5::Fields::dTdE, raw->dTdE_re, raw->lE, raw->lrho);
-  put_db2(lE, SP5::Fields::dEdRho, raw->dEdRho_re, raw->lE, raw->lrho);
-
-  h5shim::Node *cold = mat->child(SP5::Depends::coldCurve, true);
-  put_db1(cold, SP5::Fields::P, raw->PCold, raw->lrho);
-  put_db1(cold, SP5::Fields::sie, raw->sieCold, raw->lrho);
-  put_db1(cold, SP5::Fields::bMod, raw->bModCold, raw->lrho);
-  put_db1(cold, SP5::Fields::dPdRho, raw->dPdRhoCold, raw->lrho);
-  return fname;
-}
+using sgx_oracle::build_sp5;
 
 template <typename F>
 int guarded(F &&f) {
@@ -210,6 +134,15 @@ extern "C" {
 
 int ref_abi_version() { return SGX_ABI_VERSION; }
 int ref_num_threads() { return nthreads_for(0); }
+// 1 when this library is the Kokkos-OpenMP build (timed baselines), 0 for the serial-portableFor
+// build used as the parity oracle
+int ref_is_kokkos() {
+#ifdef SGREF_KOKKOS
+  return 1;
+#else
+  return 0;
+#endif
+}
 
 // ---- FastMath (base/fast-math/logs.hpp) -----------------------------------------
 void ref_fastmath_eval(int which, const double *x, double *y, int64_t n) {
@@ -428,9 +361,63 @@ int ref_eos_get_scalar(void *h, const char *name, double *out) {
 // method: enum sgx_method.  The array is cut into one chunk per OpenMP thread; each chunk is
 // ONE call of the reference vector overload with Exec::Host() on a thread-private copy of the
 // (shallow, trivially copyable) EOS object.
+extern "C++" {
+namespace {
+template <class Lam, class... Lead>
+void dispatch_method(EOS &local, int method, const double *a, const double *b, double *o,
+                     int cnt, Lam &lam, Lead &&...lead) {
+  switch (method) {
+  case SGX_P_FROM_RHO_T:
+    local.PressureFromDensityTemperature(lead..., a, b, o, cnt, lam);
+    break;
+  case SGX_E_FROM_RHO_T:
+    local.InternalEnergyFromDensityTemperature(lead..., a, b, o, cnt, lam);
+    break;
+  case SGX_T_FROM_RHO_E:
+    local.TemperatureFromDensityInternalEnergy(lead..., a, b, o, cnt, lam);
+    break;
+  case SGX_P_FROM_RHO_E:
+    local.PressureFromDensityInternalEnergy(lead..., a, b, o, cnt, lam);
+    break;
+  case SGX_CV_FROM_RHO_T:
+    local.SpecificHeatFromDensityTemperature(lead..., a, b, o, cnt, lam);
+    break;
+  case SGX_CV_FROM_RHO_E:
+    local.SpecificHeatFromDensityInternalEnergy(lead..., a, b, o, cnt, lam);
+    break;
+  case SGX_BMOD_FROM_RHO_T:
+    local.BulkModulusFromDensityTemperature(lead..., a, b, o, cnt, lam);
+    break;
+  case SGX_BMOD_FROM_RHO_E:
+    local.BulkModulusFromDensityInternalEnergy(lead..., a, b, o, cnt, lam);
+    break;
+  case SGX_GAMMA_FROM_RHO_T:
+    local.GruneisenParamFromDensityTemperature(lead..., a, b, o, cnt, lam);
+    break;
+  case SGX_GAMMA_FROM_RHO_E:
+    local.GruneisenParamFromDensityInternalEnergy(lead..., a, b, o, cnt, lam);
+    break;
+  default:
+    throw std::runtime_error("bad method");
+  }
+}
+} // namespace
+} // extern "C++"
+
 int ref_eos_eval(void *h, int method, const double *in1, const double *in2, double *out,
                  int64_t n, double *lambda, int lambda_stride, int nthreads) {
   const EOS *eos = static_cast<const EOS *>(h);
+#ifdef SGREF_KOKKOS
+  { // the whole array in one call of the reference's vector overload (Kokkos::parallel_for)
+    kokkos_init_once(nthreads);
+    EOS local = *eos;
+    StridedLambda lam{lambda, lambda_stride};
+    return guarded([&]() {
+      dispatch_method(local, method, in1, in2, out, static_cast<int>(n), lam);
+      Kokkos::fence();
+    });
+  }
+#endif
   const int nt = nthreads_for(nthreads);
   int rc = 0;
 #pragma omp parallel for num_threads(nt) schedule(static)
@@ -443,42 +430,7 @@ int ref_eos_eval(void *h, int method, const double *in1, const double *in2, doub
     double *o = out + lo;
     StridedLambda lam{lambda ? lambda + lo * lambda_stride : nullptr, lambda_stride};
     auto host = PortsOfCall::Exec::Host();
-    int lrc = guarded([&]() {
-      switch (method) {
-      case SGX_P_FROM_RHO_T:
-        local.PressureFromDensityTemperature(host, a, b, o, cnt, lam);
-        break;
-      case SGX_E_FROM_RHO_T:
-        local.InternalEnergyFromDensityTemperature(host, a, b, o, cnt, lam);
-        break;
-      case SGX_T_FROM_RHO_E:
-        local.TemperatureFromDensityInternalEnergy(host, a, b, o, cnt, lam);
-        break;
-      case SGX_P_FROM_RHO_E:
-        local.PressureFromDensityInternalEnergy(host, a, b, o, cnt, lam);
-        break;
-      case SGX_CV_FROM_RHO_T:
-        local.SpecificHeatFromDensityTemperature(host, a, b, o, cnt, lam);
-        break;
-      case SGX_CV_FROM_RHO_E:
-        local.SpecificHeatFromDensityInternalEnergy(host, a, b, o, cnt, lam);
-        break;
-      case SGX_BMOD_FROM_RHO_T:
-        local.BulkModulusFromDensityTemperature(host, a, b, o, cnt, lam);
-        break;
-      case SGX_BMOD_FROM_RHO_E:
-        local.BulkModulusFromDensityInternalEnergy(host, a, b, o, cnt, lam);
-        break;
-      case SGX_GAMMA_FROM_RHO_T:
-        local.GruneisenParamFromDensityTemperature(host, a, b, o, cnt, lam);
-        break;
-      case SGX_GAMMA_FROM_RHO_E:
-        local.GruneisenParamFromDensityInternalEnergy(host, a, b, o, cnt, lam);
-        break;
-      default:
-        throw std::runtime_error("bad method");
-      }
-    });
+    int lrc = guarded([&]() { dispatch_method(local, method, a, b, o, cnt, lam, host); });
     if (lrc != 0) {
 #pragma omp atomic write
       rc = -1;
@@ -487,11 +439,73 @@ int ref_eos_eval(void *h, int method, const double *in1, const double *in2, doub
   return rc;
 }
 
+// The remaining vector-surface members, applied per cell through the Variant's scalar forwards:
+// op 0 MinInternalEnergyFromDensity, 1 InternalEnergyFromDensityPressure (no-guess form,
+// eos_base.hpp:709-721), 2/3 EntropyFromDensity{Temperature,InternalEnergy}, 4/5
+// GibbsFreeEnergyFromDensity{Temperature,InternalEnergy}, 6 DensityEnergyFromPressureTemperature
+// (out1 = rho in/out, out2 = sie).
+int ref_eos_eval_extra(void *h, int op, const double *in1, const double *in2, double *out1,
+                       double *out2, int64_t n, double *lambda, int lambda_stride) {
+  const EOS *eos = static_cast<const EOS *>(h);
+  return guarded([&]() {
+    if (op == 1) { // only the vector overload reaches the no-guess form through the Variant
+      StridedLambda lam{lambda, lambda_stride};
+      eos->InternalEnergyFromDensityPressure(PortsOfCall::Exec::Host(), in1, in2, out1,
+                                             static_cast<int>(n), lam);
+      return;
+    }
+    for (int64_t i = 0; i < n; ++i) {
+      Real *lam = lambda ? lambda + i * lambda_stride : nullptr;
+      switch (op) {
+      case 0:
+        out1[i] = eos->MinInternalEnergyFromDensity(in1[i], lam);
+        break;
+      case 2:
+        out1[i] = eos->EntropyFromDensityTemperature(in1[i], in2[i], lam);
+        break;
+      case 3:
+        out1[i] = eos->EntropyFromDensityInternalEnergy(in1[i], in2[i], lam);
+        break;
+      case 4:
+        out1[i] = eos->GibbsFreeEnergyFromDensityTemperature(in1[i], in2[i], lam);
+        break;
+      case 5:
+        out1[i] = eos->GibbsFreeEnergyFromDensityInternalEnergy(in1[i], in2[i], lam);
+        break;
+      case 6: {
+        Real rho = out1[i], sie = 0.0;
+        eos->DensityEnergyFromPressureTemperature(in1[i], in2[i], lam, rho, sie);
+        out1[i] = rho;
+        out2[i] = sie;
+      } break;
+      default:
+        throw std::runtime_error("bad op");
+      }
+    }
+  });
+}
+
 // FillEos vector overload.  az_only != 0 => type-indexed {Abar,Zbar} lambda (no lT slot).
 int ref_eos_fill(void *h, double *rho, double *T, double *e, double *P, double *cv,
                  double *bmod, int64_t n, unsigned long output, double *lambda,
                  int lambda_stride, int az_only, int nthreads) {
   const EOS *eos = static_cast<const EOS *>(h);
+#ifdef SGREF_KOKKOS
+  { // one call of the reference's FillEos vector overload over the whole array
+    kokkos_init_once(nthreads);
+    EOS local = *eos;
+    return guarded([&]() {
+      if (az_only) {
+        StridedAZLambda lam{lambda, lambda_stride};
+        local.FillEos(rho, T, e, P, cv, bmod, static_cast<int>(n), output, lam);
+      } else {
+        StridedLambda lam{lambda, lambda_stride};
+        local.FillEos(rho, T, e, P, cv, bmod, static_cast<int>(n), output, lam);
+      }
+      Kokkos::fence();
+    });
+  }
+#endif
   const int nt = nthreads_for(nthreads);
   int rc = 0;
 #pragma omp parallel for num_threads(nt) schedule(static)
@@ -608,82 +622,115 @@ void ref_mix_params_default(sgx_mix_params *p) {
   p->pte_reduced_system_exclude_idx = m.pte_reduced_system_exclude_idx;
 }
 
+namespace {
+// One cell of the loop of test/test_pte.cpp:177-265.
+struct PteArgs {
+  int solver, nmat;
+  double *rho, *vfrac, *sie, *temp, *press;
+  const double *sie_tot_in, *vfrac_tot_in, *Tguess_in;
+  uint64_t *status;
+  double *residual, *Tguess_out;
+};
+inline int pte_one_cell(const PteArgs &A, const MixParams &mp, const EosIndexer &eos,
+                        double *scratch, const int64_t t) {
+  const int nmat = A.nmat;
+  NullIndexer lambda;
+  RowIndexer r{A.rho + t * nmat}, vf{A.vfrac + t * nmat}, e{A.sie + t * nmat},
+      tp{A.temp + t * nmat}, pr{A.press + t * nmat};
+  Real sie_tot = 0.0, rho_tot = 0.0;
+  for (int i = 0; i < nmat; i++) { // test/test_pte.cpp:188-195
+    const Real rhobar = r[i] * vf[i];
+    rho_tot += rhobar;
+    sie_tot += rhobar * e[i];
+  }
+  sie_tot /= rho_tot;
+  if (A.sie_tot_in) sie_tot = A.sie_tot_in[t];
+  const Real vfrac_tot = A.vfrac_tot_in ? A.vfrac_tot_in[t] : 1.0;
+  Real Tguess;
+  if (A.Tguess_in) {
+    Tguess = A.Tguess_in[t];
+  } else {
+    Tguess = ApproxTemperatureFromRhoMatU(nmat, eos, rho_tot * sie_tot, r, vf);
+  }
+  if (A.Tguess_out) A.Tguess_out[t] = Tguess;
+  SolverStatus st;
+  std::size_t niter = 0;
+  const int solver = A.solver;
+  int lrc = guarded([&]() {
+    if (solver == SGX_PTE_RHOT) {
+      PTESolverRhoT<EosIndexer, RowIndexer, NullIndexer> method(
+          nmat, eos, vfrac_tot, sie_tot, r, vf, e, tp, pr, lambda, scratch, Tguess, mp);
+      st = PTESolver(method);
+      niter = method.Niter();
+    } else if (solver == SGX_PTE_RHOU) {
+      PTESolverRhoU<EosIndexer, RowIndexer, NullIndexer> method(
+          nmat, eos, vfrac_tot, sie_tot, r, vf, e, tp, pr, lambda, scratch, Tguess, mp);
+      st = PTESolver(method);
+      niter = method.Niter();
+    } else if (solver == SGX_PTE_FIXED_T) {
+      PTESolverFixedT<EosIndexer, RowIndexer, NullIndexer> method(
+          nmat, eos, vfrac_tot, Tguess /* T_true */, r, vf, e, tp, pr, lambda, scratch, mp);
+      st = PTESolver(method);
+      niter = method.Niter();
+    } else {
+      PTESolverPT<EosIndexer, RowIndexer, NullIndexer> method(
+          nmat, eos, vfrac_tot, sie_tot, r, vf, e, tp, pr, lambda, scratch, Tguess, mp);
+      st = PTESolver(method);
+      niter = method.Niter();
+    }
+  });
+  if (A.status) A.status[t] = pack_status(st, niter);
+  if (A.residual) A.residual[t] = st.residual;
+  return lrc;
+}
+} // namespace
+
 int ref_pte_solve(int solver, void **eos_handles, int nmat, int64_t ncell, double *rho,
                   double *vfrac, double *sie, double *temp, double *press,
                   const double *sie_tot_in, const double *vfrac_tot_in,
                   const double *Tguess_in, const sgx_mix_params *params, uint64_t *status,
                   double *residual, double *Tguess_out, int nthreads) {
   const MixParams mp = to_params(params);
-  const int nt = nthreads_for(nthreads);
   std::vector<EOS> eos_vec(nmat);
   for (int m = 0; m < nmat; ++m)
     eos_vec[m] = *static_cast<EOS *>(eos_handles[m]);
+  const PteArgs A{solver, nmat, rho, vfrac, sie, temp, press, sie_tot_in, vfrac_tot_in,
+                  Tguess_in, status, residual, Tguess_out};
+  const int nscr = (int)std::max<std::size_t>(
+      std::max<std::size_t>(PTESolverRhoTRequiredScratch(nmat), PTESolverPTRequiredScratch(nmat)),
+      std::max<std::size_t>(PTESolverFixedTRequiredScratch(nmat),
+                            PTESolverRhoURequiredScratch(nmat)));
+#ifdef SGREF_KOKKOS
+  { // the reference test's own shape: one portableFor over cells, per-cell scratch slices
+    // (test/test_pte.cpp:146-150,177: `scratch + nscratch_vars * t`)
+    kokkos_init_once(nthreads);
+    std::vector<double> scratch_all(static_cast<std::size_t>(ncell) * nscr);
+    double *scr = scratch_all.data();
+    EOS *eos_p = eos_vec.data();
+    int nfail = 0;
+    portableReduce(
+        "PTE", 0, static_cast<int>(ncell),
+        PORTABLE_LAMBDA(const int t, int &nf) {
+          EosIndexer eos{eos_p};
+          nf += pte_one_cell(A, mp, eos, scr + static_cast<std::size_t>(t) * nscr, t) != 0;
+        },
+        nfail);
+    return nfail ? -1 : 0;
+  }
+#endif
+  const int nt = nthreads_for(nthreads);
   int rc = 0;
 #pragma omp parallel num_threads(nt)
   {
     std::vector<EOS> eos_local(eos_vec);
     EosIndexer eos{eos_local.data()};
-    const int nscr = (int)std::max<std::size_t>(
-        std::max<std::size_t>(PTESolverRhoTRequiredScratch(nmat), PTESolverPTRequiredScratch(nmat)),
-        std::max<std::size_t>(PTESolverFixedTRequiredScratch(nmat),
-                              PTESolverRhoURequiredScratch(nmat)));
     std::vector<double> scratch(nscr);
 #pragma omp for schedule(dynamic, 256)
     for (int64_t t = 0; t < ncell; ++t) {
-      NullIndexer lambda;
-      RowIndexer r{rho + t * nmat}, vf{vfrac + t * nmat}, e{sie + t * nmat},
-          tp{temp + t * nmat}, pr{press + t * nmat};
-      Real sie_tot = 0.0, rho_tot = 0.0;
-      for (int i = 0; i < nmat; i++) { // test/test_pte.cpp:188-195
-        const Real rhobar = r[i] * vf[i];
-        rho_tot += rhobar;
-        sie_tot += rhobar * e[i];
-      }
-      sie_tot /= rho_tot;
-      if (sie_tot_in) sie_tot = sie_tot_in[t];
-      const Real vfrac_tot = vfrac_tot_in ? vfrac_tot_in[t] : 1.0;
-      Real Tguess;
-      if (Tguess_in) {
-        Tguess = Tguess_in[t];
-      } else {
-        Tguess = ApproxTemperatureFromRhoMatU(nmat, eos, rho_tot * sie_tot, r, vf);
-      }
-      if (Tguess_out) Tguess_out[t] = Tguess;
-      SolverStatus st;
-      std::size_t niter = 0;
-      int lrc = guarded([&]() {
-        if (solver == SGX_PTE_RHOT) {
-          PTESolverRhoT<EosIndexer, RowIndexer, NullIndexer> method(
-              nmat, eos, vfrac_tot, sie_tot, r, vf, e, tp, pr, lambda, scratch.data(), Tguess,
-              mp);
-          st = PTESolver(method);
-          niter = method.Niter();
-        } else if (solver == SGX_PTE_RHOU) {
-          PTESolverRhoU<EosIndexer, RowIndexer, NullIndexer> method(
-              nmat, eos, vfrac_tot, sie_tot, r, vf, e, tp, pr, lambda, scratch.data(), Tguess,
-              mp);
-          st = PTESolver(method);
-          niter = method.Niter();
-        } else if (solver == SGX_PTE_FIXED_T) {
-          PTESolverFixedT<EosIndexer, RowIndexer, NullIndexer> method(
-              nmat, eos, vfrac_tot, Tguess /* T_true */, r, vf, e, tp, pr, lambda,
-              scratch.data(), mp);
-          st = PTESolver(method);
-          niter = method.Niter();
-        } else {
-          PTESolverPT<EosIndexer, RowIndexer, NullIndexer> method(
-              nmat, eos, vfrac_tot, sie_tot, r, vf, e, tp, pr, lambda, scratch.data(), Tguess,
-              mp);
-          st = PTESolver(method);
-          niter = method.Niter();
-        }
-      });
-      if (lrc != 0) {
+      if (pte_one_cell(A, mp, eos, scratch.data(), t) != 0) {
 #pragma omp atomic write
         rc = -1;
       }
-      if (status) status[t] = pack_status(st, niter);
-      if (residual) residual[t] = st.residual;
     }
   }
   return rc;

@@ -157,6 +157,14 @@ PROTOTYPES = {
     "sgx_fastmath_eval": (C.c_int, [C.c_int, _VP, _VP, _I64, _VP]),
     "sgx_libm_eval": (C.c_int, [C.c_int, _VP, _VP, _VP, _I64, _VP]),
     "sgx_eos_root_stats": (C.c_int, [_VP, C.POINTER(C.c_uint64), C.c_int]),
+    "sgx_eos_retain": (C.c_int, [_VP]),
+    "sgx_MinInternalEnergyFromDensity": (C.c_int, [_VP, _VP, _VP, _I64, _VP, C.c_int, _VP]),
+    "sgx_InternalEnergyFromDensityPressure": (C.c_int, [_VP, _VP, _VP, _VP, _I64, _VP, C.c_int, _VP]),
+    "sgx_EntropyFromDensityTemperature": (C.c_int, [_VP, _VP, _VP, _VP, _I64, _VP, C.c_int, _VP]),
+    "sgx_EntropyFromDensityInternalEnergy": (C.c_int, [_VP, _VP, _VP, _VP, _I64, _VP, C.c_int, _VP]),
+    "sgx_GibbsFreeEnergyFromDensityTemperature": (C.c_int, [_VP, _VP, _VP, _VP, _I64, _VP, C.c_int, _VP]),
+    "sgx_GibbsFreeEnergyFromDensityInternalEnergy": (C.c_int, [_VP, _VP, _VP, _VP, _I64, _VP, C.c_int, _VP]),
+    "sgx_DensityEnergyFromPressureTemperature": (C.c_int, [_VP, _VP, _VP, _VP, _VP, _I64, _VP, C.c_int, _VP]),
     "sgx_solve_Ax_b": (C.c_int, [C.c_int, _VP, _VP, _VP, _I64, _VP]),
     "sgx_comm_unique_id": (C.c_int, [C.c_char_p]),
     "sgx_comm_create": (C.c_int, [C.c_char_p, C.c_int, C.c_int, C.POINTER(_VP)]),

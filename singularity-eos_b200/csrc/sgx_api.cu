@@ -531,6 +531,21 @@ int launch_pe(const EOS &eos, const double *rho, const double *T, double *P, dou
   return SGX_OK;
 }
 
+// Lambda slots a row must hold: nlambda(), except a Helmholtz built for type-indexed
+// {Abar, Zbar} lambdas (no LogTemperature slot), which uses 2 of the 3.
+static int lambda_need(const sgx_eos_s *e) {
+  switch (e->kind) {
+  case SGX_EOS_SPINER_RHOT:
+    return 2;
+  case SGX_EOS_SPINER_RHOSIE:
+    return 1;
+  case SGX_EOS_HELMHOLTZ:
+    return e->helm.lambda_has_lT_slot ? 3 : 2;
+  default:
+    return 0;
+  }
+}
+
 static int check_handle(sgx_eos_t e) {
   if (!e) return fail(SGX_ERR_INVALID, "null EOS handle");
   cudaError_t err = cudaSetDevice(e->device);
@@ -775,8 +790,15 @@ int sgx_eos_create_helmholtz(const char *table_path, const sgx_helm_options *opt
   return SGX_OK;
 }
 
+int sgx_eos_retain(sgx_eos_t e) {
+  if (!e) return fail(SGX_ERR_INVALID, "null EOS handle");
+  e->refs.fetch_add(1, std::memory_order_relaxed);
+  return SGX_OK;
+}
+
 int sgx_eos_destroy(sgx_eos_t e) {
   if (!e) return SGX_OK;
+  if (e->refs.fetch_sub(1, std::memory_order_acq_rel) > 1) return SGX_OK; // still shared
   DeviceGuard guard;
   cudaSetDevice(e->device);
   if (e->tables.dev) cudaFree(e->tables.dev);
@@ -856,9 +878,9 @@ int sgx_eos_eval(sgx_eos_t e, int method, const double *in1, const double *in2, 
   if (n < 0) return fail(SGX_ERR_INVALID, "negative n");
   if (n == 0) return SGX_OK;
   if (!in1 || !in2 || !out) return fail(SGX_ERR_INVALID, "null array");
-  if (lambda && lambda_stride < sgx_eos_nlambda(e))
-    return fail(SGX_ERR_INVALID, "lambda_stride %d < nlambda %d", lambda_stride,
-                sgx_eos_nlambda(e));
+  if (lambda && lambda_stride < lambda_need(e))
+    return fail(SGX_ERR_INVALID, "lambda_stride %d < %d slots this EOS uses", lambda_stride,
+                lambda_need(e));
   cudaStream_t s = (cudaStream_t)stream;
   switch (e->kind) {
   case SGX_EOS_IDEAL:
@@ -915,8 +937,8 @@ int sgx_PressureEnergyFromDensityTemperature(sgx_eos_t e, const double *rhos,
   if (rc) return rc;
   if (n <= 0) return n == 0 ? SGX_OK : fail(SGX_ERR_INVALID, "negative n");
   if (!rhos || !temps || !P || !E) return fail(SGX_ERR_INVALID, "null array");
-  if (lambda && ls < sgx_eos_nlambda(e))
-    return fail(SGX_ERR_INVALID, "lambda_stride %d < nlambda %d", ls, sgx_eos_nlambda(e));
+  if (lambda && ls < lambda_need(e))
+    return fail(SGX_ERR_INVALID, "lambda_stride %d < %d slots this EOS uses", ls, lambda_need(e));
   cudaStream_t s = (cudaStream_t)stream;
   switch (e->kind) {
   case SGX_EOS_IDEAL:
@@ -944,8 +966,9 @@ int sgx_FillEos(sgx_eos_t e, double *rhos, double *temps, double *energies, doub
   if (rc) return rc;
   if (n <= 0) return n == 0 ? SGX_OK : fail(SGX_ERR_INVALID, "negative n");
   if (output == 0) return fail(SGX_ERR_UNSUPPORTED, "FillEos: output == thermalqs::none");
-  if (lambda && ls < sgx_eos_nlambda(e))
-    return fail(SGX_ERR_INVALID, "lambda_stride %d < nlambda %d", ls, sgx_eos_nlambda(e));
+  // (Helmholtz checks its own row width: 2 or 3 slots, launch_helm_fill)
+  if (lambda && ls < lambda_need(e))
+    return fail(SGX_ERR_INVALID, "lambda_stride %d < %d slots this EOS uses", ls, lambda_need(e));
   cudaStream_t s = (cudaStream_t)stream;
   switch (e->kind) {
   case SGX_EOS_IDEAL:
@@ -1044,8 +1067,8 @@ int sgx_eos_eval_host(sgx_eos_t e, int method, const double *in1, const double *
   if (rc) return rc;
   if (n <= 0) return n == 0 ? SGX_OK : fail(SGX_ERR_INVALID, "negative n");
   if (!in1 || !in2 || !out) return fail(SGX_ERR_INVALID, "null array");
-  if (lambda && ls < sgx_eos_nlambda(e))
-    return fail(SGX_ERR_INVALID, "lambda_stride %d < nlambda %d", ls, sgx_eos_nlambda(e));
+  if (lambda && ls < lambda_need(e))
+    return fail(SGX_ERR_INVALID, "lambda_stride %d < %d slots this EOS uses", ls, lambda_need(e));
   bool lam_in = false, lam_out = false;
   if (lambda) lambda_io(e, method, ls, lam_in, lam_out);
   const bool lam_dev = lam_in || lam_out; // rows that never cross the bus are not given to the kernel
@@ -1090,8 +1113,8 @@ int sgx_FillEos_host(sgx_eos_t e, double *rhos, double *temps, double *energies,
   int rc = check_handle(e);
   if (rc) return rc;
   if (n <= 0) return n == 0 ? SGX_OK : fail(SGX_ERR_INVALID, "negative n");
-  if (lambda && ls < sgx_eos_nlambda(e))
-    return fail(SGX_ERR_INVALID, "lambda_stride %d < nlambda %d", ls, sgx_eos_nlambda(e));
+  if (lambda && ls < lambda_need(e))
+    return fail(SGX_ERR_INVALID, "lambda_stride %d < %d slots this EOS uses", ls, lambda_need(e));
   // same chunk pipeline as sgx_eos_eval_host: kHostSlots device slots, one stream each
   const int64_t chunk = n < kHostChunk ? n : kHostChunk;
   const size_t per_cell = (size_t)(6 + (lambda ? ls : 0)) * sizeof(double);

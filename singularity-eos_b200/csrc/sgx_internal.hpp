@@ -99,6 +99,7 @@ struct TableStore {
 } // namespace sgx
 
 struct sgx_eos_s {
+  std::atomic<int> refs{1}; // sgx_eos_retain / sgx_eos_destroy
   int kind = -1;
   int device = 0;
   sgx::AnyEos analytic;    // kinds 0-3
@@ -146,6 +147,29 @@ int launch_pte_rhou(const EosSet &set, bool bench_mix, const MixParamsDev &prm, 
                     const double *sie_tot, const double *vfrac_tot, const double *Tguess,
                     uint64_t *status, double *residual, uint64_t *stats, int64_t ncell,
                     cudaStream_t s);
+// Search hint of the direct T(rho, sie) inversion (sgx_spiner_root.cu).  Per density row j:
+// base = sie(j, 0), s = sie(j, 1) - sie(j, 0); per pair (j, j+1), stored with row j: umin, inv_du.
+// A cell's energy is binned in the coordinate of ITS blended row,
+//     u = log10_nqt(max(e - base_b, 0) + s_b),  base_b = w0 base_j + w1 base_j+1,  s_b likewise,
+// i.e. relative to where the blended row starts: rows of neighbouring densities differ mostly by
+// a shift (the cold curve), so in this coordinate the bracketing table cell barely depends on
+// the blend weight and "sie#hint"[pair][bin] = lo | hi << 16 is 3-4 cells wide.
+// inv_du == 0 marks a pair that is not strictly monotone in T (no direct inversion).
+struct RootRowMeta {
+  double base, s, umin, inv_du;
+};
+constexpr int kRootHintBins = 512;
+// ONE definition for the host code that fills the table and the kernel that reads it (integer
+// NQT log, no FMA on either side: identical bins)
+SGX_HD int root_hint_bin(const double base, const double s, const double umin,
+                         const double inv_du, const double e) {
+  double arg = e - base;
+  arg = arg < 0.0 ? 0.0 : arg;
+  const double u = fastmath::log10(arg + s);
+  int k = (int)((u - umin) * inv_du);
+  return k < 0 ? 0 : (k >= kRootHintBins ? kRootHintBins - 1 : k);
+}
+
 // SpinerRhoT T(rho, e): direct inversion + reference iterate for the listed cells
 // (sgx_spiner_root.cu).  root_mode(): 0 hybrid (default), 1 exact, 2 direct (SGX_ROOT_MODE).
 int root_mode();

@@ -18,8 +18,9 @@ static bool percell_variant() {
 }
 
 // Cells go through in chunks: init kernel -> scratch record -> state-machine kernel, both on
-// the caller's stream; the scratch is stream-ordered (cudaMallocAsync), (2*NM+1)*8 B/cell.
-static constexpr int64_t kPteChunk = int64_t(1) << 22;
+// the caller's stream; the scratch is stream-ordered (cudaMallocAsync): (2*NM+1)*8 B/cell for the
+// hand-over record plus one 64-bit cell cursor per chunk.
+static constexpr int64_t kPteChunk = int64_t(1) << 23;
 
 template <int NM, class Acc, int THREADS = kSmThreads, int MINB = 1>
 static int launch_sm(const EosSet &set, const MixParamsDev &prm, double *rho, double *vfrac,
@@ -27,9 +28,16 @@ static int launch_sm(const EosSet &set, const MixParamsDev &prm, double *rho, do
                      const double *vfrac_tot, const double *Tguess, uint64_t *status,
                      double *residual, uint64_t *stats, int64_t ncell, cudaStream_t s) {
   const int64_t chunk = ncell < kPteChunk ? ncell : kPteChunk;
-  double *init = nullptr;
-  SGX_CUDA_OK(cudaMallocAsync(&init, (size_t)chunk * (2 * NM + 1) * sizeof(double), s));
-  for (int64_t c0 = 0; c0 < ncell; c0 += chunk) {
+  const int64_t nchunk = (ncell + chunk - 1) / chunk;
+  const size_t cursor_bytes = ((size_t)nchunk * sizeof(unsigned long long) + 255) & ~size_t(255);
+  char *scratch = nullptr;
+  SGX_CUDA_OK(cudaMallocAsync(
+      &scratch, cursor_bytes + (size_t)chunk * (2 * NM + 1) * sizeof(double), s));
+  unsigned long long *cursors = reinterpret_cast<unsigned long long *>(scratch);
+  double *init = reinterpret_cast<double *>(scratch + cursor_bytes);
+  cudaError_t err = cudaMemsetAsync(cursors, 0, cursor_bytes, s);
+  int64_t k = 0;
+  for (int64_t c0 = 0; c0 < ncell && err == cudaSuccess; c0 += chunk, ++k) {
     const int64_t n = (ncell - c0) < chunk ? (ncell - c0) : chunk;
     const int64_t o = c0 * NM;
     const LaunchCfg ci = stream_cfg(n, 256, 4);
@@ -37,28 +45,23 @@ static int launch_sm(const EosSet &set, const MixParamsDev &prm, double *rho, do
         set, prm, rho + o, vfrac + o, sie + o, temp + o, press + o,
         sie_tot ? sie_tot + c0 : nullptr, vfrac_tot ? vfrac_tot + c0 : nullptr,
         Tguess ? Tguess + c0 : nullptr, init, n);
-    // one block of kSmThreads per SM; each warp owns a contiguous range of >= 32 cells
+    // one block of THREADS per SM (fewer when the chunk has fewer cells than lanes)
     const int threads = THREADS;
-    int64_t warps = (int64_t)sm_count() * MINB * (threads / 32);
-    const int64_t min_warps = (n + 31) / 32;
-    if (warps > min_warps) warps = min_warps;
-    const int64_t blocks = (warps + threads / 32 - 1) / (threads / 32);
-    warps = blocks * (threads / 32);
-    const int64_t cpw = (n + warps - 1) / warps;
+    int64_t blocks = (int64_t)sm_count() * MINB;
+    const int64_t need = (n + threads - 1) / threads;
+    if (blocks > need) blocks = need;
     pte_rhot_sm_kernel<NM, Acc, THREADS, MINB><<<(unsigned)blocks, threads, 0, s>>>(
         set, prm, rho + o, vfrac + o, sie + o, temp + o, press + o,
         sie_tot ? sie_tot + c0 : nullptr, vfrac_tot ? vfrac_tot + c0 : nullptr, init,
         status ? reinterpret_cast<unsigned long long *>(status) + c0 : nullptr,
         residual ? residual + c0 : nullptr, reinterpret_cast<unsigned long long *>(stats), n,
-        cpw);
+        cursors + k);
     count_launch(2);
-    const cudaError_t err = cudaGetLastError();
-    if (err != cudaSuccess) { // the stream-ordered scratch is released on every exit path
-      cudaFreeAsync(init, s);
-      return fail(SGX_ERR_CUDA, "PTE RhoT launch failed: %s", cudaGetErrorString(err));
-    }
+    err = cudaGetLastError();
   }
-  SGX_CUDA_OK(cudaFreeAsync(init, s));
+  cudaFreeAsync(scratch, s); // stream-ordered; released on every exit path
+  if (err != cudaSuccess)
+    return fail(SGX_ERR_CUDA, "PTE RhoT launch failed: %s", cudaGetErrorString(err));
   return SGX_OK;
 }
 

@@ -470,8 +470,11 @@ __global__ void __launch_bounds__(256)
   }
 }
 
-// One lane per cell, one warp per contiguous range of `cells_per_warp` cells; a lane that
-// finishes its cell stores it and pulls the next one of the range.
+// One lane per cell.  A lane that finishes its cell stores it and pulls the next unsolved cell
+// of the WHOLE launch from a global cursor (one warp-aggregated atomicAdd per refill), so no
+// warp, block or SM runs dry before the range is exhausted: the only tail is the last cells'
+// own iterations.  (Round 1 gave each warp a static contiguous slice; its lanes, then its
+// block, then the grid idled while the slowest slice finished.)
 //
 // Rounds are block-synchronous (one barrier per round) and the Newton cycle is aligned to
 // the block's round counter r: the Jacobian evaluations happen when r % 2 == 0, the
@@ -493,7 +496,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
                        const double *__restrict__ init,
                        unsigned long long *__restrict__ status, double *__restrict__ residual,
                        unsigned long long *__restrict__ stats, const int64_t ncell,
-                       const int64_t cells_per_warp) {
+                       unsigned long long *__restrict__ cursor) {
   __shared__ unsigned int s_hist[SGX_PTE_NSTATS];
   if (stats) {
     for (int k = threadIdx.x; k < SGX_PTE_NSTATS; k += blockDim.x)
@@ -503,9 +506,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
   const Acc eos(set);
   mix::RhoTLane<NM, Acc> L(eos, prm);
   const unsigned lane = threadIdx.x & 31u;
-  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  int64_t next = warp * cells_per_warp;
-  const int64_t end = (next + cells_per_warp < ncell) ? next + cells_per_warp : ncell;
+  bool exhausted = false; // warp-uniform: the cursor has passed the end of the range
   int64_t cell = -1;
   double eq[NM], pq[NM], eq2[NM], pq2[NM];
 #pragma unroll
@@ -543,8 +544,17 @@ __global__ void __launch_bounds__(THREADS, MINB)
           }
           cell = -1;
         }
-        const int64_t mine = next + __popc(idle_mask & ((1u << lane) - 1u));
-        if (mine < end) {
+      }
+      // one atomic per warp per refill; lanes take consecutive cells (coalesced loads)
+      unsigned long long first = (unsigned long long)ncell;
+      if (!exhausted) {
+        if (lane == 0) first = atomicAdd(cursor, (unsigned long long)__popc(idle_mask));
+        first = __shfl_sync(0xffffffffu, first, 0);
+        exhausted = first + (unsigned long long)__popc(idle_mask) >= (unsigned long long)ncell;
+      }
+      if (idle) {
+        const int64_t mine = (int64_t)first + __popc(idle_mask & ((1u << lane) - 1u));
+        if (mine < ncell) {
           cell = mine;
           const int64_t base = cell * NM;
 #pragma unroll
@@ -566,7 +576,6 @@ __global__ void __launch_bounds__(THREADS, MINB)
                   vfrac_tot_in ? vfrac_tot_in[cell] : 1.0, rec[0], vfrac_init, rho_init);
         }
       }
-      next += __popc(idle_mask);
     }
     // block-wide round barrier; also the termination vote
     if (!__syncthreads_or(L.phase != mix::PH_IDLE)) break;

@@ -290,9 +290,13 @@ int build_spiner_rhot(const sgx_sp5_tables *raw, int reproducible, int pmin_vapo
   static const char *k2d[] = {"P", "sie", "bMod", "dPdRho", "dPdE", "dTdRho", "dTdE", "dEdRho",
                               "dEdT"};
   for (const char *nm : k2d) add_packed(ts, nm, numRho, numT);
-  // Row pairs (j, j+1) of sie whose every T-segment rises strictly (junction nodes of a piecewise
-  // grid are stored twice and may repeat): there the blend of the two rows is strictly monotone
-  // in lT and the direct T(rho,sie) inversion of sgx_spiner_root.cu has a unique root.
+  // Search hints of the direct T(rho, sie) inversion (sgx_spiner_root.cu; coordinate described at
+  // RootRowMeta, sgx_internal.hpp).  A pair (j, j+1) of density rows qualifies when every
+  // T-segment of both rows rises strictly (junction nodes of a piecewise grid are stored twice
+  // and may repeat): the blend of the two rows is then strictly monotone in lT, the root unique.
+  // For bin k the table holds the range [lo, hi] of table cells r with row(r) <= e < row(r+1)
+  // for an energy of that bin, over both rows each in its own coordinate, widened by one cell
+  // (the blended row sits between the two).  It is a hint: the kernel tests the table itself.
   {
     std::vector<char> junction(numT, 0);
     for (int g = 1; g < s.gT.ngrids; ++g) junction[s.gT.ptot[g] - 1] = 1;
@@ -303,9 +307,55 @@ int build_spiner_rhot(const sgx_sp5_tables *raw, int reproducible, int pmin_vapo
         const double a = sie_h[(size_t)j * numT + i], b = sie_h[(size_t)j * numT + i + 1];
         if (!(b > a || (junction[i] && b == a))) rising[j] = 0;
       }
-    std::vector<double> mono(numRho > 1 ? numRho - 1 : 1, 0.0);
-    for (int j = 0; j + 1 < numRho; ++j) mono[j] = (rising[j] && rising[j + 1]) ? 1.0 : 0.0;
-    ts.add("sie#mono", mono.data(), mono.size());
+    const int npair = numRho > 1 ? numRho - 1 : 1;
+    std::vector<RootRowMeta> meta(numRho, RootRowMeta{0.0, 1.0, 0.0, 0.0});
+    std::vector<unsigned int> hint((size_t)npair * kRootHintBins, 1u); // lo = 1, hi = 0: empty
+    const bool fits = numT <= 65535 && numT >= 3 &&
+                      (size_t)numRho * (sizeof(RootRowMeta) + 2 * sizeof(double)) <= 96 * 1024;
+    for (int j = 0; j < numRho; ++j) {
+      meta[j].base = sie_h[(size_t)j * numT];
+      meta[j].s = sie_h[(size_t)j * numT + 1] - sie_h[(size_t)j * numT];
+    }
+    for (int j = 0; j + 1 < numRho && fits; ++j) {
+      if (!(rising[j] && rising[j + 1])) continue;
+      const double *rows[2] = {sie_h + (size_t)j * numT, sie_h + (size_t)(j + 1) * numT};
+      const double span0 = (rows[0][numT - 1] - meta[j].base) + meta[j].s;
+      const double span1 = (rows[1][numT - 1] - meta[j + 1].base) + meta[j + 1].s;
+      const double umin = fastmath::log10(std::min(meta[j].s, meta[j + 1].s));
+      const double umax = fastmath::log10(std::max(span0, span1));
+      if (!(meta[j].s > 0.0) || !(meta[j + 1].s > 0.0) || !(umax > umin)) continue;
+      const double inv_du = (double)kRootHintBins / (umax - umin);
+      std::vector<int> lo(kRootHintBins, numT), hi(kRootHintBins, -1);
+      auto cover = [&](int k0, int k1, int r) {
+        for (int k = k0; k <= k1; ++k) {
+          lo[k] = std::min(lo[k], r);
+          hi[k] = std::max(hi[k], r);
+        }
+      };
+      for (int q = 0; q < 2; ++q) {
+        const double *row = rows[q];
+        const RootRowMeta &m = meta[j + q];
+        for (int r = 0; r + 1 < numT; ++r)
+          cover(root_hint_bin(m.base, m.s, umin, inv_du, row[r]),
+                root_hint_bin(m.base, m.s, umin, inv_du, row[r + 1]), r);
+        // energies below the row's first node / above its last clamp to the end cells
+        cover(0, root_hint_bin(m.base, m.s, umin, inv_du, row[0]), 0);
+        cover(root_hint_bin(m.base, m.s, umin, inv_du, row[numT - 1]), kRootHintBins - 1,
+              numT - 2);
+      }
+      unsigned int *hj = hint.data() + (size_t)j * kRootHintBins;
+      for (int k = 0; k < kRootHintBins; ++k) {
+        const int l = std::max(lo[k] - 1, 0), h = std::min(hi[k] + 1, numT - 2);
+        hj[k] = (unsigned)l | ((unsigned)h << 16);
+      }
+      meta[j].umin = umin;
+      meta[j].inv_du = inv_du;
+    }
+    static_assert(sizeof(RootRowMeta) == 4 * sizeof(double), "RootRowMeta is 4 doubles");
+    static_assert(kRootHintBins % 2 == 0, "hint rows are stored as doubles");
+    ts.add("sie#rootmeta", reinterpret_cast<const double *>(meta.data()), (size_t)numRho * 4);
+    ts.add("sie#hint", reinterpret_cast<const double *>(hint.data()),
+           (size_t)npair * kRootHintBins / 2);
   }
   int rc = upload_tables(e);
   if (rc) return rc;

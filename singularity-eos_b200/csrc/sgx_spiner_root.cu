@@ -42,109 +42,187 @@ namespace sgx {
 
 namespace {
 
-constexpr int64_t kRootChunk = int64_t(1) << 24; // cells per kernel pair (list scratch 64 MiB)
+constexpr int64_t kRootChunk = int64_t(1) << 24; // cells per kernel pair
+// The cells left to the reference iterate are appended to kRootSubLists lists, chosen by block:
+// one list would put every warp's atomicAdd on one address (measured: +0.9 ms per 2^26 cells).
+// Each list has room for twice its fair share; a cell that finds its list full is solved on the
+// spot by the same code the list kernel runs.
+constexpr int kRootSubLists = 32;
+constexpr int kRootCounterStride = 32; // unsigned ints between counters: one 128-byte line each
+SGX_HD int64_t root_sublist_capacity(const int64_t ncell) {
+  return 2 * (ncell / kRootSubLists) + 4096;
+}
 
 // relative-T error budget of the direct solve against the reference iterate (see header):
 // keep when  kBoundCoef * max|corner| * dx <= |h1 - h0|,
 // kBoundCoef = 4 * 2^-52 * ln(10) / 1e-12
 constexpr double kBoundCoef = 4.0 * 2.220446049250313e-16 * 2.302585092994046 / 1.0e-12;
 
-// One on-table cell.  Returns false when the reference iterate must decide.
+// Every cell: table location as the reference, then for on-table cells the bracketing table cell
+// of the (ix2, w2)-frozen blend and a linear solve in it.
+//
+// ncu history of this kernel (profiles/r2_root_*): a bisection with a data-dependent `break`
+// ran the rest of each cell once per exit depth (5 of 32 lanes active); with a fixed trip count
+// it was bound by the L1TEX wavefront rate -- 9 scattered 32-byte probes per cell, ~1.4 cycles
+// per lane-probe -- at 23 Gcells/s.  So the number of scattered global loads per cell is what
+// counts.  Now: the per-row metadata and the two 1-D curves of the table-location test live in
+// shared memory (12 KiB), one 4-byte gather of the hint table (RootRowMeta, sgx_internal.hpp)
+// starts the search 3-4 cells wide around the right cell, and the loop leaves as soon as every
+// lane of the warp has its cell (1-2 probes).  The hint only narrows the search: the hit test
+// h0 <= sie < h1 is always made on the table itself, and a search that comes up empty sends
+// the cell to the reference iterate.
 template <bool BOUNDED>
-SGX_D bool lT_direct(const SpinerRhoT &eos, const double *__restrict__ mono, const AxisPos &pr,
-                     const double sie, double &lT) {
-  // interpolation (not extrapolation) between two rows that both rise strictly with T: the
-  // blend then rises strictly too and the root is unique
-  if (!(pr.w1 >= 0.0 && pr.w1 <= 1.0) || ldg(mono + pr.ix) == 0.0) return false;
-  int lo = 0, hi = eos.numT - 2; // candidate table cells along T
-  Cell4 c;
-  double h0, h1;
-  int mid;
-  while (true) {
-    mid = (lo + hi) >> 1;
-    c = ld_cell(eos.sie, eos.numT, pr.ix, mid);
-    h0 = pr.w0 * c.c00 + pr.w1 * c.c10; // the blend at node mid   (w1 weight 0: exact)
-    h1 = pr.w0 * c.c01 + pr.w1 * c.c11; // the blend at node mid+1
-    if (sie < h0) {
-      hi = mid - 1;
-    } else if (sie >= h1) {
-      lo = mid + 1;
-    } else {
-      break; // h0 <= sie < h1 (never a junction cell of a piecewise grid: there h0 == h1)
-    }
-    if (lo > hi) return false; // outside the row's range: the reference's bracket logic decides
-  }
-  const Grid1D &g = eos.gT;
-  int ig = 0;
-  if (g.ngrids > 1) ig = (g.ngrids > 2 && mid >= g.ptot[2]) ? 2 : (mid >= g.ptot[1] ? 1 : 0);
-  const double dx = g.dx[ig];
-  const double dh = h1 - h0;
-  if (BOUNDED) {
-    const double mag = fmax(fmax(fabs(c.c00), fabs(c.c01)), fmax(fabs(c.c10), fabs(c.c11)));
-    if (!(kBoundCoef * mag * dx <= dh)) return false;
-  }
-  const double floor_x = (double)(mid - g.ptot[ig]) * dx + g.min[ig];
-  lT = floor_x + ((sie - h0) / dh) * dx;
-  return true;
-}
-
-template <bool BOUNDED>
-__global__ void __launch_bounds__(256, 3)
-    rhot_T_direct_kernel(const __grid_constant__ SpinerRhoT eos, const double *__restrict__ mono,
+__global__ void __launch_bounds__(256, 4)
+    rhot_T_direct_kernel(const __grid_constant__ SpinerRhoT eos,
+                         const RootRowMeta *__restrict__ meta_g,
+                         const unsigned int *__restrict__ hint,
                          const double *__restrict__ rho_in, const double *__restrict__ sie_in,
                          double *__restrict__ T_out, const int64_t n, double *__restrict__ lambda,
                          const int ls, const bool vec_lambda, unsigned int *__restrict__ list,
                          unsigned int *__restrict__ count) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  RootRowMeta *meta = reinterpret_cast<RootRowMeta *>(smem_raw);
+  double *s_sielTMax = reinterpret_cast<double *>(meta + eos.numRho);
+  double *s_sieCold = s_sielTMax + eos.numRho;
+  {
+    const double *src = reinterpret_cast<const double *>(meta_g);
+    double *dst = reinterpret_cast<double *>(smem_raw);
+    for (int k = threadIdx.x; k < eos.numRho * 4; k += blockDim.x)
+      dst[k] = src[k];
+    for (int k = threadIdx.x; k < eos.numRho; k += blockDim.x) {
+      s_sielTMax[k] = eos.sielTMax[k];
+      s_sieCold[k] = eos.sieCold[k];
+    }
+    __syncthreads();
+  }
   const unsigned lane = threadIdx.x & 31u;
   const int64_t nthr = (int64_t)gridDim.x * blockDim.x;
-  // warp-uniform trip count: every lane stays in the loop so the ballots below are full-warp
+  const int last_cell = eos.numT - 2;
+  const unsigned sub = blockIdx.x % kRootSubLists;
+  const unsigned sub_cap = (unsigned)root_sublist_capacity(n);
+  unsigned int *const my_count = count + sub * kRootCounterStride;
+  unsigned int *const my_list = list + (size_t)sub * sub_cap;
+  // warp-uniform trip count: every lane stays in the loop so the votes below are full-warp
   for (int64_t base = (int64_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31u); base < n;
        base += nthr) {
     const int64_t i = base + lane;
     const bool valid = i < n;
-    bool fallback = false;
+    bool fallback = false, search = false, found = false;
+    double sie = 0.0, lRho = 0.0, lT = 0.0, w0 = 0.0, w1 = 0.0;
+    int ix2 = 0, lo = 1, hi = 0;
     if (valid) {
-      double rho, sie;
+      double rho;
       asm volatile("ld.global.nc.L1::no_allocate.f64 %0, [%1];" : "=d"(rho) : "l"(rho_in + i));
       asm volatile("ld.global.nc.L1::no_allocate.f64 %0, [%1];" : "=d"(sie) : "l"(sie_in + i));
-      const double lRho = eos.lRho_(rho);
+      lRho = eos.lRho_(rho);
       const AxisPos pr(eos.gRho, lRho);
-      const TableStatus w = eos.locRhoSie(pr, sie);
-      double lT;
-      if (w == OffBottom) { // eos_spiner_rho_temp.hpp:1204-1206
-        lT = eos.lTMin;
-      } else if (w == OffTop) { // :1207-1212
+      // getLocDependsRhoSie_ (eos_spiner_rho_temp.hpp:1377-1392): same two 1-D interpolations,
+      // same expressions as SpinerRhoT::locRhoSie, the curves read from shared memory
+      const double sielTMax_ = pr.w0 * s_sielTMax[pr.ix] + pr.w1 * s_sielTMax[pr.ix + 1];
+      const double sieCold_ = pr.w0 * s_sieCold[pr.ix] + pr.w1 * s_sieCold[pr.ix + 1];
+      if (sie >= sielTMax_ - SpinerRhoT::SOFT_THRESH * fabs(sielTMax_)) { // OffTop :1207-1212
         const double Cv = interp1d(eos.dEdTMax, pr);
-        const double e0 = interp1d(eos.sielTMax, pr);
-        lT = eos.lT_(eos.TMax + ratio(sie - e0, Cv));
+        lT = eos.lT_(eos.TMax + ratio(sie - sielTMax_, Cv));
+      } else if (sie <= sieCold_ + SpinerRhoT::SOFT_THRESH * fabs(sieCold_)) { // OffBottom
+        lT = eos.lTMin;                                                         // :1204-1206
       } else {
-        fallback = !lT_direct<BOUNDED>(eos, mono, pr, sie, lT);
+        ix2 = pr.ix;
+        w0 = pr.w0;
+        w1 = pr.w1;
+        const RootRowMeta m0 = meta[ix2], m1 = meta[ix2 + 1];
+        // interpolation (not extrapolation) between two rows that both rise strictly with T
+        // (inv_du > 0 marks such pairs): the blend rises strictly too, the root is unique
+        if (w1 >= 0.0 && w1 <= 1.0 && m0.inv_du > 0.0) {
+          const double base_b = w0 * m0.base + w1 * m1.base, s_b = w0 * m0.s + w1 * m1.s;
+          const int k = root_hint_bin(base_b, s_b, m0.umin, m0.inv_du, sie);
+          const unsigned h = __ldg(hint + (size_t)ix2 * kRootHintBins + k);
+          lo = (int)(h & 0xffffu);
+          hi = (int)(h >> 16);
+          hi = hi > last_cell ? last_cell : hi;
+          search = true;
+        } else {
+          fallback = true;
+        }
       }
-      if (!fallback) {
-        asm volatile("st.global.cs.f64 [%0], %1;" ::"l"(T_out + i), "d"(eos.T_(lT)) : "memory");
-        if (lambda) { // :1244-1245
-          double *l = lambda + i * ls;
-          if (vec_lambda) { // rows 16-byte aligned (checked at launch)
-            asm volatile("st.global.cs.v2.f64 [%0], {%1,%2};" ::"l"(l), "d"(lRho), "d"(lT)
-                         : "memory");
-          } else {
-            l[0] = lRho;
-            l[1] = lT;
-          }
+    }
+    // Search for the table cell with h0 <= sie < h1 (never a junction cell of a piecewise grid:
+    // there h0 == h1).  Selects only; the warp leaves together.
+    Cell4 c{0.0, 0.0, 0.0, 0.0};
+    double h0 = 0.0, h1 = 0.0;
+    int mid = 0;
+    for (int it = 0; it < 20; ++it) {
+      const bool live = search && !found && lo <= hi;
+      if (!__any_sync(0xffffffffu, live)) break;
+      if (live) {
+        mid = (lo + hi) >> 1;
+        c = ld_cell(eos.sie, eos.numT, ix2, mid);
+        h0 = w0 * c.c00 + w1 * c.c10; // the blend at node mid   (w1 weight 0: exact)
+        h1 = w0 * c.c01 + w1 * c.c11; // the blend at node mid+1
+        const bool below = sie < h0, above = sie >= h1;
+        found = !below && !above;
+        hi = below ? mid - 1 : hi;
+        lo = above ? mid + 1 : lo;
+      }
+    }
+    if (search) {
+      if (found) {
+        const Grid1D &g = eos.gT;
+        int ig = 0;
+        if (g.ngrids > 1) ig = (g.ngrids > 2 && mid >= g.ptot[2]) ? 2 : (mid >= g.ptot[1] ? 1 : 0);
+        const double dx = g.dx[ig];
+        const double dh = h1 - h0;
+        bool keep = true;
+        if (BOUNDED) {
+          const double mag = fmax(fmax(fabs(c.c00), fabs(c.c01)), fmax(fabs(c.c10), fabs(c.c11)));
+          keep = kBoundCoef * mag * dx <= dh;
+        }
+        const double floor_x = (double)(mid - g.ptot[ig]) * dx + g.min[ig];
+        lT = floor_x + ((sie - h0) / dh) * dx;
+        fallback = !keep;
+      } else {
+        fallback = true; // outside the row pair's range: the reference's bracket logic decides
+      }
+    }
+    if (valid && !fallback) {
+      asm volatile("st.global.cs.f64 [%0], %1;" ::"l"(T_out + i), "d"(eos.T_(lT)) : "memory");
+      if (lambda) { // :1244-1245
+        double *l = lambda + i * ls;
+        if (vec_lambda) { // rows 16-byte aligned (checked at launch)
+          asm volatile("st.global.cs.v2.f64 [%0], {%1,%2};" ::"l"(l), "d"(lRho), "d"(lT)
+                       : "memory");
+        } else {
+          l[0] = lRho;
+          l[1] = lT;
         }
       }
     }
     const unsigned fbm = __ballot_sync(0xffffffffu, fallback);
     if (fbm) {
       unsigned pos = 0;
-      if (lane == 0) pos = atomicAdd(count, (unsigned)__popc(fbm));
+      if (lane == 0) pos = atomicAdd(my_count, (unsigned)__popc(fbm));
       pos = __shfl_sync(0xffffffffu, pos, 0);
-      if (fallback) list[pos + __popc(fbm & ((1u << lane) - 1u))] = (unsigned)i;
+      if (fallback) {
+        const unsigned mine = pos + __popc(fbm & ((1u << lane) - 1u));
+        if (mine < sub_cap) {
+          my_list[mine] = (unsigned)i;
+        } else { // list full (heavily skewed input): the reference iterate right here
+          double lam[2];
+          if (lambda) {
+            lam[0] = lambda[i * ls];
+            lam[1] = lambda[i * ls + 1];
+          }
+          T_out[i] = eos.T_from_rho_e(rho_in[i], sie_in[i], lambda ? lam : nullptr);
+          if (lambda) {
+            lambda[i * ls] = lam[0];
+            lambda[i * ls + 1] = lam[1];
+          }
+        }
+      }
     }
   }
 }
 
-// The listed cells through the reference iterate (SpinerRhoT::T_from_rho_e)
+// The listed cells through the reference iterate (SpinerRhoT::T_from_rho_e); blockIdx.y = list
 __global__ void __launch_bounds__(256, 4)
     rhot_T_list_kernel(const __grid_constant__ SpinerRhoT eos, const double *__restrict__ rho_in,
                        const double *__restrict__ sie_in, double *__restrict__ T_out,
@@ -152,15 +230,19 @@ __global__ void __launch_bounds__(256, 4)
                        const unsigned int *__restrict__ list,
                        const unsigned int *__restrict__ count,
                        unsigned long long *__restrict__ stats, const unsigned long long ncell) {
-  const unsigned cnt = *count;
+  const unsigned sub = blockIdx.y;
+  const unsigned sub_cap = (unsigned)root_sublist_capacity((int64_t)ncell);
+  const unsigned raw = count[sub * kRootCounterStride];
+  const unsigned cnt = raw < sub_cap ? raw : sub_cap; // the overflow was solved in place
+  const unsigned int *my_list = list + (size_t)sub * sub_cap;
   const unsigned tid = blockIdx.x * blockDim.x + threadIdx.x;
   const unsigned nthr = gridDim.x * blockDim.x;
   if (tid == 0 && stats) {
-    atomicAdd(stats + 0, ncell);
-    atomicAdd(stats + 1, (unsigned long long)cnt);
+    if (sub == 0) atomicAdd(stats + 0, ncell);
+    atomicAdd(stats + 1, (unsigned long long)raw);
   }
   for (unsigned k = tid; k < cnt; k += nthr) {
-    const int64_t i = list[k];
+    const int64_t i = my_list[k];
     double lam[2];
     if (lambda) {
       lam[0] = lambda[i * ls];
@@ -187,27 +269,46 @@ int launch_rhot_T_from_rho_e_hybrid(sgx_eos_s *e, bool bounded, const double *rh
                                     const double *sie, double *out, int64_t n, double *lambda,
                                     int ls, cudaStream_t s) {
   const SpinerRhoT &eos = e->rhot;
-  const double *mono = e->tables.d("sie#mono");
+  const RootRowMeta *meta = reinterpret_cast<const RootRowMeta *>(e->tables.d("sie#rootmeta"));
+  const unsigned int *hint = reinterpret_cast<const unsigned int *>(e->tables.d("sie#hint"));
+  const size_t smem = (size_t)eos.numRho * (sizeof(RootRowMeta) + 2 * sizeof(double));
+  if (smem > 48 * 1024) { // up to 96 KiB (build_spiner_rhot's `fits`): opt in once
+    static const bool opted = [] {
+      return cudaFuncSetAttribute(rhot_T_direct_kernel<true>,
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  96 * 1024) == cudaSuccess &&
+             cudaFuncSetAttribute(rhot_T_direct_kernel<false>,
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  96 * 1024) == cudaSuccess;
+    }();
+    if (!opted) return fail(SGX_ERR_CUDA, "cannot reserve %zu bytes of shared memory", smem);
+  }
   const int64_t chunk = n < kRootChunk ? n : kRootChunk;
-  unsigned int *scratch = nullptr; // [0] = count, [64...] = list
-  SGX_CUDA_OK(cudaMallocAsync(&scratch, (size_t)(chunk + 64) * sizeof(unsigned int), s));
+  // scratch: kRootSubLists counters (one 128-byte line each), then the lists
+  constexpr size_t kCounters = (size_t)kRootSubLists * kRootCounterStride;
+  const size_t list_len = (size_t)kRootSubLists * (size_t)root_sublist_capacity(chunk);
+  unsigned int *scratch = nullptr;
+  SGX_CUDA_OK(cudaMallocAsync(&scratch, (kCounters + list_len) * sizeof(unsigned int), s));
   int rc = SGX_OK;
   for (int64_t c0 = 0; c0 < n && rc == SGX_OK; c0 += chunk) {
     const int64_t m = (n - c0) < chunk ? (n - c0) : chunk;
     double *lam = lambda ? lambda + c0 * ls : nullptr;
     const bool vec_lambda = lam && (ls % 2) == 0 && (((uintptr_t)lam) & 15) == 0;
-    cudaError_t err = cudaMemsetAsync(scratch, 0, sizeof(unsigned int), s);
+    cudaError_t err = cudaMemsetAsync(scratch, 0, kCounters * sizeof(unsigned int), s);
     if (err == cudaSuccess) {
-      const LaunchCfg c = stream_cfg(m, 256, 3 * 4);
+      const LaunchCfg c = stream_cfg(m, 256, 4 * 2);
       if (bounded)
-        rhot_T_direct_kernel<true><<<c.blocks, c.threads, 0, s>>>(
-            eos, mono, rho + c0, sie + c0, out + c0, m, lam, ls, vec_lambda, scratch + 64, scratch);
+        rhot_T_direct_kernel<true><<<c.blocks, c.threads, smem, s>>>(
+            eos, meta, hint, rho + c0, sie + c0, out + c0, m, lam, ls, vec_lambda, scratch + kCounters,
+            scratch);
       else
-        rhot_T_direct_kernel<false><<<c.blocks, c.threads, 0, s>>>(
-            eos, mono, rho + c0, sie + c0, out + c0, m, lam, ls, vec_lambda, scratch + 64, scratch);
-      const LaunchCfg c2 = stream_cfg(m, 256, 4);
-      rhot_T_list_kernel<<<c2.blocks, c2.threads, 0, s>>>(
-          eos, rho + c0, sie + c0, out + c0, lam, ls, scratch + 64, scratch,
+        rhot_T_direct_kernel<false><<<c.blocks, c.threads, smem, s>>>(
+            eos, meta, hint, rho + c0, sie + c0, out + c0, m, lam, ls, vec_lambda, scratch + kCounters,
+            scratch);
+      // one grid row per list; a list holds ~ m / 32 / 7 cells on the bench workload
+      const LaunchCfg c2 = stream_cfg(root_sublist_capacity(m) / 4, 256, 1);
+      rhot_T_list_kernel<<<dim3(c2.blocks, kRootSubLists), c2.threads, 0, s>>>(
+          eos, rho + c0, sie + c0, out + c0, lam, ls, scratch + kCounters, scratch,
           reinterpret_cast<unsigned long long *>(e->root_stats), (unsigned long long)m);
       count_launch(2);
       err = cudaGetLastError();

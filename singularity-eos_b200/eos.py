@@ -131,6 +131,53 @@ class EosBase:
                                                 lambdas=None):
         return self._eval(_lib.GAMMA_FROM_RHO_E, rhos, sies, gm1s, num, lambdas)
 
+    # -- the rest of the vector surface (eos/eos_base.hpp:422-470,497-501,680-722) ------------
+    def _extra(self, fn, in1, in2, out, num, lambdas):
+        _require_cuda_f64(in1, in2, out, lambdas)
+        n = in1.numel() if num is None else int(num)
+        check(fn(self._h, _ptr(in1), _ptr(in2), _ptr(out), n, _ptr(lambdas),
+                 self._lambda_stride(lambdas, n), _stream()))
+        return out
+
+    def MinInternalEnergyFromDensity(self, rhos, sies, num=None, lambdas=None):
+        _require_cuda_f64(rhos, sies, lambdas)
+        n = rhos.numel() if num is None else int(num)
+        check(self._lib.sgx_MinInternalEnergyFromDensity(
+            self._h, _ptr(rhos), _ptr(sies), n, _ptr(lambdas), self._lambda_stride(lambdas, n),
+            _stream()))
+        return sies
+
+    def InternalEnergyFromDensityPressure(self, rhos, Ps, sies, num=None, lambdas=None):
+        return self._extra(self._lib.sgx_InternalEnergyFromDensityPressure, rhos, Ps, sies, num,
+                           lambdas)
+
+    def EntropyFromDensityTemperature(self, rhos, temperatures, entropies, num=None, lambdas=None):
+        return self._extra(self._lib.sgx_EntropyFromDensityTemperature, rhos, temperatures,
+                           entropies, num, lambdas)
+
+    def EntropyFromDensityInternalEnergy(self, rhos, sies, entropies, num=None, lambdas=None):
+        return self._extra(self._lib.sgx_EntropyFromDensityInternalEnergy, rhos, sies, entropies,
+                           num, lambdas)
+
+    def GibbsFreeEnergyFromDensityTemperature(self, rhos, temperatures, gibbs, num=None,
+                                              lambdas=None):
+        return self._extra(self._lib.sgx_GibbsFreeEnergyFromDensityTemperature, rhos,
+                           temperatures, gibbs, num, lambdas)
+
+    def GibbsFreeEnergyFromDensityInternalEnergy(self, rhos, sies, gibbs, num=None, lambdas=None):
+        return self._extra(self._lib.sgx_GibbsFreeEnergyFromDensityInternalEnergy, rhos, sies,
+                           gibbs, num, lambdas)
+
+    def DensityEnergyFromPressureTemperature(self, presses, temperatures, rhos, sies, num=None,
+                                             lambdas=None):
+        """Per cell (eos_base.hpp:630-671 and the models' overloads); rhos is in/out."""
+        _require_cuda_f64(presses, temperatures, rhos, sies, lambdas)
+        n = presses.numel() if num is None else int(num)
+        check(self._lib.sgx_DensityEnergyFromPressureTemperature(
+            self._h, _ptr(presses), _ptr(temperatures), _ptr(rhos), _ptr(sies), n, _ptr(lambdas),
+            self._lambda_stride(lambdas, n), _stream()))
+        return rhos, sies
+
     def PressureEnergyFromDensityTemperature(self, rhos, temperatures, pressures, sies,
                                              num=None, lambdas=None):
         """Fused P(rho,T)+e(rho,T) (one pass; not in the reference, same results)."""

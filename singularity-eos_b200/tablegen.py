@@ -304,3 +304,19 @@ def write_synthetic_helm_table(path, B=1.0e13, C=-10.0):
                             axis=1)
             np.savetxt(fh, cols, fmt="%.17e")
     return path
+
+
+def write_sp5_raw(raw, path):
+    """Dump a Sp5Raw for a C++ consumer (tests/cpp/test_plugin.cpp): the sgx_sp5_tables struct
+    bytes (pointer members meaningless), then for every table member in struct order an int64
+    element count (0 = NULL) followed by the doubles."""
+    with open(path, "wb") as fh:
+        fh.write(b"SGXSP5R1")
+        fh.write(bytes(raw.struct))
+        for name in _lib.SP5_TABLE_NAMES:
+            a = raw.arrays.get(name)
+            n = 0 if a is None else a.size
+            fh.write(np.int64(n).tobytes())
+            if n:
+                fh.write(np.ascontiguousarray(a, dtype=np.float64).tobytes())
+    return path

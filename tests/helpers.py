@@ -69,3 +69,46 @@ def build_cpp_shim_test():
              "-L" + os.path.join(cuda, "lib64"), "-lcudart", "-Wl,-rpath," + libdir,
              "-Wl,-rpath," + os.path.join(cuda, "lib64")])
     return exe
+
+
+REF_ROOT = "/root/reference"
+
+
+def build_cpp_plugin_test(force=False):
+    """Compile tests/cpp/test_plugin.cpp -- the reference-side plugin (plugins/sgx) against the
+    reference headers where they lie -- with the include paths of oracle/Makefile.  Needs
+    /root/reference (this container); on the GPU box the prebuilt binary under tests/cpp/_build
+    is used.  Returns the binary path, or None when neither is available."""
+    import os
+    import subprocess
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out_dir = os.path.join(root, "tests", "cpp", "_build")
+    exe = os.path.join(out_dir, "test_plugin")
+    if not os.path.isdir(os.path.join(REF_ROOT, "singularity-eos")):
+        return exe if os.path.exists(exe) else None
+    os.makedirs(out_dir, exist_ok=True)
+    src = os.path.join(root, "tests", "cpp", "test_plugin.cpp")
+    deps = [src, os.path.join(root, "include", "sgx_b200.h"),
+            os.path.join(root, "oracle", "sp5_tree.hpp")] + \
+        [os.path.join(root, "plugins", "sgx", f) for f in os.listdir(os.path.join(root, "plugins", "sgx"))]
+    if not force and os.path.exists(exe) and \
+            all(os.path.getmtime(d) <= os.path.getmtime(exe) for d in deps):
+        return exe
+    cuda = os.environ.get("CUDA_HOME", "/usr/local/cuda")
+    libdir = os.path.join(root, "singularity-eos_b200", "lib")
+    ref_inc = ["-I" + os.path.join(root, "oracle", "hdf5_shim"),
+               "-I" + os.path.join(root, "oracle", "ref_gen"), "-I" + REF_ROOT,
+               "-I" + os.path.join(REF_ROOT, "utils", "ports-of-call"),
+               "-I" + os.path.join(REF_ROOT, "utils", "spiner"),
+               "-I" + os.path.join(REF_ROOT, "utils", "eigen"),
+               "-I" + os.path.join(REF_ROOT, "utils", "variant", "include")]
+    defs = ["-DSINGULARITY_USE_SPINER", "-DSINGULARITY_USE_SPINER_WITH_HDF5", "-DSPINER_USE_HDF",
+            "-DSINGULARITY_USE_HELMHOLTZ", "-DPORTABLE_ALWAYS_THROW_OR_ABORT_THROWS"]
+    subprocess.check_call(
+        ["/usr/bin/g++", "-std=c++17", "-O1", "-w"] + defs + ref_inc +
+        ["-I" + os.path.join(root, "include"), "-I" + os.path.join(cuda, "include"), src, "-o", exe,
+         "-L" + libdir, "-lsgx_b200", "-L" + os.path.join(cuda, "lib64"), "-lcudart",
+         "-Wl,-rpath,$ORIGIN/../../../singularity-eos_b200/lib", "-Wl,-rpath," + libdir,
+         "-Wl,-rpath," + os.path.join(cuda, "lib64")])
+    return exe

@@ -10,7 +10,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 REF_LIB = os.path.join(ROOT, "oracle", "_ref", "libsgref.so")
 
 _VP, _I64, _D = C.c_void_p, C.c_int64, C.c_double
-_ref = None
+KOKKOS_LIB = os.path.join(ROOT, "oracle", "_ref", "libsgref_kokkos.so")
+_loaded = {}
 
 
 def _pkg():
@@ -19,17 +20,19 @@ def _pkg():
     return g.load_package()
 
 
-def load():
-    global _ref
-    if _ref is not None:
-        return _ref
-    if not os.path.exists(REF_LIB):
+def load(path=None):
+    """The parity oracle (default): the reference headers with PORTABILITY_STRATEGY_NONE, -O2."""
+    path = path or REF_LIB
+    if path in _loaded:
+        return _loaded[path]
+    if not os.path.exists(path):
         return None
     L = _pkg()._lib
-    lib = C.CDLL(REF_LIB)
+    lib = C.CDLL(path)
     protos = {
         "ref_abi_version": (C.c_int, []),
         "ref_num_threads": (C.c_int, []),
+        "ref_is_kokkos": (C.c_int, []),
         "ref_fastmath_eval": (None, [C.c_int, _VP, _VP, _I64]),
         "ref_regula_falsi_table": (C.c_int, [_VP, C.c_int, _D, _D, _D, _D, _D, _D, _D, _D,
                                              C.POINTER(_D)]),
@@ -52,6 +55,7 @@ def load():
         "ref_eos_get_scalar": (C.c_int, [_VP, C.c_char_p, C.POINTER(_D)]),
         "ref_eos_eval": (C.c_int, [_VP, C.c_int, _VP, _VP, _VP, _I64, _VP, C.c_int, C.c_int]),
         "ref_eos_fill": (C.c_int, [_VP] * 7 + [_I64, C.c_ulong, _VP, C.c_int, C.c_int, C.c_int]),
+        "ref_eos_eval_extra": (C.c_int, [_VP, C.c_int, _VP, _VP, _VP, _VP, _I64, _VP, C.c_int]),
         "ref_mix_params_default": (None, [C.POINTER(L.MixParams)]),
         "ref_pte_solve": (C.c_int, [C.c_int, C.POINTER(_VP), C.c_int, _I64] + [_VP] * 8 +
                           [C.POINTER(L.MixParams), _VP, _VP, _VP, C.c_int]),
@@ -62,8 +66,20 @@ def load():
     for name, (res, args) in protos.items():
         fn = getattr(lib, name)
         fn.restype, fn.argtypes = res, args
-    _ref = Ref(lib)
-    return _ref
+    _loaded[path] = Ref(lib)
+    return _loaded[path]
+
+
+def load_kokkos():
+    """The TIMED baseline: the same harness built -O3 against the reference's vendored Kokkos
+    (OpenMP backend, PORTABILITY_STRATEGY_KOKKOS): whole arrays go through one reference vector
+    call.  Thread placement as BASELINE.md 3 (must be set before the OpenMP runtime starts)."""
+    os.environ.setdefault("OMP_PROC_BIND", "spread")
+    os.environ.setdefault("OMP_PLACES", "threads")
+    ref = load(KOKKOS_LIB)
+    if ref is not None:
+        assert ref.lib.ref_is_kokkos() == 1
+    return ref
 
 
 def _p(a):
@@ -91,6 +107,19 @@ class RefEos:
                                    stride, nthreads)
         assert rc == 0
         return out
+
+    def eval_extra(self, op, in1, in2=None, rho_guess=None, lambdas=None):
+        """ref_eos_eval_extra: returns out1, or (rho, sie) for op 6."""
+        in1 = np.ascontiguousarray(in1, dtype=np.float64)
+        in2 = None if in2 is None else np.ascontiguousarray(in2, dtype=np.float64)
+        out1 = np.zeros_like(in1) if rho_guess is None else np.array(rho_guess, dtype=np.float64)
+        out2 = np.zeros_like(in1)
+        stride = 0 if lambdas is None else lambdas.shape[-1]
+        rc = self.lib.ref_eos_eval_extra(self.h, op, _p(in1), _p(in2), _p(out1), _p(out2),
+                                         in1.size, _p(lambdas), stride)
+        if rc != 0:
+            raise RuntimeError("the reference threw")
+        return (out1, out2) if op == 6 else out1
 
     def fill(self, rho, T, e, P, cv, bmod, output, lambdas=None, az_only=False, nthreads=1):
         n = rho.size

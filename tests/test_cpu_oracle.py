@@ -399,3 +399,17 @@ def test_lg_restatement_bits(tmp_path):
     subprocess.check_call(["/usr/bin/g++", "-O2", "-std=c++17", "-o", str(exe), str(src)])
     out = subprocess.run([str(exe)], capture_output=True, text=True, timeout=120)
     assert out.returncode == 0 and out.stdout.split() == ["0", "0"], out.stdout + out.stderr
+
+
+def test_reference_side_plugin_compiles_and_links(pkg):
+    """plugins/sgx/*.hpp are real headers: tests/cpp/test_plugin.cpp compiles against the
+    reference where it lies and links the C ABI (--link-only: no device call)."""
+    import subprocess
+
+    from helpers import build_cpp_plugin_test
+
+    exe = build_cpp_plugin_test()
+    if exe is None:
+        pytest.skip("reference not mounted and no prebuilt tests/cpp/_build/test_plugin")
+    out = subprocess.run([exe, "--link-only"], capture_output=True, text=True, timeout=60)
+    assert out.returncode == 0, out.stdout + out.stderr
