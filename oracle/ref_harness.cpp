@@ -622,7 +622,9 @@ void ref_mix_params_default(sgx_mix_params *p) {
   p->pte_reduced_system_exclude_idx = m.pte_reduced_system_exclude_idx;
 }
 
+extern "C++" {
 namespace {
+using singularity::mix_impl::CacheAccessor;
 // One cell of the loop of test/test_pte.cpp:177-265.
 struct PteArgs {
   int solver, nmat;
@@ -630,11 +632,12 @@ struct PteArgs {
   const double *sie_tot_in, *vfrac_tot_in, *Tguess_in;
   uint64_t *status;
   double *residual, *Tguess_out;
+  double *lambda; // [ncell][nmat][MAX_NUM_LAMBDAS] caches (CacheAccessor layout) or null
 };
-inline int pte_one_cell(const PteArgs &A, const MixParams &mp, const EosIndexer &eos,
-                        double *scratch, const int64_t t) {
+template <typename LambdaIndexer>
+inline int pte_one_cell_l(const PteArgs &A, const MixParams &mp, const EosIndexer &eos,
+                          double *scratch, const int64_t t, LambdaIndexer lambda) {
   const int nmat = A.nmat;
-  NullIndexer lambda;
   RowIndexer r{A.rho + t * nmat}, vf{A.vfrac + t * nmat}, e{A.sie + t * nmat},
       tp{A.temp + t * nmat}, pr{A.press + t * nmat};
   Real sie_tot = 0.0, rho_tot = 0.0;
@@ -650,7 +653,7 @@ inline int pte_one_cell(const PteArgs &A, const MixParams &mp, const EosIndexer 
   if (A.Tguess_in) {
     Tguess = A.Tguess_in[t];
   } else {
-    Tguess = ApproxTemperatureFromRhoMatU(nmat, eos, rho_tot * sie_tot, r, vf);
+    Tguess = ApproxTemperatureFromRhoMatU(nmat, eos, rho_tot * sie_tot, r, vf, 0.0, lambda);
   }
   if (A.Tguess_out) A.Tguess_out[t] = Tguess;
   SolverStatus st;
@@ -658,22 +661,27 @@ inline int pte_one_cell(const PteArgs &A, const MixParams &mp, const EosIndexer 
   const int solver = A.solver;
   int lrc = guarded([&]() {
     if (solver == SGX_PTE_RHOT) {
-      PTESolverRhoT<EosIndexer, RowIndexer, NullIndexer> method(
+      PTESolverRhoT<EosIndexer, RowIndexer, LambdaIndexer> method(
           nmat, eos, vfrac_tot, sie_tot, r, vf, e, tp, pr, lambda, scratch, Tguess, mp);
       st = PTESolver(method);
       niter = method.Niter();
     } else if (solver == SGX_PTE_RHOU) {
-      PTESolverRhoU<EosIndexer, RowIndexer, NullIndexer> method(
+      PTESolverRhoU<EosIndexer, RowIndexer, LambdaIndexer> method(
           nmat, eos, vfrac_tot, sie_tot, r, vf, e, tp, pr, lambda, scratch, Tguess, mp);
       st = PTESolver(method);
       niter = method.Niter();
+    } else if (solver == SGX_PTE_FIXED_P) {
+      PTESolverFixedP<EosIndexer, RowIndexer, LambdaIndexer> method(
+          nmat, eos, vfrac_tot, Tguess /* P */, r, vf, e, tp, pr, lambda, scratch, mp);
+      st = PTESolver(method);
+      niter = method.Niter();
     } else if (solver == SGX_PTE_FIXED_T) {
-      PTESolverFixedT<EosIndexer, RowIndexer, NullIndexer> method(
+      PTESolverFixedT<EosIndexer, RowIndexer, LambdaIndexer> method(
           nmat, eos, vfrac_tot, Tguess /* T_true */, r, vf, e, tp, pr, lambda, scratch, mp);
       st = PTESolver(method);
       niter = method.Niter();
     } else {
-      PTESolverPT<EosIndexer, RowIndexer, NullIndexer> method(
+      PTESolverPT<EosIndexer, RowIndexer, LambdaIndexer> method(
           nmat, eos, vfrac_tot, sie_tot, r, vf, e, tp, pr, lambda, scratch, Tguess, mp);
       st = PTESolver(method);
       niter = method.Niter();
@@ -683,22 +691,48 @@ inline int pte_one_cell(const PteArgs &A, const MixParams &mp, const EosIndexer 
   if (A.residual) A.residual[t] = st.residual;
   return lrc;
 }
+inline int pte_one_cell(const PteArgs &A, const MixParams &mp, const EosIndexer &eos,
+                        double *scratch, const int64_t t) {
+  if (A.lambda)
+    return pte_one_cell_l(A, mp, eos, scratch, t,
+                          CacheAccessor(A.lambda + t * A.nmat * MAX_NUM_LAMBDAS));
+  return pte_one_cell_l(A, mp, eos, scratch, t, NullIndexer());
+}
 } // namespace
+} // extern "C++"
 
+int ref_pte_solve_cached(int solver, void **eos_handles, int nmat, int64_t ncell, double *rho,
+                         double *vfrac, double *sie, double *temp, double *press,
+                         const double *sie_tot_in, const double *vfrac_tot_in,
+                         const double *Tguess_in, const sgx_mix_params *params,
+                         uint64_t *status, double *residual, double *Tguess_out, double *lambda,
+                         int nthreads);
 int ref_pte_solve(int solver, void **eos_handles, int nmat, int64_t ncell, double *rho,
                   double *vfrac, double *sie, double *temp, double *press,
                   const double *sie_tot_in, const double *vfrac_tot_in,
                   const double *Tguess_in, const sgx_mix_params *params, uint64_t *status,
                   double *residual, double *Tguess_out, int nthreads) {
+  return ref_pte_solve_cached(solver, eos_handles, nmat, ncell, rho, vfrac, sie, temp, press,
+                              sie_tot_in, vfrac_tot_in, Tguess_in, params, status, residual,
+                              Tguess_out, nullptr, nthreads);
+}
+// lambda: per-cell CacheAccessor storage [ncell][nmat][MAX_NUM_LAMBDAS], or null (NullIndexer)
+int ref_pte_solve_cached(int solver, void **eos_handles, int nmat, int64_t ncell, double *rho,
+                         double *vfrac, double *sie, double *temp, double *press,
+                         const double *sie_tot_in, const double *vfrac_tot_in,
+                         const double *Tguess_in, const sgx_mix_params *params,
+                         uint64_t *status, double *residual, double *Tguess_out, double *lambda,
+                         int nthreads) {
   const MixParams mp = to_params(params);
   std::vector<EOS> eos_vec(nmat);
   for (int m = 0; m < nmat; ++m)
     eos_vec[m] = *static_cast<EOS *>(eos_handles[m]);
   const PteArgs A{solver, nmat, rho, vfrac, sie, temp, press, sie_tot_in, vfrac_tot_in,
-                  Tguess_in, status, residual, Tguess_out};
+                  Tguess_in, status, residual, Tguess_out, lambda};
   const int nscr = (int)std::max<std::size_t>(
       std::max<std::size_t>(PTESolverRhoTRequiredScratch(nmat), PTESolverPTRequiredScratch(nmat)),
-      std::max<std::size_t>(PTESolverFixedTRequiredScratch(nmat),
+      std::max<std::size_t>(std::max<std::size_t>(PTESolverFixedTRequiredScratch(nmat),
+                                                  PTESolverFixedPRequiredScratch(nmat)),
                             PTESolverRhoURequiredScratch(nmat)));
 #ifdef SGREF_KOKKOS
   { // the reference test's own shape: one portableFor over cells, per-cell scratch slices
@@ -734,6 +768,37 @@ int ref_pte_solve(int solver, void **eos_handles, int nmat, int64_t ncell, doubl
     }
   }
   return rc;
+}
+
+// The reference's own get_sg_eos (eos/get_sg_eos.cpp:36-280; Kokkos-only code, so only the
+// Kokkos build of this library has it).  eos_handles[k] are this harness's EOS objects.
+#ifdef SGREF_KOKKOS
+// the reference's C entry point (eos/singularity_eos.hpp:114-137, defined in get_sg_eos.cpp)
+int get_sg_eos(int nmat, int ncell, int cell_dim, int input_int, int *eos_offsets,
+               singularity::EOS *eos, int *offsets, double *press, double *pmax, double *vol,
+               double *spvol, double *sie, double *temp, double *bmod, double *dpde, double *cv,
+               double *frac_mass, double *frac_vol, double *frac_ie, double *frac_bmod,
+               double *frac_dpde, double *frac_cv, double mass_frac_cutoff);
+#endif
+int ref_get_sg_eos(int nmat, int ncell, int cell_dim, int input_int, int *eos_offsets,
+                   void **eos_handles, int neos, int *offsets, double *press, double *pmax,
+                   double *vol, double *spvol, double *sie, double *temp, double *bmod,
+                   double *dpde, double *cv, double *frac_mass, double *frac_vol,
+                   double *frac_ie, double *frac_bmod, double *frac_dpde, double *frac_cv,
+                   double mass_frac_cutoff) {
+#ifdef SGREF_KOKKOS
+  kokkos_init_once(0);
+  std::vector<EOS> eos_vec(neos);
+  for (int k = 0; k < neos; ++k)
+    eos_vec[k] = *static_cast<EOS *>(eos_handles[k]);
+  return guarded([&]() {
+    get_sg_eos(nmat, ncell, cell_dim, input_int, eos_offsets, eos_vec.data(), offsets, press,
+               pmax, vol, spvol, sie, temp, bmod, dpde, cv, frac_mass, frac_vol, frac_ie,
+               frac_bmod, frac_dpde, frac_cv, mass_frac_cutoff);
+  });
+#else
+  return -99; // PORTABILITY_STRATEGY_NONE: the reference's get_sg_eos is an empty function
+#endif
 }
 
 // ApproxTemperatureFromRhoMatU alone (closure/mixed_cell_models.hpp:790-847)

@@ -90,7 +90,7 @@ METHOD_NAMES = {
     GAMMA_FROM_RHO_T: "GruneisenParamFromDensityTemperature",
     GAMMA_FROM_RHO_E: "GruneisenParamFromDensityInternalEnergy",
 }
-PTE_RHOT, PTE_PT, PTE_FIXED_T, PTE_RHOU = 0, 1, 2, 3
+PTE_RHOT, PTE_PT, PTE_FIXED_T, PTE_RHOU, PTE_FIXED_P = 0, 1, 2, 3, 4
 PTE_NSTATS = 64
 
 
@@ -151,6 +151,8 @@ PROTOTYPES = {
     "sgx_mix_params_default": (None, [C.POINTER(MixParams)]),
     "sgx_pte_solve": (C.c_int, [C.c_int, C.POINTER(_VP), C.c_int, _I64] + [_VP] * 8 +
                       [C.POINTER(MixParams), _VP, _VP, _VP, _VP]),
+    "sgx_pte_solve_cached": (C.c_int, [C.c_int, C.POINTER(_VP), C.c_int, _I64] + [_VP] * 8 +
+                      [C.POINTER(MixParams), _VP, _VP, _VP, _VP, _VP]),
     "sgx_pte_required_scratch": (C.c_int, [C.c_int, C.c_int]),
     "sgx_pte_solve_host": (C.c_int, [C.c_int, C.POINTER(_VP), C.c_int, _I64] + [_VP] * 8 +
                            [C.POINTER(MixParams), _VP, _VP]),
@@ -158,6 +160,13 @@ PROTOTYPES = {
     "sgx_libm_eval": (C.c_int, [C.c_int, _VP, _VP, _VP, _I64, _VP]),
     "sgx_eos_root_stats": (C.c_int, [_VP, C.POINTER(C.c_uint64), C.c_int]),
     "sgx_eos_retain": (C.c_int, [_VP]),
+    "sgx_eos_serialized_size": (C.c_uint64, [_VP]),
+    "sgx_eos_serialize": (C.c_int, [_VP, _VP, C.c_uint64]),
+    "sgx_eos_deserialize": (C.c_int, [_VP, C.c_uint64, C.POINTER(_VP)]),
+    "sgx_get_sg_eos": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, _VP, C.POINTER(_VP), _VP] +
+                       [_VP] * 15 + [C.c_double]),
+    "sgx_get_sg_eos_device": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, _VP, C.POINTER(_VP),
+                                         _VP] + [_VP] * 15 + [C.c_double, _VP, _VP]),
     "sgx_MinInternalEnergyFromDensity": (C.c_int, [_VP, _VP, _VP, _I64, _VP, C.c_int, _VP]),
     "sgx_InternalEnergyFromDensityPressure": (C.c_int, [_VP, _VP, _VP, _VP, _I64, _VP, C.c_int, _VP]),
     "sgx_EntropyFromDensityTemperature": (C.c_int, [_VP, _VP, _VP, _VP, _I64, _VP, C.c_int, _VP]),

@@ -51,17 +51,21 @@ def _handles(eos_list):
 
 
 def pte_solve(solver, eos_list, rho, vfrac, sie, temp, press, sie_tot=None, vfrac_tot=None,
-              Tguess=None, params=None, status=None, residual=None, stats=None):
-    """Solve all cells.  State tensors are [ncell][nmat] CUDA float64, updated in place."""
-    _require_cuda_f64(rho, vfrac, sie, temp, press, sie_tot, vfrac_tot, Tguess, residual)
+              Tguess=None, params=None, status=None, residual=None, stats=None, lambdas=None):
+    """Solve all cells.  State tensors are [ncell][nmat] CUDA float64, updated in place.
+    lambdas: [ncell][nmat][3] per-material caches (CacheAccessor layout,
+    closure/mixed_cell_models.hpp:307-324) for mixtures with tabulated materials, or None."""
+    _require_cuda_f64(rho, vfrac, sie, temp, press, sie_tot, vfrac_tot, Tguess, residual, lambdas)
     nmat = len(eos_list)
     ncell = rho.shape[0]
     assert rho.shape == (ncell, nmat)
     p = params if params is not None else MixParams()
-    check(_lib.load().sgx_pte_solve(
+    if lambdas is not None:
+        assert lambdas.numel() == ncell * nmat * 3
+    check(_lib.load().sgx_pte_solve_cached(
         int(solver), _handles(eos_list), nmat, ncell, _ptr(rho), _ptr(vfrac), _ptr(sie),
         _ptr(temp), _ptr(press), _ptr(sie_tot), _ptr(vfrac_tot), _ptr(Tguess), C.byref(p),
-        _ptr(status), _ptr(residual), _ptr(stats), _stream()))
+        _ptr(status), _ptr(residual), _ptr(stats), _ptr(lambdas), _stream()))
 
 
 def PTESolverRhoT(eos_list, rho, vfrac, sie, temp, press, **kw):
@@ -81,6 +85,14 @@ def PTESolverFixedT(eos_list, T_true, rho, vfrac, sie, temp, press, **kw):
     """PTESolverFixedT (closure/mixed_cell_models.hpp:1462-1672): the cell temperatures
     `T_true` [ncell] are given; unknowns are the volume fractions."""
     return pte_solve(_lib.PTE_FIXED_T, eos_list, rho, vfrac, sie, temp, press, Tguess=T_true,
+                     **kw)
+
+
+def PTESolverFixedP(eos_list, P_true, rho, vfrac, sie, temp, press, **kw):
+    """PTESolverFixedP (closure/mixed_cell_models.hpp:1674-1932): the cell pressures `P_true`
+    [ncell] are given; unknowns are the volume fractions and the temperature.  params must have
+    iterate_t_guess = 0 (see include/sgx_b200.h)."""
+    return pte_solve(_lib.PTE_FIXED_P, eos_list, rho, vfrac, sie, temp, press, Tguess=P_true,
                      **kw)
 
 
@@ -107,3 +119,29 @@ def set_eos_3mat_analytic():
                         0.001074e10)
     dp = DavisProducts(0.798311, 0.58, 1.35, 2.66182, 0.75419, 3.2e10, 0.001072e10)
     return [gr, dr, dp]
+
+
+def get_sg_eos(eos_list, eos_offsets, offsets, press, pmax, vol, spvol, sie, temp, bmod, dpde, cv,
+               frac_mass, frac_vol, frac_ie, frac_bmod=None, frac_dpde=None, frac_cv=None,
+               input_int=1, mass_frac_cutoff=1e-16):
+    """get_sg_eos (eos/get_sg_eos.cpp:36-58) on numpy HOST arrays, the reference's own memory
+    contract: per-cell arrays [cell_dim], per-material arrays Fortran-ordered (cell_dim, nmat),
+    1-based int32 offsets.  (rho, e) input conditions only."""
+    import numpy as np
+
+    nmat = len(eos_offsets)
+    ncell = len(offsets)
+    cell_dim = press.shape[0]
+    eo = np.ascontiguousarray(eos_offsets, dtype=np.int32)
+    of = np.ascontiguousarray(offsets, dtype=np.int32)
+    for a in (frac_mass, frac_vol, frac_ie, frac_bmod, frac_dpde, frac_cv):
+        assert a is None or (a.flags.f_contiguous and a.shape == (cell_dim, nmat))
+
+    def p(a):
+        return None if a is None else a.ctypes.data
+
+    check(_lib.load().sgx_get_sg_eos(
+        nmat, ncell, cell_dim, int(input_int), eo.ctypes.data, _handles(eos_list), of.ctypes.data,
+        p(press), p(pmax), p(vol), p(spvol), p(sie), p(temp), p(bmod), p(dpde), p(cv),
+        p(frac_mass), p(frac_vol), p(frac_ie), p(frac_bmod), p(frac_dpde), p(frac_cv),
+        float(mass_frac_cutoff)))

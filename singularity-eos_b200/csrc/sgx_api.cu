@@ -93,6 +93,39 @@ HostPin::HostPin(const void *p, size_t bytes) {
     cudaGetLastError(); // clear; the copies still work from pageable memory
 }
 
+cudaError_t scratch_alloc_async(void **ptr, size_t bytes, cudaStream_t s) {
+  static cudaMemPool_t pools[64] = {nullptr};
+  static std::atomic<int> made[64];
+  int dev = 0;
+  cudaError_t err = cudaGetDevice(&dev);
+  if (err != cudaSuccess) return err;
+  if (dev < 0 || dev >= 64) return cudaMallocAsync(ptr, bytes, s);
+  if (made[dev].load(std::memory_order_acquire) != 2) {
+    int expect = 0;
+    if (made[dev].compare_exchange_strong(expect, 1)) {
+      cudaMemPoolProps props = {};
+      props.allocType = cudaMemAllocationTypePinned;
+      props.handleTypes = cudaMemHandleTypeNone;
+      props.location.type = cudaMemLocationTypeDevice;
+      props.location.id = dev;
+      cudaMemPool_t pool = nullptr;
+      if (cudaMemPoolCreate(&pool, &props) == cudaSuccess) {
+        unsigned long long never = ~0ull;
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &never);
+        pools[dev] = pool;
+      } else {
+        cudaGetLastError(); // fall back to the default pool below
+      }
+      made[dev].store(2, std::memory_order_release);
+    } else {
+      while (made[dev].load(std::memory_order_acquire) != 2) {
+      }
+    }
+  }
+  if (pools[dev]) return cudaMallocFromPoolAsync(ptr, bytes, pools[dev], s);
+  return cudaMallocAsync(ptr, bytes, s);
+}
+
 int ensure_host_streams(sgx_eos_s *e) {
   for (int k = 0; k < 4; ++k)
     if (e->host_streams[k] == nullptr)
@@ -643,6 +676,34 @@ using namespace sgx;
 // =======================================================================================
 // extern "C"
 // =======================================================================================
+// the raw .sp5 contents + flags a Spiner handle was created from
+static int grid_points(const sgx_grid1d &g) {
+  int n = 0;
+  for (int p = 0; p < g.ngrids && p < 3; ++p)
+    n += g.npoints[p];
+  return n;
+}
+static std::vector<char> sp5_recipe(int kind, const sgx_sp5_tables *raw, int reproducible,
+                                    int vapor_dome) {
+  Recipe r(kind);
+  const int32_t flags[2] = {reproducible, vapor_dome};
+  r.put(flags, sizeof(flags));
+  r.put(raw, sizeof(*raw));
+  const size_t nr = grid_points(raw->lrho), nt = grid_points(raw->lT), ne = grid_points(raw->lE);
+  const double *t2[9] = {raw->P, raw->sie, raw->bMod, raw->dPdRho, raw->dPdE, raw->dTdRho,
+                         raw->dTdE, raw->dEdRho, raw->dEdT};
+  for (const double *p : t2)
+    r.put_array(p, nr * nt);
+  const double *c1[4] = {raw->PCold, raw->sieCold, raw->bModCold, raw->dPdRhoCold};
+  for (const double *p : c1)
+    r.put_array(p, nr);
+  const double *e2[8] = {raw->T_re, raw->P_re, raw->bMod_re, raw->dPdRho_re, raw->dPdE_re,
+                         raw->dTdRho_re, raw->dTdE_re, raw->dEdRho_re};
+  for (const double *p : e2)
+    r.put_array(p, nr * ne);
+  return std::move(r.bytes);
+}
+
 extern "C" {
 
 int sgx_abi_version(void) { return SGX_ABI_VERSION; }
@@ -667,6 +728,12 @@ int sgx_eos_create_ideal(double gm1, double Cv, sgx_eos_t *out) {
   if (rc) return rc;
   e->analytic.ideal.Cv = Cv;
   e->analytic.ideal.gm1 = gm1;
+  {
+    Recipe r(SGX_EOS_IDEAL);
+    const double a[2] = {gm1, Cv};
+    r.put(a, sizeof(a));
+    e->recipe = std::move(r.bytes);
+  }
   *out = e;
   return SGX_OK;
 }
@@ -689,6 +756,12 @@ int sgx_eos_create_gruneisen(double C0, double s1, double s2, double s3, double 
   g.P0 = P0;
   g.Cv = Cv;
   g.rho_max = rho_max > 0 ? rho_max : 0.99 * gruneisen_rho_max(s1, s2, s3, rho0);
+  {
+    Recipe r(SGX_EOS_GRUNEISEN);
+    const double a[11] = {C0, s1, s2, s3, G0, b, rho0, T0, P0, Cv, rho_max};
+    r.put(a, sizeof(a));
+    e->recipe = std::move(r.bytes);
+  }
   *out = e;
   return SGX_OK;
 }
@@ -714,6 +787,12 @@ int sgx_eos_create_davis_reactants(double rho0, double e0, double P0, double T0,
   d.i1pa = 1.0 / (1.0 + alpha);
   d.Cv0 = Cv0;
   d.A2oB = A * A / B;
+  {
+    Recipe r(SGX_EOS_DAVIS_REACTANTS);
+    const double a[11] = {rho0, e0, P0, T0, A, B, C, G0, Z, alpha, Cv0};
+    r.put(a, sizeof(a));
+    e->recipe = std::move(r.bytes);
+  }
   *out = e;
   return SGX_OK;
 }
@@ -733,6 +812,12 @@ int sgx_eos_create_davis_products(double a, double b, double k, double n, double
   d.pc = pc;
   d.Cv = Cv;
   d.Ts_coef = std::pow(2.0, -a * ratio(b, n)) * pc * ratio(vc, Cv * (k - 1 + a));
+  {
+    Recipe r(SGX_EOS_DAVIS_PRODUCTS);
+    const double p7[7] = {a, b, k, n, vc, pc, Cv};
+    r.put(p7, sizeof(p7));
+    e->recipe = std::move(r.bytes);
+  }
   *out = e;
   return SGX_OK;
 }
@@ -748,6 +833,7 @@ int sgx_eos_create_spiner_rhot(const sgx_sp5_tables *raw, int reproducibility_mo
     *out = nullptr;
     return rc;
   }
+  e->recipe = sp5_recipe(SGX_EOS_SPINER_RHOT, raw, reproducibility_mode, pmin_vapor_dome);
   *out = e;
   return SGX_OK;
 }
@@ -763,6 +849,7 @@ int sgx_eos_create_spiner_rhosie(const sgx_sp5_tables *raw, int reproducibility_
     *out = nullptr;
     return rc;
   }
+  e->recipe = sp5_recipe(SGX_EOS_SPINER_RHOSIE, raw, reproducibility_mode, pmin_vapor_dome);
   *out = e;
   return SGX_OK;
 }
@@ -805,6 +892,7 @@ int sgx_eos_destroy(sgx_eos_t e) {
   if (e->pinned) cudaFreeHost(e->pinned);
   if (e->dscratch) cudaFree(e->dscratch);
   if (e->root_stats) cudaFree(e->root_stats);
+  if (e->dev_struct) cudaFree(e->dev_struct);
   if (e->own_stream) cudaStreamDestroy(e->own_stream);
   for (int k = 0; k < 4; ++k)
     if (e->host_streams[k]) cudaStreamDestroy(e->host_streams[k]);
@@ -1158,6 +1246,83 @@ int sgx_FillEos_host(sgx_eos_t e, double *rhos, double *temps, double *energies,
   return rc;
 }
 #undef SGX_PIPE_TRY
+
+// ---- Serialize / DeSerialize (eos/eos_base.hpp:756-798) -----------------------------------
+uint64_t sgx_eos_serialized_size(sgx_eos_t e) { return e ? (uint64_t)e->recipe.size() : 0; }
+int sgx_eos_serialize(sgx_eos_t e, char *dst, uint64_t cap) {
+  if (!e || !dst) return fail(SGX_ERR_INVALID, "null argument");
+  if (e->recipe.empty()) return fail(SGX_ERR_UNSUPPORTED, "this handle carries no recipe");
+  if (cap < e->recipe.size())
+    return fail(SGX_ERR_INVALID, "buffer of %llu bytes, need %zu", (unsigned long long)cap,
+                e->recipe.size());
+  std::memcpy(dst, e->recipe.data(), e->recipe.size());
+  return SGX_OK;
+}
+int sgx_eos_deserialize(const char *src, uint64_t nbytes, sgx_eos_t *out) {
+  if (!src || !out) return fail(SGX_ERR_INVALID, "null argument");
+  *out = nullptr;
+  RecipeReader rd(src, (size_t)nbytes);
+  char magic[8];
+  int32_t kind = -1;
+  if (!rd.get(magic, 8) || std::memcmp(magic, "SGXEOS01", 8) != 0 || !rd.get(&kind, 4))
+    return fail(SGX_ERR_INVALID, "not an sgx EOS byte stream");
+  double a[11];
+  switch (kind) {
+  case SGX_EOS_IDEAL:
+    if (!rd.get(a, 2 * sizeof(double))) break;
+    return sgx_eos_create_ideal(a[0], a[1], out);
+  case SGX_EOS_GRUNEISEN:
+    if (!rd.get(a, 11 * sizeof(double))) break;
+    return sgx_eos_create_gruneisen(a[0], a[1], a[2], a[3], a[4], a[5], a[6], a[7], a[8], a[9],
+                                    a[10], out);
+  case SGX_EOS_DAVIS_REACTANTS:
+    if (!rd.get(a, 11 * sizeof(double))) break;
+    return sgx_eos_create_davis_reactants(a[0], a[1], a[2], a[3], a[4], a[5], a[6], a[7], a[8],
+                                          a[9], a[10], out);
+  case SGX_EOS_DAVIS_PRODUCTS:
+    if (!rd.get(a, 7 * sizeof(double))) break;
+    return sgx_eos_create_davis_products(a[0], a[1], a[2], a[3], a[4], a[5], a[6], out);
+  case SGX_EOS_SPINER_RHOT:
+  case SGX_EOS_SPINER_RHOSIE: {
+    int32_t flags[2];
+    sgx_sp5_tables raw;
+    if (!rd.get(flags, sizeof(flags)) || !rd.get(&raw, sizeof(raw))) break;
+    std::vector<double> store[21];
+    const double **members[21] = {
+        &raw.P,       &raw.sie,       &raw.bMod,       &raw.dPdRho,    &raw.dPdE,
+        &raw.dTdRho,  &raw.dTdE,      &raw.dEdRho,     &raw.dEdT,      &raw.PCold,
+        &raw.sieCold, &raw.bModCold,  &raw.dPdRhoCold, &raw.T_re,      &raw.P_re,
+        &raw.bMod_re, &raw.dPdRho_re, &raw.dPdE_re,    &raw.dTdRho_re, &raw.dTdE_re,
+        &raw.dEdRho_re};
+    bool good = true;
+    for (int k = 0; k < 21 && good; ++k)
+      good = rd.get_array(store[k], *members[k]);
+    if (!good) break;
+    return kind == SGX_EOS_SPINER_RHOT
+               ? sgx_eos_create_spiner_rhot(&raw, flags[0], flags[1], out)
+               : sgx_eos_create_spiner_rhosie(&raw, flags[0], flags[1], out);
+  }
+  case SGX_EOS_HELMHOLTZ: {
+    sgx_helm_options o;
+    std::vector<double> store;
+    const double *raw = nullptr;
+    if (!rd.get(&o, sizeof(o)) || !rd.get_array(store, raw)) break;
+    sgx_eos_s *e;
+    int rc = new_handle(SGX_EOS_HELMHOLTZ, &e);
+    if (rc) return rc;
+    rc = build_helmholtz_raw(raw, store.size(), &o, e);
+    if (rc) {
+      sgx_eos_destroy(e);
+      return rc;
+    }
+    *out = e;
+    return SGX_OK;
+  }
+  default:
+    return fail(SGX_ERR_INVALID, "unknown EOS kind %d in the byte stream", kind);
+  }
+  return fail(SGX_ERR_INVALID, "truncated EOS byte stream");
+}
 
 int sgx_eos_root_stats(sgx_eos_t e, uint64_t out[2], int reset) {
   if (!e || !out) return fail(SGX_ERR_INVALID, "null argument");

@@ -53,17 +53,33 @@ bool read_all(const char *path, std::vector<double> &vals, size_t expect) {
 int build_helmholtz(const char *path, const sgx_helm_options *opt, sgx_eos_s *e) {
   using namespace helm;
   if (!path) return fail(SGX_ERR_INVALID, "null Helmholtz table path");
+  const size_t nnode = (size_t)NTEMP * NRHO;
+  std::vector<double> raw;
+  if (!read_all(path, raw, nnode * 21))
+    return fail(SGX_ERR_IO, "HelmElectrons file %s not found or short (need %zu numbers)", path,
+                nnode * 21);
+  return build_helmholtz_raw(raw.data(), raw.size(), opt, e);
+}
+
+// From the 21 x 101 x 271 numbers of the table file, in file order (also the deserialization path)
+int build_helmholtz_raw(const double *raw, size_t nraw, const sgx_helm_options *opt,
+                        sgx_eos_s *e) {
+  using namespace helm;
+  const size_t nnode = (size_t)NTEMP * NRHO;
+  if (!raw || nraw != nnode * 21)
+    return fail(SGX_ERR_INVALID, "Helmholtz table: need %zu numbers", nnode * 21);
   sgx_helm_options o;
   if (opt) {
     o = *opt;
   } else {
     sgx_helm_default_options(&o);
   }
-  const size_t nnode = (size_t)NTEMP * NRHO;
-  std::vector<double> raw;
-  if (!read_all(path, raw, nnode * 21))
-    return fail(SGX_ERR_IO, "HelmElectrons file %s not found or short (need %zu numbers)", path,
-                nnode * 21);
+  { // the creation recipe, for sgx_eos_serialize
+    Recipe r(SGX_EOS_HELMHOLTZ);
+    r.put(&o, sizeof(o));
+    r.put_array(raw, nraw);
+    e->recipe = std::move(r.bytes);
+  }
   // node(j, i, block, col)
   size_t block_off[4];
   block_off[0] = 0;

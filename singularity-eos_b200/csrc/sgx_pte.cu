@@ -14,7 +14,7 @@
 
 namespace sgx {
 
-static MixParamsDev to_dev(const sgx_mix_params *p) {
+MixParamsDev mix_params_to_dev(const sgx_mix_params *p) {
   sgx_mix_params d;
   if (!p) {
     sgx_mix_params_default(&d);
@@ -93,6 +93,8 @@ void sgx_mix_params_default(sgx_mix_params *p) {
 int sgx_pte_required_scratch(int solver, int nmat) {
   if (solver == SGX_PTE_RHOT) return nmat * nmat + 4 * nmat + 6 * nmat; // :873-878
   if (solver == SGX_PTE_FIXED_T) return nmat * nmat + 4 * nmat + 4 * nmat; // :1450-1456
+  if (solver == SGX_PTE_FIXED_P)                                          // :1674-1680
+    return (nmat + 1) * (nmat + 1) + 4 * (nmat + 1) + 2 * nmat + 3 * nmat;
   if (solver == SGX_PTE_RHOU) return 4 * nmat * nmat + 8 * nmat + 8 * nmat; // :1924-1929
   return 2 * 2 + 4 * 2 + 2 * nmat;                                       // :1198-1203
 }
@@ -102,16 +104,34 @@ int sgx_pte_solve(int solver, const sgx_eos_t *eos, int nmat, int64_t ncell, dou
                   const double *sie_tot, const double *vfrac_tot, const double *Tguess,
                   const sgx_mix_params *params, uint64_t *status, double *residual,
                   uint64_t *stats, sgx_stream_t stream) {
+  return sgx_pte_solve_cached(solver, eos, nmat, ncell, rho, vfrac, sie, temp, press, sie_tot,
+                              vfrac_tot, Tguess, params, status, residual, stats, nullptr,
+                              stream);
+}
+
+int sgx_pte_solve_cached(int solver, const sgx_eos_t *eos, int nmat, int64_t ncell, double *rho,
+                         double *vfrac, double *sie, double *temp, double *press,
+                         const double *sie_tot, const double *vfrac_tot, const double *Tguess,
+                         const sgx_mix_params *params, uint64_t *status, double *residual,
+                         uint64_t *stats, double *lambda, sgx_stream_t stream) {
   DeviceGuard guard;
   if (!eos) return fail(SGX_ERR_INVALID, "null EOS array");
   if (solver != SGX_PTE_RHOT && solver != SGX_PTE_PT && solver != SGX_PTE_FIXED_T &&
-      solver != SGX_PTE_RHOU)
+      solver != SGX_PTE_RHOU && solver != SGX_PTE_FIXED_P)
     return fail(SGX_ERR_INVALID, "unknown PTE solver %d", solver);
   if (solver == SGX_PTE_RHOU && (nmat < 2 || nmat > 3))
     return fail(SGX_ERR_UNSUPPORTED, "PTESolverRhoU: nmat=%d, this build instantiates 2..3",
                 nmat);
   if (solver == SGX_PTE_FIXED_T && !Tguess)
     return fail(SGX_ERR_INVALID, "PTESolverFixedT needs the temperature array (Tguess)");
+  if (solver == SGX_PTE_FIXED_P && !Tguess)
+    return fail(SGX_ERR_INVALID, "PTESolverFixedP needs the pressure array (Tguess)");
+  if (solver == SGX_PTE_FIXED_P && (!params || params->iterate_t_guess))
+    return fail(SGX_ERR_UNSUPPORTED,
+                "PTESolverFixedP with MixParams::iterate_t_guess: the reference's GetTguess reads "
+                "uscale / utotal_scale before FixedP::Init sets them "
+                "(mixed_cell_models.hpp:536-538 vs 1747-1755), its answer is undefined; pass "
+                "iterate_t_guess = 0");
   if (nmat < 1 || nmat > 4)
     return fail(SGX_ERR_UNSUPPORTED, "nmat=%d: this build instantiates 1..4 materials", nmat);
   if (ncell < 0) return fail(SGX_ERR_INVALID, "negative ncell");
@@ -119,19 +139,34 @@ int sgx_pte_solve(int solver, const sgx_eos_t *eos, int nmat, int64_t ncell, dou
     return fail(SGX_ERR_INVALID, "null state array");
   EosSet set;
   set.nmat = nmat;
+  bool tabulated = false;
   for (int m = 0; m < nmat; ++m) {
     if (!eos[m]) return fail(SGX_ERR_INVALID, "null EOS handle for material %d", m);
-    if (eos[m]->kind > SGX_EOS_DAVIS_PRODUCTS)
-      return fail(SGX_ERR_UNSUPPORTED,
-                  "PTE with tabulated materials is not built yet (material %d kind %d)", m,
-                  eos[m]->kind);
-    set.e[m] = eos[m]->analytic;
+    if (eos[m]->device != eos[0]->device)
+      return fail(SGX_ERR_INVALID, "material %d lives on another device", m);
+    if (eos[m]->kind == SGX_EOS_SPINER_RHOT || eos[m]->kind == SGX_EOS_SPINER_RHOSIE) {
+      tabulated = true;
+      set.e[m].kind = eos[m]->kind;
+      if (eos[m]->kind == SGX_EOS_SPINER_RHOT)
+        set.e[m].rhot = static_cast<const SpinerRhoT *>(eos[m]->dev_struct);
+      else
+        set.e[m].rhosie = static_cast<const SpinerRhoSie *>(eos[m]->dev_struct);
+    } else if (eos[m]->kind > SGX_EOS_DAVIS_PRODUCTS) {
+      return fail(SGX_ERR_UNSUPPORTED, "PTE: material %d is EOS kind %d (Helmholtz mixtures are "
+                  "not built)", m, eos[m]->kind);
+    } else {
+      set.e[m] = eos[m]->analytic;
+    }
   }
+  if (tabulated && (solver == SGX_PTE_RHOU || solver == SGX_PTE_FIXED_P))
+    return fail(SGX_ERR_UNSUPPORTED,
+                "PTESolverRhoU / PTESolverFixedP with tabulated materials are not built");
+  if (lambda && !tabulated) lambda = nullptr; // the analytic models take no lambda
   cudaError_t err = cudaSetDevice(eos[0]->device);
   if (err != cudaSuccess)
     return fail(SGX_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(err));
   if (ncell == 0) return SGX_OK;
-  const MixParamsDev prm = to_dev(params);
+  const MixParamsDev prm = mix_params_to_dev(params);
   cudaStream_t s = (cudaStream_t)stream;
   const bool is_bench_mix = nmat == 3 && set.e[0].kind == SGX_EOS_GRUNEISEN &&
                             set.e[1].kind == SGX_EOS_DAVIS_REACTANTS &&
@@ -142,10 +177,14 @@ int sgx_pte_solve(int solver, const sgx_eos_t *eos, int nmat, int64_t ncell, dou
 #define SGX_PTE_ARGS                                                                     \
   set, prm, rho, vfrac, sie, temp, press, sie_tot, vfrac_tot, Tguess, status, residual,   \
       stats, ncell, s
+  if (tabulated)
+    return launch_pte_tab(solver, set, prm, rho, vfrac, sie, temp, press, sie_tot, vfrac_tot,
+                          Tguess, status, residual, stats, ncell, s, lambda);
   if (solver == SGX_PTE_RHOT) return launch_pte_rhot(set, is_bench_mix, prm, rho, vfrac, sie, temp, press, sie_tot,
                            vfrac_tot, Tguess, status, residual, stats, ncell, s);
   if (solver == SGX_PTE_RHOU) return launch_pte_rhou(set, is_bench_mix, SGX_PTE_TAIL);
   if (solver == SGX_PTE_FIXED_T) return launch_pte_fixedt(set, is_bench_mix, SGX_PTE_TAIL);
+  if (solver == SGX_PTE_FIXED_P) return launch_pte_fixedp(set, is_bench_mix, SGX_PTE_TAIL);
   if (is_bench_mix) return launch_pte_percell<3, Mix3GrDrDp, SGX_PTE_PT>(SGX_PTE_ARGS);
   switch (nmat) {
   case 1:

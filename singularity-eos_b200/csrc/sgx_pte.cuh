@@ -54,7 +54,10 @@ struct SolverStatusDev {
   double residual;
 };
 
-// One material = tagged union of the analytic models (the Variant of the reference).
+struct SpinerRhoT;
+struct SpinerRhoSie;
+// One material = tagged union of the analytic models (the Variant of the reference); the
+// tabulated models travel as the address of the handle's device copy (sgx_pte_tab.cuh).
 struct AnyEos {
   int kind; // enum sgx_eos_kind
   union {
@@ -62,6 +65,8 @@ struct AnyEos {
     Gruneisen gr;
     DavisReactants dr;
     DavisProducts dp;
+    const SpinerRhoT *rhot;
+    const SpinerRhoSie *rhosie;
   };
 };
 struct EosSet {
@@ -983,6 +988,168 @@ struct FixedT : public Base<NM, NM, Eos> {
       sie[m] = ratio(u[m], rhobar[m]);
       u[m] = ratio(u[m], uscale);
       press[m] = ratio(eos.P_from_rho_T(m, rho[m], Tequil), uscale);
+    }
+    Residual();
+    return B::ResidualNorm();
+  }
+};
+
+// ---------------------------------------------------------------------------------------
+// PTESolverFixedP (:1674-1932): pressure given; unknowns are the NM volume fractions and the
+// temperature; equations: each material's pressure equals P, and the volume sum.
+// Init calls GetTguess, whose optional Newton step (MixParams::iterate_t_guess) reads uscale and
+// utotal_scale BEFORE this solver's Init sets them (:1747-1755 vs :536-538; the base constructor
+// :371-387 leaves both uninitialised), so the reference's answer is only defined with
+// iterate_t_guess == false: the C ABI rejects the other setting.
+// ---------------------------------------------------------------------------------------
+template <int NM, class Eos>
+struct FixedP : public Base<NM, NM + 1, Eos> {
+  static constexpr int NEQ = NM + 1;
+  using B = Base<NM, NM + 1, Eos>;
+  using B::dx;
+  using B::eos;
+  using B::jacobian;
+  using B::params_;
+  using B::press;
+  using B::residual;
+  using B::rho;
+  using B::rhobar;
+  using B::sie;
+  using B::temp;
+  using B::Tnorm;
+  using B::u;
+  using B::uscale;
+  using B::vfrac;
+  double dpdv[NM], dpdT[NM], vtemp[NM];
+  double Tequil, Ttemp, Pequil;
+
+  __device__ FixedP(const Eos &e, const MixParamsDev &p) : B(e, p) {}
+
+  // Init (:1741-1774).  The kernel puts P into Pequil and 0 into Tnorm (ctor :1731-1739).
+  __device__ inline double Init() {
+    B::InitRhoBarandRho();
+    const double Tguess = B::GetTguess();
+    Tnorm = Tguess;
+    uscale = stdmax(fabs(Pequil), 1.0e-14);
+#pragma unroll
+    for (int m = 0; m < NM; m++) {
+      temp[m] = 1.0;
+      sie[m] = eos.e_from_rho_T(m, rho[m], Tguess);
+    }
+#pragma unroll
+    for (int m = 0; m < NM; ++m) {
+      u[m] = ratio(sie[m] * rhobar[m], uscale);
+      press[m] = ratio(eos.P_from_rho_T(m, rho[m], Tguess), uscale);
+    }
+    Residual();
+    Tequil = temp[0];
+    Ttemp = Tequil;
+    return B::ResidualNorm();
+  }
+  SGX_D void Fixup() {}
+  SGX_D void Finalize() { // base Finalize (:351-357)
+#pragma unroll
+    for (int m = 0; m < NM; m++) {
+      temp[m] *= Tnorm;
+      u[m] *= uscale;
+      press[m] *= uscale;
+    }
+  }
+  SGX_D void Residual() {
+    const double vsum = sum_neumaier(vfrac, NM);
+#pragma unroll
+    for (int m = 0; m < NM; ++m)
+      residual[m] = ratio(Pequil, uscale) - press[m];
+    residual[NM] = B::vfrac_total - vsum;
+  }
+  SGX_D void CheckPTE(bool &converged, bool &acceptable) const {
+    double error_p = 0;
+#pragma unroll
+    for (int m = 0; m < NM; ++m)
+      error_p += residual[m] * residual[m];
+    error_p = sqrt(error_p);
+    error_p *= uscale;
+    const double error_v = fabs(residual[NEQ - 1]);
+    const bool converged_p =
+        (error_p < params_.pte_rel_tolerance_p || error_p < params_.pte_abs_tolerance_p);
+    const bool converged_v = error_v < params_.pte_rel_tolerance_v;
+    const bool acceptable_p = (error_p < params_.pte_rel_tolerance_p_sufficient ||
+                               error_p < params_.pte_abs_tolerance_p_sufficient);
+    const bool acceptable_v = error_v < params_.pte_rel_tolerance_v_sufficient;
+    converged = converged_p && converged_v;
+    acceptable = acceptable_p && acceptable_v;
+  }
+  __device__ inline void Jacobian() {
+#pragma unroll
+    for (int m = 0; m < NM; m++) {
+      const double dv = (vfrac[m] < 0.5 ? 1.0 : -1.0) * vfrac[m] * params_.derivative_eps;
+      const double vf_pert = vfrac[m] + dv;
+      const double rho_pert = ratio(rhobar[m], vf_pert);
+      double e_pert = 0.0;
+      double p_pert = ratio(
+          B::GetPressureFromPreferred(m, rho_pert, Tnorm * Tequil, e_pert, true), uscale);
+      dpdv[m] = stdmin(ratio((p_pert - press[m]), dv), -fabs(params_.pte_max_dpdv));
+      const double dT = Tequil * params_.derivative_eps;
+      p_pert = ratio(
+          B::GetPressureFromPreferred(m, rho[m], Tnorm * (Tequil + dT), e_pert, true), uscale);
+      dpdT[m] = ratio((p_pert - press[m]), dT);
+    }
+#pragma unroll
+    for (int i = 0; i < NEQ * NEQ; ++i)
+      jacobian[i] = 0.0;
+#pragma unroll
+    for (int m = 0; m < NM; m++) {
+      jacobian[m * NEQ + m] = dpdv[m];
+      jacobian[m * NEQ + NM] = dpdT[m];
+    }
+#pragma unroll
+    for (int m = 0; m < NEQ - 1; ++m)
+      jacobian[(NEQ - 1) * NEQ + m] = 1.0;
+  }
+  __device__ inline double ScaleDx() {
+    double scale = 1.0;
+#pragma unroll
+    for (int m = 0; m < NM; ++m) {
+      if (scale * dx[m] < -params_.vfrac_safety_fac * vfrac[m]) {
+        scale = -params_.vfrac_safety_fac * ratio(vfrac[m], dx[m]);
+      }
+    }
+    const double Tnew = Tequil + scale * dx[NM];
+#pragma unroll
+    for (int m = 0; m < NM; m++) {
+      const double rho_min =
+          stdmax(eos.RhoPmin(m, Tnorm * Tequil), eos.RhoPmin(m, Tnorm * Tnew));
+      const double alpha_max = ratio(rhobar[m], rho_min);
+      if (alpha_max < vfrac[m]) continue;
+      if (scale * dx[m] > 0.5 * (alpha_max - vfrac[m])) {
+        scale = 0.5 * ratio(alpha_max - vfrac[m], dx[m]);
+      }
+    }
+    if (scale * dx[NM] < -0.95 * Tequil) {
+      scale = -0.95 * ratio(Tequil, dx[NM]);
+    }
+#pragma unroll
+    for (int i = 0; i < NEQ; ++i)
+      dx[i] *= scale;
+    return scale;
+  }
+  __device__ inline double TestUpdate(const double scale, const bool cache_state = false) {
+    if (cache_state) {
+      Ttemp = Tequil;
+#pragma unroll
+      for (int m = 0; m < NM; ++m)
+        vtemp[m] = vfrac[m];
+    }
+    Tequil = Ttemp + scale * dx[NM];
+#pragma unroll
+    for (int m = 0; m < NM; ++m) {
+      vfrac[m] = vtemp[m] + scale * dx[m];
+      rho[m] = ratio(rhobar[m], vfrac[m]);
+      u[m] = rhobar[m] * eos.e_from_rho_T(m, rho[m], Tnorm * Tequil);
+      press[m] = ratio(eos.P_from_rho_T(m, rho[m], Tnorm * Tequil), uscale);
+      sie[m] = ratio(u[m], rhobar[m]);
+      u[m] = ratio(u[m], uscale);
+      temp[m] = Tequil;
     }
     Residual();
     return B::ResidualNorm();

@@ -8,6 +8,11 @@
 
 namespace sgx {
 
+// per-cell lambda cache (CacheAccessor, closure/mixed_cell_models.hpp:307-324): only the
+// accessor of sgx_pte_tab.cuh has one
+template <class Acc>
+SGX_D void set_cell_cache(Acc &, double *) {}
+
 template <int NM, class Acc, int SOLVER>
 __global__ void __launch_bounds__(128)
     pte_kernel(const __grid_constant__ EosSet set, const __grid_constant__ MixParamsDev prm,
@@ -16,23 +21,26 @@ __global__ void __launch_bounds__(128)
                const double *__restrict__ sie_tot_in, const double *__restrict__ vfrac_tot_in,
                const double *__restrict__ Tguess_in, unsigned long long *__restrict__ status,
                double *__restrict__ residual, unsigned long long *__restrict__ stats,
-               const int64_t ncell) {
+               const int64_t ncell, double *__restrict__ lambda = nullptr) {
   __shared__ unsigned int s_hist[SGX_PTE_NSTATS];
   if (stats) {
     for (int k = threadIdx.x; k < SGX_PTE_NSTATS; k += blockDim.x)
       s_hist[k] = 0;
     __syncthreads();
   }
-  const Acc eos(set);
+  Acc eos(set);
   const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int64_t nthr = (int64_t)gridDim.x * blockDim.x;
   for (int64_t t = tid; t < ncell; t += nthr) {
+    set_cell_cache(eos, lambda ? lambda + t * (NM * 3) : nullptr);
     using System = typename std::conditional<
         SOLVER == SGX_PTE_RHOT, mix::RhoT<NM, Acc>,
         typename std::conditional<
             SOLVER == SGX_PTE_PT, mix::PT<NM, Acc>,
-            typename std::conditional<SOLVER == SGX_PTE_FIXED_T, mix::FixedT<NM, Acc>,
-                                      mix::RhoU<NM, Acc>>::type>::type>::type;
+            typename std::conditional<
+                SOLVER == SGX_PTE_FIXED_T, mix::FixedT<NM, Acc>,
+                typename std::conditional<SOLVER == SGX_PTE_FIXED_P, mix::FixedP<NM, Acc>,
+                                          mix::RhoU<NM, Acc>>::type>::type>::type>::type;
     System s(eos, prm);
     const int64_t base = t * NM;
 #pragma unroll
@@ -57,6 +65,10 @@ __global__ void __launch_bounds__(128)
     s.vfrac_total = vfrac_tot_in ? vfrac_tot_in[t] : 1.0;
     if constexpr (SOLVER == SGX_PTE_FIXED_T) {
       s.Tnorm = Tguess_in[t]; // T_true (PTESolverFixedT ctor, :1498-1510)
+    } else if constexpr (SOLVER == SGX_PTE_FIXED_P) {
+      s.Pequil = Tguess_in[t]; // P; the ctor hands the base sie_tot = 1, Tnorm = 0 (:1731-1739)
+      s.sie_total = 1.0;
+      s.Tnorm = 0.0;
     } else if (Tguess_in) {
       s.Tnorm = Tguess_in[t];
     } else {
@@ -94,12 +106,13 @@ static int launch_pte_percell(const EosSet &set, const MixParamsDev &prm, double
                               double *vfrac, double *sie, double *temp, double *press,
                               const double *sie_tot, const double *vfrac_tot,
                               const double *Tguess, uint64_t *status, double *residual,
-                              uint64_t *stats, int64_t ncell, cudaStream_t s) {
+                              uint64_t *stats, int64_t ncell, cudaStream_t s,
+                              double *lambda = nullptr) {
   const LaunchCfg c = stream_cfg(ncell, 128, 8);
   pte_kernel<NM, Acc, SOLVER><<<c.blocks, c.threads, 0, s>>>(
       set, prm, rho, vfrac, sie, temp, press, sie_tot, vfrac_tot, Tguess,
       reinterpret_cast<unsigned long long *>(status), residual,
-      reinterpret_cast<unsigned long long *>(stats), ncell);
+      reinterpret_cast<unsigned long long *>(stats), ncell, lambda);
   count_launch();
   SGX_CUDA_OK(cudaGetLastError());
   return SGX_OK;

@@ -17,8 +17,13 @@ static bool percell_variant() {
   return s && strcmp(s, "percell") == 0;
 }
 
+static bool warp_variant() {
+  const char *s = getenv("SGX_PTE_KERNEL");
+  return s && strcmp(s, "warp") == 0;
+}
+
 // Cells go through in chunks: init kernel -> scratch record -> state-machine kernel, both on
-// the caller's stream; the scratch is stream-ordered (cudaMallocAsync): (2*NM+1)*8 B/cell for the
+// the caller's stream; the scratch is stream-ordered (scratch_alloc_async, the library's own pool): (2*NM+1)*8 B/cell for the
 // hand-over record plus one 64-bit cell cursor per chunk.
 static constexpr int64_t kPteChunk = int64_t(1) << 23;
 
@@ -31,8 +36,9 @@ static int launch_sm(const EosSet &set, const MixParamsDev &prm, double *rho, do
   const int64_t nchunk = (ncell + chunk - 1) / chunk;
   const size_t cursor_bytes = ((size_t)nchunk * sizeof(unsigned long long) + 255) & ~size_t(255);
   char *scratch = nullptr;
-  SGX_CUDA_OK(cudaMallocAsync(
-      &scratch, cursor_bytes + (size_t)chunk * (2 * NM + 1) * sizeof(double), s));
+  SGX_CUDA_OK(scratch_alloc_async(
+      reinterpret_cast<void **>(&scratch),
+      cursor_bytes + (size_t)chunk * (2 * NM + 1) * sizeof(double), s));
   unsigned long long *cursors = reinterpret_cast<unsigned long long *>(scratch);
   double *init = reinterpret_cast<double *>(scratch + cursor_bytes);
   cudaError_t err = cudaMemsetAsync(cursors, 0, cursor_bytes, s);
@@ -65,6 +71,40 @@ static int launch_sm(const EosSet &set, const MixParamsDev &prm, double *rho, do
   return SGX_OK;
 }
 
+// The warp-per-cell comparison variant (SGX_PTE_KERNEL=warp), benchmark mixture only.
+template <int NM, class Acc>
+static int launch_warp(const EosSet &set, const MixParamsDev &prm, double *rho, double *vfrac,
+                       double *sie, double *temp, double *press, const double *sie_tot,
+                       const double *vfrac_tot, const double *Tguess, uint64_t *status,
+                       double *residual, int64_t ncell, cudaStream_t s) {
+  const int64_t chunk = ncell < kPteChunk ? ncell : kPteChunk;
+  double *init = nullptr;
+  SGX_CUDA_OK(scratch_alloc_async(reinterpret_cast<void **>(&init),
+                                  (size_t)chunk * (2 * NM + 1) * sizeof(double), s));
+  cudaError_t err = cudaSuccess;
+  for (int64_t c0 = 0; c0 < ncell && err == cudaSuccess; c0 += chunk) {
+    const int64_t n = (ncell - c0) < chunk ? (ncell - c0) : chunk;
+    const int64_t o = c0 * NM;
+    const LaunchCfg ci = stream_cfg(n, 256, 4);
+    pte_rhot_init_kernel<NM, Acc><<<ci.blocks, ci.threads, 0, s>>>(
+        set, prm, rho + o, vfrac + o, sie + o, temp + o, press + o,
+        sie_tot ? sie_tot + c0 : nullptr, vfrac_tot ? vfrac_tot + c0 : nullptr,
+        Tguess ? Tguess + c0 : nullptr, init, n);
+    const LaunchCfg cw = stream_cfg(n * 32, 256, 2);
+    pte_rhot_warp_kernel<NM, Acc><<<cw.blocks, cw.threads, 0, s>>>(
+        set, prm, rho + o, vfrac + o, sie + o, temp + o, press + o,
+        sie_tot ? sie_tot + c0 : nullptr, vfrac_tot ? vfrac_tot + c0 : nullptr, init,
+        status ? reinterpret_cast<unsigned long long *>(status) + c0 : nullptr,
+        residual ? residual + c0 : nullptr, n);
+    count_launch(2);
+    err = cudaGetLastError();
+  }
+  cudaFreeAsync(init, s);
+  if (err != cudaSuccess)
+    return fail(SGX_ERR_CUDA, "PTE RhoT warp-per-cell launch failed: %s", cudaGetErrorString(err));
+  return SGX_OK;
+}
+
 int launch_pte_rhot(const EosSet &set, bool bench_mix, const MixParamsDev &prm, double *rho,
                     double *vfrac, double *sie, double *temp, double *press,
                     const double *sie_tot, const double *vfrac_tot, const double *Tguess,
@@ -75,6 +115,9 @@ int launch_pte_rhot(const EosSet &set, bool bench_mix, const MixParamsDev &prm, 
       stats, ncell, s
   if (bench_mix) {
     if (percell_variant()) return launch_pte_percell<3, Mix3GrDrDp, SGX_PTE_RHOT>(SGX_PTE_ARGS);
+    if (warp_variant() && !stats)
+      return launch_warp<3, Mix3GrDrDp>(set, prm, rho, vfrac, sie, temp, press, sie_tot, vfrac_tot,
+                                        Tguess, status, residual, ncell, s);
     return launch_sm<3, Mix3GrDrDp>(SGX_PTE_ARGS);
   }
   switch (set.nmat) {

@@ -593,6 +593,129 @@ __global__ void __launch_bounds__(THREADS, MINB)
       if (s_hist[k]) atomicAdd(&stats[k], (unsigned long long)s_hist[k]);
   }
 }
+
+// ---------------------------------------------------------------------------------------
+// The warp-per-cell variant north_star names, kept for the side-by-side
+// measurement (SGX_PTE_KERNEL=warp): ONE warp owns one mixed cell.  Lane 0 runs the strictly
+// sequential part of the solve -- the same RhoTLane state machine as above: Neumaier sums,
+// pivoted Householder solve, ScaleDx, line-search acceptance -- and the EOS evaluations of each
+// round are dealt out to lanes, lane 2m + p = material m, evaluation point p (p = 1 is the
+// dT-perturbed point of the Jacobian), requests and results travelling by __shfl_sync.  Results
+// are bit-identical to the lane-per-cell kernel (same operations per cell).
+// Why it loses (profiles/r2_pte_variants.md): a 3-material cell has at most 6 independent EOS
+// evaluations per round, and the three materials are three different code paths, which SIMT
+// serialises anyway; 26+ lanes idle through every round, and lane 0's scalar handlers -- a third
+// of the instructions -- run at 1/32.
+// ---------------------------------------------------------------------------------------
+template <int NM, class Acc>
+__global__ void __launch_bounds__(256, 2)
+    pte_rhot_warp_kernel(const __grid_constant__ EosSet set,
+                         const __grid_constant__ MixParamsDev prm, double *__restrict__ rho,
+                         double *__restrict__ vfrac, double *__restrict__ sie,
+                         double *__restrict__ temp, double *__restrict__ press,
+                         const double *__restrict__ sie_tot_in,
+                         const double *__restrict__ vfrac_tot_in,
+                         const double *__restrict__ init,
+                         unsigned long long *__restrict__ status, double *__restrict__ residual,
+                         const int64_t ncell) {
+  static_assert(2 * NM <= 32, "one lane per (material, evaluation point)");
+  const Acc eos(set);
+  mix::RhoTLane<NM, Acc> L(eos, prm);
+  const unsigned lane = threadIdx.x & 31u;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarp = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  const int mm = (int)(lane >> 1), pp = (int)(lane & 1u); // my material / evaluation point
+  RhoPart my_cache{1.0, 0.0, 0.0, 0.0}; // density-only terms of material mm (lane 2 mm)
+  double eq[NM], pq[NM], eq2[NM], pq2[NM];
+  for (int64_t cell = warp; cell < ncell; cell += nwarp) {
+    if (lane == 0) {
+      const int64_t base = cell * NM;
+#pragma unroll
+      for (int m = 0; m < NM; ++m) {
+        L.s.rho[m] = rho[base + m];
+        L.s.vfrac[m] = vfrac[base + m];
+        L.s.sie[m] = sie[base + m];
+        L.s.temp[m] = temp[base + m];
+        L.s.press[m] = press[base + m];
+      }
+      const double *rec = init + cell * (2 * NM + 1);
+      double vfrac_init[NM], rho_init[NM];
+#pragma unroll
+      for (int m = 0; m < NM; ++m) {
+        vfrac_init[m] = rec[1 + m];
+        rho_init[m] = rec[1 + NM + m];
+      }
+      L.begin(sie_tot_in ? sie_tot_in[cell] : 0.0, sie_tot_in != nullptr,
+              vfrac_tot_in ? vfrac_tot_in[cell] : 1.0, rec[0], vfrac_init, rho_init);
+    }
+    while (true) {
+      const int phase = __shfl_sync(0xffffffffu, L.phase, 0);
+      if (phase == mix::PH_IDLE) break;
+      const int wants = __shfl_sync(0xffffffffu, (int)L.wants_eval(), 0);
+      if (wants) {
+        const int mode = __shfl_sync(0xffffffffu, L.mode, 0);
+        const double Tq = __shfl_sync(0xffffffffu, L.Tq, 0);
+        const double Tq2 = __shfl_sync(0xffffffffu, L.Tq2, 0);
+        double my_rq = 1.0, my_rho_c = 1.0, my_rb = 1.0;
+#pragma unroll
+        for (int m = 0; m < NM; ++m) { // requests: lane 0 -> lanes 2m, 2m+1
+          const double a = __shfl_sync(0xffffffffu, L.rq[m], 0);
+          const double b = __shfl_sync(0xffffffffu, L.s.rho[m], 0);
+          const double c = __shfl_sync(0xffffffffu, L.s.rhobar[m], 0);
+          if (mm == m) {
+            my_rq = a;
+            my_rho_c = b;
+            my_rb = c;
+          }
+        }
+        // the density-only terms kept since the last TestUpdate / InitBase live in lane 2 mm;
+        // the dT-perturbed point of the Jacobian (lane 2 mm + 1) needs them
+        RhoPart nb;
+        nb.Ts = __shfl_sync(0xffffffffu, my_cache.Ts, lane & ~1u);
+        nb.Es = __shfl_sync(0xffffffffu, my_cache.Es, lane & ~1u);
+        nb.Ps = __shfl_sync(0xffffffffu, my_cache.Ps, lane & ~1u);
+        nb.rG = __shfl_sync(0xffffffffu, my_cache.rG, lane & ~1u);
+        double e = 0.0, P = 0.0;
+        if (mm < NM) {
+          if (pp == 0) {
+            RhoPart part;
+            eos.rho_part(mm, my_rq, part);
+            e = eos.e_from_part(mm, part, my_rq, Tq);
+            double sie_for_p = e;
+            if (mode == mix::MODE_TU) sie_for_p = ratio(my_rb * e, my_rb);
+            P = eos.P_from_part(mm, part, my_rq, sie_for_p);
+            if (mode != mix::MODE_J) my_cache = part;
+          } else if (mode == mix::MODE_J) {
+            e = eos.e_from_part(mm, nb, my_rho_c, Tq2);
+            P = eos.P_from_part(mm, nb, my_rho_c, e);
+          }
+        }
+#pragma unroll
+        for (int m = 0; m < NM; ++m) { // results: lanes 2m, 2m+1 -> lane 0
+          eq[m] = __shfl_sync(0xffffffffu, e, 2 * m);
+          pq[m] = __shfl_sync(0xffffffffu, P, 2 * m);
+          eq2[m] = __shfl_sync(0xffffffffu, e, 2 * m + 1);
+          pq2[m] = __shfl_sync(0xffffffffu, P, 2 * m + 1);
+        }
+      }
+      if (lane == 0) L.advance(eq, pq, eq2, pq2);
+      __syncwarp();
+    }
+    if (lane == 0) {
+      const int64_t base = cell * NM;
+#pragma unroll
+      for (int m = 0; m < NM; ++m) {
+        rho[base + m] = L.s.rho[m];
+        vfrac[base + m] = L.s.vfrac[m];
+        sie[base + m] = L.s.sie[m];
+        temp[base + m] = L.s.temp[m];
+        press[base + m] = L.s.press[m];
+      }
+      if (status) status[cell] = mix::pack_status(L.st, L.s.niter);
+      if (residual) residual[cell] = L.st.residual;
+    }
+  }
+}
 #endif // __CUDACC__
 
 } // namespace sgx

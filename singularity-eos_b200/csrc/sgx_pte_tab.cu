@@ -1,0 +1,50 @@
+// PTE solves for mixtures that hold tabulated materials (SpinerEOSDependsRhoT / RhoSie next to
+// the analytic models): the per-cell kernels instantiated on the TabEos accessor
+// (sgx_pte_tab.cuh), with the per-material lambda caches of the reference's CacheAccessor.
+// PTESolverRhoT, PTESolverFixedT (1..4 materials) and PTESolverPT (2..3 materials); the three
+// solver families compile in three translation units (this one: the dispatcher and RhoT).
+#include "sgx_internal.hpp"
+#include "sgx_pte_kernel.cuh"
+#include "sgx_pte_tab.cuh"
+
+namespace sgx {
+
+#define SGX_TAB_PARAMS                                                                     \
+  const EosSet &set, const MixParamsDev &prm, double *rho, double *vfrac, double *sie,     \
+      double *temp, double *press, const double *sie_tot, const double *vfrac_tot,         \
+      const double *Tguess, uint64_t *status, double *residual, uint64_t *stats,           \
+      int64_t ncell, cudaStream_t s, double *lambda
+#define SGX_TAB_ARGS                                                                       \
+  set, prm, rho, vfrac, sie, temp, press, sie_tot, vfrac_tot, Tguess, status, residual,    \
+      stats, ncell, s, lambda
+
+int launch_pte_tab_fixedt(SGX_TAB_PARAMS);
+int launch_pte_tab_pt(SGX_TAB_PARAMS);
+
+int launch_pte_tab(int solver, const EosSet &set, const MixParamsDev &prm, double *rho,
+                   double *vfrac, double *sie, double *temp, double *press,
+                   const double *sie_tot, const double *vfrac_tot, const double *Tguess,
+                   uint64_t *status, double *residual, uint64_t *stats, int64_t ncell,
+                   cudaStream_t s, double *lambda) {
+  if (solver == SGX_PTE_FIXED_T) return launch_pte_tab_fixedt(SGX_TAB_ARGS);
+  if (solver == SGX_PTE_PT) return launch_pte_tab_pt(SGX_TAB_ARGS);
+  if (solver == SGX_PTE_RHOT) {
+    switch (set.nmat) {
+    case 1:
+      return launch_pte_percell<1, TabEos, SGX_PTE_RHOT>(SGX_TAB_ARGS);
+    case 2:
+      return launch_pte_percell<2, TabEos, SGX_PTE_RHOT>(SGX_TAB_ARGS);
+    case 3:
+      return launch_pte_percell<3, TabEos, SGX_PTE_RHOT>(SGX_TAB_ARGS);
+    case 4:
+      return launch_pte_percell<4, TabEos, SGX_PTE_RHOT>(SGX_TAB_ARGS);
+    default:
+      break;
+    }
+  }
+  return fail(SGX_ERR_UNSUPPORTED,
+              "PTE with tabulated materials: solver %d with %d materials is not instantiated "
+              "(RhoT / FixedT: 1..4, PT: 2..3)", solver, set.nmat);
+}
+
+} // namespace sgx

@@ -1,0 +1,24 @@
+// PTESolverPT over mixtures with tabulated materials (see sgx_pte_tab.cu).
+#include "sgx_internal.hpp"
+#include "sgx_pte_kernel.cuh"
+#include "sgx_pte_tab.cuh"
+
+namespace sgx {
+
+#define SGX_TAB_PARAMS                                                                     \
+  const EosSet &set, const MixParamsDev &prm, double *rho, double *vfrac, double *sie,     \
+      double *temp, double *press, const double *sie_tot, const double *vfrac_tot,         \
+      const double *Tguess, uint64_t *status, double *residual, uint64_t *stats,           \
+      int64_t ncell, cudaStream_t s, double *lambda
+#define SGX_TAB_ARGS                                                                       \
+  set, prm, rho, vfrac, sie, temp, press, sie_tot, vfrac_tot, Tguess, status, residual,    \
+      stats, ncell, s, lambda
+
+int launch_pte_tab_pt(SGX_TAB_PARAMS) {
+  if (set.nmat == 2) return launch_pte_percell<2, TabEos, SGX_PTE_PT>(SGX_TAB_ARGS);
+  if (set.nmat == 3) return launch_pte_percell<3, TabEos, SGX_PTE_PT>(SGX_TAB_ARGS);
+  return fail(SGX_ERR_UNSUPPORTED, "PTESolverPT with tabulated materials: nmat = %d "
+              "(2..3 instantiated)", set.nmat);
+}
+
+} // namespace sgx

@@ -263,26 +263,26 @@ struct SpinerRhoT {
   }
 
   // ---- public scalar methods ---------------------------------------------------------
-  SGX_D double T_from_rho_e(const double rho, const double sie_in, double *lambda) const {
+  SGX_D double T_from_rho_e(const double rho, const double sie_in, double *lambda = nullptr) const {
     TableStatus w;
     const double lRho = lRho_(rho);
     const AxisPos pr(gRho, lRho);
     const double lT = lTFromlRhoSie(lRho, pr, sie_in, w, lambda);
     return T_(lT);
   }
-  SGX_D double e_from_rho_T(const double rho, const double T, double *lambda) const {
+  SGX_D double e_from_rho_T(const double rho, const double T, double *lambda = nullptr) const {
     double lRho, lT;
     getLogsRhoT(rho, T, lRho, lT, lambda);
     const TableStatus w = locRhoT(lRho, lT);
     return sieFromlRhoTlT(AxisPos(gRho, lRho), T, lT, w);
   }
-  SGX_D double P_from_rho_T(const double rho, const double T, double *lambda) const {
+  SGX_D double P_from_rho_T(const double rho, const double T, double *lambda = nullptr) const {
     double lRho, lT;
     getLogsRhoT(rho, T, lRho, lT, lambda);
     const TableStatus w = locRhoT(lRho, lT);
     return PFromRholRhoTlT(rho, AxisPos(gRho, lRho), T, lT, w);
   }
-  SGX_D double P_from_rho_e(const double rho, const double sie_in, double *lambda) const {
+  SGX_D double P_from_rho_e(const double rho, const double sie_in, double *lambda = nullptr) const {
     TableStatus w;
     const double lRho = lRho_(rho);
     const AxisPos pr(gRho, lRho);
@@ -294,13 +294,13 @@ struct SpinerRhoT {
     }
     return interp2c(P, numT, pr, AxisPos(gT, lT));
   }
-  SGX_D double cv_from_rho_T(const double rho, const double T, double *lambda) const {
+  SGX_D double cv_from_rho_T(const double rho, const double T, double *lambda = nullptr) const {
     double lRho, lT;
     getLogsRhoT(rho, T, lRho, lT, lambda);
     const TableStatus w = locRhoT(lRho, lT);
     return CvFromlRholT(AxisPos(gRho, lRho), lT, w);
   }
-  SGX_D double cv_from_rho_e(const double rho, const double sie_in, double *lambda) const {
+  SGX_D double cv_from_rho_e(const double rho, const double sie_in, double *lambda = nullptr) const {
     TableStatus w;
     double Cv;
     const double lRho = lRho_(rho);
@@ -315,13 +315,13 @@ struct SpinerRhoT {
     }
     return Cv > kEps ? Cv : kEps;
   }
-  SGX_D double bmod_from_rho_T(const double rho, const double T, double *lambda) const {
+  SGX_D double bmod_from_rho_T(const double rho, const double T, double *lambda = nullptr) const {
     double lRho, lT;
     getLogsRhoT(rho, T, lRho, lT, lambda);
     const TableStatus w = locRhoT(lRho, lT);
     return bModFromRholRhoTlT(rho, AxisPos(gRho, lRho), T, lT, w);
   }
-  SGX_D double bmod_from_rho_e(const double rho, const double sie_in, double *lambda) const {
+  SGX_D double bmod_from_rho_e(const double rho, const double sie_in, double *lambda = nullptr) const {
     TableStatus w;
     const double lRho = lRho_(rho);
     const AxisPos pr(gRho, lRho);
@@ -333,7 +333,7 @@ struct SpinerRhoT {
     }
     return interp2c(bMod, numT, pr, AxisPos(gT, lT));
   }
-  SGX_D double gamma_from_rho_T(const double rho, const double T, double *lambda) const {
+  SGX_D double gamma_from_rho_T(const double rho, const double T, double *lambda = nullptr) const {
     double lRho, lT;
     getLogsRhoT(rho, T, lRho, lT, lambda);
     const AxisPos pr(gRho, lRho);
@@ -346,7 +346,7 @@ struct SpinerRhoT {
     const double dpde = interp2c(dPdE, numT, pr, AxisPos(gT, lT));
     return ratio(fabs(dpde), fabs(rho));
   }
-  SGX_D double gamma_from_rho_e(const double rho, const double sie_in, double *lambda) const {
+  SGX_D double gamma_from_rho_e(const double rho, const double sie_in, double *lambda = nullptr) const {
     TableStatus w;
     const double lRho = lRho_(rho);
     const AxisPos pr(gRho, lRho);
@@ -466,6 +466,12 @@ struct SpinerRhoT {
     if (lT >= lTMax) return 0.0;
     return interp1d(rho_at_pmin, gT, lT);
   }
+  // bounds the PTE solvers ask for (eos_spiner_rho_temp.hpp:226-246; EosBase defaults :533-557)
+  SGX_D double MinimumDensity() const { return rho_(lRhoMin); }
+  SGX_D double MinimumTemperature() const { return T_(lTMin); }
+  SGX_D double MaximumDensity() const { return rhoMax; }
+  SGX_D double MinimumPressure() const { return PMin; }
+  SGX_D double MaximumPressureAtTemperature(double) const { return 1e100; }
 #endif
 };
 
@@ -503,31 +509,31 @@ struct SpinerRhoSie {
     if (lambda) lambda[0] = lRho;
     return interp2c(db, gRho, gE, numE, lRho, lE);
   }
-  SGX_D double T_from_rho_e(double rho, double e, double *lambda) const {
+  SGX_D double T_from_rho_e(double rho, double e, double *lambda = nullptr) const {
     return interpRhoSie(rho, e, T_re, lambda);
   }
-  SGX_D double e_from_rho_T(double rho, double T, double *lambda) const {
+  SGX_D double e_from_rho_T(double rho, double T, double *lambda = nullptr) const {
     return interpRhoT(rho, T, sie, lambda);
   }
-  SGX_D double P_from_rho_T(double rho, double T, double *lambda) const {
+  SGX_D double P_from_rho_T(double rho, double T, double *lambda = nullptr) const {
     return interpRhoT(rho, T, P, lambda);
   }
-  SGX_D double P_from_rho_e(double rho, double e, double *lambda) const {
+  SGX_D double P_from_rho_e(double rho, double e, double *lambda = nullptr) const {
     return interpRhoSie(rho, e, P_re, lambda);
   }
-  SGX_D double cv_from_rho_T(double rho, double T, double *lambda) const {
+  SGX_D double cv_from_rho_T(double rho, double T, double *lambda = nullptr) const {
     return 1. / interpRhoT(rho, T, dTdE, lambda);
   }
-  SGX_D double cv_from_rho_e(double rho, double e, double *lambda) const {
+  SGX_D double cv_from_rho_e(double rho, double e, double *lambda = nullptr) const {
     return 1. / interpRhoSie(rho, e, dTdE_re, lambda);
   }
-  SGX_D double bmod_from_rho_T(double rho, double T, double *lambda) const {
+  SGX_D double bmod_from_rho_T(double rho, double T, double *lambda = nullptr) const {
     return interpRhoT(rho, T, bMod, lambda);
   }
-  SGX_D double bmod_from_rho_e(double rho, double e, double *lambda) const {
+  SGX_D double bmod_from_rho_e(double rho, double e, double *lambda = nullptr) const {
     return interpRhoSie(rho, e, bMod_re, lambda);
   }
-  SGX_D double gamma_from_rho_T(double rho, double T, double *lambda) const {
+  SGX_D double gamma_from_rho_T(double rho, double T, double *lambda = nullptr) const {
     const double dpde = interpRhoT(rho, T, dPdE, lambda);
     return dpde / rho;
   }
@@ -615,6 +621,23 @@ struct SpinerRhoSie {
     if (lambda) lambda[0] = lRho;
     return lRho;
   }
+  // DensityEnergyFromPressureTemperature (eos_spiner_rho_sie.hpp:836-848)
+  __device__ inline void rho_e_from_P_T(const double press, const double temp, double *lambda,
+                                        double &rho, double &sie_out) const {
+    const double lT = to_log(temp, lTOffset);
+    const double lRho = lRhoFromPlT(press, lT, lambda);
+    rho = from_log(lRho, lRhoOffset);
+    sie_out = interp2c(sie, gRho, gT, numT, lRho, lT);
+  }
+  // bounds the PTE solvers ask for (eos_spiner_rho_sie.hpp:242-270)
+  SGX_D double RhoPmin(const double temp) const {
+    return interp1d(rho_at_pmin, gT, to_log(temp, lTOffset));
+  }
+  SGX_D double MinimumDensity() const { return from_log(lRhoMin, lRhoOffset); }
+  SGX_D double MinimumTemperature() const { return from_log(gT.gmin(), lTOffset); }
+  SGX_D double MaximumDensity() const { return rhoMax; }
+  SGX_D double MinimumPressure() const { return PMin; }
+  SGX_D double MaximumPressureAtTemperature(double) const { return 1e100; }
   // FillEos (eos_spiner_rho_sie.hpp:842-900)
   __device__ inline bool fill(double &rho, double &temp, double &energy, double &press,
                               double &cv, double &bmod, const unsigned long output,

@@ -385,6 +385,8 @@ int build_spiner_rhot(const sgx_sp5_tables *raw, int reproducible, int pmin_vapo
   s.dTdECold = ts.d("dTdECold");
   s.dEdTCold = ts.d("dEdTCold");
   s.rho_at_pmin = ts.d("rho_at_pmin");
+  SGX_CUDA_OK(cudaMalloc(&e->dev_struct, sizeof(SpinerRhoT)));
+  SGX_CUDA_OK(cudaMemcpy(e->dev_struct, &s, sizeof(SpinerRhoT), cudaMemcpyHostToDevice));
   return SGX_OK;
 }
 
@@ -551,6 +553,8 @@ int build_spiner_rhosie(const sgx_sp5_tables *raw, int reproducible, int pmin_va
   s.rho_at_pmin = ts.d("rho_at_pmin");
   s.PlRhoMax = ts.d("PlRhoMax");
   s.dPdRhoMax = ts.d("dPdRhoMax");
+  SGX_CUDA_OK(cudaMalloc(&e->dev_struct, sizeof(SpinerRhoSie)));
+  SGX_CUDA_OK(cudaMemcpy(e->dev_struct, &s, sizeof(SpinerRhoSie), cudaMemcpyHostToDevice));
   return SGX_OK;
 }
 

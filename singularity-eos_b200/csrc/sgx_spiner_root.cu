@@ -42,7 +42,13 @@ namespace sgx {
 
 namespace {
 
-constexpr int64_t kRootChunk = int64_t(1) << 24; // cells per kernel pair
+constexpr int64_t kRootChunk = int64_t(1) << 23; // cells per kernel pair
+// A listed cell travels with its inputs, so the list kernel reads contiguous records instead of
+// gathering 8 bytes out of every other 32-byte sector of the cell arrays.
+struct RootListEntry {
+  double rho, sie;
+  unsigned long long idx;
+};
 // The cells left to the reference iterate are appended to kRootSubLists lists, chosen by block:
 // one list would put every warp's atomicAdd on one address (measured: +0.9 ms per 2^26 cells).
 // Each list has room for twice its fair share; a cell that finds its list full is solved on the
@@ -50,7 +56,7 @@ constexpr int64_t kRootChunk = int64_t(1) << 24; // cells per kernel pair
 constexpr int kRootSubLists = 32;
 constexpr int kRootCounterStride = 32; // unsigned ints between counters: one 128-byte line each
 SGX_HD int64_t root_sublist_capacity(const int64_t ncell) {
-  return 2 * (ncell / kRootSubLists) + 4096;
+  return ncell / kRootSubLists + 4096; // every cell of a fair share
 }
 
 // relative-T error budget of the direct solve against the reference iterate (see header):
@@ -78,7 +84,7 @@ __global__ void __launch_bounds__(256, 4)
                          const unsigned int *__restrict__ hint,
                          const double *__restrict__ rho_in, const double *__restrict__ sie_in,
                          double *__restrict__ T_out, const int64_t n, double *__restrict__ lambda,
-                         const int ls, const bool vec_lambda, unsigned int *__restrict__ list,
+                         const int ls, const bool vec_lambda, RootListEntry *__restrict__ list,
                          unsigned int *__restrict__ count) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   RootRowMeta *meta = reinterpret_cast<RootRowMeta *>(smem_raw);
@@ -101,17 +107,16 @@ __global__ void __launch_bounds__(256, 4)
   const unsigned sub = blockIdx.x % kRootSubLists;
   const unsigned sub_cap = (unsigned)root_sublist_capacity(n);
   unsigned int *const my_count = count + sub * kRootCounterStride;
-  unsigned int *const my_list = list + (size_t)sub * sub_cap;
+  RootListEntry *const my_list = list + (size_t)sub * sub_cap;
   // warp-uniform trip count: every lane stays in the loop so the votes below are full-warp
   for (int64_t base = (int64_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31u); base < n;
        base += nthr) {
     const int64_t i = base + lane;
     const bool valid = i < n;
     bool fallback = false, search = false, found = false;
-    double sie = 0.0, lRho = 0.0, lT = 0.0, w0 = 0.0, w1 = 0.0;
+    double rho = 0.0, sie = 0.0, lRho = 0.0, lT = 0.0, w0 = 0.0, w1 = 0.0;
     int ix2 = 0, lo = 1, hi = 0;
     if (valid) {
-      double rho;
       asm volatile("ld.global.nc.L1::no_allocate.f64 %0, [%1];" : "=d"(rho) : "l"(rho_in + i));
       asm volatile("ld.global.nc.L1::no_allocate.f64 %0, [%1];" : "=d"(sie) : "l"(sie_in + i));
       lRho = eos.lRho_(rho);
@@ -204,14 +209,14 @@ __global__ void __launch_bounds__(256, 4)
       if (fallback) {
         const unsigned mine = pos + __popc(fbm & ((1u << lane) - 1u));
         if (mine < sub_cap) {
-          my_list[mine] = (unsigned)i;
+          my_list[mine] = RootListEntry{rho, sie, (unsigned long long)i};
         } else { // list full (heavily skewed input): the reference iterate right here
           double lam[2];
           if (lambda) {
             lam[0] = lambda[i * ls];
             lam[1] = lambda[i * ls + 1];
           }
-          T_out[i] = eos.T_from_rho_e(rho_in[i], sie_in[i], lambda ? lam : nullptr);
+          T_out[i] = eos.T_from_rho_e(rho, sie, lambda ? lam : nullptr);
           if (lambda) {
             lambda[i * ls] = lam[0];
             lambda[i * ls + 1] = lam[1];
@@ -224,17 +229,16 @@ __global__ void __launch_bounds__(256, 4)
 
 // The listed cells through the reference iterate (SpinerRhoT::T_from_rho_e); blockIdx.y = list
 __global__ void __launch_bounds__(256, 4)
-    rhot_T_list_kernel(const __grid_constant__ SpinerRhoT eos, const double *__restrict__ rho_in,
-                       const double *__restrict__ sie_in, double *__restrict__ T_out,
+    rhot_T_list_kernel(const __grid_constant__ SpinerRhoT eos, double *__restrict__ T_out,
                        double *__restrict__ lambda, const int ls,
-                       const unsigned int *__restrict__ list,
+                       const RootListEntry *__restrict__ list,
                        const unsigned int *__restrict__ count,
                        unsigned long long *__restrict__ stats, const unsigned long long ncell) {
   const unsigned sub = blockIdx.y;
   const unsigned sub_cap = (unsigned)root_sublist_capacity((int64_t)ncell);
   const unsigned raw = count[sub * kRootCounterStride];
   const unsigned cnt = raw < sub_cap ? raw : sub_cap; // the overflow was solved in place
-  const unsigned int *my_list = list + (size_t)sub * sub_cap;
+  const RootListEntry *my_list = list + (size_t)sub * sub_cap;
   const unsigned tid = blockIdx.x * blockDim.x + threadIdx.x;
   const unsigned nthr = gridDim.x * blockDim.x;
   if (tid == 0 && stats) {
@@ -242,13 +246,14 @@ __global__ void __launch_bounds__(256, 4)
     atomicAdd(stats + 1, (unsigned long long)raw);
   }
   for (unsigned k = tid; k < cnt; k += nthr) {
-    const int64_t i = my_list[k];
+    const RootListEntry en = my_list[k];
+    const int64_t i = (int64_t)en.idx;
     double lam[2];
     if (lambda) {
       lam[0] = lambda[i * ls];
       lam[1] = lambda[i * ls + 1];
     }
-    T_out[i] = eos.T_from_rho_e(rho_in[i], sie_in[i], lambda ? lam : nullptr);
+    T_out[i] = eos.T_from_rho_e(en.rho, en.sie, lambda ? lam : nullptr);
     if (lambda) {
       lambda[i * ls] = lam[0];
       lambda[i * ls + 1] = lam[1];
@@ -288,7 +293,10 @@ int launch_rhot_T_from_rho_e_hybrid(sgx_eos_s *e, bool bounded, const double *rh
   constexpr size_t kCounters = (size_t)kRootSubLists * kRootCounterStride;
   const size_t list_len = (size_t)kRootSubLists * (size_t)root_sublist_capacity(chunk);
   unsigned int *scratch = nullptr;
-  SGX_CUDA_OK(cudaMallocAsync(&scratch, (kCounters + list_len) * sizeof(unsigned int), s));
+  SGX_CUDA_OK(scratch_alloc_async(
+      reinterpret_cast<void **>(&scratch),
+      kCounters * sizeof(unsigned int) + list_len * sizeof(RootListEntry), s));
+  RootListEntry *lists = reinterpret_cast<RootListEntry *>(scratch + kCounters);
   int rc = SGX_OK;
   for (int64_t c0 = 0; c0 < n && rc == SGX_OK; c0 += chunk) {
     const int64_t m = (n - c0) < chunk ? (n - c0) : chunk;
@@ -299,16 +307,14 @@ int launch_rhot_T_from_rho_e_hybrid(sgx_eos_s *e, bool bounded, const double *rh
       const LaunchCfg c = stream_cfg(m, 256, 4 * 2);
       if (bounded)
         rhot_T_direct_kernel<true><<<c.blocks, c.threads, smem, s>>>(
-            eos, meta, hint, rho + c0, sie + c0, out + c0, m, lam, ls, vec_lambda, scratch + kCounters,
-            scratch);
+            eos, meta, hint, rho + c0, sie + c0, out + c0, m, lam, ls, vec_lambda, lists, scratch);
       else
         rhot_T_direct_kernel<false><<<c.blocks, c.threads, smem, s>>>(
-            eos, meta, hint, rho + c0, sie + c0, out + c0, m, lam, ls, vec_lambda, scratch + kCounters,
-            scratch);
+            eos, meta, hint, rho + c0, sie + c0, out + c0, m, lam, ls, vec_lambda, lists, scratch);
       // one grid row per list; a list holds ~ m / 32 / 7 cells on the bench workload
       const LaunchCfg c2 = stream_cfg(root_sublist_capacity(m) / 4, 256, 1);
       rhot_T_list_kernel<<<dim3(c2.blocks, kRootSubLists), c2.threads, 0, s>>>(
-          eos, rho + c0, sie + c0, out + c0, lam, ls, scratch + kCounters, scratch,
+          eos, out + c0, lam, ls, lists, scratch,
           reinterpret_cast<unsigned long long *>(e->root_stats), (unsigned long long)m);
       count_launch(2);
       err = cudaGetLastError();

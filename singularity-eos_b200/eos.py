@@ -70,6 +70,27 @@ class EosBase:
     def MaximumDensity(self):
         return self._lib.sgx_eos_maximum_density(self._h)
 
+    # -- Serialize / DeSerialize (eos/eos_base.hpp:756-798) -------------------------------
+    def SerializedSizeInBytes(self):
+        return int(self._lib.sgx_eos_serialized_size(self._h))
+
+    def Serialize(self):
+        """The handle as a self-contained bytes object (parameters / raw tables / options)."""
+        n = self.SerializedSizeInBytes()
+        buf = C.create_string_buffer(n)
+        check(self._lib.sgx_eos_serialize(self._h, buf, n))
+        return buf.raw
+
+    @classmethod
+    def DeSerialize(cls, data):
+        """An equivalent EOS on the current device, rebuilt from Serialize()'s bytes."""
+        lib = _lib.load()
+        h = C.c_void_p()
+        check(lib.sgx_eos_deserialize(data, len(data), C.byref(h)))
+        obj = EosBase.__new__(cls)
+        EosBase.__init__(obj, h)
+        return obj
+
     def scratch_size(self, method, nelements):
         return self._lib.sgx_eos_scratch_bytes(self._h, 0, nelements)
 

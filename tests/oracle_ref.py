@@ -59,6 +59,10 @@ def load(path=None):
         "ref_mix_params_default": (None, [C.POINTER(L.MixParams)]),
         "ref_pte_solve": (C.c_int, [C.c_int, C.POINTER(_VP), C.c_int, _I64] + [_VP] * 8 +
                           [C.POINTER(L.MixParams), _VP, _VP, _VP, C.c_int]),
+        "ref_pte_solve_cached": (C.c_int, [C.c_int, C.POINTER(_VP), C.c_int, _I64] + [_VP] * 8 +
+                                 [C.POINTER(L.MixParams), _VP, _VP, _VP, _VP, C.c_int]),
+        "ref_get_sg_eos": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, _VP, C.POINTER(_VP),
+                                     C.c_int, _VP] + [_VP] * 15 + [_D]),
         "ref_pte_approx_T": (None, [C.POINTER(_VP), C.c_int, _I64, _VP, _VP, _VP, _VP]),
         "ref_bounds_log_grid": (C.c_int, [_D, _D, C.c_int, C.POINTER(L.Grid1D), C.POINTER(_D),
                                           _VP]),
@@ -226,20 +230,37 @@ class Ref:
         return p
 
     def pte_solve(self, solver, eos_list, rho, vfrac, sie, temp, press, params=None,
-                  sie_tot=None, vfrac_tot=None, Tguess=None, nthreads=1):
-        """In-place on the numpy state arrays; returns (status words, residual, Tguess)."""
+                  sie_tot=None, vfrac_tot=None, Tguess=None, nthreads=1, lambdas=None):
+        """In-place on the numpy state arrays; returns (status words, residual, Tguess).
+        lambdas: [ncell][nmat][3] CacheAccessor storage (in/out) or None (NullIndexer)."""
         nmat = len(eos_list)
         ncell = rho.shape[0]
         hs = (_VP * nmat)(*[e.h for e in eos_list])
         status = np.zeros(ncell, dtype=np.uint64)
         resid = np.zeros(ncell)
         tg = np.zeros(ncell)
-        rc = self.lib.ref_pte_solve(int(solver), hs, nmat, ncell, _p(rho), _p(vfrac), _p(sie),
-                                    _p(temp), _p(press), _p(sie_tot), _p(vfrac_tot), _p(Tguess),
-                                    None if params is None else C.byref(params), _p(status),
-                                    _p(resid), _p(tg), nthreads)
+        rc = self.lib.ref_pte_solve_cached(
+            int(solver), hs, nmat, ncell, _p(rho), _p(vfrac), _p(sie), _p(temp), _p(press),
+            _p(sie_tot), _p(vfrac_tot), _p(Tguess), None if params is None else C.byref(params),
+            _p(status), _p(resid), _p(tg), _p(lambdas), nthreads)
         assert rc == 0
         return status, resid, tg
+
+    def get_sg_eos(self, eos_list, eos_offsets, offsets, press, pmax, vol, spvol, sie, temp,
+                   bmod, dpde, cv, frac_mass, frac_vol, frac_ie, frac_bmod=None, frac_dpde=None,
+                   frac_cv=None, input_int=1, mass_frac_cutoff=1e-16):
+        """The reference's own get_sg_eos (Kokkos build of the harness only); numpy host arrays,
+        per-material arrays Fortran-ordered (cell_dim, nmat), 1-based int32 offsets."""
+        nmat, ncell, cell_dim = len(eos_offsets), len(offsets), press.shape[0]
+        eo = np.ascontiguousarray(eos_offsets, dtype=np.int32)
+        of = np.ascontiguousarray(offsets, dtype=np.int32)
+        hs = (_VP * len(eos_list))(*[e.h for e in eos_list])
+        rc = self.lib.ref_get_sg_eos(
+            nmat, ncell, cell_dim, int(input_int), _p(eo), hs, len(eos_list), _p(of), _p(press),
+            _p(pmax), _p(vol), _p(spvol), _p(sie), _p(temp), _p(bmod), _p(dpde), _p(cv),
+            _p(frac_mass), _p(frac_vol), _p(frac_ie), _p(frac_bmod), _p(frac_dpde), _p(frac_cv),
+            float(mass_frac_cutoff))
+        assert rc == 0, rc
 
     def bounds_log_grid(self, xmin, xmax, n):
         g = _pkg()._lib.Grid1D()

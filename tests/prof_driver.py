@@ -76,5 +76,5 @@ if what in ("pte", "all"):
         for a, b in zip(st, s0): a.copy_(b)
         pkg.closure.PTESolverRhoT(g3, *st, params=prm)
     n_save = n; n = npte
-    timed("pte_rhot", pte)
+    timed("pte_rhot[" + os.environ.get("SGX_PTE_KERNEL", "sm") + "]", pte)
     n = n_save

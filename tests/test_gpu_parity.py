@@ -512,6 +512,45 @@ def test_remaining_vector_methods(pkg, ref, torch_cuda, raw1, kind):
     assert_rel(sie_o.cpu().numpy(), sie_r, 1e-9, kind + " sie(P,T)")
 
 
+def test_serialize_deserialize_round_trip(pkg, torch_cuda, raw1, helm_table):
+    """SURVEY 8(f) row 4, Serialize / DeSerialize (eos/eos_base.hpp:756-798): every EOS kind as a
+    self-contained byte stream; the handle rebuilt from it returns bit-identical lookups, and a
+    damaged stream is refused."""
+    torch = torch_cuda
+    L = pkg._lib
+    n = 4096
+    rho_s, T_s = pkg.workloads.spiner_inputs(n)
+    rho_h, T_h = pkg.workloads.helm_inputs(n)
+    g3 = pkg.closure.set_eos_3mat_analytic()
+    cases = [(pkg.IdealGas(0.4, 7.16e6), rho_s, T_s, 0), (g3[0], rho_s, T_s, 0),
+             (g3[1], rho_s * 0.2, T_s, 0), (g3[2], rho_s * 0.2, T_s, 0),
+             (pkg.SpinerEOSDependsRhoT(raw1, pmin_vapor_dome=True), rho_s, T_s, 2),
+             (pkg.SpinerEOSDependsRhoSie(raw1), rho_s, T_s, 1),
+             (pkg.Helmholtz(helm_table, coul=False), rho_h, T_h, 3)]
+    for eos, rho, T, nl in cases:
+        blob = eos.Serialize()
+        assert len(blob) == eos.SerializedSizeInBytes() and blob[:8] == b"SGXEOS01"
+        twin = pkg.eos.EosBase.DeSerialize(blob)
+        assert twin.nlambda() == eos.nlambda()
+        rho_d, T_d = dev(rho), dev(T)
+        for m in (L.P_FROM_RHO_T, L.E_FROM_RHO_T):
+            outs = []
+            for e in (eos, twin):
+                o = torch.empty(n, dtype=torch.float64, device="cuda")
+                lam = None
+                if nl == 3:
+                    lam = dev(np.tile(np.array([4.0, 2.0, -1.0]), (n, 1)))
+                elif nl:
+                    lam = dev(np.full((n, nl), np.nan))
+                e._eval(m, rho_d, T_d, o, n, lam)
+                outs.append(o.cpu().numpy())
+            assert_bits(outs[1], outs[0], f"{type(eos).__name__} after DeSerialize, method {m}")
+        with pytest.raises(pkg.SgxError):
+            pkg.eos.EosBase.DeSerialize(blob[:len(blob) // 2])
+    with pytest.raises(pkg.SgxError):
+        pkg.eos.EosBase.DeSerialize(b"not an eos stream")
+
+
 def test_solve_Ax_b_known_answers(pkg, ref, torch_cuda):
     """test/test_solver_utils.cpp:52-133: 2x2 and near-singular 3x3 systems."""
     torch = torch_cuda
@@ -670,20 +709,24 @@ def test_pte_rhot_state_machine_equals_percell_kernel(pkg, torch_cuda, which, mo
         sie0.append(float(o.item()))
     for n in (1, 31, 33, 4097, (1 << 16) + 5):
         outs = {}
-        for variant in ("percell", "sm"):
+        # "warp": the warp-per-cell comparison variant (lane 0 = sequential solver logic, EOS
+        # evaluations dealt to lanes, __shfl_sync exchange); it keeps no statistics vector
+        for variant in ("percell", "sm", "warp"):
             monkeypatch.setenv("SGX_PTE_KERNEL", variant)
             state = W.pte_state_torch(n, sie0, torch.device("cuda"), start=0)
             status = torch.zeros(n, dtype=torch.int64, device="cuda")
             resid = torch.zeros(n, dtype=torch.float64, device="cuda")
             stats = torch.zeros(L.PTE_NSTATS, dtype=torch.int64, device="cuda")
             pkg.closure.pte_solve(L.PTE_RHOT, g3, *state, params=params, status=status,
-                                  residual=resid, stats=stats)
+                                  residual=resid, stats=None if variant == "warp" else stats)
             torch.cuda.synchronize()
             outs[variant] = [a.cpu().numpy() for a in state] + [
                 status.cpu().numpy(), resid.cpu().numpy(), stats.cpu().numpy()]
-        for a, b, nm in zip(outs["percell"], outs["sm"],
-                            ("rho", "vfrac", "sie", "temp", "press", "status", "residual", "stats")):
+        names = ("rho", "vfrac", "sie", "temp", "press", "status", "residual", "stats")
+        for a, b, nm in zip(outs["percell"], outs["sm"], names):
             assert a.tobytes() == b.tobytes(), f"n={n} {which}: {nm} differs between kernels"
+        for a, b, nm in zip(outs["sm"][:7], outs["warp"][:7], names):
+            assert a.tobytes() == b.tobytes(), f"n={n} {which}: {nm} differs (warp-per-cell)"
 
 
 @pytest.mark.parametrize("nmat", [1, 2, 4])
@@ -810,6 +853,196 @@ def test_pte_pt_parity(pkg, ref, torch_cuda, which):
     else:
         _pte_compare(pkg, ref, torch_cuda, pkg._lib.PTE_PT, vf, pkg.closure.MixParams(),
                      tol=PTE_TOL, what="PT/" + which, strict_flags=True)
+
+
+@pytest.mark.parametrize("solver_name", ["RhoT", "FixedT", "PT"])
+@pytest.mark.parametrize("mix", ["spiner+ideal+gruneisen", "spiner+ideal", "rhosie+ideal+davis",
+                                 "spiner(vapor dome)+ideal"])
+def test_pte_tabulated_materials(pkg, ref, torch_cuda, raw1, mix, solver_name):
+    """mixed cells that hold TABULATED materials (SpinerEOSDependsRhoT /
+    RhoSie of Vinet copper next to IdealGas, Gruneisen, Davis) with per-material lambda caches in
+    the reference's CacheAccessor layout (closure/mixed_cell_models.hpp:307-324).  Tabulated
+    models prefer (rho, T): the P(rho,T) / e, cv(rho,T) branches of PTESolverBase (:583-620); with
+    `pmin_vapor_dome` their RhoPmin(T) is non-zero, i.e. the non-trivial branch of SetVfracFromT
+    (:423-498) and the density guard of ScaleDx (:1124-1141).  Oracle: the same harness, the
+    reference's own classes and CacheAccessor.  Every SolverStatus field identical, states to
+    1e-10 on converged cells, lambda caches (lRho, lT) to 1e-10 absolute."""
+    torch = torch_cuda
+    L, W = pkg._lib, pkg.workloads
+    dome = "vapor dome" in mix
+    if mix.startswith("rhosie"):
+        g_tab = pkg.SpinerEOSDependsRhoSie(raw1)
+        r_tab = ref.SpinerRhoSie(raw1)
+    else:
+        g_tab = pkg.SpinerEOSDependsRhoT(raw1, pmin_vapor_dome=dome)
+        r_tab = ref.SpinerRhoT(raw1, pmin_vapor_dome=dome)
+    g3, r3 = pkg.closure.set_eos_3mat_analytic(), ref.set_eos_3mat()
+    g_gas, r_gas = pkg.IdealGas(0.4, 7.16e6), ref.IdealGas(0.4, 7.16e6)
+    if mix == "spiner+ideal+gruneisen":
+        g_l, r_l, rho0 = [g_tab, g_gas, g3[0]], [r_tab, r_gas, r3[0]], (8.93, 1.0e-2, 8.93)
+    elif mix == "rhosie+ideal+davis":
+        g_l, r_l, rho0 = [g_tab, g_gas, g3[1]], [r_tab, r_gas, r3[1]], (8.93, 1.0e-2, 1.89)
+    else:
+        g_l, r_l, rho0 = [g_tab, g_gas], [r_tab, r_gas], (8.93, 5.0e-3)
+    nm = len(g_l)
+    if solver_name == "PT" and nm not in (2, 3):
+        pytest.skip("PT instantiated for 2..3 materials")
+    n = 2048
+    vf = W.pte_vfracs(n, nmat=nm)
+    rho = np.tile(np.array(rho0), (n, 1)) * \
+        (0.9 + 0.2 * pkg.rng.uniform_np(57, 0, n * nm).reshape(n, nm))
+    T0 = 600.0
+    sie = np.stack([r_l[m].eval(L.E_FROM_RHO_T, rho[:, m].copy(), np.full(n, T0),
+                                np.full((n, 3), np.nan) if r_l[m].nlambda() else None)
+                    for m in range(nm)], axis=1)
+    st_h = [np.ascontiguousarray(a) for a in (rho, vf, sie, np.full((n, nm), T0),
+                                              np.zeros((n, nm)))]
+    solver = {"RhoT": L.PTE_RHOT, "FixedT": L.PTE_FIXED_T, "PT": L.PTE_PT}[solver_name]
+    Tfix = 550.0 + 200.0 * pkg.rng.uniform_np(58, 0, n) if solver_name == "FixedT" else None
+    prm = pkg.closure.MixParams()
+    lam_r = np.full((n, nm, 3), np.nan)
+    st_r = [a.copy() for a in st_h]
+    status_r, res_r, _ = ref.pte_solve(solver, r_l, *st_r, prm, Tguess=Tfix, lambdas=lam_r)
+    st_d = [dev(a) for a in st_h]
+    lam_d = dev(np.full((n, nm, 3), np.nan))
+    status = torch.zeros(n, dtype=torch.int64, device="cuda")
+    resid = torch.zeros(n, dtype=torch.float64, device="cuda")
+    pkg.closure.pte_solve(solver, g_l, *st_d, params=prm, status=status, residual=resid,
+                          Tguess=None if Tfix is None else dev(Tfix), lambdas=lam_d)
+    torch.cuda.synchronize()
+    got = status.cpu().numpy().view(np.uint64)
+    conv = (status_r & 1).astype(bool)
+    assert conv.mean() > 0.95, f"reference converged on only {conv.mean():.3f} of the cells"
+    same = got == status_r
+    assert same.all(), (f"{mix}/{solver_name}: SolverStatus differs on {int((~same).sum())} cells; "
+                        f"first: got {pkg.closure.decode_status(got[~same][:1])} want "
+                        f"{pkg.closure.decode_status(status_r[~same][:1])}")
+    nbits = 0
+    for a, b, nm_ in zip(st_d, st_r, ("rho", "vfrac", "sie", "temp", "press")):
+        ga = a.cpu().numpy()
+        assert_rel(ga[conv], b[conv], PTE_TOL, f"{mix}/{solver_name} state {nm_}")
+        nbits += int((ga.view(np.uint64) == b.view(np.uint64)).all())
+    lam_g = lam_d.cpu().numpy()
+    fin = np.isfinite(lam_r)
+    assert (np.isfinite(lam_g) == fin).all()
+    assert np.abs(lam_g[fin] - lam_r[fin]).max() <= 1e-10
+    print(f"{mix}/{solver_name}: {conv.mean():.3f} converged, {nbits}/5 state arrays bit-identical")
+
+
+@pytest.mark.parametrize("mix", ["analytic", "tabulated"])
+def test_get_sg_eos_rho_e(pkg, torch_cuda, raw1, mix):
+    """get_sg_eos (eos/get_sg_eos.cpp:36-280) for the (rho, e) input
+    condition against the REFERENCE'S OWN get_sg_eos -- its get_sg_eos*.cpp compiled where they
+    lie into the Kokkos build of the oracle harness.  Cells with 3, 2 and 1 participating
+    materials (mass fractions below the cutoff are dropped and the rest compacted: init_functor;
+    single participants take the pure-cell fast path), cell_dim > ncell with a permuted 1-based
+    offsets array, optional per-material bmod / dpde / cv outputs; pressure, temperature, bulk
+    modulus, cv, dpde, per-material volumes and energies and pmax to 1e-10."""
+    import oracle_ref
+    refk = oracle_ref.load_kokkos()
+    assert refk is not None, "oracle/_ref/libsgref_kokkos.so missing: run __graft_entry__.build()"
+    L, W = pkg._lib, pkg.workloads
+    if mix == "analytic":
+        g_l = pkg.closure.set_eos_3mat_analytic()
+        r_l = refk.set_eos_3mat()
+        rho0 = np.array(W.PTE_RHO)
+    else:
+        g_l = [pkg.SpinerEOSDependsRhoT(raw1), pkg.IdealGas(0.4, 7.16e6),
+               pkg.closure.set_eos_3mat_analytic()[0]]
+        r_l = [refk.SpinerRhoT(raw1), refk.IdealGas(0.4, 7.16e6), refk.set_eos_3mat()[0]]
+        rho0 = np.array([8.93, 1.0e-2, 8.93])
+    nmat, ncell, cell_dim = 3, 1500, 1507
+    rng = np.random.default_rng(99)
+    offsets = (rng.permutation(cell_dim)[:ncell] + 1).astype(np.int32)
+    vf = W.pte_vfracs(cell_dim, nmat=nmat)
+    # a third of the cells lose one material, a sixth are pure
+    kind = np.arange(cell_dim) % 6
+    vf[kind == 1, 2] = 0.0
+    vf[kind == 3, 0] = 0.0
+    vf[kind == 5, 1:] = 0.0
+    vf /= vf.sum(axis=1, keepdims=True)
+    rho = rho0[None, :] * (0.95 + 0.1 * rng.random((cell_dim, nmat)))
+    T0 = 500.0 + 400.0 * rng.random(cell_dim)
+    e_m = np.stack([r_l[m].eval(L.E_FROM_RHO_T, rho[:, m].copy(), T0,
+                                np.full((cell_dim, 3), np.nan) if r_l[m].nlambda() else None)
+                    for m in range(nmat)], axis=1)
+    mass = rho * vf
+    frac_mass = np.asfortranarray(mass / mass.sum(axis=1, keepdims=True))
+    spvol = 1.0 / mass.sum(axis=1)
+    sie = (mass * e_m).sum(axis=1) / mass.sum(axis=1)
+
+    def fresh():
+        a = dict(press=np.zeros(cell_dim), pmax=np.full(cell_dim, -1e300), vol=np.ones(cell_dim),
+                 spvol=spvol.copy(), sie=sie.copy(), temp=np.zeros(cell_dim),
+                 bmod=np.zeros(cell_dim), dpde=np.zeros(cell_dim), cv=np.zeros(cell_dim),
+                 frac_mass=frac_mass.copy(order="F"),
+                 frac_vol=np.zeros((cell_dim, nmat), order="F"),
+                 frac_ie=np.zeros((cell_dim, nmat), order="F"),
+                 frac_bmod=np.zeros((cell_dim, nmat), order="F"),
+                 frac_dpde=np.zeros((cell_dim, nmat), order="F"),
+                 frac_cv=np.zeros((cell_dim, nmat), order="F"))
+        return a
+    a_r, a_g = fresh(), fresh()
+    eos_offsets = [1, 2, 3]
+    refk.get_sg_eos(r_l, eos_offsets, offsets, **a_r, input_int=1, mass_frac_cutoff=1e-8)
+    pkg.closure.get_sg_eos(g_l, eos_offsets, offsets, **a_g, input_int=1, mass_frac_cutoff=1e-8)
+    idx = offsets - 1
+    assert np.isfinite(a_r["temp"][idx]).all() and (a_r["temp"][idx] > 0).all()
+    for k in ("press", "temp", "bmod", "dpde", "cv", "pmax", "frac_vol", "frac_ie", "frac_bmod",
+              "frac_dpde", "frac_cv"):
+        assert_rel(a_g[k][idx], a_r[k][idx], PTE_TOL, f"get_sg_eos[{mix}] {k}")
+    # cells the offsets array does not name are untouched, and inputs are left as they were
+    rest = np.setdiff1d(np.arange(cell_dim), idx)
+    assert (a_g["temp"][rest] == 0).all() and (a_g["frac_vol"][rest] == 0).all()
+    assert_bits(a_g["frac_mass"], frac_mass, "frac_mass is restored")
+    # other input conditions are refused, not mis-served
+    with pytest.raises(pkg.SgxError):
+        pkg.closure.get_sg_eos(g_l, eos_offsets, offsets, **fresh(), input_int=-3)
+
+
+@pytest.mark.parametrize("mix", ["3mat", "ideal+solids"])
+def test_pte_fixed_P_parity(pkg, ref, torch_cuda, mix):
+    """PTESolverFixedP (closure/mixed_cell_models.hpp:1674-1932) with iterate_t_guess = false,
+    where the reference's answer is defined: every SolverStatus field identical, states to
+    1e-10.  With iterate_t_guess on, GetTguess reads uscale / utotal_scale before this solver's
+    Init has set them (:536-538 vs :1747-1755): the library refuses that setting."""
+    torch = torch_cuda
+    L, W = pkg._lib, pkg.workloads
+    g3, r3 = pkg.closure.set_eos_3mat_analytic(), ref.set_eos_3mat()
+    if mix == "3mat":
+        g_l, r_l, rho0 = g3, r3, np.array(W.PTE_RHO)
+    else:
+        g_l = [pkg.IdealGas(0.4, 7.16e6), g3[0], g3[1]]
+        r_l = [ref.IdealGas(0.4, 7.16e6), r3[0], r3[1]]
+        rho0 = np.array([1.0e-2, 8.93, 1.89])
+    nm, n = 3, 2048
+    vf = W.pte_vfracs(n, nmat=nm)
+    rho = np.tile(rho0, (n, 1)) * (0.97 + 0.06 * pkg.rng.uniform_np(91, 0, n * nm).reshape(n, nm))
+    T0 = 600.0
+    sie = np.stack([r_l[m].eval(L.E_FROM_RHO_T, rho[:, m].copy(), np.full(n, T0))
+                    for m in range(nm)], axis=1)
+    P_m = np.stack([r_l[m].eval(L.P_FROM_RHO_T, rho[:, m].copy(), np.full(n, T0))
+                    for m in range(nm)], axis=1)
+    P_true = np.abs((vf * P_m).sum(axis=1)) + 1.0e8  # a pressure in the mixture's range
+    st_h = [np.ascontiguousarray(a) for a in (rho, vf, sie, np.full((n, nm), T0),
+                                              np.zeros((n, nm)))]
+    prm = pkg.closure.MixParams(iterate_t_guess=0)
+    st_r = [a.copy() for a in st_h]
+    status_r, res_r, _ = ref.pte_solve(L.PTE_FIXED_P, r_l, *st_r, prm, Tguess=P_true)
+    st_d = [dev(a) for a in st_h]
+    status = torch.zeros(n, dtype=torch.int64, device="cuda")
+    pkg.closure.PTESolverFixedP(g_l, dev(P_true), *st_d, params=prm, status=status)
+    torch.cuda.synchronize()
+    got = status.cpu().numpy().view(np.uint64)
+    conv = (status_r & 1).astype(bool)
+    print(f"FixedP {mix}: reference converged on {conv.mean():.3f} of the cells")
+    assert conv.mean() > 0.5
+    assert (got == status_r).all(), f"SolverStatus differs on {int((got != status_r).sum())} cells"
+    for a, b, nm_ in zip(st_d, st_r, ("rho", "vfrac", "sie", "temp", "press")):
+        assert_rel(a.cpu().numpy()[conv], b[conv], PTE_TOL, f"FixedP {mix} state {nm_}")
+    with pytest.raises(pkg.SgxError):
+        pkg.closure.PTESolverFixedP(g_l, dev(P_true), *[dev(a) for a in st_h],
+                                    params=pkg.closure.MixParams(iterate_t_guess=1))
 
 
 def test_pte_properties_full_path(pkg, torch_cuda):
