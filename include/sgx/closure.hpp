@@ -119,6 +119,35 @@ inline void PTESolverFixedT(const std::vector<EosBase> &eos, std::int64_t ncell,
               T_true, params, status, residual, stats, stream);
 }
 
+// PTESolverFixedP + PTESolver (closure/mixed_cell_models.hpp:1674-1932): the pressure of every
+// cell is given (P_true [ncell]); unknowns are the volume fractions and the temperature.
+// params.iterate_t_guess must be 0 (include/sgx_b200.h, SGX_PTE_FIXED_P).
+inline void PTESolverFixedP(const std::vector<EosBase> &eos, std::int64_t ncell,
+                            const Real *P_true, Real *rho, Real *vfrac, Real *sie, Real *temp,
+                            Real *press, const MixParams &params,
+                            std::uint64_t *status = nullptr, const Real *vfrac_tot = nullptr,
+                            Real *residual = nullptr, std::uint64_t *stats = nullptr,
+                            sgx_stream_t stream = nullptr) {
+  detail::pte(SGX_PTE_FIXED_P, eos, ncell, rho, vfrac, sie, temp, press, nullptr, vfrac_tot,
+              P_true, params, status, residual, stats, stream);
+}
+
+// PTESolverRhoT over a mixture that holds tabulated materials, with the per-material lambda
+// caches of the reference's CacheAccessor (:307-324): lambda = [ncell][nmat][3] or nullptr.
+inline void PTESolverRhoTCached(const std::vector<EosBase> &eos, std::int64_t ncell, Real *rho,
+                                Real *vfrac, Real *sie, Real *temp, Real *press, Real *lambda,
+                                const MixParams &params = MixParams(),
+                                std::uint64_t *status = nullptr, const Real *sie_tot = nullptr,
+                                const Real *vfrac_tot = nullptr, const Real *Tguess = nullptr,
+                                Real *residual = nullptr, sgx_stream_t stream = nullptr) {
+  std::vector<sgx_eos_t> h;
+  for (const EosBase &e : eos)
+    h.push_back(e.handle());
+  check(sgx_pte_solve_cached(SGX_PTE_RHOT, h.data(), static_cast<int>(h.size()), ncell, rho,
+                             vfrac, sie, temp, press, sie_tot, vfrac_tot, Tguess, &params,
+                             status, residual, nullptr, lambda, stream));
+}
+
 // The three materials of test/pte_test_3mat_analytic.hpp:38-50
 inline std::vector<EosBase> set_eos_3mat_analytic() {
   return {Gruneisen(394000.0, 1.489, 0.0, 0.0, 2.02, 0.47, 8.93, 297.0, 1.0e6, 0.383e7),

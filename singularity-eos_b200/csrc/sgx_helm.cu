@@ -300,8 +300,20 @@ int launch_helm_fill(sgx_eos_s *e, double *rho, double *T, double *en, double *P
   constexpr unsigned long kModeII = TQ_TEMPERATURE | TQ_PRESSURE | TQ_CV | TQ_BMOD;
   // mode (i): 128 registers / 4 blocks per SM measured 6 % ahead of 204 registers / 2 blocks
   if (output == kModeI && T && en && P && cv && bmod) {
-    helm_fill_kernel<kModeI, 4><<<c.blocks, c.threads, 0, s>>>(e->helm, rho, T, en, P, cv, bmod, n,
-                                                            output, lambda, stride, nullptr);
+    // SGX_HELM_MINB=3|5: the register-budget study of DESIGN.md 5.4 (168 / 96 registers)
+    static const int minb = [] {
+      const char *v = getenv("SGX_HELM_MINB");
+      return v ? atoi(v) : 4;
+    }();
+    if (minb == 3)
+      helm_fill_kernel<kModeI, 3><<<c.blocks, c.threads, 0, s>>>(
+          e->helm, rho, T, en, P, cv, bmod, n, output, lambda, stride, nullptr);
+    else if (minb == 5)
+      helm_fill_kernel<kModeI, 5><<<c.blocks, c.threads, 0, s>>>(
+          e->helm, rho, T, en, P, cv, bmod, n, output, lambda, stride, nullptr);
+    else
+      helm_fill_kernel<kModeI, 4><<<c.blocks, c.threads, 0, s>>>(
+          e->helm, rho, T, en, P, cv, bmod, n, output, lambda, stride, nullptr);
   } else if (output == kModeII && T && en && P && cv && bmod) {
     helm_fill_kernel<kModeII><<<c.blocks, c.threads, 0, s>>>(e->helm, rho, T, en, P, cv, bmod,
                                                              n, output, lambda, stride, nullptr);

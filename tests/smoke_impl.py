@@ -65,8 +65,48 @@ def run():
     conv = (st_r & 1) != 0
     for a, b, nm in zip(s_d, s_h, ("rho", "vfrac", "sie", "temp", "press")):
         assert_rel(a.cpu().numpy()[conv], b[conv], 1e-10, "PTE " + nm)
+    assert (st_g == st_r).all(), "PTE SolverStatus words differ from the reference"
+
+    # config 3b: SpinerEOSDependsRhoSie direct T(rho, sie)
+    gq, rq = pkg.SpinerEOSDependsRhoSie(raw), ref.SpinerRhoSie(raw)
+    lam1 = dev(np.full((n, 1), np.nan))
+    gq.TemperatureFromDensityInternalEnergy(rho_d, dev(e_h), out, n, lam1)
+    assert_rel(out.cpu().numpy(), rq.eval(L.T_FROM_RHO_E, rho_h, e_h, np.full((n, 1), np.nan)),
+               1e-12, "SpinerRhoSie T(rho,e)")
+
+    # config 4: Helmholtz FillEos(rho, T) -> e, P, cv, bmod on the synthetic table
+    import tempfile
+    tq = pkg.thermalqs
+    with tempfile.TemporaryDirectory() as d:
+        hp = pkg.tablegen.write_synthetic_helm_table(os.path.join(d, "helm.dat"))
+        gh = pkg.Helmholtz(hp)
+        rh = ref.Helmholtz(hp, L.HelmOptions(1, 1, 1, 1, 1, 1, 1))
+    nh = 4096
+    hr, hT = pkg.workloads.helm_inputs(nh)
+    lam3 = np.tile(np.array([4.0, 2.0, -1.0]), (nh, 1))
+    mask = tq.specific_internal_energy | tq.pressure | tq.specific_heat | tq.bulk_modulus
+    e_r, P_r, cv_r, b_r = (np.zeros(nh) for _ in range(4))
+    rh.fill(hr.copy(), hT.copy(), e_r, P_r, cv_r, b_r, mask, lam3.copy(), nthreads=0)
+    he, hP, hcv, hb = (torch.zeros(nh, dtype=torch.float64, device="cuda") for _ in range(4))
+    gh.FillEos(dev(hr), dev(hT), he, hP, hcv, hb, nh, mask, dev(lam3))
+    for got, want, nm in ((he, e_r, "e"), (hP, P_r, "P"), (hcv, cv_r, "cv"), (hb, b_r, "bmod")):
+        assert_rel(got.cpu().numpy(), want, 1e-12, "Helmholtz FillEos " + nm)
+
+    # PTESolverPT on 512 cells: identical status words, 1e-10 states
+    mp = 512
+    p_h = W.pte_state_np(mp, sie0)
+    p_d = [dev(a) for a in p_h]
+    st_r, _, _ = ref.pte_solve(L.PTE_PT, r3, *p_h, prm, nthreads=0)
+    status = torch.zeros(mp, dtype=torch.int64, device="cuda")
+    pkg.closure.PTESolverPT(g3, *p_d, params=prm, status=status)
+    torch.cuda.synchronize()
+    assert (status.cpu().numpy().view(np.uint64) == st_r).all(), "PTESolverPT status differs"
+    cpt = (st_r & 1) != 0
+    for a, b, nm in zip(p_d, p_h, ("rho", "vfrac", "sie", "temp", "press")):
+        assert_rel(a.cpu().numpy()[cpt], b[cpt], 1e-10, "PTESolverPT " + nm)
+
     launched = lib.sgx_launch_count() - before
-    assert launched >= 4
+    assert launched >= 9
     print(f"smoke ok: {launched} sgx kernels launched on {torch.cuda.get_device_name(0)}; "
           f"PTE converged {int(conv.sum())}/{m}")
 

@@ -413,3 +413,50 @@ def test_reference_side_plugin_compiles_and_links(pkg):
         pytest.skip("reference not mounted and no prebuilt tests/cpp/_build/test_plugin")
     out = subprocess.run([exe, "--link-only"], capture_output=True, text=True, timeout=60)
     assert out.returncode == 0, out.stdout + out.stderr
+
+
+def test_get_sg_eos_composed_oracle_equals_reference_driver(pkg):
+    """helpers.get_sg_eos_composed (the (rho, e) branch of get_sg_eos re-assembled from the
+    reference's own pieces, used as the oracle where the real driver's lambda cache aliases its
+    solver scratch) is BIT-IDENTICAL to the reference's own get_sg_eos
+    (eos/get_sg_eos.cpp:36-280, compiled into the Kokkos build of the harness) on a mixture
+    whose materials never write a lambda: cells with 3, 2 and 1 participating materials."""
+    import oracle_ref
+    from helpers import get_sg_eos_composed
+
+    refk = oracle_ref.load_kokkos()
+    if refk is None:
+        pytest.skip("oracle/_ref/libsgref_kokkos.so not built")
+    L, W = pkg._lib, pkg.workloads
+    r_l = refk.set_eos_3mat()
+    nmat, ncell, cell_dim = 3, 120, 125
+    rng = np.random.default_rng(5)
+    offsets = (rng.permutation(cell_dim)[:ncell] + 1).astype(np.int32)
+    vf = W.pte_vfracs(cell_dim, nmat=nmat)
+    kind = np.arange(cell_dim) % 6
+    vf[kind == 1, 2] = 0.0
+    vf[kind == 3, 0] = 0.0
+    vf[kind == 5, 1:] = 0.0
+    vf /= vf.sum(axis=1, keepdims=True)
+    rho = np.array(W.PTE_RHO)[None, :] * (0.95 + 0.1 * rng.random((cell_dim, nmat)))
+    T0 = 500.0 + 400.0 * rng.random(cell_dim)
+    e_m = np.stack([r_l[m].eval(L.E_FROM_RHO_T, rho[:, m].copy(), T0) for m in range(nmat)],
+                   axis=1)
+    mass = rho * vf
+    frac_mass = np.asfortranarray(mass / mass.sum(axis=1, keepdims=True))
+    spvol = 1.0 / mass.sum(axis=1)
+    sie = (mass * e_m).sum(axis=1) / mass.sum(axis=1)
+
+    def fresh():
+        z = lambda: np.zeros((cell_dim, nmat), order="F")  # noqa: E731
+        return dict(press=np.zeros(cell_dim), pmax=np.full(cell_dim, -1e300),
+                    vol=np.ones(cell_dim), spvol=spvol.copy(), sie=sie.copy(),
+                    temp=np.zeros(cell_dim), bmod=np.zeros(cell_dim), dpde=np.zeros(cell_dim),
+                    cv=np.zeros(cell_dim), frac_mass=frac_mass.copy(order="F"), frac_vol=z(),
+                    frac_ie=z(), frac_bmod=z(), frac_dpde=z(), frac_cv=z())
+    a1, a2 = fresh(), fresh()
+    refk.get_sg_eos(r_l, [1, 2, 3], offsets, **a1, input_int=1, mass_frac_cutoff=1e-8)
+    get_sg_eos_composed(refk, L, r_l, [1, 2, 3], offsets, a2, 1e-8, refk.mix_params_default())
+    for k in a1:
+        assert_bits(a2[k], a1[k], "get_sg_eos composed vs driver: " + k)
+    assert (a1["temp"][offsets - 1] > 0).all()

@@ -984,7 +984,27 @@ def test_get_sg_eos_rho_e(pkg, torch_cuda, raw1, mix):
         return a
     a_r, a_g = fresh(), fresh()
     eos_offsets = [1, 2, 3]
-    refk.get_sg_eos(r_l, eos_offsets, offsets, **a_r, input_int=1, mass_frac_cutoff=1e-8)
+    if mix == "analytic":
+        refk.get_sg_eos(r_l, eos_offsets, offsets, **a_r, input_int=1, mass_frac_cutoff=1e-8)
+    else:
+        # The reference driver's lambda cache aliases PTESolverRhoT's dpdv / dedv / dpdT scratch
+        # (helpers.get_sg_eos_composed explains): with lambda-WRITING materials its multi-material
+        # solves return garbage.  The oracle here is the driver re-assembled from the reference's
+        # own pieces with a separate cache buffer; the real driver still checks the cells it
+        # cannot corrupt (pure cells and cells without the tabulated material).
+        from helpers import get_sg_eos_composed
+        get_sg_eos_composed(refk, L, r_l, eos_offsets, offsets, a_r, 1e-8,
+                            refk.mix_params_default())
+        a_d = fresh()
+        refk.get_sg_eos(r_l, eos_offsets, offsets, **a_d, input_int=1, mass_frac_cutoff=1e-8)
+        clean = np.isin(kind, (3, 5))[offsets - 1]
+        ic = (offsets - 1)[clean]
+        for k in ("press", "temp", "bmod", "cv", "dpde"):
+            assert_rel(a_r[k][ic], a_d[k][ic], PTE_TOL, f"composed oracle vs the real driver {k}")
+        nbad = int((~np.isclose(a_d["press"][offsets - 1], a_r["press"][offsets - 1],
+                                rtol=1e-6)).sum())
+        print(f"reference get_sg_eos corrupted by its own cache aliasing on {nbad} of "
+              f"{ncell} cells of the tabulated mixture")
     pkg.closure.get_sg_eos(g_l, eos_offsets, offsets, **a_g, input_int=1, mass_frac_cutoff=1e-8)
     idx = offsets - 1
     assert np.isfinite(a_r["temp"][idx]).all() and (a_r["temp"][idx] > 0).all()
@@ -1021,11 +1041,12 @@ def test_pte_fixed_P_parity(pkg, ref, torch_cuda, mix):
     T0 = 600.0
     sie = np.stack([r_l[m].eval(L.E_FROM_RHO_T, rho[:, m].copy(), np.full(n, T0))
                     for m in range(nm)], axis=1)
-    P_m = np.stack([r_l[m].eval(L.P_FROM_RHO_T, rho[:, m].copy(), np.full(n, T0))
-                    for m in range(nm)], axis=1)
-    P_true = np.abs((vf * P_m).sum(axis=1)) + 1.0e8  # a pressure in the mixture's range
     st_h = [np.ascontiguousarray(a) for a in (rho, vf, sie, np.full((n, nm), T0),
                                               np.zeros((n, nm)))]
+    # pressures near each cell's own PTE pressure (from the reference's RhoT solve), +-5 %
+    eq = [a.copy() for a in st_h]
+    ref.pte_solve(L.PTE_RHOT, r_l, *eq, ref.mix_params_default())
+    P_true = eq[4][:, 0] * (1.0 + 0.1 * (pkg.rng.uniform_np(92, 0, n) - 0.5))
     prm = pkg.closure.MixParams(iterate_t_guess=0)
     st_r = [a.copy() for a in st_h]
     status_r, res_r, _ = ref.pte_solve(L.PTE_FIXED_P, r_l, *st_r, prm, Tguess=P_true)
@@ -1035,6 +1056,8 @@ def test_pte_fixed_P_parity(pkg, ref, torch_cuda, mix):
     torch.cuda.synchronize()
     got = status.cpu().numpy().view(np.uint64)
     conv = (status_r & 1).astype(bool)
+    # (without the T-guess iteration the reference itself converges on ~70-77 % of these cells;
+    # the cells it gives up on must be given up on identically: status words incl. niter)
     print(f"FixedP {mix}: reference converged on {conv.mean():.3f} of the cells")
     assert conv.mean() > 0.5
     assert (got == status_r).all(), f"SolverStatus differs on {int((got != status_r).sum())} cells"
