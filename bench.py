@@ -434,6 +434,45 @@ def run_ours(args):
                 "converged_frac": float((stg & 1).double().mean().item()),
                 "materials": [type(e).__name__ for e in eos_g]}
             del g0, gs, stg
+        # a production-like mixed cell -- tabulated copper (SpinerEOSDependsRhoT,
+        # per-material lambda caches) + IdealGas + Gruneisen, 2^22 cells
+        nt = min(npte, 1 << 22)
+        eos_t = [eos_rt, pkg.IdealGas(0.4, 7.16e6), g3[0]]
+        rho0_t = torch.tensor([8.93, 1.0e-2, 8.93], dtype=torch.float64, device=dev)
+        rho_t = (rho0_t.repeat(nt, 1) *
+                 (0.9 + 0.2 * pkg.rng.uniform_torch(57, rank * nt * 3, nt * 3, dev)
+                  .reshape(nt, 3))).contiguous()
+        T_t = torch.full((nt,), 600.0, dtype=torch.float64, device=dev)
+        sie_t = torch.empty((nt, 3), dtype=torch.float64, device=dev)
+        col = torch.empty(nt, dtype=torch.float64, device=dev)
+        lam_t = torch.full((nt, 3, 3), float("nan"), dtype=torch.float64, device=dev)
+        for m, em in enumerate(eos_t):
+            if m == 0:
+                em.InternalEnergyFromDensityTemperature(rho_t[:, m].contiguous(), T_t, col, nt,
+                                                        lam_t[:, 0, :2].contiguous())
+            else:
+                em.InternalEnergyFromDensityTemperature(rho_t[:, m].contiguous(), T_t, col, nt)
+            sie_t[:, m] = col
+        t0_ = [rho_t, W.pte_vfracs(nt, start=rank * nt, xp=torch, device=dev, nmat=3), sie_t,
+               torch.full((nt, 3), 600.0, dtype=torch.float64, device=dev),
+               torch.zeros((nt, 3), dtype=torch.float64, device=dev)]
+        ts_ = [a.clone() for a in t0_]
+        stt = torch.zeros(nt, dtype=torch.int64, device=dev)
+
+        def pte_tab():
+            for a, b in zip(ts_, t0_):
+                a.copy_(b)
+            lam_t.fill_(float("nan"))
+            pkg.closure.pte_solve(L.PTE_RHOT, eos_t, *ts_, params=prm_def, status=stt,
+                                  lambdas=lam_t)
+        s = time_steps(torch, pte_tab, ks, 1, dist)
+        results["pte_rhot_tabulated_3mat_default_mixparams"] = {
+            "cell_solves_per_s": nt * world * ks / s, "cells_per_gpu": nt,
+            "converged_frac": float((stt & 1).double().mean().item()),
+            "materials": ["SpinerEOSDependsRhoT (Vinet Cu table, lambda cache)", "IdealGas",
+                          "Gruneisen"],
+            "kernel": "pte_kernel<3, TabEos, RhoT> (per-cell)"}
+        del t0_, ts_, stt, lam_t, sie_t, rho_t
         # e2e for config 5: host buffers through sgx_pte_solve_host (chunked, 3 streams)
         npe = min(npte, 1 << 22)
         hst0 = [a[:npe].cpu() for a in state0]
