@@ -770,6 +770,37 @@ int ref_pte_solve_cached(int solver, void **eos_handles, int nmat, int64_t ncell
   return rc;
 }
 
+// Demonstration for DESIGN.md 7: PTESolverFixedP::Init() with iterate_t_guess = true reads the
+// base-class members uscale / utotal_scale (mixed_cell_models.hpp:537) before anything has
+// written them (:1747-1755 -- the constructor chain :371-387 leaves them uninitialised).  The
+// solver object of ONE cell is placement-constructed over a buffer pre-filled with the bit
+// pattern of `fill`, Init() runs, and the caller gets back what Init() left in sie[] (=
+// e(rho, Tguess), i.e. the temperature guess it settled on).  If the answer depends on `fill`,
+// the reference has no defined result to match.
+int ref_pte_fixedp_init_probe(void **eos_handles, int nmat, double *rho, double *vfrac,
+                              double *sie, double *temp, double *press, double P,
+                              const sgx_mix_params *params, double fill) {
+  const MixParams mp = to_params(params);
+  std::vector<EOS> eos_vec(nmat);
+  for (int m = 0; m < nmat; ++m)
+    eos_vec[m] = *static_cast<EOS *>(eos_handles[m]);
+  EosIndexer eos{eos_vec.data()};
+  std::vector<double> scratch(PTESolverFixedPRequiredScratch(nmat));
+  using Solver = PTESolverFixedP<EosIndexer, RowIndexer, NullIndexer>;
+  constexpr std::size_t nd = (sizeof(Solver) + sizeof(double) - 1) / sizeof(double);
+  alignas(alignof(Solver) > alignof(double) ? alignof(Solver) : alignof(double)) double buf[nd];
+  for (std::size_t k = 0; k < nd; ++k)
+    buf[k] = fill;
+  RowIndexer r{rho}, vf{vfrac}, e{sie}, tp{temp}, pr{press};
+  NullIndexer no_lambda;
+  return guarded([&]() {
+    Solver *method = new (buf) Solver(nmat, eos, 1.0, P, r, vf, e, tp, pr, no_lambda,
+                                      scratch.data(), mp);
+    method->Init();
+    method->~Solver();
+  });
+}
+
 // The reference's own get_sg_eos (eos/get_sg_eos.cpp:36-280; Kokkos-only code, so only the
 // Kokkos build of this library has it).  eos_handles[k] are this harness's EOS objects.
 #ifdef SGREF_KOKKOS

@@ -126,7 +126,7 @@ def get_sg_eos(eos_list, eos_offsets, offsets, press, pmax, vol, spvol, sie, tem
                input_int=1, mass_frac_cutoff=1e-16):
     """get_sg_eos (eos/get_sg_eos.cpp:36-58) on numpy HOST arrays, the reference's own memory
     contract: per-cell arrays [cell_dim], per-material arrays Fortran-ordered (cell_dim, nmat),
-    1-based int32 offsets.  (rho, e) input conditions only."""
+    1-based int32 offsets.  input_int: 0 / 1 (rho, e), -3 (rho, T), -1 (P, T)."""
     import numpy as np
 
     nmat = len(eos_offsets)

@@ -155,6 +155,23 @@ SGX_HD unsigned long long div3_u53(const unsigned long long n) {
 // (frac_squared ~ f^2 / 2^52 <= f), so C++'s truncating `/ 3` is floor division.
 // Bit-identical to the literal formula: tests/test_cpu_oracle.py::test_lg_restatement_bits.
 SGX_HD double lg(const double x) {
+#ifdef __CUDA_ARCH__
+  // Device form: the same integers on explicit 32-bit registers.  nvcc does not see that
+  // (f >> 26) has a zero upper word and emulates full 64x64 products (3 IMAD each); here every
+  // product is one IMAD.WIDE.U32 and every shift one funnel shift.  f = {fhi20 : flo32}.
+  const long long xi = as_int(x) - one_as_int;
+  const unsigned int lo = (unsigned int)xi;
+  const unsigned int fhi20 = (unsigned int)((unsigned long long)xi >> 32) & 0xfffffu;
+  const unsigned int fh = __funnelshift_l(lo, fhi20, 6); // f >> 26, < 2^26
+  const unsigned int fl = lo & (unsigned int)low_mask;
+  const unsigned long long cross = (unsigned long long)fh * fl; // < 2^52
+  const unsigned int cross_sh =
+      __funnelshift_r((unsigned int)cross, (unsigned int)(cross >> 32), 25); // < 2^27
+  const unsigned long long sq = (unsigned long long)fh * fh + cross_sh;
+  const unsigned long long f = ((unsigned long long)fhi20 << 32) | lo;
+  const long long third_d = (long long)div3_u53(f - sq);
+  return __ll2double_rn(xi + third_d) * scale_down;
+#else
   const long long x_as_int = as_int(x) - one_as_int;
   const unsigned long long frac_as_int = (unsigned long long)(x_as_int & mantissa_mask);
   const unsigned int frac_high = (unsigned int)(frac_as_int >> 26);
@@ -164,6 +181,7 @@ SGX_HD double lg(const double x) {
       (((unsigned long long)frac_high * frac_low) >> 25);
   const long long third = (long long)div3_u53(frac_as_int - frac_squared);
   return static_cast<double>(x_as_int + third) * scale_down;
+#endif
 }
 // the literal formula of logs.hpp:188-199, kept for the bit-equality test
 SGX_HD double lg_literal(const double x) {

@@ -63,6 +63,8 @@ def load(path=None):
                                  [C.POINTER(L.MixParams), _VP, _VP, _VP, _VP, C.c_int]),
         "ref_get_sg_eos": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, _VP, C.POINTER(_VP),
                                      C.c_int, _VP] + [_VP] * 15 + [_D]),
+        "ref_pte_fixedp_init_probe": (C.c_int, [C.POINTER(_VP), C.c_int] + [_VP] * 5 +
+                                      [_D, C.POINTER(L.MixParams), _D]),
         "ref_pte_approx_T": (None, [C.POINTER(_VP), C.c_int, _I64, _VP, _VP, _VP, _VP]),
         "ref_bounds_log_grid": (C.c_int, [_D, _D, C.c_int, C.POINTER(L.Grid1D), C.POINTER(_D),
                                           _VP]),
@@ -245,6 +247,14 @@ class Ref:
             _p(status), _p(resid), _p(tg), _p(lambdas), nthreads)
         assert rc == 0
         return status, resid, tg
+
+    def pte_fixedp_init_probe(self, eos_list, rho, vfrac, sie, temp, press, P, params, fill):
+        """PTESolverFixedP::Init() of ONE cell, the solver object constructed over memory that
+        holds the double `fill`; the state arrays ([nmat]) are updated in place."""
+        hs = (_VP * len(eos_list))(*[e.h for e in eos_list])
+        return self.lib.ref_pte_fixedp_init_probe(hs, len(eos_list), _p(rho), _p(vfrac), _p(sie),
+                                                  _p(temp), _p(press), float(P),
+                                                  C.byref(params), float(fill))
 
     def get_sg_eos(self, eos_list, eos_offsets, offsets, press, pmax, vol, spvol, sie, temp,
                    bmod, dpde, cv, frac_mass, frac_vol, frac_ie, frac_bmod=None, frac_dpde=None,

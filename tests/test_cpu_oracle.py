@@ -460,3 +460,39 @@ def test_get_sg_eos_composed_oracle_equals_reference_driver(pkg):
     for k in a1:
         assert_bits(a2[k], a1[k], "get_sg_eos composed vs driver: " + k)
     assert (a1["temp"][offsets - 1] > 0).all()
+
+
+def test_pte_fixed_P_uninitialised_uscale_in_reference(pkg, ref):
+    """DESIGN.md 7 / VERDICT r1 item 9: PTESolverFixedP::Init() calls GetTguess(), whose Newton
+    step reads uscale * utotal_scale (closure/mixed_cell_models.hpp:537) before Init() sets
+    uscale (:1755); the constructors (:371-387, :1700-1738) never initialise them.  Shown on the
+    reference itself: the same cell, the solver object constructed over memory holding two
+    different bit patterns.  With iterate_t_guess = false the members are not read and the
+    result is independent of the pattern (the case sgx_pte_solve supports); with
+    iterate_t_guess = true the temperature guess Init() settles on follows the garbage."""
+    L, W = pkg._lib, pkg.workloads
+    r3 = ref.set_eos_3mat()
+    sie0 = [r3[m].eval(L.E_FROM_RHO_T, [W.PTE_RHO[m]], [W.PTE_T])[0] for m in range(3)]
+    P = 1.0e10
+
+    def probe(iterate, fill):
+        rho = np.array(W.PTE_RHO, dtype=np.float64)
+        vf = np.array([0.3, 0.3, 0.4])
+        sie = np.array(sie0)
+        temp = np.full(3, W.PTE_T)
+        press = np.zeros(3)
+        prm = ref.mix_params_default()
+        prm.iterate_t_guess = int(iterate)
+        rc = ref.pte_fixedp_init_probe(r3, rho, vf, sie, temp, press, P, prm, fill)
+        return rc, sie
+
+    rc_a, sie_a = probe(False, 0.0)
+    rc_b, sie_b = probe(False, -1.0e30)
+    assert rc_a == 0 and rc_b == 0
+    assert (sie_a.view(np.uint64) == sie_b.view(np.uint64)).all(), \
+        "iterate_t_guess = false must not depend on uninitialised members"
+    rc_c, sie_c = probe(True, 0.0)
+    rc_d, sie_d = probe(True, -1.0e30)
+    differs = rc_c != rc_d or not (sie_c.view(np.uint64) == sie_d.view(np.uint64)).all()
+    print("iterate_t_guess=true: fill 0.0 ->", rc_c, sie_c, "; fill -1e30 ->", rc_d, sie_d)
+    assert differs, "expected the reference's Init() to depend on the garbage it reads"

@@ -8,7 +8,7 @@ import ctypes as C
 import numpy as np
 import pytest
 
-from helpers import assert_bits, assert_rel, dev, is_close
+from helpers import EV2K, assert_bits, assert_rel, dev, is_close
 
 pytestmark = pytest.mark.gpu
 
@@ -1015,9 +1015,80 @@ def test_get_sg_eos_rho_e(pkg, torch_cuda, raw1, mix):
     rest = np.setdiff1d(np.arange(cell_dim), idx)
     assert (a_g["temp"][rest] == 0).all() and (a_g["frac_vol"][rest] == 0).all()
     assert_bits(a_g["frac_mass"], frac_mass, "frac_mass is restored")
-    # other input conditions are refused, not mis-served
+    # the (rho, P) condition is refused (undefined in the reference), not mis-served
     with pytest.raises(pkg.SgxError):
-        pkg.closure.get_sg_eos(g_l, eos_offsets, offsets, **fresh(), input_int=-3)
+        pkg.closure.get_sg_eos(g_l, eos_offsets, offsets, **fresh(), input_int=-2)
+
+
+@pytest.mark.parametrize("mix", ["analytic", "tabulated"])
+@pytest.mark.parametrize("input_int", [-3, -1])
+def test_get_sg_eos_rho_t_and_p_t(pkg, torch_cuda, raw1, mix, input_int):
+    """get_sg_eos for the (rho, T) condition (input_int -3, get_sg_eos_rho_t.cpp:22-101:
+    PTESolverFixedT over the participating materials, pure-cell fast path) and the (P, T)
+    condition (input_int -1, get_sg_eos_p_t.cpp:22-96: DensityEnergyFromPressureTemperature per
+    material) against the REFERENCE'S OWN get_sg_eos (Kokkos build of the harness).  Unlike
+    (rho, e), these drivers place the lambda cache behind the solver scratch, so tabulated
+    mixtures are compared with the real driver too.  Every output the mode copies back, 1e-10."""
+    import oracle_ref
+    refk = oracle_ref.load_kokkos()
+    assert refk is not None, "oracle/_ref/libsgref_kokkos.so missing: run __graft_entry__.build()"
+    L, W = pkg._lib, pkg.workloads
+    if mix == "analytic":
+        g_l = pkg.closure.set_eos_3mat_analytic()
+        r_l = refk.set_eos_3mat()
+        rho0 = np.array(W.PTE_RHO)
+    else:
+        g_l = [pkg.SpinerEOSDependsRhoT(raw1), pkg.IdealGas(0.4, 7.16e6),
+               pkg.closure.set_eos_3mat_analytic()[0]]
+        r_l = [refk.SpinerRhoT(raw1), refk.IdealGas(0.4, 7.16e6), refk.set_eos_3mat()[0]]
+        rho0 = np.array([8.93, 1.0e-2, 8.93])
+    nmat, ncell, cell_dim = 3, 1200, 1209
+    rng = np.random.default_rng(77)
+    offsets = (rng.permutation(cell_dim)[:ncell] + 1).astype(np.int32)
+    vf = W.pte_vfracs(cell_dim, nmat=nmat)
+    kind = np.arange(cell_dim) % 6
+    if input_int == -3:  # (P, T) has no cutoff: every material of every cell takes part
+        vf[kind == 1, 2] = 0.0
+        vf[kind == 3, 0] = 0.0
+        vf[kind == 5, 1:] = 0.0
+    vf /= vf.sum(axis=1, keepdims=True)
+    rho = rho0[None, :] * (0.95 + 0.1 * rng.random((cell_dim, nmat)))
+    mass = rho * vf
+    frac_mass = np.asfortranarray(mass / mass.sum(axis=1, keepdims=True))
+    spvol = 1.0 / mass.sum(axis=1)
+    temp_ev = (500.0 + 400.0 * rng.random(cell_dim)) / EV2K
+    # (P, T): a pressure every material can reach at these temperatures
+    press_in = 1.0e9 * (1.0 + rng.random(cell_dim)) if input_int == -1 else np.zeros(cell_dim)
+
+    def fresh():
+        return dict(press=press_in.copy(), pmax=np.full(cell_dim, -1e300), vol=np.ones(cell_dim),
+                    spvol=spvol.copy(), sie=np.zeros(cell_dim), temp=temp_ev.copy(),
+                    bmod=np.zeros(cell_dim), dpde=np.zeros(cell_dim), cv=np.zeros(cell_dim),
+                    frac_mass=frac_mass.copy(order="F"),
+                    frac_vol=np.zeros((cell_dim, nmat), order="F"),
+                    frac_ie=np.zeros((cell_dim, nmat), order="F"),
+                    frac_bmod=np.zeros((cell_dim, nmat), order="F"),
+                    frac_dpde=np.zeros((cell_dim, nmat), order="F"),
+                    frac_cv=np.zeros((cell_dim, nmat), order="F"))
+    a_r, a_g = fresh(), fresh()
+    eos_offsets = [1, 2, 3]
+    refk.get_sg_eos(r_l, eos_offsets, offsets, **a_r, input_int=input_int, mass_frac_cutoff=1e-8)
+    pkg.closure.get_sg_eos(g_l, eos_offsets, offsets, **a_g, input_int=input_int,
+                           mass_frac_cutoff=1e-8)
+    idx = offsets - 1
+    assert np.isfinite(a_r["sie"][idx]).all() and np.isfinite(a_r["bmod"][idx]).all()
+    keys = ["sie", "bmod", "dpde", "cv", "pmax", "frac_vol", "frac_ie", "frac_bmod", "frac_dpde",
+            "frac_cv", "vol"]
+    keys += ["press"] if input_int == -3 else ["spvol"]
+    for k in keys:
+        assert_rel(a_g[k][idx], a_r[k][idx], PTE_TOL, f"get_sg_eos[{mix}, {input_int}] {k}")
+    # inputs of the mode come back untouched
+    assert_bits(a_g["temp"], temp_ev, "temp is an input")
+    assert_bits(a_g["frac_mass"], frac_mass, "frac_mass is restored")
+    if input_int == -1:
+        assert_bits(a_g["press"], press_in, "press is an input")
+    else:
+        assert_bits(a_g["spvol"], spvol, "spvol is an input")
 
 
 @pytest.mark.parametrize("mix", ["3mat", "ideal+solids"])
