@@ -143,6 +143,9 @@ PROTOTYPES = {
                                                            C.c_int, _VP]),
     "sgx_PressureFromDensityInternalEnergy": (C.c_int, [_VP, _VP, _VP, _VP, _I64, _VP,
                                                         C.c_int, _VP]),
+    "sgx_noalloc_max_cells": (C.c_int64, []),
+    "sgx_TemperatureFromDensityInternalEnergy_noalloc": (C.c_int, [_VP, _VP, _VP, _VP, _I64, _VP,
+                                                                   C.c_int, _VP]),
     "sgx_PressureEnergyFromDensityTemperature": (C.c_int, [_VP, _VP, _VP, _VP, _VP, _I64, _VP,
                                                            C.c_int, _VP]),
     "sgx_FillEos": (C.c_int, [_VP] * 7 + [_I64, C.c_ulong, _VP, C.c_int, _VP]),

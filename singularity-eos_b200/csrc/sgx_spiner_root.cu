@@ -327,3 +327,108 @@ int launch_rhot_T_from_rho_e_hybrid(sgx_eos_s *e, bool bounded, const double *rh
 }
 
 } // namespace sgx
+
+// ---------------------------------------------------------------------------------------
+// Allocation-free variant of the hybrid T(rho, sie) launch above, for callers that cannot
+// call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  It has
+// no counterpart in the reference.
+// The two kernels are the ones above; only the scratch (counters + sub-lists) differs: it is
+// this file-scope device array, resident on every GPU that loads the library until exit.
+// In host code the array's NAME is a host-side stand-in, not a device address: the address
+// the kernels get is taken once per device with cudaGetSymbolAddress, that device current.
+// ---------------------------------------------------------------------------------------
+#include <mutex>
+
+#define SGX_NOALLOC_MAX_CELLS_ (1ll << 20)
+// counters: kRootSubLists x kRootCounterStride unsigned ints (4 KiB), then kRootSubLists lists
+// of root_sublist_capacity(max) 24-byte records: 4096 + 32 * (32768 + 4096) * 24 = 28 315 648 B
+#define SGX_NOALLOC_SCRATCH_BYTES_                                                             \
+  (32ull * 32ull * 4ull + 32ull * (SGX_NOALLOC_MAX_CELLS_ / 32ull + 4096ull) * 24ull)
+static __device__ __align__(256) unsigned char sgx_root_noalloc_scratch[SGX_NOALLOC_SCRATCH_BYTES_];
+
+namespace sgx {
+namespace {
+static_assert(sizeof(RootListEntry) == 24, "scratch size above assumes 24-byte records");
+// root_sublist_capacity(max) = max / kRootSubLists + 4096, written out (it is not constexpr)
+static_assert(SGX_NOALLOC_SCRATCH_BYTES_ ==
+                  (size_t)kRootSubLists * kRootCounterStride * sizeof(unsigned int) +
+                      (size_t)kRootSubLists *
+                          (size_t)(SGX_NOALLOC_MAX_CELLS_ / kRootSubLists + 4096) *
+                          sizeof(RootListEntry),
+              "scratch array must hold the counters and every sub-list of a maximum-size call");
+
+constexpr int kNoAllocMaxDevices = 64;
+std::mutex g_noalloc_mutex;
+unsigned int *g_noalloc_ptr[kNoAllocMaxDevices] = {};
+
+// Once per device, that device current: the array's device address and the shared-memory opt-in
+// of the direct kernel (function attributes are per device).  No allocation.
+int noalloc_setup(const int device, const size_t smem, unsigned int **out) {
+  if (device < 0 || device >= kNoAllocMaxDevices)
+    return fail(SGX_ERR_UNSUPPORTED, "no-alloc T(rho,sie): device %d (this build tracks %d)",
+                device, kNoAllocMaxDevices);
+  std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+  if (!g_noalloc_ptr[device]) {
+    void *p = nullptr;
+    const cudaError_t err = cudaGetSymbolAddress(&p, sgx_root_noalloc_scratch);
+    if (err != cudaSuccess || !p)
+      return fail(SGX_ERR_CUDA, "cudaGetSymbolAddress(sgx_root_noalloc_scratch): %s",
+                  cudaGetErrorString(err));
+    if (cudaFuncSetAttribute(rhot_T_direct_kernel<true>,
+                             cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             96 * 1024) != cudaSuccess)
+      return fail(SGX_ERR_CUDA, "cannot reserve shared memory for the direct kernel");
+    g_noalloc_ptr[device] = static_cast<unsigned int *>(p);
+  }
+  if (smem > 96 * 1024) return fail(SGX_ERR_UNSUPPORTED, "table too large: %zu B of smem", smem);
+  *out = g_noalloc_ptr[device];
+  return SGX_OK;
+}
+} // namespace
+} // namespace sgx
+
+extern "C" int64_t sgx_noalloc_max_cells(void) { return SGX_NOALLOC_MAX_CELLS_; }
+
+extern "C" int sgx_TemperatureFromDensityInternalEnergy_noalloc(
+    sgx_eos_t e, const double *rho, const double *sie, double *T, int64_t n, double *lambda,
+    int lambda_stride, sgx_stream_t stream) {
+  using namespace sgx;
+  if (!e || e->kind != SGX_EOS_SPINER_RHOT)
+    return fail(SGX_ERR_INVALID, "no-alloc T(rho,sie) needs a SpinerEOSDependsRhoT handle");
+  if (n < 0) return fail(SGX_ERR_INVALID, "negative cell count");
+  if (n > SGX_NOALLOC_MAX_CELLS_)
+    return fail(SGX_ERR_INVALID,
+                "no-alloc T(rho,sie): %lld cells exceed the static scratch's maximum of %lld; "
+                "split the call or use sgx_TemperatureFromDensityInternalEnergy",
+                (long long)n, (long long)SGX_NOALLOC_MAX_CELLS_);
+  if (n == 0) return SGX_OK;
+  if (!rho || !sie || !T) return fail(SGX_ERR_INVALID, "null array");
+  if (lambda && lambda_stride < 2)
+    return fail(SGX_ERR_INVALID, "lambda_stride %d < nlambda 2", lambda_stride);
+  DeviceGuard guard;
+  SGX_CUDA_OK(cudaSetDevice(e->device));
+  const SpinerRhoT &eos = e->rhot;
+  const size_t smem = (size_t)eos.numRho * (sizeof(RootRowMeta) + 2 * sizeof(double));
+  unsigned int *scratch = nullptr;
+  const int rc = noalloc_setup(e->device, smem, &scratch);
+  if (rc != SGX_OK) return rc;
+  const RootRowMeta *meta = reinterpret_cast<const RootRowMeta *>(e->tables.d("sie#rootmeta"));
+  const unsigned int *hint = reinterpret_cast<const unsigned int *>(e->tables.d("sie#hint"));
+  constexpr size_t kCounters = (size_t)kRootSubLists * kRootCounterStride;
+  RootListEntry *lists = reinterpret_cast<RootListEntry *>(scratch + kCounters);
+  cudaStream_t s = (cudaStream_t)stream;
+  // the array keeps the last call's contents: the counters must start at zero; the lists need
+  // no clearing (only entries below the new counts are read)
+  SGX_CUDA_OK(cudaMemsetAsync(scratch, 0, kCounters * sizeof(unsigned int), s));
+  const bool vec_lambda = lambda && (lambda_stride % 2) == 0 && (((uintptr_t)lambda) & 15) == 0;
+  const LaunchCfg c = stream_cfg(n, 256, 4 * 2);
+  rhot_T_direct_kernel<true><<<c.blocks, c.threads, smem, s>>>(
+      eos, meta, hint, rho, sie, T, n, lambda, lambda_stride, vec_lambda, lists, scratch);
+  const LaunchCfg c2 = stream_cfg(root_sublist_capacity(n) / 4, 256, 1);
+  rhot_T_list_kernel<<<dim3(c2.blocks, kRootSubLists), c2.threads, 0, s>>>(
+      eos, T, lambda, lambda_stride, lists, scratch,
+      reinterpret_cast<unsigned long long *>(e->root_stats), (unsigned long long)n);
+  count_launch(2);
+  SGX_CUDA_OK(cudaGetLastError());
+  return SGX_OK;
+}
