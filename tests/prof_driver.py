@@ -9,6 +9,13 @@ what = sys.argv[1] if len(sys.argv) > 1 else "all"
 lg = int(sys.argv[2]) if len(sys.argv) > 2 else 24
 n = 1 << lg
 dev = torch.device("cuda", 0)
+if os.environ.get("PROF_INIT_NCCL") == "1":  # study: does a live NCCL communicator change kernel timings?
+    import torch.distributed as dist
+    torch.cuda.set_device(0)
+    dist.init_process_group("nccl", init_method="tcp://127.0.0.1:29531", rank=0, world_size=1,
+                            device_id=dev)
+    t_ = torch.ones(1, device=dev); dist.all_reduce(t_); torch.cuda.synchronize()
+    print("NCCL communicator up", flush=True)
 raw = pkg.tablegen.vinet_sp5_tables()
 rt = pkg.SpinerEOSDependsRhoT(raw)
 rho, T = W.spiner_inputs(n, 0, xp=torch, device=dev)
