@@ -108,17 +108,36 @@ __global__ void __launch_bounds__(256, 4)
   const unsigned sub_cap = (unsigned)root_sublist_capacity(n);
   unsigned int *const my_count = count + sub * kRootCounterStride;
   RootListEntry *const my_list = list + (size_t)sub * sub_cap;
+  // Software pipeline: the next trip's (rho, sie) leave for HBM before this trip's chain of
+  // dependent gathers (hint -> table cell -> next probe) starts; ncu had 66 % of the stall
+  // cycles of this kernel on L1TEX scoreboards with < 1 eligible warp per scheduler.
+  int64_t base = (int64_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31u);
+  double rho_next = 0.0, sie_next = 0.0;
+  if (base + lane < n) {
+    asm volatile("ld.global.nc.L1::no_allocate.f64 %0, [%1];"
+                 : "=d"(rho_next)
+                 : "l"(rho_in + base + lane));
+    asm volatile("ld.global.nc.L1::no_allocate.f64 %0, [%1];"
+                 : "=d"(sie_next)
+                 : "l"(sie_in + base + lane));
+  }
   // warp-uniform trip count: every lane stays in the loop so the votes below are full-warp
-  for (int64_t base = (int64_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31u); base < n;
-       base += nthr) {
+  for (; base < n; base += nthr) {
     const int64_t i = base + lane;
     const bool valid = i < n;
     bool fallback = false, search = false, found = false;
-    double rho = 0.0, sie = 0.0, lRho = 0.0, lT = 0.0, w0 = 0.0, w1 = 0.0;
+    double rho = rho_next, sie = sie_next;
+    double lRho = 0.0, lT = 0.0, w0 = 0.0, w1 = 0.0;
     int ix2 = 0, lo = 1, hi = 0;
+    if (i + nthr < n) {
+      asm volatile("ld.global.nc.L1::no_allocate.f64 %0, [%1];"
+                   : "=d"(rho_next)
+                   : "l"(rho_in + i + nthr));
+      asm volatile("ld.global.nc.L1::no_allocate.f64 %0, [%1];"
+                   : "=d"(sie_next)
+                   : "l"(sie_in + i + nthr));
+    }
     if (valid) {
-      asm volatile("ld.global.nc.L1::no_allocate.f64 %0, [%1];" : "=d"(rho) : "l"(rho_in + i));
-      asm volatile("ld.global.nc.L1::no_allocate.f64 %0, [%1];" : "=d"(sie) : "l"(sie_in + i));
       lRho = eos.lRho_(rho);
       const AxisPos pr(eos.gRho, lRho);
       // getLocDependsRhoSie_ (eos_spiner_rho_temp.hpp:1377-1392): same two 1-D interpolations,
