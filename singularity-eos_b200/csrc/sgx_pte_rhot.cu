@@ -2,6 +2,7 @@
 // Default: the lane-refill state-machine kernel of sgx_pte_sm.cuh.  The straight
 // one-thread-walks-one-cell transcription (pte_kernel in sgx_pte_kernel.cuh) is kept for the
 // benchmark mixture as the comparison variant (SGX_PTE_KERNEL=percell).
+#include <atomic>
 #include <cstdlib>
 #include <cstring>
 
@@ -105,6 +106,28 @@ static int launch_warp(const EosSet &set, const MixParamsDev &prm, double *rho, 
   return SGX_OK;
 }
 
+// The state-machine kernels keep a spill frame and call the out-of-line libm cores, so their
+// local memory is laid out by the DEVICE stack-size limit.  At CUDA's default of 1024 bytes per
+// thread the layout costs 4-13 % (3-material benchmark mixture 112.6 -> 119.5 M solves/s at
+// 2048; profiles/r2ab_pte_stack_limit.txt) -- which is why the same kernel ran faster in any
+// process that had created a multi-rank NCCL communicator: NCCL raises the limit to 1872 for
+// its own kernels.  Once per device, if the limit is below 2048 it is raised to 2048 (never
+// lowered; about 0.3 GB more local-memory backing on a B200).  SGX_STACK_LIMIT=<bytes> picks
+// another value, SGX_STACK_LIMIT=0 leaves the device alone.
+static void raise_stack_limit_once() {
+  static std::atomic<unsigned long long> done{0};
+  int device = 0;
+  if (cudaGetDevice(&device) != cudaSuccess || device < 0 || device >= 64) return;
+  const unsigned long long bit = 1ull << device;
+  if (done.fetch_or(bit) & bit) return;
+  size_t want = 2048;
+  if (const char *v = getenv("SGX_STACK_LIMIT")) want = (size_t)strtoull(v, nullptr, 10);
+  if (want == 0) return;
+  size_t now = 0;
+  if (cudaDeviceGetLimit(&now, cudaLimitStackSize) != cudaSuccess || now >= want) return;
+  if (cudaDeviceSetLimit(cudaLimitStackSize, want) != cudaSuccess) cudaGetLastError();
+}
+
 int launch_pte_rhot(const EosSet &set, bool bench_mix, const MixParamsDev &prm, double *rho,
                     double *vfrac, double *sie, double *temp, double *press,
                     const double *sie_tot, const double *vfrac_tot, const double *Tguess,
@@ -113,6 +136,7 @@ int launch_pte_rhot(const EosSet &set, bool bench_mix, const MixParamsDev &prm, 
 #define SGX_PTE_ARGS                                                                     \
   set, prm, rho, vfrac, sie, temp, press, sie_tot, vfrac_tot, Tguess, status, residual,   \
       stats, ncell, s
+  raise_stack_limit_once();
   if (bench_mix) {
     if (percell_variant()) return launch_pte_percell<3, Mix3GrDrDp, SGX_PTE_RHOT>(SGX_PTE_ARGS);
     if (warp_variant() && !stats)

@@ -13,9 +13,24 @@ rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE"
 local = int(os.environ.get("LOCAL_RANK", "0"))
 torch.cuda.set_device(local); dev = torch.device("cuda", local)
 dist = None
-if world > 1:
+late = os.environ.get("ALLOC_BEFORE_INIT") == "1"  # state arrays first, communicator afterwards
+if world > 1 and not late:
     import torch.distributed as dist
     dist.init_process_group("nccl", device_id=dev)
+    t_ = torch.ones(1, device=dev); dist.all_reduce(t_); torch.cuda.synchronize()
+if os.environ.get("ENABLE_PEER") == "1":  # what a 2-rank NCCL communicator does to the context
+    import ctypes
+    rt = ctypes.CDLL("libcudart.so.12")
+    torch.zeros(1, device=dev)
+    peer = 1 - local
+    rc = rt.cudaDeviceEnablePeerAccess(ctypes.c_int(peer), ctypes.c_uint(0))
+    print(f"cudaDeviceEnablePeerAccess({peer}) -> {rc}", flush=True)
+if os.environ.get("STACK_LIMIT"):  # cudaLimitStackSize = 0
+    import ctypes
+    rt = ctypes.CDLL("libcudart.so.12")
+    torch.zeros(1, device=dev)
+    rc = rt.cudaDeviceSetLimit(ctypes.c_int(0), ctypes.c_size_t(int(os.environ["STACK_LIMIT"])))
+    print(f"cudaDeviceSetLimit(stack, {os.environ['STACK_LIMIT']}) -> {rc}", flush=True)
 pkg = g.load_package(); L = pkg._lib; W = pkg.workloads
 npte = 1 << int(os.environ.get("LOG2_CELLS", "27"))
 g3 = pkg.closure.set_eos_3mat_analytic()
@@ -31,6 +46,17 @@ state0 = W.pte_state_torch(npte, sie0, dev, start=srank * npte)
 state = [a.clone() for a in state0]
 status = torch.zeros(npte, dtype=torch.int64, device=dev)
 prm = pkg.closure.test_pte_params()
+if world > 1 and late:
+    import torch.distributed as dist
+    dist.init_process_group("nccl", device_id=dev)
+    t_ = torch.ones(1, device=dev); dist.all_reduce(t_); torch.cuda.synchronize()
+if True:
+    import ctypes
+    rt_ = ctypes.CDLL("libcudart.so.12"); v_ = ctypes.c_size_t(0)
+    rt_.cudaDeviceGetLimit(ctypes.byref(v_), ctypes.c_int(0))
+    print(f"rank {rank} cudaLimitStackSize now {v_.value}", flush=True)
+print(f"rank {rank} state ptrs mod 2MiB:", [a.data_ptr() % (1 << 21) for a in state], "first ptr", hex(state[0].data_ptr()),
+      "reserved MiB", torch.cuda.memory_reserved() >> 20, flush=True)
 
 
 def pte():
