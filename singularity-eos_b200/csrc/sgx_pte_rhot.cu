@@ -142,6 +142,17 @@ int launch_pte_rhot(const EosSet &set, bool bench_mix, const MixParamsDev &prm, 
     if (warp_variant() && !stats)
       return launch_warp<3, Mix3GrDrDp>(set, prm, rho, vfrac, sie, temp, press, sie_tot, vfrac_tot,
                                         Tguess, status, residual, ncell, s);
+    // SGX_PTE_SM_SHAPE: block shape study of the state machine: threads per
+    // block x resident blocks per SM -> register budget.  Default 512 x 1 (128 registers).
+    static const int shape = [] {
+      const char *v = getenv("SGX_PTE_SM_SHAPE");
+      return v ? atoi(v) : 0;
+    }();
+    if (shape == 384) return launch_sm<3, Mix3GrDrDp, 384, 1>(SGX_PTE_ARGS); // 168 registers
+    if (shape == 256) return launch_sm<3, Mix3GrDrDp, 256, 1>(SGX_PTE_ARGS); // 255 registers
+    if (shape == 2562) return launch_sm<3, Mix3GrDrDp, 256, 2>(SGX_PTE_ARGS); // 2 blocks, 128
+    if (shape == 640) return launch_sm<3, Mix3GrDrDp, 640, 1>(SGX_PTE_ARGS); // 96 registers
+    if (shape == 768) return launch_sm<3, Mix3GrDrDp, 768, 1>(SGX_PTE_ARGS); // 80 registers
     return launch_sm<3, Mix3GrDrDp>(SGX_PTE_ARGS);
   }
   switch (set.nmat) {
