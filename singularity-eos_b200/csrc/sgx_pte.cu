@@ -119,8 +119,8 @@ int sgx_pte_solve_cached(int solver, const sgx_eos_t *eos, int nmat, int64_t nce
   if (solver != SGX_PTE_RHOT && solver != SGX_PTE_PT && solver != SGX_PTE_FIXED_T &&
       solver != SGX_PTE_RHOU && solver != SGX_PTE_FIXED_P)
     return fail(SGX_ERR_INVALID, "unknown PTE solver %d", solver);
-  if (solver == SGX_PTE_RHOU && (nmat < 2 || nmat > 3))
-    return fail(SGX_ERR_UNSUPPORTED, "PTESolverRhoU: nmat=%d, this build instantiates 2..3",
+  if (solver == SGX_PTE_RHOU && (nmat < 2 || nmat > 4))
+    return fail(SGX_ERR_UNSUPPORTED, "PTESolverRhoU: nmat=%d, this build instantiates 2..4",
                 nmat);
   if (solver == SGX_PTE_FIXED_T && !Tguess)
     return fail(SGX_ERR_INVALID, "PTESolverFixedT needs the temperature array (Tguess)");

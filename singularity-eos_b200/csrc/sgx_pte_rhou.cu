@@ -16,8 +16,10 @@ int launch_pte_rhou(const EosSet &set, bool bench_mix, const MixParamsDev &prm, 
   switch (set.nmat) {
   case 2:
     return launch_pte_percell<2, DynEos, SGX_PTE_RHOU>(SGX_PTE_ARGS);
-  default:
+  case 3:
     return launch_pte_percell<3, DynEos, SGX_PTE_RHOU>(SGX_PTE_ARGS);
+  default: // 4 materials: the 8 x 8 system through the same static-index pivoted Householder
+    return launch_pte_percell<4, DynEos, SGX_PTE_RHOU>(SGX_PTE_ARGS);
   }
 #undef SGX_PTE_ARGS
 }
