@@ -283,7 +283,12 @@ def run_ours(args):
         lam1 = torch.full((n, 1), float("nan"), dtype=torch.float64, device=dev)
         lookup("spiner_rhosie_T_rhoe", lambda: eos_rs.TemperatureFromDensityInternalEnergy(
             rho, sie, out, n, lam1), 32)
-        del lam1, lam_warm
+        # a modified handle, ScaledEOS(ShiftedEOS(SpinerEOSDependsRhoT)), through
+        # the run-time-dispatched modifier kernel (csrc/sgx_modifiers.cu)
+        eos_mod = pkg.ScaledEOS(pkg.ShiftedEOS(eos_rt, 2.0e8), 1.05)
+        lookup("modified_scaled_shifted_spiner_rhot_P_rhoT_lambda",
+               lambda: eos_mod.PressureFromDensityTemperature(rho, T, out, n, lam), 40, steps=5)
+        del lam1, lam_warm, eos_mod
         # config 1: IdealGas at 2^20 (launch-latency bound; CUDA graph of 100 pairs) and 2^26
         ideal = pkg.IdealGas(0.4, 7.16e6)
         r1, t1 = W.ideal_inputs(N_IDEAL, rank * N_IDEAL, xp=torch, device=dev)

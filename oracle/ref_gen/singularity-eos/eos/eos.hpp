@@ -20,9 +20,23 @@
 #include <singularity-eos/eos/eos_spiner.hpp>
 #include <singularity-eos/eos/eos_vinet.hpp>
 
+#include <singularity-eos/eos/modifiers/ramps_eos.hpp>
+#include <singularity-eos/eos/modifiers/scaled_eos.hpp>
+#include <singularity-eos/eos/modifiers/shifted_eos.hpp>
+
 namespace singularity {
+// The seven modifier combinations of the default variant (eos/eos_type_lists.hpp:69-94) around
+// three of the models (an analytic one that prefers pressure, one that prefers energy, and the
+// tabulated one with a lambda cache); more bases only lengthen the oracle build.
+#define SGX_ORACLE_MODS(T)                                                              \
+  ShiftedEOS<T>, ScaledEOS<T>, ScaledEOS<ShiftedEOS<T>>, BilinearRampEOS<T>,              \
+      BilinearRampEOS<ShiftedEOS<T>>, BilinearRampEOS<ScaledEOS<T>>,                      \
+      BilinearRampEOS<ScaledEOS<ShiftedEOS<T>>>
 using EOS = Variant<IdealGas, Gruneisen, DavisReactants, DavisProducts, Vinet,
-                    SpinerEOSDependsRhoT, SpinerEOSDependsRhoSie, Helmholtz>;
+                    SpinerEOSDependsRhoT, SpinerEOSDependsRhoSie, Helmholtz,
+                    SGX_ORACLE_MODS(IdealGas), SGX_ORACLE_MODS(Gruneisen),
+                    SGX_ORACLE_MODS(SpinerEOSDependsRhoT)>;
+#undef SGX_ORACLE_MODS
 } // namespace singularity
 
 #endif

@@ -210,6 +210,25 @@ void *ref_eos_davis_products(double a, double b, double k, double n, double vc, 
                              double Cv) {
   return new EOS(DavisProducts(a, b, k, n, vc, pc, Cv));
 }
+// Modifier layers through the reference's own Variant::Modify (eos_variant.hpp:213-223): a NEW
+// handle holding Mod<T>(copy of T, args).  which: 0 ShiftedEOS(shift = p[0]), 1 ScaledEOS(scale
+// = p[0]), 2 BilinearRampEOS(r0, a, b, c = p[0..3]).  Null when the modified type is not in the
+// oracle's variant.  Tabulated models are shallow copies: free the modified handle with
+// ref_eos_free_shallow and keep the base alive.
+void *ref_eos_modify(void *h, int which, const double *p) {
+  EOS *e = static_cast<EOS *>(h);
+  void *out = nullptr;
+  guarded([&]() {
+    if (which == 0 && e->ModifiedInVariant<ShiftedEOS>())
+      out = new EOS(e->Modify<ShiftedEOS>(p[0]));
+    else if (which == 1 && e->ModifiedInVariant<ScaledEOS>())
+      out = new EOS(e->Modify<ScaledEOS>(p[0]));
+    else if (which == 2 && e->ModifiedInVariant<BilinearRampEOS>())
+      out = new EOS(e->Modify<BilinearRampEOS>(p[0], p[1], p[2], p[3]));
+  });
+  return out;
+}
+void ref_eos_free_shallow(void *h) { delete static_cast<EOS *>(h); }
 void *ref_eos_vinet(double rho0, double T0, double B0, double BP0, double A0, double Cv0,
                     double E0, double S0, const double *d2to40) {
   return new EOS(Vinet(rho0, T0, B0, BP0, A0, Cv0, E0, S0, d2to40));

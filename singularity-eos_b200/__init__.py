@@ -6,5 +6,5 @@ through `__graft_entry__.load_package()` or as `singularity_eos_b200` after that
 """
 from . import _lib, closure, dist, eos, rng, tablegen, workloads  # noqa: F401
 from ._lib import SgxError, SgxLibraryMissing, thermalqs  # noqa: F401
-from .eos import (DavisProducts, DavisReactants, Gruneisen, Helmholtz, IdealGas,  # noqa: F401
+from .eos import (BilinearRampEOS, ScaledEOS, ShiftedEOS, DavisProducts, DavisReactants, Gruneisen, Helmholtz, IdealGas,  # noqa: F401
                   SpinerEOSDependsRhoSie, SpinerEOSDependsRhoT)

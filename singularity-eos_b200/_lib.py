@@ -116,6 +116,9 @@ PROTOTYPES = {
     "sgx_set_device": (C.c_int, [C.c_int]),
     "sgx_launch_count": (C.c_uint64, []),
     "sgx_eos_create_ideal": (C.c_int, [_D, _D, C.POINTER(_VP)]),
+    "sgx_eos_modify_shifted": (C.c_int, [_VP, _D, C.POINTER(_VP)]),
+    "sgx_eos_modify_scaled": (C.c_int, [_VP, _D, C.POINTER(_VP)]),
+    "sgx_eos_modify_bilinear_ramp": (C.c_int, [_VP, _D, _D, _D, _D, C.POINTER(_VP)]),
     "sgx_eos_create_gruneisen": (C.c_int, [_D] * 11 + [C.POINTER(_VP)]),
     "sgx_eos_create_davis_reactants": (C.c_int, [_D] * 11 + [C.POINTER(_VP)]),
     "sgx_eos_create_davis_products": (C.c_int, [_D] * 7 + [C.POINTER(_VP)]),

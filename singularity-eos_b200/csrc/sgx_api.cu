@@ -567,6 +567,7 @@ int launch_pe(const EOS &eos, const double *rho, const double *T, double *P, dou
 // Lambda slots a row must hold: nlambda(), except a Helmholtz built for type-indexed
 // {Abar, Zbar} lambdas (no LogTemperature slot), which uses 2 of the 3.
 static int lambda_need(const sgx_eos_s *e) {
+  if (e->kind == SGX_EOS_MODIFIED) e = e->base;
   switch (e->kind) {
   case SGX_EOS_SPINER_RHOT:
     return 2;
@@ -877,6 +878,62 @@ int sgx_eos_create_helmholtz(const char *table_path, const sgx_helm_options *opt
   return SGX_OK;
 }
 
+// Modifier layers (include/sgx_b200.h).  The new handle refers to the UNMODIFIED model; the
+// layers accumulate in ModParams in the reference's nesting order.
+static int new_modified(sgx_eos_t base, int layer, sgx_eos_s **out) {
+  if (!out) return fail(SGX_ERR_INVALID, "null output handle pointer");
+  *out = nullptr;
+  if (!base) return fail(SGX_ERR_INVALID, "null EOS handle");
+  const sgx_eos_s *root = base->kind == SGX_EOS_MODIFIED ? base->base : base;
+  if (root->kind < 0 || root->kind > SGX_EOS_SPINER_RHOSIE)
+    return fail(SGX_ERR_UNSUPPORTED, "modifiers are built for IdealGas, Gruneisen, Davis and "
+                "Spiner models (EOS kind %d given)", root->kind);
+  const int have = base->kind == SGX_EOS_MODIFIED ? base->mod.flags : 0;
+  if (have >= layer) // flags are ordered: shift 1 < scale 2 < ramp 4
+    return fail(SGX_ERR_UNSUPPORTED, "modifier order: the reference's default variant nests "
+                "BilinearRamp(Scaled(Shifted(T))), one layer of each at most "
+                "(eos/eos_type_lists.hpp:69-94)");
+  DeviceGuard guard;
+  SGX_CUDA_OK(cudaSetDevice(base->device));
+  sgx_eos_s *e = nullptr;
+  const int rc = new_handle(SGX_EOS_MODIFIED, &e);
+  if (rc) return rc;
+  e->base = const_cast<sgx_eos_s *>(root);
+  e->base->refs.fetch_add(1, std::memory_order_relaxed);
+  if (base->kind == SGX_EOS_MODIFIED) e->mod = base->mod;
+  e->mod.flags |= layer;
+  *out = e;
+  return SGX_OK;
+}
+int sgx_eos_modify_shifted(sgx_eos_t base, double shift, sgx_eos_t *out) {
+  const int rc = new_modified(base, kModShift, out);
+  if (rc) return rc;
+  (*out)->mod.shift = shift;
+  return SGX_OK;
+}
+int sgx_eos_modify_scaled(sgx_eos_t base, double scale, sgx_eos_t *out) {
+  if (!(scale != 0.0)) return fail(SGX_ERR_INVALID, "ScaledEOS: scale must be non-zero");
+  const int rc = new_modified(base, kModScale, out);
+  if (rc) return rc;
+  (*out)->mod.scale = scale;
+  (*out)->mod.inv_scale = 1. / scale; // scaled_eos.hpp:45
+  return SGX_OK;
+}
+int sgx_eos_modify_bilinear_ramp(sgx_eos_t base, double r0, double a, double b, double c,
+                                 sgx_eos_t *out) {
+  // BilinearRampEOS::CheckParams (ramps_eos.hpp:84-92)
+  if (!(r0 > 0.0) || !(a > 0.0) || !(b >= 0.0) || a == b)
+    return fail(SGX_ERR_INVALID, "BilinearRampEOS: needs r0 > 0, a > 0, b >= 0, a != b");
+  const double rmid = r0 * (a - b * c) / (a - b), Pmid = a * (rmid / r0 - 1.0); // :80-81
+  if (rmid != rmid || Pmid != Pmid)
+    return fail(SGX_ERR_INVALID, "BilinearRampEOS: mid density / pressure not defined");
+  const int rc = new_modified(base, kModRamp, out);
+  if (rc) return rc;
+  ModParams &q = (*out)->mod;
+  q.r0 = r0, q.a = a, q.b = b, q.c = c, q.rmid = rmid, q.Pmid = Pmid;
+  return SGX_OK;
+}
+
 int sgx_eos_retain(sgx_eos_t e) {
   if (!e) return fail(SGX_ERR_INVALID, "null EOS handle");
   e->refs.fetch_add(1, std::memory_order_relaxed);
@@ -886,6 +943,7 @@ int sgx_eos_retain(sgx_eos_t e) {
 int sgx_eos_destroy(sgx_eos_t e) {
   if (!e) return SGX_OK;
   if (e->refs.fetch_sub(1, std::memory_order_acq_rel) > 1) return SGX_OK; // still shared
+  if (e->base) sgx_eos_destroy(e->base); // a modified handle kept its base alive
   DeviceGuard guard;
   cudaSetDevice(e->device);
   if (e->tables.dev) cudaFree(e->tables.dev);
@@ -903,6 +961,7 @@ int sgx_eos_destroy(sgx_eos_t e) {
 int sgx_eos_type(sgx_eos_t e) { return e ? e->kind : SGX_ERR_INVALID; }
 int sgx_eos_nlambda(sgx_eos_t e) {
   if (!e) return SGX_ERR_INVALID;
+  if (e->kind == SGX_EOS_MODIFIED) e = e->base; // shifted_eos.hpp:366, scaled_eos.hpp:224
   switch (e->kind) {
   case SGX_EOS_SPINER_RHOT:
     return 2;
@@ -916,6 +975,7 @@ int sgx_eos_nlambda(sgx_eos_t e) {
 }
 unsigned long sgx_eos_preferred_input(sgx_eos_t e) {
   if (!e) return 0;
+  if (e->kind == SGX_EOS_MODIFIED) e = e->base; // shifted_eos.hpp:372
   switch (e->kind) {
   case SGX_EOS_IDEAL:
     return IdealGas::preferred_input;
@@ -930,6 +990,10 @@ unsigned long sgx_eos_preferred_input(sgx_eos_t e) {
 uint64_t sgx_eos_scratch_bytes(sgx_eos_t, int, int64_t) { return 0; }
 double sgx_eos_maximum_density(sgx_eos_t e) {
   if (!e) return 0;
+  if (e->kind == SGX_EOS_MODIFIED) { // scaled_eos.hpp:259-261; the other layers forward
+    const double m = sgx_eos_maximum_density(e->base);
+    return (e->mod.flags & kModScale) ? e->mod.inv_scale * m : m;
+  }
   if (e->kind == SGX_EOS_GRUNEISEN) return e->analytic.gr.rho_max;
   if (e->kind == SGX_EOS_HELMHOLTZ) return 1e15;
   return 1e100;
@@ -990,6 +1054,8 @@ int sgx_eos_eval(sgx_eos_t e, int method, const double *in1, const double *in2, 
     return launch_eval(e->rhosie, method, in1, in2, out, n, lambda, lambda_stride, s, 8);
   case SGX_EOS_HELMHOLTZ:
     return launch_helm_eval(e, method, in1, in2, out, n, lambda, lambda_stride, s);
+  case SGX_EOS_MODIFIED:
+    return launch_mod_eval(e, method, in1, in2, out, n, lambda, lambda_stride, s);
   default:
     return fail(SGX_ERR_INVALID, "bad EOS kind %d", e->kind);
   }

@@ -332,21 +332,13 @@ int sgx_get_sg_eos_device(int nmat, int ncell, int cell_dim, int input_int,
     if (!eos[k]) { // an index no material refers to
       set.e[k].kind = SGX_EOS_IDEAL;
       set.e[k].ideal = IdealGas{1.0, 1.0};
+      set.mod[k] = ModParams();
       continue;
     }
     if (device < 0) device = eos[k]->device;
     if (eos[k]->device != device) return fail(SGX_ERR_INVALID, "EOS %d lives on another device", k);
-    if (eos[k]->kind == SGX_EOS_SPINER_RHOT) {
-      set.e[k].kind = eos[k]->kind;
-      set.e[k].rhot = static_cast<const SpinerRhoT *>(eos[k]->dev_struct);
-    } else if (eos[k]->kind == SGX_EOS_SPINER_RHOSIE) {
-      set.e[k].kind = eos[k]->kind;
-      set.e[k].rhosie = static_cast<const SpinerRhoSie *>(eos[k]->dev_struct);
-    } else if (eos[k]->kind <= SGX_EOS_DAVIS_PRODUCTS) {
-      set.e[k] = eos[k]->analytic;
-    } else {
+    if (!set_material(eos[k], set, k))
       return fail(SGX_ERR_UNSUPPORTED, "get_sg_eos: EOS %d is kind %d", k, eos[k]->kind);
-    }
   }
   SGX_CUDA_OK(cudaSetDevice(device));
   sgx_mix_params dflt;

@@ -163,9 +163,37 @@ struct sgx_eos_s {
   // Everything the handle was created from (parameters / raw tables / options), as the byte
   // stream sgx_eos_serialize hands out and sgx_eos_deserialize rebuilds a handle from.
   std::vector<char> recipe;
+  // kind SGX_EOS_MODIFIED: the unmodified model (retained) and the layers around it
+  sgx_eos_s *base = nullptr;
+  sgx::ModParams mod;
 };
 
 namespace sgx {
+// One material of a mixed-cell EosSet from a handle (modified handles: base model + layers).
+// Returns false for models that cannot sit in a mixed cell (Helmholtz).
+inline bool set_material(const sgx_eos_s *h, EosSet &set, const int k) {
+  const sgx_eos_s *b = h->kind == SGX_EOS_MODIFIED ? h->base : h;
+  set.mod[k] = h->kind == SGX_EOS_MODIFIED ? h->mod : ModParams();
+  if (b->kind == SGX_EOS_SPINER_RHOT) {
+    set.e[k].kind = b->kind;
+    set.e[k].rhot = static_cast<const SpinerRhoT *>(b->dev_struct);
+  } else if (b->kind == SGX_EOS_SPINER_RHOSIE) {
+    set.e[k].kind = b->kind;
+    set.e[k].rhosie = static_cast<const SpinerRhoSie *>(b->dev_struct);
+  } else if (b->kind >= 0 && b->kind <= SGX_EOS_DAVIS_PRODUCTS) {
+    set.e[k] = b->analytic;
+  } else {
+    return false;
+  }
+  return true;
+}
+// the run-time accessor (TabEos kernels) is needed for tabulated and for modified materials
+inline bool needs_tab_accessor(const sgx_eos_s *h) {
+  return h->kind == SGX_EOS_MODIFIED || h->kind == SGX_EOS_SPINER_RHOT ||
+         h->kind == SGX_EOS_SPINER_RHOSIE;
+}
+int launch_mod_eval(sgx_eos_s *e, int method, const double *in1, const double *in2, double *out,
+                    int64_t n, double *lambda, int lambda_stride, cudaStream_t s);
 int upload_tables(sgx_eos_s *e);   // cudaMalloc + H2D of e->tables.host
 int ensure_staging(sgx_eos_s *e, size_t pinned_bytes, size_t device_bytes);
 // Stream-ordered kernel scratch from the library's OWN memory pool (one per device, release

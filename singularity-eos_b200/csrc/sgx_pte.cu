@@ -144,24 +144,19 @@ int sgx_pte_solve_cached(int solver, const sgx_eos_t *eos, int nmat, int64_t nce
     if (!eos[m]) return fail(SGX_ERR_INVALID, "null EOS handle for material %d", m);
     if (eos[m]->device != eos[0]->device)
       return fail(SGX_ERR_INVALID, "material %d lives on another device", m);
-    if (eos[m]->kind == SGX_EOS_SPINER_RHOT || eos[m]->kind == SGX_EOS_SPINER_RHOSIE) {
-      tabulated = true;
-      set.e[m].kind = eos[m]->kind;
-      if (eos[m]->kind == SGX_EOS_SPINER_RHOT)
-        set.e[m].rhot = static_cast<const SpinerRhoT *>(eos[m]->dev_struct);
-      else
-        set.e[m].rhosie = static_cast<const SpinerRhoSie *>(eos[m]->dev_struct);
-    } else if (eos[m]->kind > SGX_EOS_DAVIS_PRODUCTS) {
+    if (needs_tab_accessor(eos[m])) tabulated = true;
+    if (!set_material(eos[m], set, m))
       return fail(SGX_ERR_UNSUPPORTED, "PTE: material %d is EOS kind %d (Helmholtz mixtures are "
                   "not built)", m, eos[m]->kind);
-    } else {
-      set.e[m] = eos[m]->analytic;
-    }
   }
   if (tabulated && (solver == SGX_PTE_RHOU || solver == SGX_PTE_FIXED_P))
     return fail(SGX_ERR_UNSUPPORTED,
-                "PTESolverRhoU / PTESolverFixedP with tabulated materials are not built");
+                "PTESolverRhoU / PTESolverFixedP with tabulated or modified materials are not built");
   if (lambda && !tabulated) lambda = nullptr; // the analytic models take no lambda
+  bool any_lambda_user = false;
+  for (int m = 0; m < nmat; ++m)
+    any_lambda_user = any_lambda_user || set.e[m].kind >= SGX_EOS_SPINER_RHOT;
+  if (!any_lambda_user) lambda = nullptr; // modified analytic materials only
   cudaError_t err = cudaSetDevice(eos[0]->device);
   if (err != cudaSuccess)
     return fail(SGX_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(err));

@@ -69,9 +69,21 @@ struct AnyEos {
     const SpinerRhoSie *rhosie;
   };
 };
+// The modifiers the reference's default variant wraps around every model
+// (eos/eos_type_lists.hpp:69-94), always nested BilinearRamp(Scaled(Shifted(T))); each layer is
+// optional.  eos/modifiers/shifted_eos.hpp, scaled_eos.hpp, ramps_eos.hpp.  Applied by the
+// run-time accessor TabEos (sgx_pte_tab.cuh).
+enum { kModShift = 1, kModScale = 2, kModRamp = 4 };
+struct ModParams {
+  int flags = 0;
+  double shift = 0.0;                    // ShiftedEOS::shift_
+  double scale = 1.0, inv_scale = 1.0;   // ScaledEOS::scale_, inv_scale_ = 1 / scale_
+  double r0 = 0.0, a = 0.0, b = 0.0, c = 0.0, rmid = 0.0, Pmid = 0.0; // BilinearRampEOS
+};
 struct EosSet {
   int nmat;
   AnyEos e[kMaxMat];
+  ModParams mod[kMaxMat];
 };
 
 #ifdef __CUDACC__

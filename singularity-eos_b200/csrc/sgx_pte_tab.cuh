@@ -49,33 +49,128 @@ struct TabEos {
   default:                                                                                 \
     return mat(m).rhosie->TABCALL;                                                       \
   }
-  SGX_D double e_from_rho_T(int m, double rho, double T) const {
+  // ---- the unmodified model (the innermost T of BilinearRamp(Scaled(Shifted(T)))) ----
+  SGX_D double b_e_from_rho_T(int m, double rho, double T) const {
     SGX_TAB_DISPATCH(m, e_from_rho_T(rho, T), e_from_rho_T(rho, T, cache(m)))
   }
-  SGX_D double P_from_rho_e(int m, double rho, double e) const {
+  SGX_D double b_P_from_rho_e(int m, double rho, double e) const {
     SGX_TAB_DISPATCH(m, P_from_rho_e(rho, e), P_from_rho_e(rho, e, cache(m)))
   }
-  SGX_D double T_from_rho_e(int m, double rho, double e) const {
+  SGX_D double b_T_from_rho_e(int m, double rho, double e) const {
     SGX_TAB_DISPATCH(m, T_from_rho_e(rho, e), T_from_rho_e(rho, e, cache(m)))
   }
-  SGX_D double P_from_rho_T(int m, double rho, double T) const {
+  SGX_D double b_P_from_rho_T(int m, double rho, double T) const {
     SGX_TAB_DISPATCH(m, P_from_rho_T(rho, T), P_from_rho_T(rho, T, cache(m)))
   }
-  SGX_D double cv_from_rho_T(int m, double rho, double T) const {
+  SGX_D double b_cv_from_rho_T(int m, double rho, double T) const {
     SGX_TAB_DISPATCH(m, cv_from_rho_T(rho, T), cv_from_rho_T(rho, T, cache(m)))
   }
-  SGX_D double cv_from_rho_e(int m, double rho, double e) const {
+  SGX_D double b_cv_from_rho_e(int m, double rho, double e) const {
     SGX_TAB_DISPATCH(m, cv_from_rho_e(rho, e), cv_from_rho_e(rho, e, cache(m)))
   }
-  SGX_D double bmod_from_rho_T(int m, double rho, double T) const {
+  SGX_D double b_bmod_from_rho_T(int m, double rho, double T) const {
     SGX_TAB_DISPATCH(m, bmod_from_rho_T(rho, T), bmod_from_rho_T(rho, T, cache(m)))
   }
-  SGX_D double gamma_from_rho_T(int m, double rho, double T) const {
+  SGX_D double b_bmod_from_rho_e(int m, double rho, double e) const {
+    SGX_TAB_DISPATCH(m, bmod_from_rho_e(rho, e), bmod_from_rho_e(rho, e, cache(m)))
+  }
+  SGX_D double b_gamma_from_rho_T(int m, double rho, double T) const {
     SGX_TAB_DISPATCH(m, gamma_from_rho_T(rho, T), gamma_from_rho_T(rho, T, cache(m)))
   }
-  SGX_D double RhoPmin(int m, double T) const { SGX_TAB_DISPATCH(m, RhoPmin(T), RhoPmin(T)) }
-  SGX_D double MaximumDensity(int m) const {
+  SGX_D double b_gamma_from_rho_e(int m, double rho, double e) const {
+    SGX_TAB_DISPATCH(m, gamma_from_rho_e(rho, e), gamma_from_rho_e(rho, e, cache(m)))
+  }
+  // ---- modifier layers (sgx_pte.cuh ModParams) ----
+  SGX_D const ModParams &mod(const int m) const { return set.mod[idx ? idx[m] : m]; }
+  // density and energy as the unmodified model sees them: ScaledEOS hands scale * rho and
+  // inv_scale * sie down (scaled_eos.hpp:71-75), ShiftedEOS sie - shift (shifted_eos.hpp:69)
+  SGX_D double in_rho(const ModParams &q, const double rho) const {
+    return (q.flags & kModScale) ? q.scale * rho : rho;
+  }
+  SGX_D double in_sie(const ModParams &q, double sie) const {
+    if (q.flags & kModScale) sie = q.inv_scale * sie;
+    if (q.flags & kModShift) sie = sie - q.shift;
+    return sie;
+  }
+  // BilinearRampEOS::get_ramp_pressure / get_ramp_dpdrho (ramps_eos.hpp:104-124)
+  SGX_D double ramp_pressure(const ModParams &q, const double rho) const {
+    const double r_r0 = ratio(rho, q.r0);
+    return rho < q.r0 ? 0.0 : (rho < q.rmid ? q.a * (r_r0 - 1.0) : q.b * (r_r0 - q.c));
+  }
+  SGX_D double ramp_dpdrho(const ModParams &q, const double rho) const {
+    return rho < q.rmid ? ratio(q.a, q.r0) : ratio(q.b, q.r0);
+  }
+  SGX_D double e_from_rho_T(int m, double rho, double T) const {
+    const ModParams &q = mod(m);
+    // sic: ScaledEOS::InternalEnergyFromDensityTemperature passes rho on UNSCALED (:76-80)
+    double e = b_e_from_rho_T(m, rho, T);
+    if (q.flags & kModShift) e = e + q.shift;
+    if (q.flags & kModScale) e = q.scale * e;
+    return e;
+  }
+  SGX_D double P_from_rho_e(int m, double rho, double e) const {
+    const ModParams &q = mod(m);
+    const double p_eos = b_P_from_rho_e(m, in_rho(q, rho), in_sie(q, e));
+    if (!(q.flags & kModRamp)) return p_eos;
+    const double p_ramp = ramp_pressure(q, rho);
+    return p_eos < p_ramp ? p_ramp : p_eos;
+  }
+  SGX_D double T_from_rho_e(int m, double rho, double e) const {
+    const ModParams &q = mod(m);
+    return b_T_from_rho_e(m, in_rho(q, rho), in_sie(q, e));
+  }
+  SGX_D double P_from_rho_T(int m, double rho, double T) const {
+    const ModParams &q = mod(m);
+    const double p_eos = b_P_from_rho_T(m, in_rho(q, rho), T);
+    if (!(q.flags & kModRamp)) return p_eos;
+    const double p_ramp = ramp_pressure(q, rho);
+    return p_eos < p_ramp ? p_ramp : p_eos;
+  }
+  SGX_D double cv_from_rho_T(int m, double rho, double T) const {
+    return b_cv_from_rho_T(m, in_rho(mod(m), rho), T);
+  }
+  SGX_D double cv_from_rho_e(int m, double rho, double e) const {
+    const ModParams &q = mod(m);
+    return b_cv_from_rho_e(m, in_rho(q, rho), in_sie(q, e));
+  }
+  SGX_D double bmod_from_rho_T(int m, double rho, double T) const {
+    const ModParams &q = mod(m);
+    if (q.flags & kModRamp) { // ramps_eos.hpp:196-204
+      const double p_ramp = ramp_pressure(q, rho);
+      const double p_eos = b_P_from_rho_T(m, in_rho(q, rho), T);
+      if (p_eos < p_ramp) return rho * ramp_dpdrho(q, rho);
+    }
+    return b_bmod_from_rho_T(m, in_rho(q, rho), T);
+  }
+  SGX_D double bmod_from_rho_e(int m, double rho, double e) const {
+    const ModParams &q = mod(m);
+    if (q.flags & kModRamp) { // ramps_eos.hpp:160-168
+      const double p_ramp = ramp_pressure(q, rho);
+      const double p_eos = b_P_from_rho_e(m, in_rho(q, rho), in_sie(q, e));
+      if (p_eos < p_ramp) return rho * ramp_dpdrho(q, rho);
+    }
+    return b_bmod_from_rho_e(m, in_rho(q, rho), in_sie(q, e));
+  }
+  SGX_D double gamma_from_rho_T(int m, double rho, double T) const {
+    return b_gamma_from_rho_T(m, in_rho(mod(m), rho), T);
+  }
+  SGX_D double gamma_from_rho_e(int m, double rho, double e) const {
+    const ModParams &q = mod(m);
+    return b_gamma_from_rho_e(m, in_rho(q, rho), in_sie(q, e));
+  }
+  // bounds: ShiftedEOS and BilinearRampEOS forward, ScaledEOS scales the densities
+  // (scaled_eos.hpp:253-269)
+  SGX_D double b_RhoPmin(int m, double T) const { SGX_TAB_DISPATCH(m, RhoPmin(T), RhoPmin(T)) }
+  SGX_D double b_MaximumDensity(int m) const {
     SGX_TAB_DISPATCH(m, MaximumDensity(), MaximumDensity())
+  }
+  SGX_D double RhoPmin(int m, double T) const {
+    const ModParams &q = mod(m);
+    return (q.flags & kModScale) ? q.inv_scale * b_RhoPmin(m, T) : b_RhoPmin(m, T);
+  }
+  SGX_D double MaximumDensity(int m) const {
+    const ModParams &q = mod(m);
+    return (q.flags & kModScale) ? q.inv_scale * b_MaximumDensity(m) : b_MaximumDensity(m);
   }
   SGX_D double MinimumTemperature(int m) const {
     SGX_TAB_DISPATCH(m, MinimumTemperature(), MinimumTemperature())
@@ -86,8 +181,20 @@ struct TabEos {
   SGX_D double MaximumPressureAtTemperature(int m, double T) const {
     SGX_TAB_DISPATCH(m, MaximumPressureAtTemperature(T), MaximumPressureAtTemperature(T))
   }
+  // DensityEnergyFromPressureTemperature: shifted_eos.hpp:398-403, scaled_eos.hpp:245-251,
+  // ramps_eos.hpp:522-525 (forwards)
   __device__ inline void rho_e_from_P_T(int m, double P, double T, double &rho,
                                         double &sie) const {
+    const ModParams &q = mod(m);
+    b_rho_e_from_P_T(m, P, T, rho, sie);
+    if (q.flags & kModShift) sie = sie + q.shift;
+    if (q.flags & kModScale) {
+      rho = rho * q.inv_scale;
+      sie = sie * q.scale;
+    }
+  }
+  __device__ inline void b_rho_e_from_P_T(int m, double P, double T, double &rho,
+                                          double &sie) const {
     switch (mat(m).kind) {
     case 0:
       mat(m).ideal.rho_e_from_P_T(P, T, nullptr, rho, sie);
@@ -111,7 +218,16 @@ struct TabEos {
   }
   __device__ inline void rho_e_from_P_T_pressure_preferred(int m, double P, double T,
                                                            double &rho, double &sie) const {
-    if (mat(m).kind == 0) mat(m).ideal.rho_e_from_P_T(P, T, nullptr, rho, sie);
+    // only IdealGas prefers pressure; through the modifier layers like every other call
+    if (mat(m).kind == 0) {
+      const ModParams &q = mod(m);
+      mat(m).ideal.rho_e_from_P_T(P, T, nullptr, rho, sie);
+      if (q.flags & kModShift) sie = sie + q.shift;
+      if (q.flags & kModScale) {
+        rho = rho * q.inv_scale;
+        sie = sie * q.scale;
+      }
+    }
   }
 #undef SGX_TAB_DISPATCH
 };

@@ -321,3 +321,27 @@ class Helmholtz(EosBase):
         opt = _lib.HelmOptions(int(rad), int(gas), int(coul), int(ion), int(ele),
                                int(newton_raphson), int(lambda_has_lT_slot))
         super().__init__(_new(lib.sgx_eos_create_helmholtz, filename.encode(), C.byref(opt)))
+
+
+# -- modifiers (eos/modifiers/shifted_eos.hpp, scaled_eos.hpp, ramps_eos.hpp) ------------------
+# The reference writes ShiftedEOS<T>(T&&, shift) etc.; here the wrapper takes a host-mirror
+# object (plain or already modified) and returns a new one that keeps the base alive.  Nesting
+# order is the default variant's: BilinearRampEOS(ScaledEOS(ShiftedEOS(T))), each layer optional.
+class _Modified(EosBase):
+    def __init__(self, handle, base):
+        super().__init__(handle)
+        self.base = base
+
+
+def ShiftedEOS(eos, shift):
+    return _Modified(_new(_lib.load().sgx_eos_modify_shifted, eos.handle, float(shift)), eos)
+
+
+def ScaledEOS(eos, scale):
+    return _Modified(_new(_lib.load().sgx_eos_modify_scaled, eos.handle, float(scale)), eos)
+
+
+def BilinearRampEOS(eos, r0, a, b, c):
+    return _Modified(_new(_lib.load().sgx_eos_modify_bilinear_ramp, eos.handle, float(r0),
+                          float(a), float(b), float(c)), eos)
+

@@ -48,6 +48,8 @@ def load(path=None):
         "ref_eos_spiner_rhosie": (_VP, [C.POINTER(L.Sp5Tables), C.c_int, C.c_int]),
         "ref_eos_helmholtz": (_VP, [C.c_char_p, C.POINTER(L.HelmOptions)]),
         "ref_eos_free": (None, [_VP]),
+        "ref_eos_modify": (_VP, [_VP, C.c_int, _VP]),
+        "ref_eos_free_shallow": (None, [_VP]),
         "ref_eos_nlambda": (C.c_int, [_VP]),
         "ref_eos_preferred_input": (C.c_ulong, [_VP]),
         "ref_eos_maximum_density": (_D, [_VP]),
@@ -104,6 +106,18 @@ class RefEos:
         except Exception:
             pass
 
+    def modify(self, which, *params):
+        """Variant::Modify: 0 ShiftedEOS(shift), 1 ScaledEOS(scale), 2 BilinearRampEOS(r0,a,b,c).
+        The result shares the base's tables and keeps it alive."""
+        p = np.zeros(4)
+        p[:len(params)] = params
+        h = self.lib.ref_eos_modify(self.h, int(which), _p(p))
+        if not h:
+            raise RuntimeError("modified type not in the oracle's variant")
+        m = RefEosShallow(self.lib, h)
+        m.base = self
+        return m
+
     def eval(self, method, a, b, lambdas=None, nthreads=1):
         a = np.ascontiguousarray(a, dtype=np.float64)
         b = np.ascontiguousarray(b, dtype=np.float64)
@@ -154,6 +168,16 @@ class RefEos:
     def MaximumDensity(self):
         return self.lib.ref_eos_maximum_density(self.h)
 
+
+
+class RefEosShallow(RefEos):
+    """A modified copy: deleting it must not Finalize() the tables it shares with its base."""
+
+    def __del__(self):
+        try:
+            self.lib.ref_eos_free_shallow(self.h)
+        except Exception:
+            pass
 
 class Ref:
     def __init__(self, lib):

@@ -943,7 +943,7 @@ def test_pte_tabulated_materials(pkg, ref, torch_cuda, raw1, mix, solver_name):
     print(f"{mix}/{solver_name}: {conv.mean():.3f} converged, {nbits}/5 state arrays bit-identical")
 
 
-@pytest.mark.parametrize("mix", ["analytic", "tabulated"])
+@pytest.mark.parametrize("mix", ["analytic", "tabulated", "modified"])
 def test_get_sg_eos_rho_e(pkg, torch_cuda, raw1, mix):
     """get_sg_eos (eos/get_sg_eos.cpp:36-280) for the (rho, e) input
     condition against the REFERENCE'S OWN get_sg_eos -- its get_sg_eos*.cpp compiled where they
@@ -960,6 +960,15 @@ def test_get_sg_eos_rho_e(pkg, torch_cuda, raw1, mix):
         g_l = pkg.closure.set_eos_3mat_analytic()
         r_l = refk.set_eos_3mat()
         rho0 = np.array(W.PTE_RHO)
+    elif mix == "modified":
+        # ShiftedEOS(IdealGas), BilinearRampEOS(Gruneisen), ScaledEOS(Gruneisen): no material
+        # writes a lambda, so the reference's real driver is the oracle in every mode
+        gg, rg = pkg.closure.set_eos_3mat_analytic()[0], refk.set_eos_3mat()[0]
+        g_l = [pkg.ShiftedEOS(pkg.IdealGas(0.4, 7.16e6), 1.0e9),
+               pkg.BilinearRampEOS(gg, 8.0, 1.0e10, 4.0e10, 1.05), pkg.ScaledEOS(gg, 1.05)]
+        r_l = [refk.IdealGas(0.4, 7.16e6).modify(0, 1.0e9),
+               rg.modify(2, 8.0, 1.0e10, 4.0e10, 1.05), rg.modify(1, 1.05)]
+        rho0 = np.array([1.0e-2, 8.93, 8.93 / 1.05])
     else:
         g_l = [pkg.SpinerEOSDependsRhoT(raw1), pkg.IdealGas(0.4, 7.16e6),
                pkg.closure.set_eos_3mat_analytic()[0]]
@@ -998,7 +1007,7 @@ def test_get_sg_eos_rho_e(pkg, torch_cuda, raw1, mix):
         return a
     a_r, a_g = fresh(), fresh()
     eos_offsets = [1, 2, 3]
-    if mix == "analytic":
+    if mix != "tabulated":
         refk.get_sg_eos(r_l, eos_offsets, offsets, **a_r, input_int=1, mass_frac_cutoff=1e-8)
     else:
         # The reference driver's lambda cache aliases PTESolverRhoT's dpdv / dedv / dpdT scratch
@@ -1034,7 +1043,7 @@ def test_get_sg_eos_rho_e(pkg, torch_cuda, raw1, mix):
         pkg.closure.get_sg_eos(g_l, eos_offsets, offsets, **fresh(), input_int=-2)
 
 
-@pytest.mark.parametrize("mix", ["analytic", "tabulated"])
+@pytest.mark.parametrize("mix", ["analytic", "tabulated", "modified"])
 @pytest.mark.parametrize("input_int", [-3, -1])
 def test_get_sg_eos_rho_t_and_p_t(pkg, torch_cuda, raw1, mix, input_int):
     """get_sg_eos for the (rho, T) condition (input_int -3, get_sg_eos_rho_t.cpp:22-101:
@@ -1051,6 +1060,15 @@ def test_get_sg_eos_rho_t_and_p_t(pkg, torch_cuda, raw1, mix, input_int):
         g_l = pkg.closure.set_eos_3mat_analytic()
         r_l = refk.set_eos_3mat()
         rho0 = np.array(W.PTE_RHO)
+    elif mix == "modified":
+        # ShiftedEOS(IdealGas), BilinearRampEOS(Gruneisen), ScaledEOS(Gruneisen): no material
+        # writes a lambda, so the reference's real driver is the oracle in every mode
+        gg, rg = pkg.closure.set_eos_3mat_analytic()[0], refk.set_eos_3mat()[0]
+        g_l = [pkg.ShiftedEOS(pkg.IdealGas(0.4, 7.16e6), 1.0e9),
+               pkg.BilinearRampEOS(gg, 8.0, 1.0e10, 4.0e10, 1.05), pkg.ScaledEOS(gg, 1.05)]
+        r_l = [refk.IdealGas(0.4, 7.16e6).modify(0, 1.0e9),
+               rg.modify(2, 8.0, 1.0e10, 4.0e10, 1.05), rg.modify(1, 1.05)]
+        rho0 = np.array([1.0e-2, 8.93, 8.93 / 1.05])
     else:
         g_l = [pkg.SpinerEOSDependsRhoT(raw1), pkg.IdealGas(0.4, 7.16e6),
                pkg.closure.set_eos_3mat_analytic()[0]]
@@ -1441,3 +1459,162 @@ def test_stats_allreduce_single_rank(pkg, torch_cuda):
                          timeout=600)
     assert out.returncode == 0, out.stdout + out.stderr
     assert "OK" in out.stdout
+
+
+# ---------------------------------------------------------------------------------------
+# SURVEY 8(f) row 3, second half: the modifiers the default variant wraps around every model
+# (eos/eos_type_lists.hpp:69-94): ShiftedEOS, ScaledEOS, BilinearRampEOS, nested
+# BilinearRamp(Scaled(Shifted(T))).  Oracle: the reference's own wrappers through
+# Variant::Modify (oracle/ref_harness.cpp ref_eos_modify).
+# ---------------------------------------------------------------------------------------
+MOD_COMBOS = ["shift", "scale", "scale(shift)", "ramp", "ramp(shift)", "ramp(scale)",
+              "ramp(scale(shift))"]
+# per base: (shift, scale, (r0, a, b, c), rho range, T range); ramps active on part of the range
+MOD_CASES = {
+    "ideal": (1.0e9, 2.0, (5.0e-3, 3.0e7, 1.0e8, 2.0), (1.0e-3, 1.0e-1), (200.0, 2000.0)),
+    "gruneisen": (5.0e8, 1.1, (8.0, 1.0e11, 4.0e11, 1.05), (7.5, 10.5), (200.0, 1500.0)),
+    "spiner_rhot": (5.0e8, 1.1, (8.0, 1.0e11, 2.0e11, 1.2), (2.0, 24.0), (50.0, 1.0e4)),
+}
+
+
+def _mod_base(pkg, ref, raw1, base):
+    if base == "ideal":
+        return pkg.IdealGas(0.4, 7.16e6), ref.IdealGas(0.4, 7.16e6)
+    if base == "gruneisen":
+        return pkg.closure.set_eos_3mat_analytic()[0], ref.set_eos_3mat()[0]
+    return pkg.SpinerEOSDependsRhoT(raw1), ref.SpinerRhoT(raw1)
+
+
+def _mod_apply(pkg, g, r, combo, shift, scale, ramp):
+    """The same layers on the library handle and on the reference object, inside out."""
+    if "shift" in combo:
+        g, r = pkg.ShiftedEOS(g, shift), r.modify(0, shift)
+    if "scale" in combo:
+        g, r = pkg.ScaledEOS(g, scale), r.modify(1, scale)
+    if "ramp" in combo:
+        g, r = pkg.BilinearRampEOS(g, *ramp), r.modify(2, *ramp)
+    return g, r
+
+
+@pytest.mark.parametrize("combo", MOD_COMBOS)
+@pytest.mark.parametrize("base", ["ideal", "gruneisen", "spiner_rhot"])
+def test_modifiers_vector_parity(pkg, ref, torch_cuda, raw1, base, combo):
+    """All ten vector methods of a modified handle against the reference's wrapper classes:
+    1e-12, lambda rows of the tabulated base included; handle introspection forwards like the
+    wrappers (nlambda, PreferredInput, ScaledEOS::MaximumDensity)."""
+    torch = torch_cuda
+    L = pkg._lib
+    shift, scale, ramp, (r_lo, r_hi), (T_lo, T_hi) = MOD_CASES[base]
+    g0, r0 = _mod_base(pkg, ref, raw1, base)
+    g, r = _mod_apply(pkg, g0, r0, combo, shift, scale, ramp)
+    assert L.load().sgx_eos_type(g.handle) == 7 and g.nlambda() == g0.nlambda()
+    assert g.PreferredInput() == g0.PreferredInput()
+    if "scale" in combo:
+        assert g.MaximumDensity() == (1.0 / scale) * g0.MaximumDensity()
+    n = 1 << 14
+    u = pkg.rng.uniform_np(71, 0, 2 * n)
+    rho_h = r_lo * (r_hi / r_lo) ** u[:n]
+    T_h = T_lo * (T_hi / T_lo) ** u[n:]
+    nl = g.nlambda()
+
+    def lam_np():
+        return np.full((n, nl), np.nan) if nl else None
+    sie_h = r.eval(L.E_FROM_RHO_T, rho_h, T_h, lam_np())
+    rho_d, T_d, sie_d = dev(rho_h), dev(T_h), dev(sie_h)
+    out = torch.empty_like(rho_d)
+    on_ramp = 0
+    for m in range(len(L.METHOD_NAMES)):
+        from_e = m in (L.T_FROM_RHO_E, L.P_FROM_RHO_E, L.CV_FROM_RHO_E, L.BMOD_FROM_RHO_E,
+                       L.GAMMA_FROM_RHO_E)
+        lam_r = lam_np()
+        want = r.eval(m, rho_h, sie_h if from_e else T_h, lam_r)
+        lam_d = dev(lam_np()) if nl else None
+        g._eval(m, rho_d, sie_d if from_e else T_d, out, n, lam_d)
+        torch.cuda.synchronize()
+        assert_rel(out.cpu().numpy(), want, LOOKUP_TOL, f"{combo}({base}) {L.METHOD_NAMES[m]}")
+        if nl:
+            assert_rel(lam_d.cpu().numpy(), lam_r, LOOKUP_TOL, f"{combo}({base}) lambda, method {m}")
+        if m == L.P_FROM_RHO_T and "ramp" in combo:
+            inner = combo[5:-1] if combo.startswith("ramp(") else ""  # the layers under the ramp
+            plain = _mod_apply(pkg, g0, r0, inner, shift, scale, ramp)[1]
+            on_ramp = int((want != plain.eval(m, rho_h, T_h, lam_np())).sum())
+    if "ramp" in combo:
+        assert 0 < on_ramp < n, f"the ramp must be active on part of the range ({on_ramp}/{n})"
+    # the order of the layers is the default variant's: anything else is refused
+    with pytest.raises(pkg.SgxError):
+        pkg.ShiftedEOS(g, 1.0)
+
+
+def test_modifiers_refuse_what_they_do_not_serve(pkg, torch_cuda, helm_table):
+    """Helmholtz takes no modifier here; FillEos and serialization do not take modified handles
+    (they fail, they do not silently ignore the layers)."""
+    torch = torch_cuda
+    with pytest.raises(pkg.SgxError):
+        pkg.ShiftedEOS(pkg.Helmholtz(helm_table), 1.0)
+    g = pkg.ScaledEOS(pkg.IdealGas(0.4, 7.16e6), 2.0)
+    with pytest.raises(pkg.SgxError):
+        g.Serialize()
+    a = torch.ones(8, dtype=torch.float64, device="cuda")
+    tq = pkg.thermalqs
+    with pytest.raises(pkg.SgxError):
+        g.FillEos(a, a.clone(), a.clone(), a.clone(), a.clone(), a.clone(), 8,
+                  tq.pressure | tq.specific_internal_energy)
+    with pytest.raises(pkg.SgxError):
+        pkg.ScaledEOS(pkg.IdealGas(0.4, 7.16e6), 0.0)
+    with pytest.raises(pkg.SgxError):
+        pkg.BilinearRampEOS(pkg.IdealGas(0.4, 7.16e6), 1.0, 2.0, 2.0, 1.0)  # a == b
+
+
+@pytest.mark.parametrize("solver_name", ["RhoT", "FixedT", "PT"])
+def test_pte_modified_materials(pkg, ref, torch_cuda, raw1, solver_name):
+    """Mixed cells whose materials carry modifiers, as the reference's default variant allows:
+    ScaledEOS(ShiftedEOS(SpinerEOSDependsRhoT)) with its lambda cache, ShiftedEOS(IdealGas) and
+    BilinearRampEOS(Gruneisen) (the ramp is active: the Gruneisen material sits on it in most
+    cells).  The solvers see the wrappers' bounds (ScaledEOS scales RhoPmin / MaximumDensity) and
+    DensityEnergyFromPressureTemperature.  Every SolverStatus field identical to the reference,
+    states to 1e-10, caches to 1e-10."""
+    torch = torch_cuda
+    L, W = pkg._lib, pkg.workloads
+    g_l = [pkg.ScaledEOS(pkg.ShiftedEOS(pkg.SpinerEOSDependsRhoT(raw1), 2.0e8), 1.05),
+           pkg.ShiftedEOS(pkg.IdealGas(0.4, 7.16e6), 1.0e9),
+           pkg.BilinearRampEOS(pkg.closure.set_eos_3mat_analytic()[0], 8.0, 1.0e10, 4.0e10, 1.05)]
+    r_l = [ref.SpinerRhoT(raw1).modify(0, 2.0e8).modify(1, 1.05),
+           ref.IdealGas(0.4, 7.16e6).modify(0, 1.0e9),
+           ref.set_eos_3mat()[0].modify(2, 8.0, 1.0e10, 4.0e10, 1.05)]
+    nm, n, T0 = 3, 2048, 600.0
+    vf = W.pte_vfracs(n, nmat=nm)
+    rho = np.tile(np.array((8.93 / 1.05, 1.0e-2, 8.93)), (n, 1)) * \
+        (0.9 + 0.2 * pkg.rng.uniform_np(57, 0, n * nm).reshape(n, nm))
+    sie = np.stack([r_l[m].eval(L.E_FROM_RHO_T, rho[:, m].copy(), np.full(n, T0),
+                                np.full((n, 3), np.nan) if g_l[m].nlambda() else None)
+                    for m in range(nm)], axis=1)
+    st_h = [np.ascontiguousarray(a) for a in (rho, vf, sie, np.full((n, nm), T0),
+                                              np.zeros((n, nm)))]
+    solver = {"RhoT": L.PTE_RHOT, "FixedT": L.PTE_FIXED_T, "PT": L.PTE_PT}[solver_name]
+    Tfix = 550.0 + 200.0 * pkg.rng.uniform_np(58, 0, n) if solver_name == "FixedT" else None
+    prm = pkg.closure.MixParams()
+    lam_r = np.full((n, nm, 3), np.nan)
+    st_r = [a.copy() for a in st_h]
+    status_r, _, _ = ref.pte_solve(solver, r_l, *st_r, prm, Tguess=Tfix, lambdas=lam_r)
+    st_d = [dev(a) for a in st_h]
+    lam_d = dev(np.full((n, nm, 3), np.nan))
+    status = torch.zeros(n, dtype=torch.int64, device="cuda")
+    pkg.closure.pte_solve(solver, g_l, *st_d, params=prm, status=status,
+                          Tguess=None if Tfix is None else dev(Tfix), lambdas=lam_d)
+    torch.cuda.synchronize()
+    got = status.cpu().numpy().view(np.uint64)
+    conv = (status_r & 1).astype(bool)
+    assert conv.mean() > 0.95, f"reference converged on only {conv.mean():.3f} of the cells"
+    same = got == status_r
+    assert same.all(), (f"modified/{solver_name}: SolverStatus differs on {int((~same).sum())} "
+                        f"cells; first: got {pkg.closure.decode_status(got[~same][:1])} want "
+                        f"{pkg.closure.decode_status(status_r[~same][:1])}")
+    for a, b, nm_ in zip(st_d, st_r, ("rho", "vfrac", "sie", "temp", "press")):
+        assert_rel(a.cpu().numpy()[conv], b[conv], PTE_TOL, f"modified/{solver_name} state {nm_}")
+    lam_g = lam_d.cpu().numpy()
+    fin = np.isfinite(lam_r)
+    assert (np.isfinite(lam_g) == fin).all()
+    assert np.abs(lam_g[fin] - lam_r[fin]).max() <= 1e-10
+    # RhoU / FixedP are not built for such mixtures: refused, not mis-served
+    with pytest.raises(pkg.SgxError):
+        pkg.closure.pte_solve(L.PTE_RHOU, g_l, *[dev(a) for a in st_h], params=prm)
