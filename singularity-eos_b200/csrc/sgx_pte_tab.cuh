@@ -20,13 +20,17 @@ namespace sgx {
 constexpr int kMaxNumLambdas = 3; // MAX_NUM_LAMBDAS
 
 #ifdef __CUDACC__
-struct TabEos {
+// MODS = false: an accessor for mixtures without modifier layers (every `flags &` test below
+// folds away; measured: the unmodified tabulated mixture lost 17 % when it carried them).
+template <bool MODS>
+struct TabEosT {
   const EosSet &set;
   double *lam = nullptr; // this cell's cache: [nmat][kMaxNumLambdas], or null (NullIndexer)
   // participating-material compaction (get_sg_eos: EOSAccessor_, eos/get_sg_eos.hpp:38-47):
   // solver material m is set.e[idx[m]]; null = identity
   const int *idx = nullptr;
-  __device__ TabEos(const EosSet &s) : set(s) {}
+  __device__ TabEosT(const EosSet &s) : set(s) {}
+  SGX_D int flags_of(const ModParams &q) const { return MODS ? q.flags : 0; }
   SGX_D const AnyEos &mat(const int m) const { return set.e[idx ? idx[m] : m]; }
   SGX_D double *cache(const int m) const { return lam ? lam + kMaxNumLambdas * m : nullptr; }
   SGX_D bool tab(const int m) const { return mat(m).kind >= SGX_EOS_SPINER_RHOT; }
@@ -85,11 +89,11 @@ struct TabEos {
   // density and energy as the unmodified model sees them: ScaledEOS hands scale * rho and
   // inv_scale * sie down (scaled_eos.hpp:71-75), ShiftedEOS sie - shift (shifted_eos.hpp:69)
   SGX_D double in_rho(const ModParams &q, const double rho) const {
-    return (q.flags & kModScale) ? q.scale * rho : rho;
+    return (flags_of(q) & kModScale) ? q.scale * rho : rho;
   }
   SGX_D double in_sie(const ModParams &q, double sie) const {
-    if (q.flags & kModScale) sie = q.inv_scale * sie;
-    if (q.flags & kModShift) sie = sie - q.shift;
+    if (flags_of(q) & kModScale) sie = q.inv_scale * sie;
+    if (flags_of(q) & kModShift) sie = sie - q.shift;
     return sie;
   }
   // BilinearRampEOS::get_ramp_pressure / get_ramp_dpdrho (ramps_eos.hpp:104-124)
@@ -104,14 +108,14 @@ struct TabEos {
     const ModParams &q = mod(m);
     // sic: ScaledEOS::InternalEnergyFromDensityTemperature passes rho on UNSCALED (:76-80)
     double e = b_e_from_rho_T(m, rho, T);
-    if (q.flags & kModShift) e = e + q.shift;
-    if (q.flags & kModScale) e = q.scale * e;
+    if (flags_of(q) & kModShift) e = e + q.shift;
+    if (flags_of(q) & kModScale) e = q.scale * e;
     return e;
   }
   SGX_D double P_from_rho_e(int m, double rho, double e) const {
     const ModParams &q = mod(m);
     const double p_eos = b_P_from_rho_e(m, in_rho(q, rho), in_sie(q, e));
-    if (!(q.flags & kModRamp)) return p_eos;
+    if (!(flags_of(q) & kModRamp)) return p_eos;
     const double p_ramp = ramp_pressure(q, rho);
     return p_eos < p_ramp ? p_ramp : p_eos;
   }
@@ -122,7 +126,7 @@ struct TabEos {
   SGX_D double P_from_rho_T(int m, double rho, double T) const {
     const ModParams &q = mod(m);
     const double p_eos = b_P_from_rho_T(m, in_rho(q, rho), T);
-    if (!(q.flags & kModRamp)) return p_eos;
+    if (!(flags_of(q) & kModRamp)) return p_eos;
     const double p_ramp = ramp_pressure(q, rho);
     return p_eos < p_ramp ? p_ramp : p_eos;
   }
@@ -135,7 +139,7 @@ struct TabEos {
   }
   SGX_D double bmod_from_rho_T(int m, double rho, double T) const {
     const ModParams &q = mod(m);
-    if (q.flags & kModRamp) { // ramps_eos.hpp:196-204
+    if (flags_of(q) & kModRamp) { // ramps_eos.hpp:196-204
       const double p_ramp = ramp_pressure(q, rho);
       const double p_eos = b_P_from_rho_T(m, in_rho(q, rho), T);
       if (p_eos < p_ramp) return rho * ramp_dpdrho(q, rho);
@@ -144,7 +148,7 @@ struct TabEos {
   }
   SGX_D double bmod_from_rho_e(int m, double rho, double e) const {
     const ModParams &q = mod(m);
-    if (q.flags & kModRamp) { // ramps_eos.hpp:160-168
+    if (flags_of(q) & kModRamp) { // ramps_eos.hpp:160-168
       const double p_ramp = ramp_pressure(q, rho);
       const double p_eos = b_P_from_rho_e(m, in_rho(q, rho), in_sie(q, e));
       if (p_eos < p_ramp) return rho * ramp_dpdrho(q, rho);
@@ -166,11 +170,11 @@ struct TabEos {
   }
   SGX_D double RhoPmin(int m, double T) const {
     const ModParams &q = mod(m);
-    return (q.flags & kModScale) ? q.inv_scale * b_RhoPmin(m, T) : b_RhoPmin(m, T);
+    return (flags_of(q) & kModScale) ? q.inv_scale * b_RhoPmin(m, T) : b_RhoPmin(m, T);
   }
   SGX_D double MaximumDensity(int m) const {
     const ModParams &q = mod(m);
-    return (q.flags & kModScale) ? q.inv_scale * b_MaximumDensity(m) : b_MaximumDensity(m);
+    return (flags_of(q) & kModScale) ? q.inv_scale * b_MaximumDensity(m) : b_MaximumDensity(m);
   }
   SGX_D double MinimumTemperature(int m) const {
     SGX_TAB_DISPATCH(m, MinimumTemperature(), MinimumTemperature())
@@ -187,8 +191,8 @@ struct TabEos {
                                         double &sie) const {
     const ModParams &q = mod(m);
     b_rho_e_from_P_T(m, P, T, rho, sie);
-    if (q.flags & kModShift) sie = sie + q.shift;
-    if (q.flags & kModScale) {
+    if (flags_of(q) & kModShift) sie = sie + q.shift;
+    if (flags_of(q) & kModScale) {
       rho = rho * q.inv_scale;
       sie = sie * q.scale;
     }
@@ -222,8 +226,8 @@ struct TabEos {
     if (mat(m).kind == 0) {
       const ModParams &q = mod(m);
       mat(m).ideal.rho_e_from_P_T(P, T, nullptr, rho, sie);
-      if (q.flags & kModShift) sie = sie + q.shift;
-      if (q.flags & kModScale) {
+      if (flags_of(q) & kModShift) sie = sie + q.shift;
+      if (flags_of(q) & kModScale) {
         rho = rho * q.inv_scale;
         sie = sie * q.scale;
       }
@@ -231,7 +235,12 @@ struct TabEos {
   }
 #undef SGX_TAB_DISPATCH
 };
-SGX_D void set_cell_cache(TabEos &eos, double *p) { eos.lam = p; }
+using TabEos = TabEosT<true>;       // any mixture
+using TabEosPlain = TabEosT<false>; // no material carries a modifier
+template <bool MODS>
+SGX_D void set_cell_cache(TabEosT<MODS> &eos, double *p) {
+  eos.lam = p;
+}
 #endif // __CUDACC__
 
 } // namespace sgx
