@@ -20,6 +20,7 @@ namespace sgx {
 
 int launch_pte_tab_fixedt(SGX_TAB_PARAMS);
 int launch_pte_tab_pt(SGX_TAB_PARAMS);
+int launch_pte_tab_rhot_plain(SGX_TAB_PARAMS);
 
 int launch_pte_tab(int solver, const EosSet &set, const MixParamsDev &prm, double *rho,
                    double *vfrac, double *sie, double *temp, double *press,
@@ -31,20 +32,9 @@ int launch_pte_tab(int solver, const EosSet &set, const MixParamsDev &prm, doubl
   bool modified = false;
   for (int m = 0; m < set.nmat; ++m)
     modified = modified || set.mod[m].flags != 0;
-  if (solver == SGX_PTE_RHOT && !modified) { // the accessor without the modifier layers
-    switch (set.nmat) {
-    case 1:
-      return launch_pte_percell<1, TabEosPlain, SGX_PTE_RHOT>(SGX_TAB_ARGS);
-    case 2:
-      return launch_pte_percell<2, TabEosPlain, SGX_PTE_RHOT>(SGX_TAB_ARGS);
-    case 3:
-      return launch_pte_percell<3, TabEosPlain, SGX_PTE_RHOT>(SGX_TAB_ARGS);
-    case 4:
-      return launch_pte_percell<4, TabEosPlain, SGX_PTE_RHOT>(SGX_TAB_ARGS);
-    default:
-      break;
-    }
-  }
+  // the accessor without the modifier layers (sgx_pte_tab_plain.cu)
+  if (solver == SGX_PTE_RHOT && !modified && set.nmat >= 1 && set.nmat <= 4)
+    return launch_pte_tab_rhot_plain(SGX_TAB_ARGS);
   if (solver == SGX_PTE_RHOT) {
     switch (set.nmat) {
     case 1:
