@@ -476,7 +476,7 @@ def run_ours(args):
             "converged_frac": float((stt & 1).double().mean().item()),
             "materials": ["SpinerEOSDependsRhoT (Vinet Cu table, lambda cache)", "IdealGas",
                           "Gruneisen"],
-            "kernel": "pte_kernel<3, TabEos, RhoT> (per-cell)"}
+            "kernel": "pte_rhot_sm_kernel<3, TabEosT<false>> (lane-refill state machine, per-lane caches)"}
         del t0_, ts_, stt, lam_t, sie_t, rho_t
         # e2e for config 5: host buffers through sgx_pte_solve_host (chunked, 3 streams)
         npe = min(npte, 1 << 22)

@@ -178,6 +178,12 @@ struct DynEos {
   SGX_D double P_from_part(int m, const RhoPart &p, double rho, double sie) const {
     SGX_EOS_DISPATCH(m, P_from_part(p, rho, sie))
   }
+  // GetPressureFromPreferred(..., do_e_lookup = false) (:583-597) for the state machine: every
+  // model this accessor holds has sie among its preferred inputs, so T is not used
+  SGX_D double P_pref_from_part(int m, const RhoPart &p, double rho, double sie, double) const {
+    return P_from_part(m, p, rho, sie);
+  }
+  static constexpr int kCacheSlots = 0; // no lambda cache
   SGX_D double cv_from_part(int m, const RhoPart &p, double rho, double sie) const {
     SGX_EOS_DISPATCH(m, cv_from_part(p, rho, sie))
   }
@@ -254,6 +260,10 @@ struct Mix3GrDrDp {
   SGX_D double P_from_part(int m, const RhoPart &p, double rho, double sie) const {
     SGX_MIX3(P_from_part(p, rho, sie))
   }
+  SGX_D double P_pref_from_part(int m, const RhoPart &p, double rho, double sie, double) const {
+    return P_from_part(m, p, rho, sie);
+  }
+  static constexpr int kCacheSlots = 0;
   SGX_D double cv_from_part(int m, const RhoPart &p, double rho, double sie) const {
     SGX_MIX3(cv_from_part(p, rho, sie))
   }

@@ -9,6 +9,7 @@
 #include "sgx_internal.hpp"
 #include "sgx_pte_kernel.cuh"
 #include "sgx_pte_sm.cuh"
+#include "sgx_pte_rhot_launch.cuh"
 
 namespace sgx {
 
@@ -21,55 +22,6 @@ static bool percell_variant() {
 static bool warp_variant() {
   const char *s = getenv("SGX_PTE_KERNEL");
   return s && strcmp(s, "warp") == 0;
-}
-
-// Cells go through in chunks: init kernel -> scratch record -> state-machine kernel, both on
-// the caller's stream; the scratch is stream-ordered (scratch_alloc_async, the library's own pool): (2*NM+1)*8 B/cell for the
-// hand-over record plus one 64-bit cell cursor per chunk.
-static constexpr int64_t kPteChunk = int64_t(1) << 23;
-
-template <int NM, class Acc, int THREADS = kSmThreads, int MINB = 1>
-static int launch_sm(const EosSet &set, const MixParamsDev &prm, double *rho, double *vfrac,
-                     double *sie, double *temp, double *press, const double *sie_tot,
-                     const double *vfrac_tot, const double *Tguess, uint64_t *status,
-                     double *residual, uint64_t *stats, int64_t ncell, cudaStream_t s) {
-  const int64_t chunk = ncell < kPteChunk ? ncell : kPteChunk;
-  const int64_t nchunk = (ncell + chunk - 1) / chunk;
-  const size_t cursor_bytes = ((size_t)nchunk * sizeof(unsigned long long) + 255) & ~size_t(255);
-  char *scratch = nullptr;
-  SGX_CUDA_OK(scratch_alloc_async(
-      reinterpret_cast<void **>(&scratch),
-      cursor_bytes + (size_t)chunk * (2 * NM + 1) * sizeof(double), s));
-  unsigned long long *cursors = reinterpret_cast<unsigned long long *>(scratch);
-  double *init = reinterpret_cast<double *>(scratch + cursor_bytes);
-  cudaError_t err = cudaMemsetAsync(cursors, 0, cursor_bytes, s);
-  int64_t k = 0;
-  for (int64_t c0 = 0; c0 < ncell && err == cudaSuccess; c0 += chunk, ++k) {
-    const int64_t n = (ncell - c0) < chunk ? (ncell - c0) : chunk;
-    const int64_t o = c0 * NM;
-    const LaunchCfg ci = stream_cfg(n, 256, 4);
-    pte_rhot_init_kernel<NM, Acc><<<ci.blocks, ci.threads, 0, s>>>(
-        set, prm, rho + o, vfrac + o, sie + o, temp + o, press + o,
-        sie_tot ? sie_tot + c0 : nullptr, vfrac_tot ? vfrac_tot + c0 : nullptr,
-        Tguess ? Tguess + c0 : nullptr, init, n);
-    // one block of THREADS per SM (fewer when the chunk has fewer cells than lanes)
-    const int threads = THREADS;
-    int64_t blocks = (int64_t)sm_count() * MINB;
-    const int64_t need = (n + threads - 1) / threads;
-    if (blocks > need) blocks = need;
-    pte_rhot_sm_kernel<NM, Acc, THREADS, MINB><<<(unsigned)blocks, threads, 0, s>>>(
-        set, prm, rho + o, vfrac + o, sie + o, temp + o, press + o,
-        sie_tot ? sie_tot + c0 : nullptr, vfrac_tot ? vfrac_tot + c0 : nullptr, init,
-        status ? reinterpret_cast<unsigned long long *>(status) + c0 : nullptr,
-        residual ? residual + c0 : nullptr, reinterpret_cast<unsigned long long *>(stats), n,
-        cursors + k);
-    count_launch(2);
-    err = cudaGetLastError();
-  }
-  cudaFreeAsync(scratch, s); // stream-ordered; released on every exit path
-  if (err != cudaSuccess)
-    return fail(SGX_ERR_CUDA, "PTE RhoT launch failed: %s", cudaGetErrorString(err));
-  return SGX_OK;
 }
 
 // The warp-per-cell comparison variant (SGX_PTE_KERNEL=warp), benchmark mixture only.
@@ -114,7 +66,7 @@ static int launch_warp(const EosSet &set, const MixParamsDev &prm, double *rho, 
 // its own kernels.  Once per device, if the limit is below 2048 it is raised to 2048 (never
 // lowered; about 0.3 GB more local-memory backing on a B200).  SGX_STACK_LIMIT=<bytes> picks
 // another value, SGX_STACK_LIMIT=0 leaves the device alone.
-static void raise_stack_limit_once() {
+void raise_stack_limit_once() {
   static std::atomic<unsigned long long> done{0};
   int device = 0;
   if (cudaGetDevice(&device) != cudaSuccess || device < 0 || device >= 64) return;

@@ -61,8 +61,8 @@ enum SmMode : int { MODE_EP = 1, MODE_TU = 3, MODE_J = 4 };
 //   MODE_J   Jacobian: (e,P) at the dv-perturbed densities rq and T = Tq, and (e2,P2) at the
 //            state densities rho_c -- whose density-only terms are in `cache` since the last
 //            TestUpdate / InitBase -- and T = Tq2                          (:1042-1075)
-// Every material here has specific internal energy among its preferred inputs, so
-// GetPressureFromPreferred always takes the P(rho, e) branch.
+// GetPressureFromPreferred is the accessor's P_pref_from_part: P(rho, e) for the analytic
+// models (sie among their preferred inputs), P(rho, T) for the tabulated ones (sgx_pte_tab.cuh).
 template <int NM, class Eos>
 __device__ __forceinline__ void eval_round(const Eos &eos, const int mode, const double Tq,
                                            const double Tq2, const double (&rq)[NM],
@@ -78,11 +78,11 @@ __device__ __forceinline__ void eval_round(const Eos &eos, const int mode, const
     eq[m] = e;
     double sie_for_p = e;
     if (mode == MODE_TU) sie_for_p = ratio(rb[m] * e, rb[m]);
-    pq[m] = eos.P_from_part(m, part, rq[m], sie_for_p);
+    pq[m] = eos.P_pref_from_part(m, part, rq[m], sie_for_p, Tq);
     if (mode == MODE_J) {
       const double e2 = eos.e_from_part(m, cache[m], rho_c[m], Tq2);
       eq2[m] = e2;
-      pq2[m] = eos.P_from_part(m, cache[m], rho_c[m], e2);
+      pq2[m] = eos.P_pref_from_part(m, cache[m], rho_c[m], e2, Tq2);
     } else {
       cache[m] = part;
     }
@@ -496,15 +496,22 @@ __global__ void __launch_bounds__(THREADS, MINB)
                        const double *__restrict__ init,
                        unsigned long long *__restrict__ status, double *__restrict__ residual,
                        unsigned long long *__restrict__ stats, const int64_t ncell,
-                       unsigned long long *__restrict__ cursor) {
+                       unsigned long long *__restrict__ cursor,
+                       double *__restrict__ lambda = nullptr) {
   __shared__ unsigned int s_hist[SGX_PTE_NSTATS];
   if (stats) {
     for (int k = threadIdx.x; k < SGX_PTE_NSTATS; k += blockDim.x)
       s_hist[k] = 0;
     __syncthreads();
   }
-  const Acc eos(set);
+  Acc eos(set);
   mix::RhoTLane<NM, Acc> L(eos, prm);
+  // Accessors with a lambda cache (tabulated materials, CacheAccessor layout [cell][NM][slots]):
+  // the lane keeps its cell's cache here and stores it when the cell retires.  In this solver
+  // the tabulated models only WRITE their cache (no call reads the cached lT), so the init
+  // kernel runs without one.
+  constexpr int kLam = Acc::kCacheSlots > 0 ? NM * Acc::kCacheSlots : 1;
+  double lamreg[kLam];
   const unsigned lane = threadIdx.x & 31u;
   bool exhausted = false; // warp-uniform: the cursor has passed the end of the range
   int64_t cell = -1;
@@ -534,6 +541,11 @@ __global__ void __launch_bounds__(THREADS, MINB)
           }
           if (status) status[cell] = mix::pack_status(L.st, L.s.niter);
           if (residual) residual[cell] = L.st.residual;
+          if constexpr (Acc::kCacheSlots > 0) {
+            if (lambda)
+              for (int k = 0; k < kLam; ++k)
+                lambda[cell * kLam + k] = lamreg[k];
+          }
           if (stats) {
             atomicAdd(&s_hist[SGX_PTE_STAT_NCELL], 1u);
             if (L.st.converged) atomicAdd(&s_hist[SGX_PTE_STAT_CONVERGED], 1u);
@@ -564,6 +576,12 @@ __global__ void __launch_bounds__(THREADS, MINB)
             L.s.sie[m] = sie[base + m];
             L.s.temp[m] = temp[base + m];
             L.s.press[m] = press[base + m];
+          }
+          if constexpr (Acc::kCacheSlots > 0) {
+            if (lambda)
+              for (int k = 0; k < kLam; ++k)
+                lamreg[k] = lambda[cell * kLam + k];
+            set_cell_cache(eos, lambda ? lamreg : nullptr);
           }
           const double *rec = init + cell * (2 * NM + 1);
           double vfrac_init[NM], rho_init[NM];
@@ -683,11 +701,11 @@ __global__ void __launch_bounds__(256, 2)
             e = eos.e_from_part(mm, part, my_rq, Tq);
             double sie_for_p = e;
             if (mode == mix::MODE_TU) sie_for_p = ratio(my_rb * e, my_rb);
-            P = eos.P_from_part(mm, part, my_rq, sie_for_p);
+            P = eos.P_pref_from_part(mm, part, my_rq, sie_for_p, Tq);
             if (mode != mix::MODE_J) my_cache = part;
           } else if (mode == mix::MODE_J) {
             e = eos.e_from_part(mm, nb, my_rho_c, Tq2);
-            P = eos.P_from_part(mm, nb, my_rho_c, e);
+            P = eos.P_pref_from_part(mm, nb, my_rho_c, e, Tq2);
           }
         }
 #pragma unroll

@@ -3,6 +3,9 @@
 // (sgx_pte_tab.cuh), with the per-material lambda caches of the reference's CacheAccessor.
 // PTESolverRhoT, PTESolverFixedT (1..4 materials) and PTESolverPT (2..3 materials); the three
 // solver families compile in three translation units (this one: the dispatcher and RhoT).
+#include <cstdlib>
+#include <cstring>
+
 #include "sgx_internal.hpp"
 #include "sgx_pte_kernel.cuh"
 #include "sgx_pte_tab.cuh"
@@ -21,6 +24,8 @@ namespace sgx {
 int launch_pte_tab_fixedt(SGX_TAB_PARAMS);
 int launch_pte_tab_pt(SGX_TAB_PARAMS);
 int launch_pte_tab_rhot_plain(SGX_TAB_PARAMS);
+int launch_pte_tab_rhot_sm_plain(SGX_TAB_PARAMS);
+int launch_pte_tab_rhot_sm_mod(SGX_TAB_PARAMS);
 
 int launch_pte_tab(int solver, const EosSet &set, const MixParamsDev &prm, double *rho,
                    double *vfrac, double *sie, double *temp, double *press,
@@ -32,7 +37,13 @@ int launch_pte_tab(int solver, const EosSet &set, const MixParamsDev &prm, doubl
   bool modified = false;
   for (int m = 0; m < set.nmat; ++m)
     modified = modified || set.mod[m].flags != 0;
-  // the accessor without the modifier layers (sgx_pte_tab_plain.cu)
+  // RhoT: the lane-refill state machine (sgx_pte_tab_sm*.cu); SGX_PTE_KERNEL=percell keeps the
+  // thread-per-cell kernels (sgx_pte_tab_plain.cu and below), bit-identical results
+  const char *variant = getenv("SGX_PTE_KERNEL"); // read per call: the tests switch it
+  const bool percell = variant && strcmp(variant, "percell") == 0;
+  if (solver == SGX_PTE_RHOT && !percell && set.nmat >= 1 && set.nmat <= 4)
+    return modified ? launch_pte_tab_rhot_sm_mod(SGX_TAB_ARGS)
+                    : launch_pte_tab_rhot_sm_plain(SGX_TAB_ARGS);
   if (solver == SGX_PTE_RHOT && !modified && set.nmat >= 1 && set.nmat <= 4)
     return launch_pte_tab_rhot_plain(SGX_TAB_ARGS);
   if (solver == SGX_PTE_RHOT) {

@@ -53,6 +53,21 @@ struct TabEosT {
   default:                                                                                 \
     return mat(m).rhosie->TABCALL;                                                       \
   }
+  // ---- the staged interface of the lane-refill state machine (sgx_pte_sm.cuh) ----
+  // Tabulated models have no density-only part worth caching (two log transforms); the
+  // adapters go through the same layered methods as the per-cell kernels, so both paths do
+  // the same arithmetic per cell.
+  static constexpr int kCacheSlots = kMaxNumLambdas;
+  SGX_D void rho_part(int, double, RhoPart &p) const { p = RhoPart{1.0, 0.0, 0.0, 0.0}; }
+  SGX_D double e_from_part(int m, const RhoPart &, double rho, double T) const {
+    return e_from_rho_T(m, rho, T);
+  }
+  // GetPressureFromPreferred(..., do_e_lookup = false) (:583-597)
+  SGX_D double P_pref_from_part(int m, const RhoPart &, double rho, double sie,
+                                double T) const {
+    if (preferred(m) & TQ_SIE) return P_from_rho_e(m, rho, sie);
+    return P_from_rho_T(m, rho, T);
+  }
   // ---- the unmodified model (the innermost T of BilinearRamp(Scaled(Shifted(T)))) ----
   SGX_D double b_e_from_rho_T(int m, double rho, double T) const {
     SGX_TAB_DISPATCH(m, e_from_rho_T(rho, T), e_from_rho_T(rho, T, cache(m)))

@@ -1,0 +1,31 @@
+// PTESolverRhoT over mixtures with tabulated materials (no modifier layer) through the lane-refill
+// state machine (sgx_pte_sm.cuh) on the TabEosPlain accessor (sgx_pte_tab.cuh), 1..4 materials, with
+// the per-material lambda caches held per lane.  Same arithmetic per cell as the per-cell kernels
+// (sgx_pte_tab*.cu), which stay reachable with SGX_PTE_KERNEL=percell.
+#include "sgx_pte_rhot_launch.cuh"
+#include "sgx_pte_tab.cuh"
+
+namespace sgx {
+
+int launch_pte_tab_rhot_sm_plain(const EosSet &set, const MixParamsDev &prm, double *rho, double *vfrac, double *sie,
+         double *temp, double *press, const double *sie_tot, const double *vfrac_tot,
+         const double *Tguess, uint64_t *status, double *residual, uint64_t *stats,
+         int64_t ncell, cudaStream_t s, double *lambda) {
+#define SGX_ARGS                                                                           \
+  set, prm, rho, vfrac, sie, temp, press, sie_tot, vfrac_tot, Tguess, status, residual,    \
+      stats, ncell, s, lambda
+  raise_stack_limit_once();
+  switch (set.nmat) {
+  case 1:
+    return launch_sm<1, TabEosPlain>(SGX_ARGS);
+  case 2:
+    return launch_sm<2, TabEosPlain>(SGX_ARGS);
+  case 3:
+    return launch_sm<3, TabEosPlain>(SGX_ARGS);
+  default:
+    return launch_sm<4, TabEosPlain>(SGX_ARGS);
+  }
+#undef SGX_ARGS
+}
+
+} // namespace sgx

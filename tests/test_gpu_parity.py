@@ -1618,3 +1618,55 @@ def test_pte_modified_materials(pkg, ref, torch_cuda, raw1, solver_name):
     # RhoU / FixedP are not built for such mixtures: refused, not mis-served
     with pytest.raises(pkg.SgxError):
         pkg.closure.pte_solve(L.PTE_RHOU, g_l, *[dev(a) for a in st_h], params=prm)
+
+
+@pytest.mark.parametrize("mix", ["tabulated", "modified"])
+def test_pte_tab_state_machine_equals_percell_kernel(pkg, torch_cuda, raw1, monkeypatch, mix):
+    """Mixtures with tabulated / modified materials run PTESolverRhoT through the lane-refill
+    state machine (csrc/sgx_pte_tab_sm*.cu); SGX_PTE_KERNEL=percell keeps the thread-per-cell
+    kernel.  Same arithmetic per cell: states, status words, residuals and lambda caches must be
+    bit-identical, ragged sizes included (both are checked against the reference elsewhere)."""
+    torch = torch_cuda
+    L, W = pkg._lib, pkg.workloads
+    if mix == "tabulated":
+        g_l = [pkg.SpinerEOSDependsRhoT(raw1, pmin_vapor_dome=True), pkg.IdealGas(0.4, 7.16e6),
+               pkg.closure.set_eos_3mat_analytic()[0]]
+        rho0 = (8.93, 1.0e-2, 8.93)
+    else:
+        g_l = [pkg.ScaledEOS(pkg.ShiftedEOS(pkg.SpinerEOSDependsRhoT(raw1), 2.0e8), 1.05),
+               pkg.ShiftedEOS(pkg.IdealGas(0.4, 7.16e6), 1.0e9),
+               pkg.BilinearRampEOS(pkg.closure.set_eos_3mat_analytic()[0], 8.0, 1.0e10, 4.0e10,
+                                   1.05)]
+        rho0 = (8.93 / 1.05, 1.0e-2, 8.93)
+    nm, T0 = 3, 600.0
+    for n in (1, 33, 4097, (1 << 15) + 3):
+        vf = W.pte_vfracs(n, nmat=nm)
+        rho = np.tile(np.array(rho0), (n, 1)) * \
+            (0.9 + 0.2 * pkg.rng.uniform_np(57, 0, n * nm).reshape(n, nm))
+        sie = torch.empty((n, nm), dtype=torch.float64, device="cuda")
+        col = torch.empty(n, dtype=torch.float64, device="cuda")
+        for m in range(nm):
+            lam_m = dev(np.full((n, 2), np.nan)) if g_l[m].nlambda() else None
+            g_l[m].InternalEnergyFromDensityTemperature(dev(rho[:, m].copy()),
+                                                        dev(np.full(n, T0)), col, n, lam_m)
+            sie[:, m] = col
+        st_h = [np.ascontiguousarray(a) for a in (rho, vf, sie.cpu().numpy(),
+                                                  np.full((n, nm), T0), np.zeros((n, nm)))]
+        outs = {}
+        for variant in ("percell", "sm"):
+            monkeypatch.setenv("SGX_PTE_KERNEL", variant)
+            st_d = [dev(a) for a in st_h]
+            lam_d = dev(np.full((n, nm, 3), np.nan))
+            status = torch.zeros(n, dtype=torch.int64, device="cuda")
+            resid = torch.zeros(n, dtype=torch.float64, device="cuda")
+            stats = torch.zeros(L.PTE_NSTATS, dtype=torch.int64, device="cuda")
+            pkg.closure.pte_solve(L.PTE_RHOT, g_l, *st_d, params=pkg.closure.MixParams(),
+                                  status=status, residual=resid, stats=stats, lambdas=lam_d)
+            torch.cuda.synchronize()
+            outs[variant] = [a.cpu().numpy() for a in st_d] + [
+                status.cpu().numpy(), resid.cpu().numpy(), lam_d.cpu().numpy(),
+                stats.cpu().numpy()]
+        names = ("rho", "vfrac", "sie", "temp", "press", "status", "residual", "lambda", "stats")
+        for a, b, nm_ in zip(outs["percell"], outs["sm"], names):
+            assert a.tobytes() == b.tobytes(), f"{mix} n={n}: {nm_} differs between kernels"
+        assert (outs["sm"][5] & 1).mean() > 0.9
