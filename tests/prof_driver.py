@@ -85,3 +85,28 @@ if what in ("pte", "all"):
     n_save = n; n = npte
     timed("pte_rhot[" + os.environ.get("SGX_PTE_KERNEL", "sm") + "]", pte)
     n = n_save
+if what in ("ptetab",):
+    # tabulated mixture (Spiner Cu + IdealGas + Gruneisen) with per-material lambda caches
+    npte = 1 << (lg - 4)
+    g_t = [rt, pkg.IdealGas(0.4, 7.16e6), pkg.closure.set_eos_3mat_analytic()[0]]
+    rho0 = torch.tensor([8.93, 1.0e-2, 8.93], dtype=torch.float64, device=dev)
+    rho_t = (rho0.repeat(npte, 1) * (0.9 + 0.2 * pkg.rng.uniform_torch(57, 0, npte * 3, dev).reshape(npte, 3))).contiguous()
+    T_t = torch.full((npte,), 600.0, dtype=torch.float64, device=dev)
+    sie_t = torch.empty((npte, 3), dtype=torch.float64, device=dev)
+    col = torch.empty(npte, dtype=torch.float64, device=dev)
+    for m, em in enumerate(g_t):
+        if m == 0:
+            em.InternalEnergyFromDensityTemperature(rho_t[:, m].contiguous(), T_t, col, npte, torch.full((npte, 2), float("nan"), dtype=torch.float64, device=dev))
+        else:
+            em.InternalEnergyFromDensityTemperature(rho_t[:, m].contiguous(), T_t, col, npte)
+        sie_t[:, m] = col
+    t0_ = [rho_t, W.pte_vfracs(npte, start=0, xp=torch, device=dev, nmat=3), sie_t,
+           torch.full((npte, 3), 600.0, dtype=torch.float64, device=dev), torch.zeros((npte, 3), dtype=torch.float64, device=dev)]
+    ts_ = [a.clone() for a in t0_]
+    lam_t = torch.full((npte, 3, 3), float("nan"), dtype=torch.float64, device=dev)
+    def ptetab():
+        for a, b in zip(ts_, t0_): a.copy_(b)
+        pkg.closure.pte_solve(L.PTE_RHOT, g_t, *ts_, params=pkg.closure.MixParams(), lambdas=lam_t)
+    n_save = n; n = npte
+    timed("pte_rhot_tabulated[" + os.environ.get("SGX_PTE_KERNEL", "sm") + "]", ptetab)
+    n = n_save
