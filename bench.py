@@ -478,6 +478,37 @@ def run_ours(args):
                           "Gruneisen"],
             "kernel": "pte_rhot_sm_kernel<3, TabEosT<false>> (lane-refill state machine, per-lane caches)"}
         del t0_, ts_, stt, lam_t, sie_t, rho_t
+        # the get_sg_eos batch driver, (rho, e) input, on HOST arrays in and out
+        # (the reference's memory contract: it mirrors every array to the device and back)
+        nsg = 1 << 20
+
+        def e_gpu(m, rho_col, T_col):
+            o = torch.empty(rho_col.size, dtype=torch.float64, device=dev)
+            g3[m].InternalEnergyFromDensityTemperature(
+                torch.from_numpy(rho_col).to(dev), torch.from_numpy(T_col).to(dev), o,
+                rho_col.size)
+            return o.cpu().numpy()
+        a0, offs = sg_eos_inputs(pkg, nsg, e_gpu)
+        t_sg = []
+        for k in range(5):
+            a1 = {kk: vv.copy(order="K") for kk, vv in a0.items()}
+            if dist is not None:
+                dist.barrier()
+            t0 = time.perf_counter()
+            pkg.closure.get_sg_eos(g3, [1, 2, 3], offs, **a1, input_int=1, mass_frac_cutoff=1e-8)
+            dt = time.perf_counter() - t0
+            if dist is not None:
+                tt = torch.tensor([dt], dtype=torch.float64, device=dev)
+                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+                dt = float(tt.item())
+            if k >= 2:
+                t_sg.append(dt)
+        results["get_sg_eos_rho_e_3mat_host"] = {
+            "cells_per_s": nsg * world / float(np.median(t_sg)), "cells_per_gpu": nsg,
+            "temp_eV_mean": float(a1["temp"].mean()),
+            "api": "sgx_get_sg_eos: host arrays in and out, 1 launch of get_sg_eos_kernel<rho_e>; "
+                   "2 warm-up + 3 timed calls, median, max over ranks"}
+        del a0, a1
         # e2e for config 5: host buffers through sgx_pte_solve_host (chunked, 3 streams)
         npe = min(npte, 1 << 22)
         hst0 = [a[:npe].cpu() for a in state0]
@@ -630,6 +661,26 @@ def baseline_ref():
                  "g++ -O2; PTE 3x3 solves through Eigen")
 
 
+def sg_eos_inputs(pkg, ncell, e_of):
+    """Inputs of get_sg_eos (rho, e) for the test/test_pte.cpp mixture (Gruneisen / DavisReactants /
+    DavisProducts): ncell cells, three materials each, cell_dim = ncell, identity offsets.
+    e_of(m, rho, T) -> specific internal energies of material m (numpy)."""
+    W = pkg.workloads
+    vf = W.pte_vfracs(ncell)
+    rho = np.array(W.PTE_RHO)[None, :] * (0.95 + 0.1 * pkg.rng.uniform_np(91, 0, ncell * 3)
+                                           .reshape(ncell, 3))
+    T0 = np.full(ncell, float(W.PTE_T))
+    e_m = np.stack([e_of(m, rho[:, m].copy(), T0) for m in range(3)], axis=1)
+    mass = rho * vf
+    msum = mass.sum(axis=1)
+    a = dict(press=np.zeros(ncell), pmax=np.full(ncell, -1e300), vol=np.ones(ncell),
+             spvol=1.0 / msum, sie=(mass * e_m).sum(axis=1) / msum, temp=np.zeros(ncell),
+             bmod=np.zeros(ncell), dpde=np.zeros(ncell), cv=np.zeros(ncell),
+             frac_mass=np.asfortranarray(mass / msum[:, None]),
+             frac_vol=np.zeros((ncell, 3), order="F"), frac_ie=np.zeros((ncell, 3), order="F"))
+    return a, (np.arange(ncell, dtype=np.int32) + 1)
+
+
 def cpu_baseline(pkg, raw, sample, reps):
     """The reference's own code (oracle/_ref) on the host cores, bounded sample of the headline
     workload.  This is the checker being *timed*, never part of the product path."""
@@ -723,6 +774,24 @@ def cpu_baseline(pkg, raw, sample, reps):
         out["other_configs_Gcells_per_s"] = other
     except Exception as exc:
         out["other_configs_error"] = repr(exc)
+    # the reference's own get_sg_eos (Kokkos build only) on a 2^18-cell sample of the same inputs
+    try:
+        if ref.lib.ref_is_kokkos():
+            r3 = ref.set_eos_3mat()
+            nsg = 1 << 18
+            a0, offs = sg_eos_inputs(
+                pkg, nsg, lambda m, r_, t_: r3[m].eval(L.E_FROM_RHO_T, r_, t_, nthreads=cores))
+            tsg = []
+            for k in range(4):
+                a1 = {kk: vv.copy(order="K") for kk, vv in a0.items()}
+                t0 = time.perf_counter()
+                ref.get_sg_eos(r3, [1, 2, 3], offs, **a1, input_int=1, mass_frac_cutoff=1e-8)
+                if k >= 1:
+                    tsg.append(time.perf_counter() - t0)
+            out["get_sg_eos_rho_e_cells_per_s"] = nsg / float(np.median(tsg))
+            out["get_sg_eos_sample"] = f"{nsg} cells, 1 warm-up + 3 timed calls, median, {cores} threads"
+    except Exception as exc:
+        out["get_sg_eos_error"] = repr(exc)
     return out
 
 
