@@ -1112,6 +1112,13 @@ int sgx_PressureEnergyFromDensityTemperature(sgx_eos_t e, const double *rhos,
   }
 }
 
+extern "C++" {
+namespace sgx {
+int launch_mod_fill(sgx_eos_s *e, double *rho, double *T, double *en, double *P, double *cv,
+                    double *bmod, int64_t n, unsigned long output, double *lambda, int ls,
+                    cudaStream_t s);
+}
+}
 int sgx_FillEos(sgx_eos_t e, double *rhos, double *temps, double *energies, double *presses,
                 double *cvs, double *bmods, int64_t n, unsigned long output, double *lambda,
                 int ls, sgx_stream_t stream) {
@@ -1146,6 +1153,15 @@ int sgx_FillEos(sgx_eos_t e, double *rhos, double *temps, double *energies, doub
   case SGX_EOS_HELMHOLTZ:
     return launch_helm_fill(e, rhos, temps, energies, presses, cvs, bmods, n, output, lambda,
                             ls, s);
+  case SGX_EOS_MODIFIED: { // the wrappers' FillEos (csrc/sgx_modifiers.cu)
+    const unsigned long inner = (e->mod.flags & kModRamp) ? (output & ~(unsigned long)TQ_PRESSURE)
+                                                           : output;
+    if (inner != 0)
+      if (const char *why = fill_mask_error(e->base->kind, inner))
+        return fail(SGX_ERR_UNSUPPORTED, "%s", why);
+    return launch_mod_fill(e, rhos, temps, energies, presses, cvs, bmods, n, output, lambda, ls,
+                           s);
+  }
   default:
     return fail(SGX_ERR_INVALID, "bad EOS kind %d", e->kind);
   }
