@@ -1,6 +1,18 @@
 // get_sg_eos host entry points (the kernel: sgx_get_sg_eos.cuh; its three input modes are
 // instantiated in sgx_get_sg_eos_rho_e.cu, _rho_t.cu, _p_t.cu).
+#include <cstdlib>
+#include <cstring>
+
 #include "sgx_get_sg_eos.cuh"
+
+namespace sgx {
+int launch_pte_tab_rhot_sm_mod(const EosSet &set, const MixParamsDev &prm, double *rho,
+                               double *vfrac, double *sie, double *temp, double *press,
+                               const double *sie_tot, const double *vfrac_tot,
+                               const double *Tguess, uint64_t *status, double *residual,
+                               uint64_t *stats, int64_t ncell, cudaStream_t s, double *lambda,
+                               const unsigned char *skip);
+}
 
 using namespace sgx;
 using namespace sgx::sg;
@@ -76,8 +88,61 @@ int sgx_get_sg_eos_device(int nmat, int ncell, int cell_dim, int input_int,
     launch_get_sg_eos_rho_t(set, prm, A, c, st);
   else if (input_int == kPT)
     launch_get_sg_eos_p_t(set, prm, A, c, st);
-  else
+  else {
+    // (rho, e): cells in which every material participates -- the usual mixed cell -- go through
+    // the lane-refill state machine; SGX_SG_EOS_KERNEL=percell solves every cell in the one
+    // thread-per-cell kernel as before (same results).
+    const char *v = getenv("SGX_SG_EOS_KERNEL");
+    const bool staged = nmat >= 2 && nmat <= 4 && !(v && strcmp(v, "percell") == 0);
+    char *scratch = nullptr;
+    if (staged) {
+      const size_t nc = (size_t)ncell, nf = nc * (size_t)nmat;
+      // 5 state arrays + lambda caches [ncell][nmat][3] + sie_tot, vfrac_tot, zero Tguess,
+      // status words, skip bytes
+      const size_t doubles = 5 * nf + 3 * nf + 3 * nc;
+      const size_t bytes = doubles * sizeof(double) + nc * sizeof(unsigned long long) +
+                           ((nc + 255) & ~size_t(255));
+      SGX_CUDA_OK(scratch_alloc_async(reinterpret_cast<void **>(&scratch), bytes, st));
+      double *p = reinterpret_cast<double *>(scratch);
+      double *s_rho = p, *s_vf = p + nf, *s_sie = p + 2 * nf, *s_temp = p + 3 * nf,
+             *s_press = p + 4 * nf, *lam = p + 5 * nf, *sie_tot = p + 8 * nf,
+             *vfrac_tot = p + 8 * nf + nc, *Tzero = p + 8 * nf + 2 * nc;
+      unsigned long long *status = reinterpret_cast<unsigned long long *>(p + 8 * nf + 3 * nc);
+      unsigned char *skip = reinterpret_cast<unsigned char *>(status + nc);
+      cudaError_t err = cudaMemsetAsync(lam, 0, 3 * nf * sizeof(double), st); // zeroed caches
+      if (err == cudaSuccess) err = cudaMemsetAsync(Tzero, 0, nc * sizeof(double), st);
+      if (err != cudaSuccess) {
+        cudaFreeAsync(scratch, st);
+        return fail(SGX_ERR_CUDA, "get_sg_eos: %s", cudaGetErrorString(err));
+      }
+      const LaunchCfg cp = stream_cfg(ncell, 256, 8);
+      get_sg_eos_prep_kernel<<<cp.blocks, cp.threads, 0, st>>>(A, skip, s_rho, s_vf, s_sie, s_temp,
+                                                               s_press, sie_tot, vfrac_tot);
+      // the solver's materials in participation order = the caller's material order
+      EosSet set2;
+      set2.nmat = nmat;
+      for (int m = 0; m < nmat; ++m) {
+        set2.e[m] = set.e[A.eos_idx[m]];
+        set2.mod[m] = set.mod[A.eos_idx[m]];
+      }
+      // Tguess = 0: PTESolverRhoT is constructed without a guess there (get_sg_eos_rho_e.cpp:
+      // 61-64), so GetTguess starts from default_tguess
+      const int rc = launch_pte_tab_rhot_sm_mod(
+          set2, prm, s_rho, s_vf, s_sie, s_temp, s_press, sie_tot, vfrac_tot, Tzero,
+          reinterpret_cast<uint64_t *>(status), nullptr, nullptr, ncell, st, lam, skip);
+      if (rc != SGX_OK) {
+        cudaFreeAsync(scratch, st);
+        return rc;
+      }
+      A.pre_skip = skip;
+      A.pre_rho = s_rho, A.pre_vfrac = s_vf, A.pre_sie = s_sie, A.pre_temp = s_temp;
+      A.pre_press = s_press;
+      A.pre_status = status;
+      count_launch(1);
+    }
     launch_get_sg_eos_rho_e(set, prm, A, c, st);
+    if (scratch) cudaFreeAsync(scratch, st);
+  }
   count_launch();
   SGX_CUDA_OK(cudaGetLastError());
   return SGX_OK;

@@ -42,7 +42,58 @@ struct SgArgs {
   double *frac_mass, *frac_vol, *frac_ie, *frac_bmod, *frac_dpde, *frac_cv;
   double mass_frac_cutoff;
   int *nfail; // cells whose PTE solve did not converge (or whose participant count is not built)
+  // (rho, e) mode, staged form: cells in which EVERY material participates are solved by the
+  // lane-refill state machine (sgx_pte_tab_sm_mod.cu) between a prep and this kernel; pre_skip
+  // [iloop] != 0 marks the cells that were not (solved here as before).  Null: solve all here.
+  const unsigned char *pre_skip = nullptr;
+  const double *pre_rho = nullptr, *pre_vfrac = nullptr, *pre_sie = nullptr, *pre_temp = nullptr,
+               *pre_press = nullptr; // [ncell][nmat] by loop index, as the solver left them
+  const unsigned long long *pre_status = nullptr;
 };
+
+// Stages the full cells of the (rho, e) mode for the state machine: init_functor's arithmetic
+// (get_sg_eos_functors.hpp:66-121 with t_mult = 0, s_mult = 1, p_mult = 0) on LOCAL copies --
+// the caller's arrays are written by the finishing kernel only, exactly once.
+static __global__ void __launch_bounds__(256)
+    get_sg_eos_prep_kernel(const __grid_constant__ SgArgs A, unsigned char *__restrict__ skip,
+                           double *__restrict__ s_rho, double *__restrict__ s_vfrac,
+                           double *__restrict__ s_sie, double *__restrict__ s_temp,
+                           double *__restrict__ s_press, double *__restrict__ sie_tot,
+                           double *__restrict__ vfrac_tot) {
+  const int nmat = A.nmat;
+  const int64_t cd = A.cell_dim;
+  for (int iloop = blockIdx.x * blockDim.x + threadIdx.x; iloop < A.ncell;
+       iloop += gridDim.x * blockDim.x) {
+    const int64_t i = A.offsets[iloop] - 1;
+    double fm[kMaxMat];
+    double mass_sum = 0.0;
+    for (int m = 0; m < nmat; ++m)
+      mass_sum += A.frac_mass[i + cd * m];
+    int npte = 0;
+    for (int m = 0; m < nmat; ++m) {
+      fm[m] = A.frac_mass[i + cd * m] / mass_sum;
+      if (fm[m] > A.mass_frac_cutoff) npte += 1;
+    }
+    if (npte != nmat) {
+      skip[iloop] = 1;
+      continue;
+    }
+    skip[iloop] = 0;
+    double vfrac_sum = 0.;
+    const int64_t base = (int64_t)iloop * nmat;
+    for (int m = 0; m < nmat; ++m) {
+      const double vf = fm[m];
+      vfrac_sum += vf;
+      s_vfrac[base + m] = vf;
+      s_rho[base + m] = fm[m] / A.spvol[i] / vf;
+      s_temp[base + m] = A.temp[i] * kEv2K * 0.0;
+      s_press[base + m] = A.press[i] * 0.0;
+      s_sie[base + m] = A.sie[i] * fm[m] * 1.0;
+    }
+    sie_tot[iloop] = A.sie[i];
+    vfrac_tot[iloop] = vfrac_sum;
+  }
+}
 
 template <int NM>
 __device__ bool solve_rhot(TabEos &eos, const MixParamsDev &prm, const double vfrac_sum,
@@ -262,7 +313,18 @@ __global__ void __launch_bounds__(128)
       A.pmax[i] = A.press[i] > A.pmax[i] ? A.press[i] : A.pmax[i];
       continue;
     }
-    if (npte > 1) {
+    if (npte > 1 && A.pre_skip && !A.pre_skip[iloop]) { // solved by the state machine
+      const int64_t pb = (int64_t)iloop * nmat;
+      for (int mp = 0; mp < npte; ++mp) {
+        rho_pte[mp] = A.pre_rho[pb + mp];
+        vfrac_pte[mp] = A.pre_vfrac[pb + mp];
+        sie_pte[mp] = A.pre_sie[pb + mp];
+        temp_pte[mp] = A.pre_temp[pb + mp];
+        press_pte[mp] = A.pre_press[pb + mp];
+      }
+      pte_converged = (A.pre_status[iloop] & 1ull) != 0;
+      if (!pte_converged && A.nfail) atomicAdd(A.nfail, 1);
+    } else if (npte > 1) {
       switch (npte) {
       case 2:
         pte_converged = solve_rhot<2>(eos, prm, vfrac_sum, A.sie[i], rho_pte, vfrac_pte, sie_pte,

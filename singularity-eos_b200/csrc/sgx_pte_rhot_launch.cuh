@@ -22,7 +22,7 @@ inline int launch_sm(const EosSet &set, const MixParamsDev &prm, double *rho, do
                      double *sie, double *temp, double *press, const double *sie_tot,
                      const double *vfrac_tot, const double *Tguess, uint64_t *status,
                      double *residual, uint64_t *stats, int64_t ncell, cudaStream_t s,
-                     double *lambda = nullptr) {
+                     double *lambda = nullptr, const unsigned char *skip = nullptr) {
   const int64_t chunk = ncell < kPteChunk ? ncell : kPteChunk;
   const int64_t nchunk = (ncell + chunk - 1) / chunk;
   const size_t cursor_bytes = ((size_t)nchunk * sizeof(unsigned long long) + 255) & ~size_t(255);
@@ -52,7 +52,8 @@ inline int launch_sm(const EosSet &set, const MixParamsDev &prm, double *rho, do
         sie_tot ? sie_tot + c0 : nullptr, vfrac_tot ? vfrac_tot + c0 : nullptr, init,
         status ? reinterpret_cast<unsigned long long *>(status) + c0 : nullptr,
         residual ? residual + c0 : nullptr, reinterpret_cast<unsigned long long *>(stats), n,
-        cursors + k, lambda ? lambda + c0 * NM * (Acc::kCacheSlots > 0 ? Acc::kCacheSlots : 1) : nullptr);
+        cursors + k, lambda ? lambda + c0 * NM * (Acc::kCacheSlots > 0 ? Acc::kCacheSlots : 1) : nullptr,
+        skip ? skip + c0 : nullptr);
     count_launch(2);
     err = cudaGetLastError();
   }

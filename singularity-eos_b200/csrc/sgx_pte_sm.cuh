@@ -497,7 +497,8 @@ __global__ void __launch_bounds__(THREADS, MINB)
                        unsigned long long *__restrict__ status, double *__restrict__ residual,
                        unsigned long long *__restrict__ stats, const int64_t ncell,
                        unsigned long long *__restrict__ cursor,
-                       double *__restrict__ lambda = nullptr) {
+                       double *__restrict__ lambda = nullptr,
+                       const unsigned char *__restrict__ skip = nullptr) {
   __shared__ unsigned int s_hist[SGX_PTE_NSTATS];
   if (stats) {
     for (int k = threadIdx.x; k < SGX_PTE_NSTATS; k += blockDim.x)
@@ -566,7 +567,9 @@ __global__ void __launch_bounds__(THREADS, MINB)
       }
       if (idle) {
         const int64_t mine = (int64_t)first + __popc(idle_mask & ((1u << lane) - 1u));
-        if (mine < ncell) {
+        // skip[]: cells the caller solves elsewhere (get_sg_eos: cells whose participating
+        // materials are fewer than NM); the lane stays idle and draws again next round
+        if (mine < ncell && !(skip && skip[mine])) {
           cell = mine;
           const int64_t base = cell * NM;
 #pragma unroll
@@ -596,7 +599,7 @@ __global__ void __launch_bounds__(THREADS, MINB)
       }
     }
     // block-wide round barrier; also the termination vote
-    if (!__syncthreads_or(L.phase != mix::PH_IDLE)) break;
+    if (!__syncthreads_or(L.phase != mix::PH_IDLE || !exhausted)) break;
     const bool hold = (L.phase == mix::PH_J) && (r % 2u != 0u); // wait for the Newton beat
     if (L.wants_eval() && !hold)
       mix::eval_round<NM>(eos, L.mode, L.Tq, L.Tq2, L.rq, L.s.rho, L.s.rhobar, L.cache, eq,

@@ -24,8 +24,8 @@ namespace sgx {
 int launch_pte_tab_fixedt(SGX_TAB_PARAMS);
 int launch_pte_tab_pt(SGX_TAB_PARAMS);
 int launch_pte_tab_rhot_plain(SGX_TAB_PARAMS);
-int launch_pte_tab_rhot_sm_plain(SGX_TAB_PARAMS);
-int launch_pte_tab_rhot_sm_mod(SGX_TAB_PARAMS);
+int launch_pte_tab_rhot_sm_plain(SGX_TAB_PARAMS, const unsigned char *skip);
+int launch_pte_tab_rhot_sm_mod(SGX_TAB_PARAMS, const unsigned char *skip);
 
 int launch_pte_tab(int solver, const EosSet &set, const MixParamsDev &prm, double *rho,
                    double *vfrac, double *sie, double *temp, double *press,
@@ -42,8 +42,8 @@ int launch_pte_tab(int solver, const EosSet &set, const MixParamsDev &prm, doubl
   const char *variant = getenv("SGX_PTE_KERNEL"); // read per call: the tests switch it
   const bool percell = variant && strcmp(variant, "percell") == 0;
   if (solver == SGX_PTE_RHOT && !percell && set.nmat >= 1 && set.nmat <= 4)
-    return modified ? launch_pte_tab_rhot_sm_mod(SGX_TAB_ARGS)
-                    : launch_pte_tab_rhot_sm_plain(SGX_TAB_ARGS);
+    return modified ? launch_pte_tab_rhot_sm_mod(SGX_TAB_ARGS, nullptr)
+                    : launch_pte_tab_rhot_sm_plain(SGX_TAB_ARGS, nullptr);
   if (solver == SGX_PTE_RHOT && !modified && set.nmat >= 1 && set.nmat <= 4)
     return launch_pte_tab_rhot_plain(SGX_TAB_ARGS);
   if (solver == SGX_PTE_RHOT) {

@@ -10,10 +10,10 @@ namespace sgx {
 int launch_pte_tab_rhot_sm_plain(const EosSet &set, const MixParamsDev &prm, double *rho, double *vfrac, double *sie,
          double *temp, double *press, const double *sie_tot, const double *vfrac_tot,
          const double *Tguess, uint64_t *status, double *residual, uint64_t *stats,
-         int64_t ncell, cudaStream_t s, double *lambda) {
+         int64_t ncell, cudaStream_t s, double *lambda, const unsigned char *skip) {
 #define SGX_ARGS                                                                           \
   set, prm, rho, vfrac, sie, temp, press, sie_tot, vfrac_tot, Tguess, status, residual,    \
-      stats, ncell, s, lambda
+      stats, ncell, s, lambda, skip
   raise_stack_limit_once();
   switch (set.nmat) {
   case 1:

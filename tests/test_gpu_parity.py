@@ -1719,3 +1719,54 @@ def test_pte_tab_state_machine_equals_percell_kernel(pkg, torch_cuda, raw1, monk
         for a, b, nm_ in zip(outs["percell"], outs["sm"], names):
             assert a.tobytes() == b.tobytes(), f"{mix} n={n}: {nm_} differs between kernels"
         assert (outs["sm"][5] & 1).mean() > 0.9
+
+
+def test_get_sg_eos_staged_equals_percell(pkg, torch_cuda, raw1, monkeypatch):
+    """get_sg_eos (rho, e): cells in which every material participates are solved by the
+    lane-refill state machine between a prep and a finishing kernel; SGX_SG_EOS_KERNEL=percell
+    solves every cell in the one thread-per-cell kernel.  Same arithmetic per cell: every output
+    array bit-identical, on a mixture with a tabulated material, cells with 3, 2 and 1
+    participants, cell_dim > ncell and permuted offsets."""
+    L, W = pkg._lib, pkg.workloads
+    g_l = [pkg.SpinerEOSDependsRhoT(raw1), pkg.IdealGas(0.4, 7.16e6),
+           pkg.closure.set_eos_3mat_analytic()[0]]
+    nmat, ncell, cell_dim = 3, 3000, 3011
+    rng = np.random.default_rng(5)
+    offsets = (rng.permutation(cell_dim)[:ncell] + 1).astype(np.int32)
+    vf = W.pte_vfracs(cell_dim, nmat=nmat)
+    kind = np.arange(cell_dim) % 6
+    vf[kind == 1, 2] = 0.0
+    vf[kind == 3, 0] = 0.0
+    vf[kind == 5, 1:] = 0.0
+    vf /= vf.sum(axis=1, keepdims=True)
+    rho = np.array([8.93, 1.0e-2, 8.93])[None, :] * (0.95 + 0.1 * rng.random((cell_dim, nmat)))
+    mass = rho * vf
+    msum = mass.sum(axis=1)
+    # energies of a 700 K state, from the library itself (this test compares two of its paths)
+    import torch
+    e_m = np.empty((cell_dim, nmat))
+    for m in range(nmat):
+        o = torch.empty(cell_dim, dtype=torch.float64, device="cuda")
+        lam = dev(np.full((cell_dim, 2), np.nan)) if g_l[m].nlambda() else None
+        g_l[m].InternalEnergyFromDensityTemperature(dev(rho[:, m].copy()),
+                                                    dev(np.full(cell_dim, 700.0)), o, cell_dim, lam)
+        e_m[:, m] = o.cpu().numpy()
+    outs = {}
+    for variant in ("percell", "staged"):
+        monkeypatch.setenv("SGX_SG_EOS_KERNEL", variant)
+        a = dict(press=np.zeros(cell_dim), pmax=np.full(cell_dim, -1e300), vol=np.ones(cell_dim),
+                 spvol=1.0 / msum, sie=(mass * e_m).sum(axis=1) / msum, temp=np.zeros(cell_dim),
+                 bmod=np.zeros(cell_dim), dpde=np.zeros(cell_dim), cv=np.zeros(cell_dim),
+                 frac_mass=np.asfortranarray(mass / msum[:, None]),
+                 frac_vol=np.zeros((cell_dim, nmat), order="F"),
+                 frac_ie=np.zeros((cell_dim, nmat), order="F"),
+                 frac_bmod=np.zeros((cell_dim, nmat), order="F"),
+                 frac_dpde=np.zeros((cell_dim, nmat), order="F"),
+                 frac_cv=np.zeros((cell_dim, nmat), order="F"))
+        pkg.closure.get_sg_eos(g_l, [1, 2, 3], offsets, **a, input_int=1, mass_frac_cutoff=1e-8)
+        outs[variant] = a
+    idx = offsets - 1
+    assert (outs["staged"]["temp"][idx] > 0).all()
+    for k in outs["percell"]:
+        assert outs["percell"][k].tobytes() == outs["staged"][k].tobytes(), \
+            f"get_sg_eos {k} differs between the staged and the per-cell path"
