@@ -149,9 +149,6 @@ int sgx_pte_solve_cached(int solver, const sgx_eos_t *eos, int nmat, int64_t nce
       return fail(SGX_ERR_UNSUPPORTED, "PTE: material %d is EOS kind %d (Helmholtz mixtures are "
                   "not built)", m, eos[m]->kind);
   }
-  if (tabulated && (solver == SGX_PTE_RHOU || solver == SGX_PTE_FIXED_P))
-    return fail(SGX_ERR_UNSUPPORTED,
-                "PTESolverRhoU / PTESolverFixedP with tabulated or modified materials are not built");
   if (lambda && !tabulated) lambda = nullptr; // the analytic models take no lambda
   bool any_lambda_user = false;
   for (int m = 0; m < nmat; ++m)

@@ -1,8 +1,9 @@
 // PTE solves for mixtures that hold tabulated materials (SpinerEOSDependsRhoT / RhoSie next to
 // the analytic models): the per-cell kernels instantiated on the TabEos accessor
 // (sgx_pte_tab.cuh), with the per-material lambda caches of the reference's CacheAccessor.
-// PTESolverRhoT, PTESolverFixedT (1..4 materials) and PTESolverPT (2..3 materials); the three
-// solver families compile in three translation units (this one: the dispatcher and RhoT).
+// PTESolverRhoT, PTESolverFixedT (1..4 materials), PTESolverPT, PTESolverRhoU (2..3) and
+// PTESolverFixedP (1..3); every solver family compiles in a translation unit of its own (this
+// one: the dispatcher and RhoT).
 #include <cstdlib>
 #include <cstring>
 
@@ -23,6 +24,8 @@ namespace sgx {
 
 int launch_pte_tab_fixedt(SGX_TAB_PARAMS);
 int launch_pte_tab_pt(SGX_TAB_PARAMS);
+int launch_pte_tab_rhou(SGX_TAB_PARAMS);
+int launch_pte_tab_fixedp(SGX_TAB_PARAMS);
 int launch_pte_tab_rhot_plain(SGX_TAB_PARAMS);
 int launch_pte_tab_rhot_sm_plain(SGX_TAB_PARAMS, const unsigned char *skip);
 int launch_pte_tab_rhot_sm_mod(SGX_TAB_PARAMS, const unsigned char *skip);
@@ -34,6 +37,8 @@ int launch_pte_tab(int solver, const EosSet &set, const MixParamsDev &prm, doubl
                    cudaStream_t s, double *lambda) {
   if (solver == SGX_PTE_FIXED_T) return launch_pte_tab_fixedt(SGX_TAB_ARGS);
   if (solver == SGX_PTE_PT) return launch_pte_tab_pt(SGX_TAB_ARGS);
+  if (solver == SGX_PTE_RHOU) return launch_pte_tab_rhou(SGX_TAB_ARGS);
+  if (solver == SGX_PTE_FIXED_P) return launch_pte_tab_fixedp(SGX_TAB_ARGS);
   bool modified = false;
   for (int m = 0; m < set.nmat; ++m)
     modified = modified || set.mod[m].flags != 0;
@@ -62,7 +67,7 @@ int launch_pte_tab(int solver, const EosSet &set, const MixParamsDev &prm, doubl
   }
   return fail(SGX_ERR_UNSUPPORTED,
               "PTE with tabulated materials: solver %d with %d materials is not instantiated "
-              "(RhoT / FixedT: 1..4, PT: 2..3)", solver, set.nmat);
+              "(RhoT / FixedT: 1..4, PT / RhoU: 2..3, FixedP: 1..3)", solver, set.nmat);
 }
 
 } // namespace sgx

@@ -869,7 +869,7 @@ def test_pte_pt_parity(pkg, ref, torch_cuda, which):
                      tol=PTE_TOL, what="PT/" + which, strict_flags=True)
 
 
-@pytest.mark.parametrize("solver_name", ["RhoT", "FixedT", "PT"])
+@pytest.mark.parametrize("solver_name", ["RhoT", "FixedT", "PT", "RhoU", "FixedP"])
 @pytest.mark.parametrize("mix", ["spiner+ideal+gruneisen", "spiner+ideal", "rhosie+ideal+davis",
                                  "spiner(vapor dome)+ideal"])
 def test_pte_tabulated_materials(pkg, ref, torch_cuda, raw1, mix, solver_name):
@@ -911,9 +911,22 @@ def test_pte_tabulated_materials(pkg, ref, torch_cuda, raw1, mix, solver_name):
                     for m in range(nm)], axis=1)
     st_h = [np.ascontiguousarray(a) for a in (rho, vf, sie, np.full((n, nm), T0),
                                               np.zeros((n, nm)))]
-    solver = {"RhoT": L.PTE_RHOT, "FixedT": L.PTE_FIXED_T, "PT": L.PTE_PT}[solver_name]
+    solver = {"RhoT": L.PTE_RHOT, "FixedT": L.PTE_FIXED_T, "PT": L.PTE_PT, "RhoU": L.PTE_RHOU,
+              "FixedP": L.PTE_FIXED_P}[solver_name]
     Tfix = 550.0 + 200.0 * pkg.rng.uniform_np(58, 0, n) if solver_name == "FixedT" else None
     prm = pkg.closure.MixParams()
+    min_conv = 0.95
+    if solver_name == "FixedP":
+        # the given pressures: each cell's own PTE pressure (the reference's RhoT solve) +-5 %;
+        # iterate_t_guess = false, where the reference's answer is defined.  From
+        # the fixed 600 K guess the reference itself converges on 31-49 % of these cells; the
+        # cells it gives up on must be given up on identically (status words incl. niter)
+        eq = [a.copy() for a in st_h]
+        ref.pte_solve(L.PTE_RHOT, r_l, *eq, ref.mix_params_default(),
+                      lambdas=np.full((n, nm, 3), np.nan))
+        Tfix = eq[4][:, 0] * (1.0 + 0.1 * (pkg.rng.uniform_np(92, 0, n) - 0.5))
+        prm = pkg.closure.MixParams(iterate_t_guess=0)
+        min_conv = 0.3
     lam_r = np.full((n, nm, 3), np.nan)
     st_r = [a.copy() for a in st_h]
     status_r, res_r, _ = ref.pte_solve(solver, r_l, *st_r, prm, Tguess=Tfix, lambdas=lam_r)
@@ -926,7 +939,7 @@ def test_pte_tabulated_materials(pkg, ref, torch_cuda, raw1, mix, solver_name):
     torch.cuda.synchronize()
     got = status.cpu().numpy().view(np.uint64)
     conv = (status_r & 1).astype(bool)
-    assert conv.mean() > 0.95, f"reference converged on only {conv.mean():.3f} of the cells"
+    assert conv.mean() > min_conv, f"reference converged on only {conv.mean():.3f} of the cells"
     same = got == status_r
     assert same.all(), (f"{mix}/{solver_name}: SolverStatus differs on {int((~same).sum())} cells; "
                         f"first: got {pkg.closure.decode_status(got[~same][:1])} want "
@@ -1614,7 +1627,7 @@ def test_modifiers_refuse_what_they_do_not_serve(pkg, torch_cuda, helm_table):
         pkg.BilinearRampEOS(pkg.IdealGas(0.4, 7.16e6), 1.0, 2.0, 2.0, 1.0)  # a == b
 
 
-@pytest.mark.parametrize("solver_name", ["RhoT", "FixedT", "PT"])
+@pytest.mark.parametrize("solver_name", ["RhoT", "FixedT", "PT", "RhoU", "FixedP"])
 def test_pte_modified_materials(pkg, ref, torch_cuda, raw1, solver_name):
     """Mixed cells whose materials carry modifiers, as the reference's default variant allows:
     ScaledEOS(ShiftedEOS(SpinerEOSDependsRhoT)) with its lambda cache, ShiftedEOS(IdealGas) and
@@ -1639,9 +1652,18 @@ def test_pte_modified_materials(pkg, ref, torch_cuda, raw1, solver_name):
                     for m in range(nm)], axis=1)
     st_h = [np.ascontiguousarray(a) for a in (rho, vf, sie, np.full((n, nm), T0),
                                               np.zeros((n, nm)))]
-    solver = {"RhoT": L.PTE_RHOT, "FixedT": L.PTE_FIXED_T, "PT": L.PTE_PT}[solver_name]
+    solver = {"RhoT": L.PTE_RHOT, "FixedT": L.PTE_FIXED_T, "PT": L.PTE_PT, "RhoU": L.PTE_RHOU,
+              "FixedP": L.PTE_FIXED_P}[solver_name]
     Tfix = 550.0 + 200.0 * pkg.rng.uniform_np(58, 0, n) if solver_name == "FixedT" else None
     prm = pkg.closure.MixParams()
+    min_conv = 0.95
+    if solver_name == "FixedP":  # as in test_pte_tabulated_materials: the reference gives up on
+        eq = [a.copy() for a in st_h]  # half of these cells, identically
+        ref.pte_solve(L.PTE_RHOT, r_l, *eq, ref.mix_params_default(),
+                      lambdas=np.full((n, nm, 3), np.nan))
+        Tfix = eq[4][:, 0] * (1.0 + 0.1 * (pkg.rng.uniform_np(92, 0, n) - 0.5))
+        prm = pkg.closure.MixParams(iterate_t_guess=0)
+        min_conv = 0.3
     lam_r = np.full((n, nm, 3), np.nan)
     st_r = [a.copy() for a in st_h]
     status_r, _, _ = ref.pte_solve(solver, r_l, *st_r, prm, Tguess=Tfix, lambdas=lam_r)
@@ -1653,7 +1675,7 @@ def test_pte_modified_materials(pkg, ref, torch_cuda, raw1, solver_name):
     torch.cuda.synchronize()
     got = status.cpu().numpy().view(np.uint64)
     conv = (status_r & 1).astype(bool)
-    assert conv.mean() > 0.95, f"reference converged on only {conv.mean():.3f} of the cells"
+    assert conv.mean() > min_conv, f"reference converged on only {conv.mean():.3f} of the cells"
     same = got == status_r
     assert same.all(), (f"modified/{solver_name}: SolverStatus differs on {int((~same).sum())} "
                         f"cells; first: got {pkg.closure.decode_status(got[~same][:1])} want "
@@ -1664,9 +1686,6 @@ def test_pte_modified_materials(pkg, ref, torch_cuda, raw1, solver_name):
     fin = np.isfinite(lam_r)
     assert (np.isfinite(lam_g) == fin).all()
     assert np.abs(lam_g[fin] - lam_r[fin]).max() <= 1e-10
-    # RhoU / FixedP are not built for such mixtures: refused, not mis-served
-    with pytest.raises(pkg.SgxError):
-        pkg.closure.pte_solve(L.PTE_RHOU, g_l, *[dev(a) for a in st_h], params=prm)
 
 
 @pytest.mark.parametrize("mix", ["tabulated", "modified"])
