@@ -18,7 +18,8 @@ SOURCES = ["sgx_api.cu", "sgx_spiner_host.cu", "sgx_pte.cu", "sgx_pte_rhot.cu", 
            "sgx_tune_lookup.cu", "sgx_modifiers.cu", "sgx_get_sg_eos_rho_e.cu",
            "sgx_get_sg_eos_rho_t.cu", "sgx_get_sg_eos_p_t.cu", "sgx_pte_tab_plain.cu",
            "sgx_pte_tab_sm.cu", "sgx_pte_tab_sm_mod.cu", "sgx_pte_tab_rhou.cu",
-           "sgx_pte_tab_fixedp.cu"]
+           "sgx_pte_tab_fixedp.cu", "sgx_pte_tab_pt4.cu", "sgx_pte_tab_rhou4.cu",
+           "sgx_pte_tab_fixedp4.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 # -fmad=false: no FMA contraction, so device arithmetic rounds like the reference's x86-64
 # build (parity contract: 1e-12 lookups, 1e-10 PTE states, identical flags).

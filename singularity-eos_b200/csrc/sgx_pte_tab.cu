@@ -1,9 +1,10 @@
 // PTE solves for mixtures that hold tabulated materials (SpinerEOSDependsRhoT / RhoSie next to
 // the analytic models): the per-cell kernels instantiated on the TabEos accessor
 // (sgx_pte_tab.cuh), with the per-material lambda caches of the reference's CacheAccessor.
-// PTESolverRhoT, PTESolverFixedT (1..4 materials), PTESolverPT, PTESolverRhoU (2..3) and
-// PTESolverFixedP (1..3); every solver family compiles in a translation unit of its own (this
-// one: the dispatcher and RhoT).
+// PTESolverRhoT, PTESolverFixedT, PTESolverFixedP (1..4 materials), PTESolverPT and
+// PTESolverRhoU (2..4); every solver family compiles in a translation unit of its own, the
+// four-material PT / RhoU / FixedP instantiations in a further one each (this one: the
+// dispatcher and RhoT).
 #include <cstdlib>
 #include <cstring>
 
@@ -26,6 +27,9 @@ int launch_pte_tab_fixedt(SGX_TAB_PARAMS);
 int launch_pte_tab_pt(SGX_TAB_PARAMS);
 int launch_pte_tab_rhou(SGX_TAB_PARAMS);
 int launch_pte_tab_fixedp(SGX_TAB_PARAMS);
+int launch_pte_tab_pt4(SGX_TAB_PARAMS);
+int launch_pte_tab_rhou4(SGX_TAB_PARAMS);
+int launch_pte_tab_fixedp4(SGX_TAB_PARAMS);
 int launch_pte_tab_rhot_plain(SGX_TAB_PARAMS);
 int launch_pte_tab_rhot_sm_plain(SGX_TAB_PARAMS, const unsigned char *skip);
 int launch_pte_tab_rhot_sm_mod(SGX_TAB_PARAMS, const unsigned char *skip);
@@ -36,6 +40,11 @@ int launch_pte_tab(int solver, const EosSet &set, const MixParamsDev &prm, doubl
                    uint64_t *status, double *residual, uint64_t *stats, int64_t ncell,
                    cudaStream_t s, double *lambda) {
   if (solver == SGX_PTE_FIXED_T) return launch_pte_tab_fixedt(SGX_TAB_ARGS);
+  if (set.nmat == 4) { // sgx_pte_tab_{pt,rhou,fixedp}4.cu
+    if (solver == SGX_PTE_PT) return launch_pte_tab_pt4(SGX_TAB_ARGS);
+    if (solver == SGX_PTE_RHOU) return launch_pte_tab_rhou4(SGX_TAB_ARGS);
+    if (solver == SGX_PTE_FIXED_P) return launch_pte_tab_fixedp4(SGX_TAB_ARGS);
+  }
   if (solver == SGX_PTE_PT) return launch_pte_tab_pt(SGX_TAB_ARGS);
   if (solver == SGX_PTE_RHOU) return launch_pte_tab_rhou(SGX_TAB_ARGS);
   if (solver == SGX_PTE_FIXED_P) return launch_pte_tab_fixedp(SGX_TAB_ARGS);
@@ -67,7 +76,7 @@ int launch_pte_tab(int solver, const EosSet &set, const MixParamsDev &prm, doubl
   }
   return fail(SGX_ERR_UNSUPPORTED,
               "PTE with tabulated materials: solver %d with %d materials is not instantiated "
-              "(RhoT / FixedT: 1..4, PT / RhoU: 2..3, FixedP: 1..3)", solver, set.nmat);
+              "(RhoT / FixedT / FixedP: 1..4, PT / RhoU: 2..4)", solver, set.nmat);
 }
 
 } // namespace sgx

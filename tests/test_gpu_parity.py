@@ -871,7 +871,7 @@ def test_pte_pt_parity(pkg, ref, torch_cuda, which):
 
 @pytest.mark.parametrize("solver_name", ["RhoT", "FixedT", "PT", "RhoU", "FixedP"])
 @pytest.mark.parametrize("mix", ["spiner+ideal+gruneisen", "spiner+ideal", "rhosie+ideal+davis",
-                                 "spiner(vapor dome)+ideal"])
+                                 "spiner(vapor dome)+ideal", "spiner+ideal+gruneisen+davis"])
 def test_pte_tabulated_materials(pkg, ref, torch_cuda, raw1, mix, solver_name):
     """mixed cells that hold TABULATED materials (SpinerEOSDependsRhoT /
     RhoSie of Vinet copper next to IdealGas, Gruneisen, Davis) with per-material lambda caches in
@@ -894,13 +894,16 @@ def test_pte_tabulated_materials(pkg, ref, torch_cuda, raw1, mix, solver_name):
     g_gas, r_gas = pkg.IdealGas(0.4, 7.16e6), ref.IdealGas(0.4, 7.16e6)
     if mix == "spiner+ideal+gruneisen":
         g_l, r_l, rho0 = [g_tab, g_gas, g3[0]], [r_tab, r_gas, r3[0]], (8.93, 1.0e-2, 8.93)
+    elif mix == "spiner+ideal+gruneisen+davis":  # four materials: 8 x 8 RhoU, 5 x 5 FixedP
+        g_l, r_l = [g_tab, g_gas, g3[0], g3[1]], [r_tab, r_gas, r3[0], r3[1]]
+        rho0 = (8.93, 1.0e-2, 8.93, 1.89)
     elif mix == "rhosie+ideal+davis":
         g_l, r_l, rho0 = [g_tab, g_gas, g3[1]], [r_tab, r_gas, r3[1]], (8.93, 1.0e-2, 1.89)
     else:
         g_l, r_l, rho0 = [g_tab, g_gas], [r_tab, r_gas], (8.93, 5.0e-3)
     nm = len(g_l)
-    if solver_name == "PT" and nm not in (2, 3):
-        pytest.skip("PT instantiated for 2..3 materials")
+    if solver_name == "PT" and nm not in (2, 3, 4):
+        pytest.skip("PT instantiated for 2..4 materials")
     n = 2048
     vf = W.pte_vfracs(n, nmat=nm)
     rho = np.tile(np.array(rho0), (n, 1)) * \
@@ -919,14 +922,14 @@ def test_pte_tabulated_materials(pkg, ref, torch_cuda, raw1, mix, solver_name):
     if solver_name == "FixedP":
         # the given pressures: each cell's own PTE pressure (the reference's RhoT solve) +-5 %;
         # iterate_t_guess = false, where the reference's answer is defined.  From
-        # the fixed 600 K guess the reference itself converges on 31-49 % of these cells; the
+        # the fixed 600 K guess the reference itself converges on 29-49 % of these cells; the
         # cells it gives up on must be given up on identically (status words incl. niter)
         eq = [a.copy() for a in st_h]
         ref.pte_solve(L.PTE_RHOT, r_l, *eq, ref.mix_params_default(),
                       lambdas=np.full((n, nm, 3), np.nan))
         Tfix = eq[4][:, 0] * (1.0 + 0.1 * (pkg.rng.uniform_np(92, 0, n) - 0.5))
         prm = pkg.closure.MixParams(iterate_t_guess=0)
-        min_conv = 0.3
+        min_conv = 0.25
     lam_r = np.full((n, nm, 3), np.nan)
     st_r = [a.copy() for a in st_h]
     status_r, res_r, _ = ref.pte_solve(solver, r_l, *st_r, prm, Tguess=Tfix, lambdas=lam_r)
