@@ -75,7 +75,7 @@ class MixParams(C.Structure):
 
 # enums
 (EOS_IDEAL, EOS_GRUNEISEN, EOS_DAVIS_REACTANTS, EOS_DAVIS_PRODUCTS, EOS_SPINER_RHOT,
- EOS_SPINER_RHOSIE, EOS_HELMHOLTZ) = range(7)
+ EOS_SPINER_RHOSIE, EOS_HELMHOLTZ, EOS_MODIFIED) = range(8)
 (P_FROM_RHO_T, E_FROM_RHO_T, T_FROM_RHO_E, P_FROM_RHO_E, CV_FROM_RHO_T, CV_FROM_RHO_E,
  BMOD_FROM_RHO_T, BMOD_FROM_RHO_E, GAMMA_FROM_RHO_T, GAMMA_FROM_RHO_E) = range(10)
 METHOD_NAMES = {

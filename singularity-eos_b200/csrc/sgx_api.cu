@@ -905,10 +905,26 @@ static int new_modified(sgx_eos_t base, int layer, sgx_eos_s **out) {
   *out = e;
   return SGX_OK;
 }
+// The byte stream of a modified handle: the header with kind SGX_EOS_MODIFIED, the layer flags,
+// the arguments the three sgx_eos_modify_* calls were given, then the base model's own stream
+// (the reference's wrappers do the same: their own members, then the wrapped EOS's dynamic
+// memory, shifted_eos.hpp:381-392).  A base without a recipe leaves this one empty.
+static void set_modified_recipe(sgx_eos_s *e) {
+  e->recipe.clear();
+  if (e->base->recipe.empty()) return;
+  Recipe r(SGX_EOS_MODIFIED);
+  const int32_t flags = e->mod.flags;
+  const double a[6] = {e->mod.shift, e->mod.scale, e->mod.r0, e->mod.a, e->mod.b, e->mod.c};
+  r.put(&flags, sizeof(flags));
+  r.put(a, sizeof(a));
+  r.put(e->base->recipe.data(), e->base->recipe.size());
+  e->recipe = std::move(r.bytes);
+}
 int sgx_eos_modify_shifted(sgx_eos_t base, double shift, sgx_eos_t *out) {
   const int rc = new_modified(base, kModShift, out);
   if (rc) return rc;
   (*out)->mod.shift = shift;
+  set_modified_recipe(*out);
   return SGX_OK;
 }
 int sgx_eos_modify_scaled(sgx_eos_t base, double scale, sgx_eos_t *out) {
@@ -917,6 +933,7 @@ int sgx_eos_modify_scaled(sgx_eos_t base, double scale, sgx_eos_t *out) {
   if (rc) return rc;
   (*out)->mod.scale = scale;
   (*out)->mod.inv_scale = 1. / scale; // scaled_eos.hpp:45
+  set_modified_recipe(*out);
   return SGX_OK;
 }
 int sgx_eos_modify_bilinear_ramp(sgx_eos_t base, double r0, double a, double b, double c,
@@ -931,6 +948,7 @@ int sgx_eos_modify_bilinear_ramp(sgx_eos_t base, double r0, double a, double b, 
   if (rc) return rc;
   ModParams &q = (*out)->mod;
   q.r0 = r0, q.a = a, q.b = b, q.c = c, q.rmid = rmid, q.Pmid = Pmid;
+  set_modified_recipe(*out);
   return SGX_OK;
 }
 
@@ -1398,6 +1416,27 @@ int sgx_eos_deserialize(const char *src, uint64_t nbytes, sgx_eos_t *out) {
       return rc;
     }
     *out = e;
+    return SGX_OK;
+  }
+  case SGX_EOS_MODIFIED: { // the base model from the rest of the stream, then the layers again
+    int32_t flags = 0;
+    if (!rd.get(&flags, sizeof(flags)) || !rd.get(a, 6 * sizeof(double))) break;
+    if (flags <= 0 || (flags & ~(kModShift | kModScale | kModRamp)))
+      return fail(SGX_ERR_INVALID, "modifier flags %d in the byte stream", flags);
+    sgx_eos_t cur = nullptr;
+    int rc = sgx_eos_deserialize(rd.p, (uint64_t)(rd.end - rd.p), &cur);
+    if (rc) return rc;
+    for (int layer = kModShift; layer <= kModRamp && !rc; layer <<= 1) {
+      if (!(flags & layer)) continue;
+      sgx_eos_t next = nullptr;
+      rc = layer == kModShift   ? sgx_eos_modify_shifted(cur, a[0], &next)
+           : layer == kModScale ? sgx_eos_modify_scaled(cur, a[1], &next)
+                                : sgx_eos_modify_bilinear_ramp(cur, a[2], a[3], a[4], a[5], &next);
+      sgx_eos_destroy(cur); // the new handle keeps the base model alive
+      cur = next;
+    }
+    if (rc) return rc; // `cur` is null: the failed call stored nothing
+    *out = cur;
     return SGX_OK;
   }
   default:

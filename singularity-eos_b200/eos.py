@@ -61,6 +61,10 @@ class EosBase:
     def handle(self):
         return self._h
 
+    def type(self):
+        """enum sgx_eos_kind of the handle (SGX_EOS_MODIFIED for the modifier wrappers)."""
+        return self._lib.sgx_eos_type(self._h)
+
     def nlambda(self):
         return self._lib.sgx_eos_nlambda(self._h)
 
@@ -331,6 +335,13 @@ class _Modified(EosBase):
     def __init__(self, handle, base):
         super().__init__(handle)
         self.base = base
+
+    def base_model(self):
+        """The unmodified model under every layer."""
+        b = self.base
+        while isinstance(b, _Modified):
+            b = b.base
+        return b
 
 
 def ShiftedEOS(eos, shift):

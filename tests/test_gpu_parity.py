@@ -551,6 +551,56 @@ def test_serialize_deserialize_round_trip(pkg, torch_cuda, raw1, helm_table):
         pkg.eos.EosBase.DeSerialize(b"not an eos stream")
 
 
+def test_serialize_deserialize_modified_handles(pkg, torch_cuda, raw1):
+    """Serialize / DeSerialize of the modifier wrappers (modifiers/shifted_eos.hpp:375-392,
+    scaled_eos.hpp, ramps_eos.hpp: the wrapper's members, then the wrapped EOS's bytes): the stream
+    of a modified handle holds its layers and the base model; the twin rebuilt from it -- a new
+    base, new layers -- returns bit-identical lookups for all ten methods and writes bit-identical
+    lambda rows."""
+    torch = torch_cuda
+    L = pkg._lib
+    n = 4096
+    rho_s, T_s = pkg.workloads.spiner_inputs(n)
+    gr = pkg.closure.set_eos_3mat_analytic()[0]
+    cases = [(pkg.ShiftedEOS(pkg.IdealGas(0.4, 7.16e6), 1.0e9), 0),
+             (pkg.BilinearRampEOS(gr, 8.0, 1.0e10, 4.0e10, 1.05), 0),
+             (pkg.ScaledEOS(pkg.ShiftedEOS(pkg.SpinerEOSDependsRhoT(raw1), 2.0e8), 1.05), 2),
+             (pkg.BilinearRampEOS(pkg.ScaledEOS(pkg.ShiftedEOS(
+                 pkg.SpinerEOSDependsRhoSie(raw1), -1.0e8), 0.95), 8.0, 1.0e10, 4.0e10, 1.05), 1)]
+    rho_d, T_d = dev(rho_s), dev(T_s)
+    for eos, nl in cases:
+        blob = eos.Serialize()
+        assert len(blob) == eos.SerializedSizeInBytes() and blob[:8] == b"SGXEOS01"
+        assert len(blob) == 8 + 4 + 4 + 48 + eos.base_model().SerializedSizeInBytes()
+        twin = pkg.eos.EosBase.DeSerialize(blob)
+        assert twin.type() == L.EOS_MODIFIED and twin.nlambda() == eos.nlambda() == nl
+        again = twin.Serialize()  # (the Spiner records carry their source pointers: stale bytes)
+        assert again == blob if nl == 0 else len(again) == len(blob)
+        want = {}
+        for who in (eos, twin):
+            sie_d = torch.empty(n, dtype=torch.float64, device="cuda")
+            who._eval(L.E_FROM_RHO_T, rho_d, T_d, sie_d, n,
+                      dev(np.full((n, nl), np.nan)) if nl else None)
+            for m in range(10):
+                second = T_d if m in (L.P_FROM_RHO_T, L.E_FROM_RHO_T, L.CV_FROM_RHO_T,
+                                      L.BMOD_FROM_RHO_T, L.GAMMA_FROM_RHO_T) else sie_d
+                o = torch.empty(n, dtype=torch.float64, device="cuda")
+                lam = dev(np.full((n, nl), np.nan)) if nl else None
+                who._eval(m, rho_d, second, o, n, lam)
+                got = (o.cpu().numpy(), lam.cpu().numpy() if nl else np.zeros(0))
+                if who is eos:
+                    want[m] = got
+                else:
+                    assert_bits(got[0], want[m][0], f"modified twin, method {m}")
+                    assert_bits(got[1], want[m][1], f"modified twin lambda, method {m}")
+        with pytest.raises(pkg.SgxError):
+            pkg.eos.EosBase.DeSerialize(blob[:40])
+        bad = bytearray(blob)
+        bad[12] = 0x40  # modifier flags outside shift | scale | ramp
+        with pytest.raises(pkg.SgxError):
+            pkg.eos.EosBase.DeSerialize(bytes(bad))
+
+
 def test_solve_Ax_b_known_answers(pkg, ref, torch_cuda):
     """test/test_solver_utils.cpp:52-133: 2x2 and near-singular 3x3 systems."""
     torch = torch_cuda
@@ -1610,15 +1660,13 @@ def test_modifiers_fill_eos(pkg, ref, torch_cuda, raw1, base, combo):
 
 
 def test_modifiers_refuse_what_they_do_not_serve(pkg, torch_cuda, helm_table):
-    """Helmholtz takes no modifier here; serialization does not take modified handles and FillEos
-    refuses what the reference's wrappers abort on (they fail, they do not silently ignore the
-    layers)."""
+    """Helmholtz takes no modifier here; the fused P+e entry does not take modified handles and
+    FillEos refuses what the reference's wrappers abort on (they fail, they do not silently
+    ignore the layers)."""
     torch = torch_cuda
     with pytest.raises(pkg.SgxError):
         pkg.ShiftedEOS(pkg.Helmholtz(helm_table), 1.0)
     g = pkg.ScaledEOS(pkg.IdealGas(0.4, 7.16e6), 2.0)
-    with pytest.raises(pkg.SgxError):
-        g.Serialize()
     a = torch.ones(8, dtype=torch.float64, device="cuda")
     tq = pkg.thermalqs
     with pytest.raises(pkg.SgxError):  # ScaledEOS<IdealGas>::FillEos is EOS_ERROR in the reference
