@@ -1100,6 +1100,12 @@ int sgx_PressureFromDensityInternalEnergy(sgx_eos_t e, const double *rhos, const
   return sgx_eos_eval(e, SGX_P_FROM_RHO_E, rhos, sies, out, n, lambda, ls, s);
 }
 
+extern "C++" {
+namespace sgx {
+int launch_mod_pe(sgx_eos_s *e, const double *rho, const double *T, double *P, double *E,
+                  int64_t n, double *lambda, int ls, cudaStream_t s);
+}
+}
 int sgx_PressureEnergyFromDensityTemperature(sgx_eos_t e, const double *rhos,
                                              const double *temps, double *P, double *E,
                                              int64_t n, double *lambda, int ls,
@@ -1125,6 +1131,8 @@ int sgx_PressureEnergyFromDensityTemperature(sgx_eos_t e, const double *rhos,
     return launch_pe(e->rhot, rhos, temps, P, E, n, lambda, ls, s);
   case SGX_EOS_SPINER_RHOSIE:
     return launch_pe(e->rhosie, rhos, temps, P, E, n, lambda, ls, s);
+  case SGX_EOS_MODIFIED:
+    return launch_mod_pe(e, rhos, temps, P, E, n, lambda, ls, s);
   default:
     return fail(SGX_ERR_UNSUPPORTED, "fused P+e not available for EOS kind %d", e->kind);
   }

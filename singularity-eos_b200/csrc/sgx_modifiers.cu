@@ -73,6 +73,34 @@ __global__ void __launch_bounds__(256)
   }
 }
 
+// P and e of one (rho, T) pair in one pass (sgx_PressureEnergyFromDensityTemperature): the two
+// wrapper calls back to back on the same lambda row, i.e. what a host code's P-then-e sequence
+// computes, with one read of the inputs and one round trip of the row.
+__global__ void __launch_bounds__(256)
+    mod_pe_kernel(const __grid_constant__ EosSet set, const double *__restrict__ rho,
+                  const double *__restrict__ T, double *__restrict__ P, double *__restrict__ E,
+                  const int64_t n, double *__restrict__ lambda, const int ls, const int nl) {
+  TabEos eos(set);
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t nthr = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = tid; i < n; i += nthr) {
+    double lam[kMaxNumLambdas];
+    const bool has_lambda = lambda != nullptr && nl > 0;
+    if (has_lambda)
+      for (int k = 0; k < nl; ++k)
+        lam[k] = lambda[i * ls + k];
+    eos.lam = has_lambda ? lam : nullptr;
+    const double a = rho[i], b = T[i];
+    const double p = eos.P_from_rho_T(0, a, b);
+    const double e = eos.e_from_rho_T(0, a, b);
+    P[i] = p;
+    E[i] = e;
+    if (has_lambda)
+      for (int k = 0; k < nl; ++k)
+        lambda[i * ls + k] = lam[k];
+  }
+}
+
 // ---- FillEos of the wrappers (shifted_eos.hpp:148-170, scaled_eos.hpp:160-180,
 // ramps_eos.hpp:217-239), quirks included: with a (rho, sie)-preferring base the shifted / scaled
 // energy is a LOCAL of the wrapper, so an energy the base computes is not handed back; ScaledEOS
@@ -218,6 +246,21 @@ int launch_mod_fill(sgx_eos_s *e, double *rho, double *T, double *en, double *P,
   const LaunchCfg c = stream_cfg(n, 256, 8);
   mod_fill_kernel<<<c.blocks, c.threads, 0, s>>>(set, rho, T, en, P, cv, bmod, n, output, lambda,
                                                   ls, nl, nullptr);
+  count_launch();
+  SGX_CUDA_OK(cudaGetLastError());
+  return SGX_OK;
+}
+
+int launch_mod_pe(sgx_eos_s *e, const double *rho, const double *T, double *P, double *E,
+                  int64_t n, double *lambda, int ls, cudaStream_t s) {
+  EosSet set;
+  set.nmat = 1;
+  if (!e->base || !set_material(e, set, 0))
+    return fail(SGX_ERR_INVALID, "modified handle without a usable base model");
+  const int nl = e->base->kind == SGX_EOS_SPINER_RHOT ? 2
+                 : e->base->kind == SGX_EOS_SPINER_RHOSIE ? 1 : 0;
+  const LaunchCfg c = stream_cfg(n, 256, 8);
+  mod_pe_kernel<<<c.blocks, c.threads, 0, s>>>(set, rho, T, P, E, n, lambda, ls, nl);
   count_launch();
   SGX_CUDA_OK(cudaGetLastError());
   return SGX_OK;

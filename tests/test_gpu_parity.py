@@ -1606,6 +1606,22 @@ def test_modifiers_vector_parity(pkg, ref, torch_cuda, raw1, base, combo):
             on_ramp = int((want != plain.eval(m, rho_h, T_h, lam_np())).sum())
     if "ramp" in combo:
         assert 0 < on_ramp < n, f"the ramp must be active on part of the range ({on_ramp}/{n})"
+    # the fused P+e entry: the wrapper's two calls back to back on the cell's lambda row
+    P_d, E_d = torch.empty_like(rho_d), torch.empty_like(rho_d)
+    lam_d = dev(lam_np()) if nl else None
+    g.PressureEnergyFromDensityTemperature(rho_d, T_d, P_d, E_d, n, lam_d)
+    lam_r = lam_np()
+    want_P = r.eval(L.P_FROM_RHO_T, rho_h, T_h, lam_r)
+    want_E = r.eval(L.E_FROM_RHO_T, rho_h, T_h, lam_r)
+    assert_rel(P_d.cpu().numpy(), want_P, LOOKUP_TOL, f"{combo}({base}) fused P")
+    assert_rel(E_d.cpu().numpy(), want_E, LOOKUP_TOL, f"{combo}({base}) fused e")
+    lam_s = dev(lam_np()) if nl else None
+    for m, fused in ((L.P_FROM_RHO_T, P_d), (L.E_FROM_RHO_T, E_d)):
+        g._eval(m, rho_d, T_d, out, n, lam_s)
+        assert_bits(fused.cpu().numpy(), out.cpu().numpy(), f"{combo}({base}) fused vs method {m}")
+    if nl:
+        assert_rel(lam_d.cpu().numpy(), lam_r, LOOKUP_TOL, f"{combo}({base}) lambda, fused")
+        assert_bits(lam_d.cpu().numpy(), lam_s.cpu().numpy(), f"{combo}({base}) lambda, fused")
     # the order of the layers is the default variant's: anything else is refused
     with pytest.raises(pkg.SgxError):
         pkg.ShiftedEOS(g, 1.0)
@@ -1660,9 +1676,8 @@ def test_modifiers_fill_eos(pkg, ref, torch_cuda, raw1, base, combo):
 
 
 def test_modifiers_refuse_what_they_do_not_serve(pkg, torch_cuda, helm_table):
-    """Helmholtz takes no modifier here; the fused P+e entry does not take modified handles and
-    FillEos refuses what the reference's wrappers abort on (they fail, they do not silently
-    ignore the layers)."""
+    """Helmholtz takes no modifier here and FillEos refuses what the reference's wrappers abort
+    on (they fail, they do not silently ignore the layers)."""
     torch = torch_cuda
     with pytest.raises(pkg.SgxError):
         pkg.ShiftedEOS(pkg.Helmholtz(helm_table), 1.0)
