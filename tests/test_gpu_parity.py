@@ -1693,14 +1693,16 @@ def test_modifiers_refuse_what_they_do_not_serve(pkg, torch_cuda, helm_table):
         pkg.BilinearRampEOS(pkg.IdealGas(0.4, 7.16e6), 1.0, 2.0, 2.0, 1.0)  # a == b
 
 
+@pytest.mark.parametrize("nm", [3, 4])
 @pytest.mark.parametrize("solver_name", ["RhoT", "FixedT", "PT", "RhoU", "FixedP"])
-def test_pte_modified_materials(pkg, ref, torch_cuda, raw1, solver_name):
+def test_pte_modified_materials(pkg, ref, torch_cuda, raw1, solver_name, nm):
     """Mixed cells whose materials carry modifiers, as the reference's default variant allows:
     ScaledEOS(ShiftedEOS(SpinerEOSDependsRhoT)) with its lambda cache, ShiftedEOS(IdealGas) and
     BilinearRampEOS(Gruneisen) (the ramp is active: the Gruneisen material sits on it in most
     cells).  The solvers see the wrappers' bounds (ScaledEOS scales RhoPmin / MaximumDensity) and
-    DensityEnergyFromPressureTemperature.  Every SolverStatus field identical to the reference,
-    states to 1e-10, caches to 1e-10."""
+    DensityEnergyFromPressureTemperature.  nm = 4 adds an unmodified DavisReactants (the four-
+    material instantiations, csrc/sgx_pte_tab_*4.cu).  Every SolverStatus field identical to the
+    reference, states to 1e-10, caches to 1e-10."""
     torch = torch_cuda
     L, W = pkg._lib, pkg.workloads
     g_l = [pkg.ScaledEOS(pkg.ShiftedEOS(pkg.SpinerEOSDependsRhoT(raw1), 2.0e8), 1.05),
@@ -1709,9 +1711,14 @@ def test_pte_modified_materials(pkg, ref, torch_cuda, raw1, solver_name):
     r_l = [ref.SpinerRhoT(raw1).modify(0, 2.0e8).modify(1, 1.05),
            ref.IdealGas(0.4, 7.16e6).modify(0, 1.0e9),
            ref.set_eos_3mat()[0].modify(2, 8.0, 1.0e10, 4.0e10, 1.05)]
-    nm, n, T0 = 3, 2048, 600.0
+    rho0 = [8.93 / 1.05, 1.0e-2, 8.93]
+    if nm == 4:
+        g_l.append(pkg.closure.set_eos_3mat_analytic()[1])
+        r_l.append(ref.set_eos_3mat()[1])
+        rho0.append(1.89)
+    n, T0 = 2048, 600.0
     vf = W.pte_vfracs(n, nmat=nm)
-    rho = np.tile(np.array((8.93 / 1.05, 1.0e-2, 8.93)), (n, 1)) * \
+    rho = np.tile(np.array(rho0), (n, 1)) * \
         (0.9 + 0.2 * pkg.rng.uniform_np(57, 0, n * nm).reshape(n, nm))
     sie = np.stack([r_l[m].eval(L.E_FROM_RHO_T, rho[:, m].copy(), np.full(n, T0),
                                 np.full((n, 3), np.nan) if g_l[m].nlambda() else None)
