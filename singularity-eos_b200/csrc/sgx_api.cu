@@ -689,7 +689,18 @@ static std::vector<char> sp5_recipe(int kind, const sgx_sp5_tables *raw, int rep
   Recipe r(kind);
   const int32_t flags[2] = {reproducible, vapor_dome};
   r.put(flags, sizeof(flags));
-  r.put(raw, sizeof(*raw));
+  {
+    // the header record without the caller's addresses (the arrays follow as records of their
+    // own): the stream depends on the contents only, so equal models give equal bytes
+    sgx_sp5_tables hdr;
+    std::memcpy(&hdr, raw, sizeof(hdr));
+    hdr.P = hdr.sie = hdr.bMod = hdr.dPdRho = hdr.dPdE = hdr.dTdRho = hdr.dTdE = hdr.dEdRho =
+        hdr.dEdT = nullptr;
+    hdr.PCold = hdr.sieCold = hdr.bModCold = hdr.dPdRhoCold = nullptr;
+    hdr.T_re = hdr.P_re = hdr.bMod_re = hdr.dPdRho_re = hdr.dPdE_re = hdr.dTdRho_re =
+        hdr.dTdE_re = hdr.dEdRho_re = nullptr;
+    r.put(&hdr, sizeof(hdr));
+  }
   const size_t nr = grid_points(raw->lrho), nt = grid_points(raw->lT), ne = grid_points(raw->lE);
   const double *t2[9] = {raw->P, raw->sie, raw->bMod, raw->dPdRho, raw->dPdE, raw->dTdRho,
                          raw->dTdE, raw->dEdRho, raw->dEdT};
